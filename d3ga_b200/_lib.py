@@ -1,0 +1,103 @@
+"""ctypes binding of libd3ga_b200.so (the C-ABI declared in include/d3ga_b200.h).
+
+There is no fallback: if the CUDA library is missing this module raises, and every op that needs it fails loudly.
+PyTorch is used by the callers only for device memory and streams; nothing in the library links against it.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libd3ga_b200.so")
+
+# every symbol include/d3ga_b200.h declares (tests/test_abi.py checks the header against this list)
+EXPORTS = [
+    "d3ga_version", "d3ga_error_string", "d3ga_last_cuda_error", "d3ga_launch_count",
+    "d3ga_raster_workspace_bytes", "d3ga_raster_forward_geometry", "d3ga_raster_forward_render",
+    "d3ga_raster_backward_scratch_bytes", "d3ga_raster_backward", "d3ga_raster_layout",
+    "d3ga_deform_forward", "d3ga_deform_backward", "d3ga_compute_bary",
+]
+
+LAYOUT_NAMES = [
+    "geom_header", "geom_depth", "geom_xy", "geom_conic_opacity", "geom_rgb", "geom_cov3D", "geom_tiles",
+    "geom_offsets", "geom_clamped", "bin_keys0", "bin_keys1", "bin_vals0", "bin_vals1", "img_ranges", "img_final_T",
+    "img_n_contrib",
+]
+
+_lib = None
+
+
+class D3GAError(RuntimeError):
+    pass
+
+
+def load() -> C.CDLL:
+    """Load the library (once).  Raises D3GAError when it has not been built -- never falls back to anything."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise D3GAError(
+            f"{LIB_PATH} is missing: build it with `python -m d3ga_b200.build` (nvcc, sm_100a). "
+            "d3ga_b200 has no CPU or PyTorch fallback."
+        )
+    lib = C.CDLL(LIB_PATH)
+    vp, i32, u64, f32 = C.c_void_p, C.c_int, C.c_uint64, C.c_float
+    lib.d3ga_version.restype = C.c_int
+    lib.d3ga_error_string.restype = C.c_char_p
+    lib.d3ga_error_string.argtypes = [C.c_int]
+    lib.d3ga_last_cuda_error.restype = C.c_int
+    lib.d3ga_launch_count.restype = C.c_uint64
+    lib.d3ga_raster_workspace_bytes.argtypes = [i32, i32, i32, u64, C.POINTER(u64), C.POINTER(u64), C.POINTER(u64)]
+    lib.d3ga_raster_layout.argtypes = [i32, i32, i32, u64, C.POINTER(u64)]
+    lib.d3ga_raster_forward_geometry.argtypes = (
+        [i32, i32, i32, vp, vp, f32, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, f32, f32, i32, i32, vp, vp, u64, vp, vp, vp]
+    )
+    lib.d3ga_raster_forward_render.argtypes = [i32, i32, i32, vp, vp, vp, vp, u64, vp, vp, vp, vp]
+    lib.d3ga_raster_backward_scratch_bytes.restype = C.c_uint64
+    lib.d3ga_raster_backward_scratch_bytes.argtypes = [i32]
+    lib.d3ga_raster_backward.argtypes = (
+        [i32, i32, i32, i32, i32, vp, vp, vp, vp, vp, f32, vp, vp, vp, vp, vp, vp, f32, f32, i32, vp, vp, vp, u64, vp,
+         vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp]
+    )
+    lib.d3ga_deform_forward.argtypes = [i32, i32, i32, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp]
+    lib.d3ga_deform_backward.argtypes = [i32, i32, i32, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp]
+    lib.d3ga_compute_bary.argtypes = [i32, i32, i32, vp, vp, vp, vp, vp, vp, vp, vp, vp]
+    for name in EXPORTS:
+        getattr(lib, name)   # AttributeError if the build is stale
+    _lib = lib
+    return lib
+
+
+def check(rc: int, what: str) -> None:
+    if rc != 0:
+        lib = load()
+        msg = lib.d3ga_error_string(rc).decode()
+        extra = f" (cudaError {lib.d3ga_last_cuda_error()})" if rc == -2 else ""
+        raise D3GAError(f"{what}: {msg}{extra}")
+
+
+def ptr(t):
+    """Device pointer of a tensor, or NULL for None / empty."""
+    if t is None or t.numel() == 0:
+        return None
+    return t.data_ptr()
+
+
+def workspace_bytes(P: int, W: int, H: int, capacity: int):
+    lib = load()
+    g, b, i = C.c_uint64(), C.c_uint64(), C.c_uint64()
+    check(lib.d3ga_raster_workspace_bytes(P, W, H, capacity, C.byref(g), C.byref(b), C.byref(i)), "workspace_bytes")
+    return g.value, b.value, i.value
+
+
+def raster_layout(P: int, W: int, H: int, capacity: int) -> dict:
+    lib = load()
+    out = (C.c_uint64 * len(LAYOUT_NAMES))()
+    check(lib.d3ga_raster_layout(P, W, H, capacity, out), "raster_layout")
+    return dict(zip(LAYOUT_NAMES, [int(v) for v in out]))
+
+
+def launch_count() -> int:
+    return int(load().d3ga_launch_count())

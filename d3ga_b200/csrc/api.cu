@@ -1,0 +1,160 @@
+// api.cu -- the extern "C" surface of libd3ga_b200.so declared in include/d3ga_b200.h (rasterizer part; the
+// deformation and embedding entry points live beside their kernels in deform.cu / bary.cu).
+#include <atomic>
+
+#include "common.cuh"
+
+namespace d3ga {
+
+static std::atomic<uint64_t> g_launches{0};
+static std::atomic<int> g_last_cuda_error{0};
+
+void count_launch(int n) { g_launches.fetch_add((uint64_t)n, std::memory_order_relaxed); }
+int set_cuda_error(cudaError_t e) {
+    g_last_cuda_error.store((int)e);
+    (void)cudaGetLastError();   // clear the sticky-free error state
+    return D3GA_ECUDA;
+}
+
+// upstream getHigherMsb: number of bits needed for the tile id
+static int higher_msb(uint32_t n) {
+    uint32_t msb = sizeof(n) * 4, step = msb;
+    while (step > 1) {
+        step /= 2;
+        if (n >> msb) msb += step; else msb -= step;
+    }
+    if (n >> msb) msb++;
+    return (int)msb;
+}
+
+}  // namespace d3ga
+
+using namespace d3ga;
+
+extern "C" {
+
+int d3ga_version(void) { return 100; }
+
+const char *d3ga_error_string(int code) {
+    switch (code) {
+        case D3GA_OK: return "ok";
+        case D3GA_EINVAL: return "invalid argument";
+        case D3GA_ECUDA: return "CUDA runtime error (see d3ga_last_cuda_error)";
+        case D3GA_ETOOBIG: return "size exceeds the 2^30-1 duplicate limit";
+        case D3GA_ENOTREADY: return "staged call out of order";
+        default: return "unknown error";
+    }
+}
+
+int d3ga_last_cuda_error(void) { return g_last_cuda_error.load(); }
+uint64_t d3ga_launch_count(void) { return g_launches.load(); }
+
+int d3ga_raster_workspace_bytes(int P, int W, int H, uint64_t capacity, uint64_t *geom_bytes, uint64_t *binning_bytes,
+                                uint64_t *image_bytes) {
+    if (P < 0 || W <= 0 || H <= 0) return D3GA_EINVAL;
+    if (capacity > MAX_DUPLICATES) return D3GA_ETOOBIG;
+    if (geom_bytes) *geom_bytes = geom_layout(P).total;
+    if (binning_bytes) *binning_bytes = bin_layout(capacity).total;
+    if (image_bytes) *image_bytes = img_layout(W, H).total;
+    return D3GA_OK;
+}
+
+int d3ga_raster_layout(int P, int W, int H, uint64_t capacity, uint64_t *out) {
+    if (P < 0 || W <= 0 || H <= 0 || !out) return D3GA_EINVAL;
+    const GeomLayout G = geom_layout(P);
+    const BinLayout B = bin_layout(capacity);
+    const ImgLayout I = img_layout(W, H);
+    out[D3GA_L_GEOM_HEADER] = G.header; out[D3GA_L_GEOM_DEPTH] = G.depth; out[D3GA_L_GEOM_XY] = G.xy;
+    out[D3GA_L_GEOM_CONIC_OPACITY] = G.conic_opacity; out[D3GA_L_GEOM_RGB] = G.rgb; out[D3GA_L_GEOM_COV3D] = G.cov3D;
+    out[D3GA_L_GEOM_TILES] = G.tiles; out[D3GA_L_GEOM_OFFSETS] = G.offsets; out[D3GA_L_GEOM_CLAMPED] = G.clamped;
+    out[D3GA_L_BIN_KEYS0] = B.keys0; out[D3GA_L_BIN_KEYS1] = B.keys1; out[D3GA_L_BIN_VALS0] = B.vals0;
+    out[D3GA_L_BIN_VALS1] = B.vals1;
+    out[D3GA_L_IMG_RANGES] = I.ranges; out[D3GA_L_IMG_FINAL_T] = I.final_T; out[D3GA_L_IMG_N_CONTRIB] = I.n_contrib;
+    return D3GA_OK;
+}
+
+int d3ga_raster_forward_geometry(int P, int sh_degree, int sh_coeffs, const float *means3D, const float *scales,
+                                 float scale_modifier, const float *rotations, const float *opacities,
+                                 const float *shs, const float *cov3D_precomp, const float *colors_precomp,
+                                 const float *viewmatrix, const float *projmatrix, const float *campos, int W, int H,
+                                 float tanfovx, float tanfovy, int prefiltered, int antialiasing, void *geom,
+                                 void *binning, uint64_t capacity, int32_t *radii, uint32_t *num_rendered_host,
+                                 d3ga_stream_t stream_) {
+    (void)prefiltered;   // upstream only uses it to trap on culled points in debug builds
+    cudaStream_t stream = (cudaStream_t)stream_;
+    if (P < 0 || W <= 0 || H <= 0 || !geom || !binning || !viewmatrix || !projmatrix || !campos) return D3GA_EINVAL;
+    if (P > 0 && (!means3D || !opacities || !radii)) return D3GA_EINVAL;
+    if ((cov3D_precomp != nullptr) == (scales != nullptr && rotations != nullptr) && P > 0) return D3GA_EINVAL;
+    if ((colors_precomp != nullptr) == (shs != nullptr) && P > 0) return D3GA_EINVAL;
+    if (shs && (sh_degree < 0 || sh_degree > 3 || sh_coeffs < (sh_degree + 1) * (sh_degree + 1))) return D3GA_EINVAL;
+    if (capacity > MAX_DUPLICATES) return D3GA_ETOOBIG;
+    const GeomLayout GL = geom_layout(P);
+    const BinLayout BL = bin_layout(capacity);
+    int rc = launch_geometry(P, sh_degree, sh_coeffs, means3D, scales, scale_modifier, rotations, opacities, shs,
+                             cov3D_precomp, colors_precomp, viewmatrix, projmatrix, campos, W, H, tanfovx, tanfovy,
+                             antialiasing, (uint8_t *)geom, GL, (uint8_t *)binning, BL, capacity, radii, stream);
+    if (rc) return rc;
+    if (num_rendered_host)
+        D3GA_CUDA(cudaMemcpyAsync(num_rendered_host, (uint8_t *)geom + GL.header, 8, cudaMemcpyDeviceToHost, stream));
+    return D3GA_OK;
+}
+
+int d3ga_raster_forward_render(int P, int W, int H, const float *background, const float *colors_precomp, void *geom,
+                               void *binning, uint64_t capacity, void *image, float *out_color, float *out_invdepth,
+                               d3ga_stream_t stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    if (P < 0 || W <= 0 || H <= 0 || !geom || !binning || !image || !background || !out_color) return D3GA_EINVAL;
+    if (capacity > MAX_DUPLICATES) return D3GA_ETOOBIG;
+    const GeomLayout GL = geom_layout(P);
+    const BinLayout BL = bin_layout(capacity);
+    const ImgLayout IL = img_layout(W, H);
+    const int num_tiles = ((W + TILE - 1) / TILE) * ((H + TILE - 1) / TILE);
+    const int sort_bits = 32 + higher_msb((uint32_t)num_tiles);
+    int rc = launch_sort_and_ranges((uint8_t *)geom, (uint8_t *)binning, BL, capacity, sort_bits, (uint8_t *)image, IL,
+                                    num_tiles, stream);
+    if (rc) return rc;
+    const float *colors = colors_precomp ? colors_precomp : reinterpret_cast<const float *>((uint8_t *)geom + GL.rgb);
+    return launch_blend_forward(W, H, background, colors, (const uint8_t *)geom, GL, (const uint8_t *)binning, BL,
+                                (uint8_t *)image, IL, out_color, out_invdepth, stream);
+}
+
+uint64_t d3ga_raster_backward_scratch_bytes(int P) { return align256((uint64_t)(P > 0 ? P : 1) * GRAD_ACC_FLOATS * 4); }
+
+int d3ga_raster_backward(int P, int sh_degree, int sh_coeffs, int W, int H, const float *background,
+                         const float *means3D, const float *colors_precomp, const float *opacities,
+                         const float *scales, float scale_modifier, const float *rotations,
+                         const float *cov3D_precomp, const float *shs, const float *viewmatrix,
+                         const float *projmatrix, const float *campos, float tanfovx, float tanfovy, int antialiasing,
+                         const int32_t *radii, const void *geom, const void *binning, uint64_t capacity,
+                         const void *image, const float *dL_dout_color, const float *dL_dout_invdepth,
+                         void *grad_scratch, float *dL_dmeans2D, float *dL_dopacity, float *dL_dcolors,
+                         float *dL_dmeans3D, float *dL_dcov3D, float *dL_dsh, float *dL_dscales, float *dL_drotations,
+                         d3ga_stream_t stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    if (P < 0 || W <= 0 || H <= 0 || !geom || !binning || !image || !background || !dL_dout_color || !grad_scratch ||
+        !viewmatrix || !projmatrix || !campos)
+        return D3GA_EINVAL;
+    if (P == 0) return D3GA_OK;
+    if (!means3D || !opacities || !radii || !dL_dmeans3D || !dL_dopacity) return D3GA_EINVAL;
+    if ((cov3D_precomp != nullptr) == (scales != nullptr && rotations != nullptr)) return D3GA_EINVAL;
+    if ((colors_precomp != nullptr) == (shs != nullptr)) return D3GA_EINVAL;
+    if (shs && !dL_dsh) return D3GA_EINVAL;
+    if (scales && (!dL_dscales || !dL_drotations)) return D3GA_EINVAL;
+    if (capacity > MAX_DUPLICATES) return D3GA_ETOOBIG;
+    const GeomLayout GL = geom_layout(P);
+    const BinLayout BL = bin_layout(capacity);
+    const ImgLayout IL = img_layout(W, H);
+    float *acc = (float *)grad_scratch;
+    D3GA_CUDA(cudaMemsetAsync(acc, 0, (size_t)P * GRAD_ACC_FLOATS * 4, stream));
+    const float *colors = colors_precomp ? colors_precomp : reinterpret_cast<const float *>((const uint8_t *)geom + GL.rgb);
+    int rc = launch_blend_backward(W, H, background, colors, (const uint8_t *)geom, GL, (const uint8_t *)binning, BL,
+                                   (const uint8_t *)image, IL, dL_dout_color, dL_dout_invdepth, acc, stream);
+    if (rc) return rc;
+    return launch_preprocess_backward(P, sh_degree, sh_coeffs, W, H, means3D, opacities, scales, scale_modifier,
+                                      rotations, cov3D_precomp, shs, viewmatrix, projmatrix, campos, tanfovx, tanfovy,
+                                      antialiasing, radii, (const uint8_t *)geom, GL, acc, dL_dout_invdepth != nullptr,
+                                      dL_dmeans2D, dL_dopacity, dL_dcolors, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales,
+                                      dL_drotations, stream);
+}
+
+}  // extern "C"

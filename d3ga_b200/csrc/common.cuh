@@ -1,0 +1,170 @@
+// common.cuh -- shared declarations of libd3ga_b200 (sm_100a).  Host + device.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/d3ga_b200.h"
+
+namespace d3ga {
+
+constexpr int TILE = 16;           // 16x16 pixel tiles (upstream BLOCK_X / BLOCK_Y)
+constexpr int TILE_PIX = TILE * TILE;
+constexpr int GEO_THREADS = 256;   // Gaussians per CTA in the per-Gaussian kernels
+constexpr int SORT_THREADS = 256;
+constexpr int SORT_ITEMS = 16;     // keys per thread per onesweep tile
+constexpr int SORT_TILE = SORT_THREADS * SORT_ITEMS;  // 4096 pairs = 48 KB of payload per CTA
+constexpr int SORT_MAX_PASSES = 8;
+constexpr uint32_t MAX_DUPLICATES = (1u << 30) - 1;  // look-back words keep 2 flag bits
+
+// ---- workspace layouts ------------------------------------------------------------------------------------------
+struct RasterHeader {          // first 256 bytes of the geom workspace; zeroed at the start of every forward
+    uint32_t num_rendered;     // D: total (tile, Gaussian) duplicates; may exceed capacity
+    uint32_t overflow;         // 1 when D > capacity (later stages then do nothing)
+    uint32_t geo_ticket;       // dynamic CTA id of the fused geometry kernel (look-back needs in-order ids)
+    uint32_t final_sel;        // which key/value buffer (0/1) holds the sorted list
+    uint32_t hist_done;        // CTAs of the histogram kernel that have finished
+    uint32_t sort_bits;        // 32 + bits(tile id)
+    uint32_t num_passes;
+    uint32_t pad0;
+    uint32_t pass_skip[SORT_MAX_PASSES];   // 1 = every key has the same digit in this pass
+    uint32_t pass_src[SORT_MAX_PASSES];    // buffer (0/1) a pass reads from
+    uint32_t pass_ticket[SORT_MAX_PASSES]; // dynamic tile id per pass
+    uint32_t pad1[64 - 8 - 3 * SORT_MAX_PASSES];
+};
+static_assert(sizeof(RasterHeader) == 256, "header is 256 bytes");
+
+struct GeomLayout {
+    uint64_t header, depth, xy, conic_opacity, rgb, cov3D, tiles, offsets, clamped, scan_state, total;
+};
+struct BinLayout {
+    uint64_t keys0, keys1, vals0, vals1, hist, bins, tile_state, total;
+    uint64_t tile_state_bytes;
+};
+struct ImgLayout {
+    uint64_t ranges, final_T, n_contrib, total;
+};
+
+__host__ __device__ inline uint64_t align256(uint64_t x) { return (x + 255) & ~uint64_t(255); }
+
+inline GeomLayout geom_layout(int P) {
+    GeomLayout L;
+    uint64_t o = 0, p = (uint64_t)P;
+    L.header = o;        o += 256;
+    L.depth = o;         o = align256(o + 4 * p);
+    L.xy = o;            o = align256(o + 8 * p);
+    L.conic_opacity = o; o = align256(o + 16 * p);
+    L.rgb = o;           o = align256(o + 12 * p);
+    L.cov3D = o;         o = align256(o + 24 * p);
+    L.tiles = o;         o = align256(o + 4 * p);
+    L.offsets = o;       o = align256(o + 4 * p);
+    L.clamped = o;       o = align256(o + 3 * p);
+    L.scan_state = o;    o = align256(o + 8 * ((p + GEO_THREADS - 1) / GEO_THREADS + 1));
+    L.total = o;
+    return L;
+}
+inline uint64_t sort_tiles(uint64_t capacity) { return (capacity + SORT_TILE - 1) / SORT_TILE; }
+inline BinLayout bin_layout(uint64_t capacity) {
+    BinLayout L;
+    uint64_t o = 0, c = capacity < 1 ? 1 : capacity;
+    L.keys0 = o; o = align256(o + 8 * c);
+    L.keys1 = o; o = align256(o + 8 * c);
+    L.vals0 = o; o = align256(o + 4 * c);
+    L.vals1 = o; o = align256(o + 4 * c);
+    L.hist = o;  o = align256(o + 4 * 256 * SORT_MAX_PASSES);   // digit counts per pass
+    L.bins = o;  o = align256(o + 4 * 256 * SORT_MAX_PASSES);   // exclusive prefix per pass
+    L.tile_state = o;
+    L.tile_state_bytes = 4ull * 256 * sort_tiles(c) * SORT_MAX_PASSES;
+    o = align256(o + L.tile_state_bytes);
+    L.total = o;
+    return L;
+}
+inline ImgLayout img_layout(int W, int H) {
+    ImgLayout L;
+    uint64_t o = 0, tiles = (uint64_t)((W + TILE - 1) / TILE) * ((H + TILE - 1) / TILE), px = (uint64_t)W * H;
+    L.ranges = o;    o = align256(o + 8 * tiles);
+    L.final_T = o;   o = align256(o + 4 * px);
+    L.n_contrib = o; o = align256(o + 4 * px);
+    L.total = o;
+    return L;
+}
+
+// Packed per-Gaussian gradient accumulator of the blend backward: three 16-byte vectors per Gaussian so one
+// (tile, Gaussian) pair costs three vector reductions (REDG.E.ADD.F32x4) instead of ten scalar atomics.
+//   v0 = (dmean2D.x, dmean2D.y, dconic.xx, dconic.xy)   v1 = (dconic.yy, dopacity, dcolor.r, dcolor.g)
+//   v2 = (dcolor.b, dinvdepth, 0, 0)
+constexpr int GRAD_ACC_FLOATS = 12;
+
+// ---- host-side helpers -----------------------------------------------------------------------------------------
+void count_launch(int n = 1);
+int set_cuda_error(cudaError_t e);
+#define D3GA_CUDA(expr)                                         \
+    do {                                                        \
+        cudaError_t _e = (expr);                                \
+        if (_e != cudaSuccess) return d3ga::set_cuda_error(_e); \
+    } while (0)
+#define D3GA_LAUNCH_CHECK()                                     \
+    do {                                                        \
+        d3ga::count_launch();                                   \
+        cudaError_t _e = cudaPeekAtLastError();                 \
+        if (_e != cudaSuccess) return d3ga::set_cuda_error(_e); \
+    } while (0)
+
+// stage launchers (defined in the per-stage .cu files)
+int launch_geometry(int P, int sh_degree, int sh_coeffs, const float *means3D, const float *scales,
+                    float scale_modifier, const float *rotations, const float *opacities, const float *shs,
+                    const float *cov3D_precomp, const float *colors_precomp, const float *viewmatrix,
+                    const float *projmatrix, const float *campos, int W, int H, float tanfovx, float tanfovy,
+                    int antialiasing, uint8_t *geom, const GeomLayout &GL, uint8_t *binning, const BinLayout &BL,
+                    uint64_t capacity, int32_t *radii, cudaStream_t stream);
+int launch_sort_and_ranges(uint8_t *geom, uint8_t *binning, const BinLayout &BL, uint64_t capacity, int sort_bits,
+                           uint8_t *image, const ImgLayout &IL, int num_tiles, cudaStream_t stream);
+int launch_blend_forward(int W, int H, const float *background, const float *colors, const uint8_t *geom,
+                         const GeomLayout &GL, const uint8_t *binning, const BinLayout &BL, uint8_t *image,
+                         const ImgLayout &IL, float *out_color, float *out_invdepth, cudaStream_t stream);
+int launch_blend_backward(int W, int H, const float *background, const float *colors, const uint8_t *geom,
+                          const GeomLayout &GL, const uint8_t *binning, const BinLayout &BL, const uint8_t *image,
+                          const ImgLayout &IL, const float *dL_dpix, const float *dL_dinvdepth_pix, float *grad_acc,
+                          cudaStream_t stream);
+int launch_preprocess_backward(int P, int sh_degree, int sh_coeffs, int W, int H, const float *means3D,
+                               const float *opacities, const float *scales, float scale_modifier,
+                               const float *rotations, const float *cov3D_precomp, const float *shs,
+                               const float *viewmatrix, const float *projmatrix, const float *campos, float tanfovx,
+                               float tanfovy, int antialiasing, const int32_t *radii, const uint8_t *geom,
+                               const GeomLayout &GL, const float *grad_acc, int has_invdepth_grad,
+                               float *dL_dmeans2D, float *dL_dopacity, float *dL_dcolors, float *dL_dmeans3D,
+                               float *dL_dcov3D, float *dL_dsh, float *dL_dscales, float *dL_drotations,
+                               cudaStream_t stream);
+
+#ifdef __CUDACC__
+// ---- device helpers ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t lane_id() { return threadIdx.x & 31; }
+__device__ __forceinline__ uint32_t lanemask_lt() {
+    uint32_t m;
+    asm("mov.u32 %0, %%lanemask_lt;" : "=r"(m));
+    return m;
+}
+__device__ __forceinline__ uint32_t ld_volatile_u32(const uint32_t *p) {
+    uint32_t v;
+    asm volatile("ld.volatile.global.u32 %0, [%1];" : "=r"(v) : "l"(p));
+    return v;
+}
+__device__ __forceinline__ uint64_t ld_volatile_u64(const uint64_t *p) {
+    uint64_t v;
+    asm volatile("ld.volatile.global.u64 %0, [%1];" : "=l"(v) : "l"(p));
+    return v;
+}
+__device__ __forceinline__ void st_volatile_u32(uint32_t *p, uint32_t v) {
+    asm volatile("st.volatile.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ void st_volatile_u64(uint64_t *p, uint64_t v) {
+    asm volatile("st.volatile.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ void red_add_v4(float *addr, float a, float b, float c, float d) {
+    asm volatile("red.global.add.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+__device__ __forceinline__ void red_add_v2(float *addr, float a, float b) {
+    asm volatile("red.global.add.v2.f32 [%0], {%1,%2};" ::"l"(addr), "f"(a), "f"(b) : "memory");
+}
+#endif
+
+}  // namespace d3ga

@@ -1,0 +1,232 @@
+// deform.cu -- rows A1 / A2 of SURVEY.md section 8: cage -> Gaussian deformation, forward and backward, one kernel each.
+//
+// Replaces the ~25-launch torch chain of models/cage_net.py:218-230:
+//   deformed_tetras = tetpoints[tetra_faces]                               cage_net.py:218
+//   J   = G(deformed_tetras[tetra_id]) @ canonical_gradient                lib/cage.py:339-342, tetra.py:74-80
+//   cov = J (L L^T) J^T,  L = R(q / |q|) diag(s)                           cage_net.py:161-164,221-222,
+//                                                                          utils/general_utils.py:58-90
+//   cov3D_precomp = (xx, xy, xz, yy, yz, zz)                               utils/general_utils.py:24-34
+//   means3D = sum_k barys[:, k] * deformed_tetras[tetra_id][:, k]          cage_net.py:228-230
+// and its autograd backward (index_put_ with accumulate into tetpoints).
+// One thread per Gaussian; nothing but inputs and outputs touches HBM (84 B read + 36 B written per Gaussian forward
+// against >= 0.6 kB of temporaries in the torch chain).  The cage (<= a few hundred kB) stays L2 resident.
+#include "common.cuh"
+
+namespace d3ga {
+
+namespace {
+
+struct Tet4 {
+    float v[4][3];
+};
+
+__device__ __forceinline__ void load_tet(const float *__restrict__ tetpoints, const int64_t *__restrict__ tets,
+                                         int64_t t, int64_t (&vid)[4], Tet4 &X) {
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        vid[k] = tets[4 * t + k];
+#pragma unroll
+        for (int c = 0; c < 3; c++) X.v[k][c] = __ldg(tetpoints + 3 * vid[k] + c);
+    }
+}
+
+__device__ __forceinline__ void rotation_from_unit_quat(float r, float x, float y, float z, float (&Rm)[3][3]) {
+    Rm[0][0] = 1.f - 2.f * (y * y + z * z); Rm[0][1] = 2.f * (x * y - r * z); Rm[0][2] = 2.f * (x * z + r * y);
+    Rm[1][0] = 2.f * (x * y + r * z); Rm[1][1] = 1.f - 2.f * (x * x + z * z); Rm[1][2] = 2.f * (y * z - r * x);
+    Rm[2][0] = 2.f * (x * z - r * y); Rm[2][1] = 2.f * (y * z + r * x); Rm[2][2] = 1.f - 2.f * (x * x + y * y);
+}
+
+__global__ void __launch_bounds__(GEO_THREADS) deform_forward_kernel(
+    int N, int T, const float *__restrict__ tetpoints, const int64_t *__restrict__ tets,
+    const int64_t *__restrict__ tetra_id, const float *__restrict__ barys, const float *__restrict__ cgrad,
+    const float *__restrict__ scales, const float *__restrict__ rotation, float *__restrict__ means3D,
+    float *__restrict__ cov3D) {
+    const int n = blockIdx.x * GEO_THREADS + threadIdx.x;
+    if (n >= N) return;
+    int64_t t = tetra_id[n];
+    if (t < 0) t += T;   // torch indexing wraps a -1 from compute_bary to the last tet
+    int64_t vid[4];
+    Tet4 X;
+    load_tet(tetpoints, tets, t, vid, X);
+    const float4 b = *reinterpret_cast<const float4 *>(barys + 4 * (size_t)n);
+    const float bw[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll
+    for (int c = 0; c < 3; c++)
+        means3D[3 * (size_t)n + c] = X.v[0][c] * bw[0] + X.v[1][c] * bw[1] + X.v[2][c] * bw[2] + X.v[3][c] * bw[3];
+    // G: edges (v3-v0, v2-v0, v1-v0) as columns
+    float G[3][3], Cg[3][3], J[3][3];
+#pragma unroll
+    for (int i = 0; i < 3; i++) {
+        G[i][0] = X.v[3][i] - X.v[0][i]; G[i][1] = X.v[2][i] - X.v[0][i]; G[i][2] = X.v[1][i] - X.v[0][i];
+    }
+#pragma unroll
+    for (int k = 0; k < 9; k++) Cg[k / 3][k % 3] = cgrad[9 * (size_t)n + k];
+#pragma unroll
+    for (int i = 0; i < 3; i++)
+#pragma unroll
+        for (int j = 0; j < 3; j++) J[i][j] = G[i][0] * Cg[0][j] + G[i][1] * Cg[1][j] + G[i][2] * Cg[2][j];
+    const float4 q = *reinterpret_cast<const float4 *>(rotation + 4 * (size_t)n);
+    const float inv = 1.f / sqrtf(q.x * q.x + q.y * q.y + q.z * q.z + q.w * q.w);
+    float Rm[3][3];
+    rotation_from_unit_quat(q.x * inv, q.y * inv, q.z * inv, q.w * inv, Rm);
+    const float s[3] = {scales[3 * (size_t)n], scales[3 * (size_t)n + 1], scales[3 * (size_t)n + 2]};
+    float B[3][3];   // B = J R diag(s); cov = B B^T
+#pragma unroll
+    for (int i = 0; i < 3; i++)
+#pragma unroll
+        for (int k = 0; k < 3; k++) B[i][k] = (J[i][0] * Rm[0][k] + J[i][1] * Rm[1][k] + J[i][2] * Rm[2][k]) * s[k];
+    int o = 0;
+#pragma unroll
+    for (int i = 0; i < 3; i++)
+#pragma unroll
+        for (int j = i; j < 3; j++)
+            cov3D[6 * (size_t)n + o++] = B[i][0] * B[j][0] + B[i][1] * B[j][1] + B[i][2] * B[j][2];
+}
+
+__global__ void __launch_bounds__(GEO_THREADS) deform_backward_kernel(
+    int N, int T, const float *__restrict__ tetpoints, const int64_t *__restrict__ tets,
+    const int64_t *__restrict__ tetra_id, const float *__restrict__ barys, const float *__restrict__ cgrad,
+    const float *__restrict__ scales, const float *__restrict__ rotation, const float *__restrict__ dL_dmeans,
+    const float *__restrict__ dL_dcov, float *__restrict__ dL_dtetpoints, float *__restrict__ dL_dbarys,
+    float *__restrict__ dL_dscales, float *__restrict__ dL_drotation) {
+    const int n = blockIdx.x * GEO_THREADS + threadIdx.x;
+    if (n >= N) return;
+    int64_t t = tetra_id[n];
+    if (t < 0) t += T;
+    int64_t vid[4];
+    Tet4 X;
+    load_tet(tetpoints, tets, t, vid, X);
+    const float4 b = *reinterpret_cast<const float4 *>(barys + 4 * (size_t)n);
+    const float bw[4] = {b.x, b.y, b.z, b.w};
+    const float dm[3] = {dL_dmeans[3 * (size_t)n], dL_dmeans[3 * (size_t)n + 1], dL_dmeans[3 * (size_t)n + 2]};
+    float g6[6];
+#pragma unroll
+    for (int k = 0; k < 6; k++) g6[k] = dL_dcov[6 * (size_t)n + k];
+
+    // recompute the forward
+    float G[3][3], Cg[3][3], J[3][3];
+#pragma unroll
+    for (int i = 0; i < 3; i++) {
+        G[i][0] = X.v[3][i] - X.v[0][i]; G[i][1] = X.v[2][i] - X.v[0][i]; G[i][2] = X.v[1][i] - X.v[0][i];
+    }
+#pragma unroll
+    for (int k = 0; k < 9; k++) Cg[k / 3][k % 3] = cgrad[9 * (size_t)n + k];
+#pragma unroll
+    for (int i = 0; i < 3; i++)
+#pragma unroll
+        for (int j = 0; j < 3; j++) J[i][j] = G[i][0] * Cg[0][j] + G[i][1] * Cg[1][j] + G[i][2] * Cg[2][j];
+    const float4 q = *reinterpret_cast<const float4 *>(rotation + 4 * (size_t)n);
+    const float inv = 1.f / sqrtf(q.x * q.x + q.y * q.y + q.z * q.z + q.w * q.w);
+    const float qr = q.x * inv, qx = q.y * inv, qy = q.z * inv, qz = q.w * inv;
+    float Rm[3][3];
+    rotation_from_unit_quat(qr, qx, qy, qz, Rm);
+    const float s[3] = {scales[3 * (size_t)n], scales[3 * (size_t)n + 1], scales[3 * (size_t)n + 2]};
+    float JR[3][3], B[3][3];
+#pragma unroll
+    for (int i = 0; i < 3; i++)
+#pragma unroll
+        for (int k = 0; k < 3; k++) {
+            JR[i][k] = J[i][0] * Rm[0][k] + J[i][1] * Rm[1][k] + J[i][2] * Rm[2][k];
+            B[i][k] = JR[i][k] * s[k];
+        }
+    // cov = B B^T, only the upper triangle is an output: dB = (D + D^T) B with D the upper-triangular gradient
+    const float Ds[3][3] = {{2.f * g6[0], g6[1], g6[2]}, {g6[1], 2.f * g6[3], g6[4]}, {g6[2], g6[4], 2.f * g6[5]}};
+    float dB[3][3];
+#pragma unroll
+    for (int i = 0; i < 3; i++)
+#pragma unroll
+        for (int k = 0; k < 3; k++) dB[i][k] = Ds[i][0] * B[0][k] + Ds[i][1] * B[1][k] + Ds[i][2] * B[2][k];
+    // B = (J R) diag(s)
+    float ds[3], dJR[3][3];
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+        ds[k] = dB[0][k] * JR[0][k] + dB[1][k] * JR[1][k] + dB[2][k] * JR[2][k];
+#pragma unroll
+        for (int i = 0; i < 3; i++) dJR[i][k] = dB[i][k] * s[k];
+    }
+    // JR = J R : dJ = dJR R^T, dR = J^T dJR
+    float dJ[3][3], A[3][3];
+#pragma unroll
+    for (int i = 0; i < 3; i++)
+#pragma unroll
+        for (int j = 0; j < 3; j++) {
+            dJ[i][j] = dJR[i][0] * Rm[j][0] + dJR[i][1] * Rm[j][1] + dJR[i][2] * Rm[j][2];
+            A[i][j] = J[0][i] * dJR[0][j] + J[1][i] * dJR[1][j] + J[2][i] * dJR[2][j];
+        }
+    if (dL_dscales) {
+#pragma unroll
+        for (int k = 0; k < 3; k++) dL_dscales[3 * (size_t)n + k] = ds[k];
+    }
+    if (dL_drotation) {
+        const float r = qr, x = qx, y = qy, z = qz;
+        float dq[4];
+        dq[0] = 2.f * (-z * A[0][1] + y * A[0][2] + z * A[1][0] - x * A[1][2] - y * A[2][0] + x * A[2][1]);
+        dq[1] = 2.f * (y * A[0][1] + z * A[0][2] + y * A[1][0] - 2.f * x * A[1][1] - r * A[1][2] + z * A[2][0] + r * A[2][1] - 2.f * x * A[2][2]);
+        dq[2] = 2.f * (-2.f * y * A[0][0] + x * A[0][1] + r * A[0][2] + x * A[1][0] + z * A[1][2] - r * A[2][0] + z * A[2][1] - 2.f * y * A[2][2]);
+        dq[3] = 2.f * (-2.f * z * A[0][0] - r * A[0][1] + x * A[0][2] + r * A[1][0] - 2.f * z * A[1][1] + y * A[1][2] + x * A[2][0] + y * A[2][1]);
+        // through q / |q|
+        const float dotp = r * dq[0] + x * dq[1] + y * dq[2] + z * dq[3];
+        *reinterpret_cast<float4 *>(dL_drotation + 4 * (size_t)n) =
+            make_float4((dq[0] - r * dotp) * inv, (dq[1] - x * dotp) * inv, (dq[2] - y * dotp) * inv, (dq[3] - z * dotp) * inv);
+    }
+    if (dL_dbarys) {
+        float db[4];
+#pragma unroll
+        for (int k = 0; k < 4; k++) db[k] = X.v[k][0] * dm[0] + X.v[k][1] * dm[1] + X.v[k][2] * dm[2];
+        *reinterpret_cast<float4 *>(dL_dbarys + 4 * (size_t)n) = make_float4(db[0], db[1], db[2], db[3]);
+    }
+    if (dL_dtetpoints) {
+        // J = G Cg : dG = dJ Cg^T ; columns of G are (v3-v0, v2-v0, v1-v0)
+        float dv[4][3];
+#pragma unroll
+        for (int i = 0; i < 3; i++) {
+            const float g0 = dJ[i][0] * Cg[0][0] + dJ[i][1] * Cg[0][1] + dJ[i][2] * Cg[0][2];
+            const float g1 = dJ[i][0] * Cg[1][0] + dJ[i][1] * Cg[1][1] + dJ[i][2] * Cg[1][2];
+            const float g2 = dJ[i][0] * Cg[2][0] + dJ[i][1] * Cg[2][1] + dJ[i][2] * Cg[2][2];
+            dv[3][i] = g0 + bw[3] * dm[i];
+            dv[2][i] = g1 + bw[2] * dm[i];
+            dv[1][i] = g2 + bw[1] * dm[i];
+            dv[0][i] = -(g0 + g1 + g2) + bw[0] * dm[i];
+        }
+#pragma unroll
+        for (int k = 0; k < 4; k++)
+#pragma unroll
+            for (int c = 0; c < 3; c++) atomicAdd(dL_dtetpoints + 3 * vid[k] + c, dv[k][c]);
+    }
+}
+
+}  // namespace
+}  // namespace d3ga
+
+using namespace d3ga;
+
+extern "C" int d3ga_deform_forward(int N, int V, int T, const float *tetpoints, const int64_t *tets,
+                                   const int64_t *tetra_id, const float *barys, const float *canonical_gradient,
+                                   const float *scales, const float *rotation, float *means3D, float *cov3D,
+                                   d3ga_stream_t stream) {
+    if (N < 0 || V <= 0 || T <= 0) return D3GA_EINVAL;
+    if (!tetpoints || !tets || !tetra_id || !barys || !canonical_gradient || !scales || !rotation || !means3D || !cov3D)
+        return D3GA_EINVAL;
+    if (N == 0) return D3GA_OK;
+    deform_forward_kernel<<<(N + GEO_THREADS - 1) / GEO_THREADS, GEO_THREADS, 0, (cudaStream_t)stream>>>(
+        N, T, tetpoints, tets, tetra_id, barys, canonical_gradient, scales, rotation, means3D, cov3D);
+    D3GA_LAUNCH_CHECK();
+    return D3GA_OK;
+}
+
+extern "C" int d3ga_deform_backward(int N, int V, int T, const float *tetpoints, const int64_t *tets,
+                                    const int64_t *tetra_id, const float *barys, const float *canonical_gradient,
+                                    const float *scales, const float *rotation, const float *dL_dmeans3D,
+                                    const float *dL_dcov3D, float *dL_dtetpoints, float *dL_dbarys, float *dL_dscales,
+                                    float *dL_drotation, d3ga_stream_t stream) {
+    if (N < 0 || V <= 0 || T <= 0) return D3GA_EINVAL;
+    if (!tetpoints || !tets || !tetra_id || !barys || !canonical_gradient || !scales || !rotation || !dL_dmeans3D ||
+        !dL_dcov3D)
+        return D3GA_EINVAL;
+    if (N == 0) return D3GA_OK;
+    deform_backward_kernel<<<(N + GEO_THREADS - 1) / GEO_THREADS, GEO_THREADS, 0, (cudaStream_t)stream>>>(
+        N, T, tetpoints, tets, tetra_id, barys, canonical_gradient, scales, rotation, dL_dmeans3D, dL_dcov3D,
+        dL_dtetpoints, dL_dbarys, dL_dscales, dL_drotation);
+    D3GA_LAUNCH_CHECK();
+    return D3GA_OK;
+}

@@ -1,0 +1,308 @@
+// raster_sort.cu -- rows R4 (radix sort of the (tile|depth) keys) and R5 (per-tile ranges) of SURVEY.md section 8.
+//
+// Replaces cub::DeviceRadixSort::SortPairs(keys, values, num_rendered, 0, 32 + bit) and identifyTileRanges inside
+// diff_gaussian_rasterization._C.rasterize_gaussians (reached from renderer.py:130-141).
+//
+// Design: a onesweep least-significant-digit radix sort, 8-bit digits, stable (equal keys keep Gaussian order, as
+// the upstream sort does), with everything that depends on the duplicate count D read from DEVICE memory so the
+// host never waits for it:
+//   1. one histogram kernel counts all passes' digits in a single read of the keys; its last CTA turns the counts
+//      into per-pass exclusive bin offsets and a *plan*: a pass in which every key has the same digit (constant
+//      float exponent byte of the depth, unused tile bits) is skipped -- the output is bit-identical to a full sort;
+//   2. one kernel per remaining pass: each CTA takes a 4096-pair tile (dynamic ticket), ranks its keys with
+//      warp-level match-any multi-split, publishes its digit counts and resolves its global offsets with a
+//      decoupled look-back (one word per digit per tile), reorders the tile in shared memory and writes runs of
+//      equal digits with coalesced stores.  HBM traffic per pass: 12 B read + 12 B written per pair.
+//   3. ranges: neighbour compare of key >> 32 on the sorted list.
+// Algorithmic bytes: 8 D (histogram) + 24 D per executed pass + 8 D + 8 Tl (ranges).
+#include "common.cuh"
+
+namespace d3ga {
+
+namespace {
+
+constexpr uint32_t ST_AGG = 1u << 30, ST_INC = 2u << 30, ST_FLAGS = 3u << 30, ST_VALUE = ~ST_FLAGS;
+constexpr int HIST_THREADS = 256;
+constexpr int HIST_ITEMS = 8;
+
+// exclusive scan of one value per thread over a 256-thread CTA; s_tmp needs 8 words
+__device__ __forceinline__ uint32_t block_excl_scan_256(uint32_t v, uint32_t *s_tmp, uint32_t *total) {
+    const uint32_t lane = lane_id(), warp = threadIdx.x >> 5;
+    uint32_t incl = v;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        uint32_t n = __shfl_up_sync(0xffffffffu, incl, d);
+        if (lane >= (uint32_t)d) incl += n;
+    }
+    __syncthreads();   // s_tmp may still be in use by a previous call
+    if (lane == 31) s_tmp[warp] = incl;
+    __syncthreads();
+    uint32_t off = 0, tot = 0;
+#pragma unroll
+    for (int w = 0; w < 8; w++) {
+        uint32_t x = s_tmp[w];
+        if (w < (int)warp) off += x;
+        tot += x;
+    }
+    if (total) *total = tot;
+    return off + incl - v;
+}
+
+__global__ void __launch_bounds__(HIST_THREADS) sort_histogram_kernel(RasterHeader *hdr, const uint64_t *keys,
+                                                                      uint32_t *ghist, uint32_t *bins, int sort_bits,
+                                                                      int num_passes) {
+    __shared__ uint32_t s_hist[SORT_MAX_PASSES][256];
+    __shared__ uint32_t s_tmp[8];
+    __shared__ uint32_t s_flag;
+    if (hdr->overflow) return;
+    const uint32_t D = hdr->num_rendered;
+    const int tid = threadIdx.x;
+    for (int p = 0; p < num_passes; p++) s_hist[p][tid] = 0;
+    __syncthreads();
+    const uint64_t stride = (uint64_t)gridDim.x * HIST_THREADS * HIST_ITEMS;
+    for (uint64_t base = (uint64_t)blockIdx.x * HIST_THREADS * HIST_ITEMS; base < D; base += stride) {
+        uint64_t k[HIST_ITEMS];
+        bool ok[HIST_ITEMS];
+#pragma unroll
+        for (int i = 0; i < HIST_ITEMS; i++) {
+            const uint64_t idx = base + (uint64_t)i * HIST_THREADS + tid;
+            ok[i] = idx < D;
+            k[i] = ok[i] ? __ldcs(keys + idx) : 0;
+        }
+#pragma unroll
+        for (int i = 0; i < HIST_ITEMS; i++) {
+            const uint32_t active = __ballot_sync(0xffffffffu, ok[i]);
+            if (!active) continue;
+            for (int p = 0; p < num_passes; p++) {
+                const int shift = 8 * p;
+                const uint32_t nb = min(8, sort_bits - shift);
+                const uint32_t d = (uint32_t)(k[i] >> shift) & ((1u << nb) - 1u);
+                // neighbouring keys often share a digit (constant exponent byte, same tile): one add per warp then
+                const uint32_t d0 = __shfl_sync(0xffffffffu, d, __ffs(active) - 1);
+                const bool uniform = __all_sync(0xffffffffu, !ok[i] || d == d0);
+                if (uniform) {
+                    if (lane_id() == (uint32_t)(__ffs(active) - 1)) atomicAdd(&s_hist[p][d0], __popc(active));
+                } else if (ok[i]) {
+                    atomicAdd(&s_hist[p][d], 1u);
+                }
+            }
+        }
+    }
+    __syncthreads();
+    for (int p = 0; p < num_passes; p++) {
+        const uint32_t c = s_hist[p][tid];
+        if (c) atomicAdd(&ghist[p * 256 + tid], c);
+    }
+    __threadfence();
+    __syncthreads();
+    if (tid == 0) s_flag = atomicAdd(&hdr->hist_done, 1u) == gridDim.x - 1;
+    __syncthreads();
+    if (!s_flag) return;
+    // ---- last CTA: bin offsets and the pass plan ---------------------------------------------------------------------
+    __threadfence();
+    uint32_t src = 0;
+    for (int p = 0; p < num_passes; p++) {
+        const uint32_t c = __ldcg(ghist + p * 256 + tid);
+        const int all_in_one = __syncthreads_or(D == 0 || c == D);
+        const uint32_t ex = block_excl_scan_256(c, s_tmp, nullptr);
+        bins[p * 256 + tid] = ex;
+        if (tid == 0) {
+            hdr->pass_skip[p] = all_in_one ? 1u : 0u;
+            hdr->pass_src[p] = src;
+        }
+        if (!all_in_one) src ^= 1u;
+    }
+    if (tid == 0) {
+        hdr->final_sel = src;
+        hdr->sort_bits = (uint32_t)sort_bits;
+        hdr->num_passes = (uint32_t)num_passes;
+    }
+}
+
+constexpr int SORT_SMEM_KEYS = SORT_TILE * 8;
+constexpr int SORT_SMEM_VALS = SORT_TILE * 4;
+constexpr int SORT_WARPS = SORT_THREADS / 32;
+constexpr int SORT_SMEM_BYTES = SORT_SMEM_KEYS + SORT_SMEM_VALS + 4 * (SORT_WARPS * 256 + 256 + 256 + 16);
+
+__global__ void __launch_bounds__(SORT_THREADS) sort_pass_kernel(RasterHeader *hdr, uint64_t *keys0, uint64_t *keys1,
+                                                                 uint32_t *vals0, uint32_t *vals1,
+                                                                 const uint32_t *bins, uint32_t *tile_state,
+                                                                 uint32_t tiles_cap, int pass, int shift,
+                                                                 uint32_t mask) {
+    extern __shared__ __align__(16) uint8_t smem[];
+    uint64_t *s_keys = reinterpret_cast<uint64_t *>(smem);
+    uint32_t *s_vals = reinterpret_cast<uint32_t *>(smem + SORT_SMEM_KEYS);
+    uint32_t *s_whist = s_vals + SORT_TILE;         // [warps][256] per-warp digit counts -> exclusive over warps
+    uint32_t *s_start = s_whist + SORT_WARPS * 256; // [256] first slot of each digit inside the tile
+    uint32_t *s_gbase = s_start + 256;              // [256] global slot of s_start[d] minus s_start[d]
+    uint32_t *s_misc = s_gbase + 256;               // [0..7] scan scratch, [8] tile id
+
+    if (hdr->overflow || hdr->pass_skip[pass]) return;
+    const uint32_t D = hdr->num_rendered;
+    const int tid = threadIdx.x;
+    const uint32_t lane = lane_id(), warp = tid >> 5;
+    if (tid == 0) s_misc[8] = atomicAdd(&hdr->pass_ticket[pass], 1u);
+    __syncthreads();
+    const uint32_t tile = s_misc[8];
+    const uint64_t tile_base = (uint64_t)tile * SORT_TILE;
+    if (tile_base >= D) return;
+    const uint32_t n_valid = (uint32_t)min((uint64_t)SORT_TILE, (uint64_t)D - tile_base);
+    const uint32_t src = hdr->pass_src[pass];
+    const uint64_t *kin = src ? keys1 : keys0;
+    const uint32_t *vin = src ? vals1 : vals0;
+    uint64_t *kout = src ? keys0 : keys1;
+    uint32_t *vout = src ? vals0 : vals1;
+
+    uint32_t *wh = s_whist + warp * 256;
+#pragma unroll
+    for (int i = 0; i < 8; i++) wh[i * 32 + lane] = 0;
+
+    // warp w owns the contiguous chunk [w*512, (w+1)*512) of the tile, read 32 consecutive pairs at a time, so
+    // (warp, round, lane) order is the input order -- which is what makes the ranking stable.
+    uint64_t key[SORT_ITEMS];
+    uint32_t val[SORT_ITEMS];
+    const uint32_t chunk = warp * (32 * SORT_ITEMS);
+#pragma unroll
+    for (int r = 0; r < SORT_ITEMS; r++) {
+        const uint32_t local = chunk + r * 32 + lane;
+        const bool ok = local < n_valid;
+        key[r] = ok ? __ldcs(kin + tile_base + local) : ~0ull;
+        val[r] = ok ? __ldcs(vin + tile_base + local) : 0u;
+    }
+    __syncwarp();
+    uint32_t rank[SORT_ITEMS];
+#pragma unroll
+    for (int r = 0; r < SORT_ITEMS; r++) {
+        const uint32_t local = chunk + r * 32 + lane;
+        const uint32_t d = local < n_valid ? ((uint32_t)(key[r] >> shift) & mask) : 255u;
+        const uint32_t peers = __match_any_sync(0xffffffffu, d);
+        const uint32_t pre = wh[d];
+        __syncwarp();
+        if (lane == 31u - (uint32_t)__clz(peers)) wh[d] = pre + __popc(peers);
+        __syncwarp();
+        rank[r] = pre + __popc(peers & lanemask_lt());
+    }
+    __syncthreads();
+
+    // thread d: exclusive prefix of digit d over the warps, tile total, look-back for the global offset
+    const uint32_t d = tid;
+    uint32_t total = 0;
+#pragma unroll
+    for (int w = 0; w < SORT_WARPS; w++) {
+        const uint32_t c = s_whist[w * 256 + d];
+        s_whist[w * 256 + d] = total;
+        total += c;
+    }
+    const uint32_t n_invalid = SORT_TILE - n_valid;
+    const uint32_t count = total - (d == 255u ? n_invalid : 0u);   // padding sorts to the very end of digit 255
+    uint32_t *state = tile_state + ((size_t)pass * tiles_cap + tile) * 256;
+    uint32_t excl = 0;
+    if (tile == 0) {
+        st_volatile_u32(state + d, ST_INC | count);
+    } else {
+        st_volatile_u32(state + d, ST_AGG | count);
+        const uint32_t *prev = state + d - 256;
+        while (true) {
+            const uint32_t s = ld_volatile_u32(prev);
+            if ((s & ST_FLAGS) == 0) continue;
+            excl += s & ST_VALUE;
+            if ((s & ST_FLAGS) == ST_INC) break;
+            prev -= 256;
+        }
+        st_volatile_u32(state + d, ST_INC | (excl + count));
+    }
+    const uint32_t start = block_excl_scan_256(total, s_misc, nullptr);
+    s_start[d] = start;
+    s_gbase[d] = bins[pass * 256 + d] + excl - start;
+    __syncthreads();
+
+    // reorder inside the tile
+#pragma unroll
+    for (int r = 0; r < SORT_ITEMS; r++) {
+        const uint32_t local = chunk + r * 32 + lane;
+        const uint32_t dg = local < n_valid ? ((uint32_t)(key[r] >> shift) & mask) : 255u;
+        const uint32_t pos = s_start[dg] + s_whist[warp * 256 + dg] + rank[r];
+        s_keys[pos] = key[r];
+        s_vals[pos] = val[r];
+    }
+    __syncthreads();
+    // runs of equal digits go to consecutive global slots
+    for (uint32_t i = tid; i < n_valid; i += SORT_THREADS) {
+        const uint64_t k = s_keys[i];
+        const uint32_t dg = (uint32_t)(k >> shift) & mask;
+        const uint32_t dst = s_gbase[dg] + i;
+        kout[dst] = k;
+        vout[dst] = s_vals[i];
+    }
+}
+
+__global__ void __launch_bounds__(256) tile_ranges_kernel(const RasterHeader *hdr, const uint64_t *keys0,
+                                                          const uint64_t *keys1, uint2 *ranges) {
+    if (hdr->overflow) return;
+    const uint32_t D = hdr->num_rendered;
+    const uint64_t *keys = hdr->final_sel ? keys1 : keys0;
+    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < D; i += stride) {
+        const uint32_t cur = (uint32_t)(keys[i] >> 32);
+        if (i == 0) {
+            ranges[cur].x = 0;
+        } else {
+            const uint32_t prev = (uint32_t)(keys[i - 1] >> 32);
+            if (cur != prev) {
+                ranges[prev].y = (uint32_t)i;
+                ranges[cur].x = (uint32_t)i;
+            }
+        }
+        if (i == D - 1) ranges[cur].y = D;
+    }
+}
+
+}  // namespace
+
+static int g_sort_attr_set = 0;
+
+int launch_sort_and_ranges(uint8_t *geom, uint8_t *binning, const BinLayout &BL, uint64_t capacity, int sort_bits,
+                           uint8_t *image, const ImgLayout &IL, int num_tiles, cudaStream_t stream) {
+    RasterHeader *hdr = reinterpret_cast<RasterHeader *>(geom);
+    uint64_t *keys0 = reinterpret_cast<uint64_t *>(binning + BL.keys0);
+    uint64_t *keys1 = reinterpret_cast<uint64_t *>(binning + BL.keys1);
+    uint32_t *vals0 = reinterpret_cast<uint32_t *>(binning + BL.vals0);
+    uint32_t *vals1 = reinterpret_cast<uint32_t *>(binning + BL.vals1);
+    uint32_t *ghist = reinterpret_cast<uint32_t *>(binning + BL.hist);
+    uint32_t *bins = reinterpret_cast<uint32_t *>(binning + BL.bins);
+    uint32_t *tile_state = reinterpret_cast<uint32_t *>(binning + BL.tile_state);
+    uint2 *ranges = reinterpret_cast<uint2 *>(image + IL.ranges);
+    const int num_passes = (sort_bits + 7) / 8;
+    if (num_passes > SORT_MAX_PASSES) return D3GA_EINVAL;
+    const uint32_t tiles_cap = (uint32_t)sort_tiles(capacity);
+
+    if (!g_sort_attr_set) {
+        D3GA_CUDA(cudaFuncSetAttribute(sort_pass_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SORT_SMEM_BYTES));
+        g_sort_attr_set = 1;
+    }
+    D3GA_CUDA(cudaMemsetAsync(ghist, 0, 4 * 256 * SORT_MAX_PASSES, stream));
+    D3GA_CUDA(cudaMemsetAsync(tile_state, 0, 4ull * 256 * tiles_cap * num_passes, stream));
+    D3GA_CUDA(cudaMemsetAsync(ranges, 0, 8ull * num_tiles, stream));
+
+    const uint64_t per_cta = (uint64_t)HIST_THREADS * HIST_ITEMS;
+    int hist_grid = (int)((capacity + per_cta - 1) / per_cta);
+    if (hist_grid > 148 * 8) hist_grid = 148 * 8;
+    if (hist_grid < 1) hist_grid = 1;
+    sort_histogram_kernel<<<hist_grid, HIST_THREADS, 0, stream>>>(hdr, keys0, ghist, bins, sort_bits, num_passes);
+    D3GA_LAUNCH_CHECK();
+    for (int p = 0; p < num_passes; p++) {
+        const int shift = 8 * p;
+        const int nb = sort_bits - shift < 8 ? sort_bits - shift : 8;
+        sort_pass_kernel<<<tiles_cap, SORT_THREADS, SORT_SMEM_BYTES, stream>>>(
+            hdr, keys0, keys1, vals0, vals1, bins, tile_state, tiles_cap, p, shift, (1u << nb) - 1u);
+        D3GA_LAUNCH_CHECK();
+    }
+    int rg = (int)((capacity + 255) / 256);
+    if (rg > 148 * 16) rg = 148 * 16;
+    if (rg < 1) rg = 1;
+    tile_ranges_kernel<<<rg, 256, 0, stream>>>(hdr, keys0, keys1, ranges);
+    D3GA_LAUNCH_CHECK();
+    return D3GA_OK;
+}
+
+}  // namespace d3ga

@@ -1,0 +1,223 @@
+"""Drop-in for the ``diff_gaussian_rasterization`` package that D3GA imports at renderer.py:13-16.
+
+Same names, fields, argument meaning and return arity as the upstream Python glue (branch ``dr_aa`` of
+graphdeco-inria/diff-gaussian-rasterization, absent from the reference tree -- .SUBMODULES.json:16-22):
+
+* ``GaussianRasterizationSettings`` -- NamedTuple with the 13 fields renderer.py:79-93 passes by keyword;
+* ``GaussianRasterizer(raster_settings)`` -- nn.Module; ``forward(means3D, means2D, opacities, shs=None,
+  colors_precomp=None, scales=None, rotations=None, cov3D_precomp=None)`` returns ``(color[3,H,W], radii[P] int32,
+  invdepth[1,H,W])``; raises when both/neither of ``shs | colors_precomp`` or of ``(scales, rotations) |
+  cov3D_precomp`` are given;
+* gradients flow to means3D, means2D, shs | colors_precomp, opacities, scales + rotations | cov3D_precomp.
+
+All compute goes through the C-ABI of libd3ga_b200.so (hand-written sm_100a kernels); there is no PyTorch or CPU
+fallback.  torch is used for device memory, the current stream and autograd bookkeeping only.
+"""
+from __future__ import annotations
+
+from typing import NamedTuple
+
+import torch
+import torch.nn as nn
+
+from d3ga_b200 import _lib
+
+
+class GaussianRasterizationSettings(NamedTuple):
+    image_height: int
+    image_width: int
+    tanfovx: float
+    tanfovy: float
+    bg: torch.Tensor
+    scale_modifier: float
+    viewmatrix: torch.Tensor
+    projmatrix: torch.Tensor
+    sh_degree: int
+    campos: torch.Tensor
+    prefiltered: bool
+    debug: bool
+    antialiasing: bool = False
+
+
+# ---- workspace policy ---------------------------------------------------------------------------------------------
+# The number of (tile, Gaussian) duplicates is only known on the device.  Instead of stopping the pipeline to read
+# it (upstream), both forward stages are enqueued against a capacity guessed from the previous frame; the count
+# arrives by an async copy while the sort and blend are already running, and the stages are re-run with a larger
+# workspace only if it did not fit.
+_capacity_hint: dict = {}
+_pinned_slots: dict = {}
+CAPACITY_SLACK = 1.25
+
+
+def _pinned_counter(device):
+    slot = _pinned_slots.get(device)
+    if slot is None:
+        slot = [torch.zeros(16, 2, dtype=torch.int32).pin_memory(), 0]
+        _pinned_slots[device] = slot
+    buf, k = slot
+    slot[1] = (k + 1) % buf.shape[0]
+    return buf[k]
+
+
+def _f32c(t, name):
+    if t is None:
+        return None
+    if not t.is_cuda:
+        raise RuntimeError(f"{name} must be a CUDA tensor")
+    if t.dtype != torch.float32:
+        raise RuntimeError(f"{name} must be float32, got {t.dtype}")
+    return t.contiguous()
+
+
+class RasterState:
+    """What the forward keeps alive for the backward (upstream: geomBuffer, binningBuffer, imgBuffer)."""
+
+    __slots__ = ("geom", "binning", "image", "capacity", "num_rendered", "P", "W", "H")
+
+
+def rasterize_forward(means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp, rs,
+                      want_invdepth=True):
+    lib = _lib.load()
+    dev = means3D.device
+    P = int(means3D.shape[0])
+    W, H = int(rs.image_width), int(rs.image_height)
+    M = 0 if sh is None else int(sh.shape[1])
+    key = (dev, P, W, H)
+    cap = _capacity_hint.get(key, max(1 << 16, 6 * P))
+    bg = _f32c(rs.bg, "bg")
+    view = _f32c(rs.viewmatrix, "viewmatrix")
+    proj = _f32c(rs.projmatrix, "projmatrix")
+    campos = _f32c(rs.campos, "campos")
+    with torch.cuda.device(dev):
+        stream = torch.cuda.current_stream().cuda_stream
+        color = torch.empty((3, H, W), dtype=torch.float32, device=dev)
+        invdepth = torch.empty((1, H, W), dtype=torch.float32, device=dev) if want_invdepth else None
+        radii = torch.empty((P,), dtype=torch.int32, device=dev)
+        st = RasterState()
+        st.P, st.W, st.H = P, W, H
+        gb, _, ib = _lib.workspace_bytes(P, W, H, 0)
+        st.geom = torch.empty(gb, dtype=torch.uint8, device=dev)
+        st.image = torch.empty(ib, dtype=torch.uint8, device=dev)
+        host = _pinned_counter(dev)
+        ev = torch.cuda.Event()
+        while True:
+            _, bb, _ = _lib.workspace_bytes(P, W, H, cap)
+            st.binning = torch.empty(bb, dtype=torch.uint8, device=dev)
+            st.capacity = cap
+            _lib.check(lib.d3ga_raster_forward_geometry(
+                P, int(rs.sh_degree), M, _lib.ptr(means3D), _lib.ptr(scales), float(rs.scale_modifier),
+                _lib.ptr(rotations), _lib.ptr(opacities), _lib.ptr(sh), _lib.ptr(cov3Ds_precomp),
+                _lib.ptr(colors_precomp), view.data_ptr(), proj.data_ptr(), campos.data_ptr(), W, H,
+                float(rs.tanfovx), float(rs.tanfovy), int(bool(rs.prefiltered)), int(bool(rs.antialiasing)),
+                st.geom.data_ptr(), st.binning.data_ptr(), cap, _lib.ptr(radii), host.data_ptr(), stream),
+                "raster_forward_geometry")
+            ev.record()
+            _lib.check(lib.d3ga_raster_forward_render(
+                P, W, H, bg.data_ptr(), _lib.ptr(colors_precomp), st.geom.data_ptr(), st.binning.data_ptr(), cap,
+                st.image.data_ptr(), color.data_ptr(), _lib.ptr(invdepth), stream), "raster_forward_render")
+            ev.synchronize()   # waits for stage 1 only; stage 2 keeps running
+            D = int(host[0].item()) & 0xFFFFFFFF
+            overflow = int(host[1].item())
+            st.num_rendered = D
+            if not overflow:
+                break
+            if D >= (1 << 30) - 1:
+                raise _lib.D3GAError(f"{D} (tile, Gaussian) duplicates exceed the 2^30-1 limit")
+            cap = min((1 << 30) - 1, int(D * CAPACITY_SLACK) + 4096)
+        _capacity_hint[key] = min((1 << 30) - 1, int(D * CAPACITY_SLACK) + 4096)
+    return color, radii, invdepth, st
+
+
+def rasterize_backward(st, grad_color, grad_invdepth, means3D, sh, colors_precomp, opacities, scales, rotations,
+                       cov3Ds_precomp, radii, rs):
+    lib = _lib.load()
+    dev = means3D.device
+    P, W, H = st.P, st.W, st.H
+    M = 0 if sh is None else int(sh.shape[1])
+    with torch.cuda.device(dev):
+        stream = torch.cuda.current_stream().cuda_stream
+        grad_color = _f32c(grad_color, "grad_color")
+        grad_invdepth = _f32c(grad_invdepth, "grad_invdepth")
+        scratch = torch.empty(int(lib.d3ga_raster_backward_scratch_bytes(P)), dtype=torch.uint8, device=dev)
+        g_means3D = torch.empty((P, 3), dtype=torch.float32, device=dev)
+        g_means2D = torch.empty((P, 3), dtype=torch.float32, device=dev)
+        g_opacity = torch.empty((P, 1), dtype=torch.float32, device=dev)
+        g_colors = torch.empty((P, 3), dtype=torch.float32, device=dev) if colors_precomp is not None else None
+        g_sh = torch.empty((P, M, 3), dtype=torch.float32, device=dev) if sh is not None else None
+        g_cov = torch.empty((P, 6), dtype=torch.float32, device=dev) if cov3Ds_precomp is not None else None
+        g_scales = torch.empty((P, 3), dtype=torch.float32, device=dev) if scales is not None else None
+        g_rot = torch.empty((P, 4), dtype=torch.float32, device=dev) if rotations is not None else None
+        _lib.check(lib.d3ga_raster_backward(
+            P, int(rs.sh_degree), M, W, H, _f32c(rs.bg, "bg").data_ptr(), _lib.ptr(means3D), _lib.ptr(colors_precomp),
+            _lib.ptr(opacities), _lib.ptr(scales), float(rs.scale_modifier), _lib.ptr(rotations),
+            _lib.ptr(cov3Ds_precomp), _lib.ptr(sh), _f32c(rs.viewmatrix, "viewmatrix").data_ptr(),
+            _f32c(rs.projmatrix, "projmatrix").data_ptr(), _f32c(rs.campos, "campos").data_ptr(), float(rs.tanfovx),
+            float(rs.tanfovy), int(bool(rs.antialiasing)), _lib.ptr(radii), st.geom.data_ptr(), st.binning.data_ptr(),
+            st.capacity, st.image.data_ptr(), grad_color.data_ptr(), _lib.ptr(grad_invdepth), scratch.data_ptr(),
+            g_means2D.data_ptr(), g_opacity.data_ptr(), _lib.ptr(g_colors), g_means3D.data_ptr(), _lib.ptr(g_cov),
+            _lib.ptr(g_sh), _lib.ptr(g_scales), _lib.ptr(g_rot), stream), "raster_backward")
+    return g_means3D, g_means2D, g_sh, g_colors, g_opacity, g_scales, g_rot, g_cov
+
+
+class _RasterizeGaussians(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
+                raster_settings):
+        means3D = _f32c(means3D, "means3D")
+        sh = _f32c(sh, "shs")
+        colors_precomp = _f32c(colors_precomp, "colors_precomp")
+        opacities = _f32c(opacities, "opacities")
+        scales = _f32c(scales, "scales")
+        rotations = _f32c(rotations, "rotations")
+        cov3Ds_precomp = _f32c(cov3Ds_precomp, "cov3D_precomp")
+        color, radii, invdepth, st = rasterize_forward(means3D, sh, colors_precomp, opacities, scales, rotations,
+                                                       cov3Ds_precomp, raster_settings)
+        ctx.raster_settings = raster_settings
+        ctx.state = st
+        ctx.save_for_backward(means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp, radii)
+        ctx.mark_non_differentiable(radii)
+        ctx.set_materialize_grads(False)   # an unused invdepth output costs nothing in the backward
+        return color, radii, invdepth
+
+    @staticmethod
+    def backward(ctx, grad_color, _grad_radii, grad_invdepth):
+        means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp, radii = ctx.saved_tensors
+        st, rs = ctx.state, ctx.raster_settings
+        if grad_color is None:
+            grad_color = torch.zeros((3, st.H, st.W), dtype=torch.float32, device=means3D.device)
+        g = rasterize_backward(st, grad_color, grad_invdepth, means3D, sh, colors_precomp, opacities, scales,
+                               rotations, cov3Ds_precomp, radii, rs)
+        g_means3D, g_means2D, g_sh, g_colors, g_opacity, g_scales, g_rot, g_cov = g
+        if opacities is not None and g_opacity.shape != opacities.shape:
+            g_opacity = g_opacity.reshape(opacities.shape)
+        return g_means3D, g_means2D, g_sh, g_colors, g_opacity, g_scales, g_rot, g_cov, None
+
+
+def rasterize_gaussians(means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
+                        raster_settings):
+    return _RasterizeGaussians.apply(means3D, means2D, sh, colors_precomp, opacities, scales, rotations,
+                                     cov3Ds_precomp, raster_settings)
+
+
+class GaussianRasterizer(nn.Module):
+    def __init__(self, raster_settings):
+        super().__init__()
+        self.raster_settings = raster_settings
+
+    def markVisible(self, positions):
+        """Boolean mask of the points in front of the near plane (z_view > 0.2), like upstream's mark_visible."""
+        with torch.no_grad():
+            v = self.raster_settings.viewmatrix
+            z = positions[:, 0] * v[0, 2] + positions[:, 1] * v[1, 2] + positions[:, 2] * v[2, 2] + v[3, 2]
+            return z > 0.2
+
+    def forward(self, means3D, means2D, opacities, shs=None, colors_precomp=None, scales=None, rotations=None,
+                cov3D_precomp=None):
+        if (shs is None and colors_precomp is None) or (shs is not None and colors_precomp is not None):
+            raise Exception("Please provide excatly one of either SHs or precomputed colors!")
+        if ((scales is None or rotations is None) and cov3D_precomp is None) or (
+            (scales is not None or rotations is not None) and cov3D_precomp is not None
+        ):
+            raise Exception("Please provide exactly one of either scale/rotation pair or precomputed 3D covariance!")
+        return rasterize_gaussians(means3D, means2D, shs, colors_precomp, opacities, scales, rotations,
+                                   cov3D_precomp, self.raster_settings)

@@ -1,0 +1,186 @@
+"""Drop-in for the part of ``tetra_sampler`` that D3GA uses (lib/cage.py:17: ``from tetra_sampler import Tetra,
+compute_bary``), plus the fused deformation op that replaces the torch chain of models/cage_net.py:218-230.
+
+* ``Tetra`` -- tet-mesh container with the attributes lib/cage*.py reads (``tetras, points, triangles, tetra_faces,
+  triangle_to_tetra, gradient(), get_positions(), get_triangles(), n(), n_points()``), see
+  submodules/tetra-sampler/tetra_sampler/tetra.py:12-130.  ``Tetra(path)`` reads a ``cage.mesh`` through meshio like
+  the reference when meshio is installed; ``Tetra.from_tensors(points, tetras)`` builds one from tensors.
+* ``compute_bary(points, tetras, triangles, tri_to_tetra, tetra_model)`` -> ``(barys[N,4] f32, tetra_id[N] i64,
+  active[N] i32)``; backward raises NotImplementedError (tetra_sampler/barys.py:9-33).
+* ``deform_gaussians(tetpoints, tets, tetra_id, barys, canonical_gradient, scales, rotation)`` ->
+  ``(means3D[N,3], cov3D_precomp[N,6])``, differentiable in tetpoints, barys, scales and rotation.
+
+The ray/segment samplers and the bundled SMPL layer of the reference package are not on D3GA's render path
+ and are not provided.
+"""
+from __future__ import annotations
+
+import numpy as np
+import torch
+
+from d3ga_b200 import _lib
+
+
+def _check(t, name, dtype):
+    if not t.is_cuda:
+        raise RuntimeError(f"{name} must be a CUDA tensor")   # CHECK_INPUT of include/common.h:3-7
+    if t.dtype != dtype:
+        raise RuntimeError(f"{name} must be {dtype}, got {t.dtype}")
+    return t.contiguous()
+
+
+def unique_faces_and_topology(tetras: np.ndarray):
+    """Unique sorted faces [F,3] and face -> (tet, tet | -1) map [F,2] int32 (tetra.py:45-48,88-130).
+
+    Faces are the rows of ``unique(sort(ABCD))`` in lexicographic order like ``torch.unique(dim=0)``; the two slots of
+    a face are filled in increasing tet id, which is the order the reference's dict loop produces.
+    """
+    t = np.asarray(tetras, dtype=np.int64)
+    T = t.shape[0]
+    a, b, c, d = t[:, 0], t[:, 1], t[:, 2], t[:, 3]
+    faces = np.stack([np.stack([a, b, c], 1), np.stack([a, b, d], 1), np.stack([a, c, d], 1), np.stack([b, c, d], 1)], 1)
+    faces = np.sort(faces.reshape(-1, 3), axis=1)
+    owner = np.repeat(np.arange(T, dtype=np.int64), 4)
+    uniq, inv = np.unique(faces, axis=0, return_inverse=True)
+    inv = inv.reshape(-1)
+    order = np.lexsort((owner, inv))   # by face, then by tet id
+    inv_s, own_s = inv[order], owner[order]
+    first = np.ones(inv_s.shape[0], dtype=bool)
+    first[1:] = inv_s[1:] != inv_s[:-1]
+    topo = -np.ones((uniq.shape[0], 2), dtype=np.int32)
+    topo[inv_s[first], 0] = own_s[first]
+    second = ~first
+    topo[inv_s[second], 1] = own_s[second]
+    return uniq.astype(np.int64), topo
+
+
+class Tetra:
+    def __init__(self, path=None):
+        if path is None:
+            return
+        try:
+            import meshio   # the reference's reader (tetra.py:5,15); not part of the hot path
+        except ImportError as e:   # pragma: no cover
+            raise ImportError("Tetra(path) needs meshio to read cage.mesh; use Tetra.from_tensors instead") from e
+        mesh = meshio.read(path)
+        tris = mesh.cells_dict.get("triangle")
+        self._init(torch.from_numpy(np.asarray(mesh.points)).float(), torch.from_numpy(mesh.cells_dict["tetra"]).long(),
+                   None if tris is None else torch.from_numpy(tris).long())
+
+    @classmethod
+    def from_tensors(cls, points, tetras, triangles=None, device=None):
+        self = cls(None)
+        self._init(points, tetras, triangles, device)
+        return self
+
+    def _init(self, points, tetras, triangles=None, device=None):
+        if device is None:
+            device = points.device if points.is_cuda else ("cuda" if torch.cuda.is_available() else "cpu")
+        self.points = points.float().to(device)
+        self.tetras = tetras.long().to(device)
+        self.A, self.B, self.C, self.D = (self.tetras[:, k] for k in range(4))
+        v0 = torch.stack([self.A, self.B, self.C], dim=1)
+        v1 = torch.stack([self.A, self.B, self.D], dim=1)
+        v2 = torch.stack([self.A, self.C, self.D], dim=1)
+        v3 = torch.stack([self.B, self.C, self.D], dim=1)
+        self.ABCD = torch.stack([v0, v1, v2, v3], dim=1)
+        faces, topo = unique_faces_and_topology(self.tetras.cpu().numpy())
+        self.tetra_faces = torch.from_numpy(faces).to(device)
+        self.triangle_to_tetra = torch.from_numpy(topo).int().to(device)
+        surf = self.triangle_to_tetra[:, 1] == -1
+        self.surface_triangle = self.tetra_faces[surf]
+        self.surface_tetras = self.triangle_to_tetra[surf][:, 0].long()
+        self.triangles = triangles.long().to(device) if triangles is not None else self.surface_triangle
+
+    def get_positions(self, points=None):
+        return (self.points if points is None else points)[self.tetras]
+
+    def get_triangles(self, points=None):
+        return (self.points if points is None else points)[self.tetra_faces]
+
+    def gradient(self, tetras):
+        v0, v1, v2, v3 = tetras[:, 0], tetras[:, 1], tetras[:, 2], tetras[:, 3]
+        return torch.stack([v3 - v0, v2 - v0, v1 - v0], dim=2)
+
+    def n(self):
+        return self.tetras.shape[0]
+
+    def n_points(self):
+        return self.points.size(0)
+
+
+class BarycentricCuda(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, points, tetras, triangles, tri_to_tetra, tetra_model):
+        lib = _lib.load()
+        points = _check(points, "points", torch.float32)
+        tetras = _check(tetras, "tetras", torch.float32)
+        triangles = _check(triangles, "triangles", torch.float32)
+        tri_to_tetra = _check(tri_to_tetra, "tri_to_tetra", torch.int32)
+        n, dev = points.size(0), points.device
+        with torch.cuda.device(dev):
+            barys = torch.zeros(n, 4, dtype=torch.float32, device=dev)
+            tetra_id = torch.zeros(n, dtype=torch.int32, device=dev)
+            active_points = torch.zeros(n, dtype=torch.int32, device=dev)
+            _lib.check(lib.d3ga_compute_bary(
+                n, int(tetras.shape[0]), int(triangles.shape[0]), _lib.ptr(points), tetras.data_ptr(),
+                triangles.data_ptr(), tri_to_tetra.data_ptr(), _lib.ptr(barys), _lib.ptr(tetra_id),
+                _lib.ptr(active_points), None, torch.cuda.current_stream().cuda_stream), "compute_bary")
+        return barys, tetra_id.long(), active_points
+
+    @staticmethod
+    def backward(ctx, grad_output, *args, **kwargs):
+        raise NotImplementedError
+
+
+def compute_bary(points, tetras, triangles, tri_to_tetra, tetra_model):
+    return BarycentricCuda.apply(points, tetras, triangles, tri_to_tetra, tetra_model)
+
+
+class _DeformGaussians(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, tetpoints, tets, tetra_id, barys, canonical_gradient, scales, rotation):
+        lib = _lib.load()
+        tetpoints = _check(tetpoints, "tetpoints", torch.float32)
+        tets = _check(tets, "tets", torch.int64)
+        tetra_id = _check(tetra_id, "tetra_id", torch.int64)
+        barys = _check(barys, "barys", torch.float32)
+        canonical_gradient = _check(canonical_gradient, "canonical_gradient", torch.float32)
+        scales = _check(scales, "scales", torch.float32)
+        rotation = _check(rotation, "rotation", torch.float32)
+        N, V, T, dev = int(tetra_id.shape[0]), int(tetpoints.shape[0]), int(tets.shape[0]), tetpoints.device
+        with torch.cuda.device(dev):
+            means3D = torch.empty((N, 3), dtype=torch.float32, device=dev)
+            cov3D = torch.empty((N, 6), dtype=torch.float32, device=dev)
+            _lib.check(lib.d3ga_deform_forward(
+                N, V, T, tetpoints.data_ptr(), tets.data_ptr(), _lib.ptr(tetra_id), _lib.ptr(barys),
+                _lib.ptr(canonical_gradient), _lib.ptr(scales), _lib.ptr(rotation), _lib.ptr(means3D),
+                _lib.ptr(cov3D), torch.cuda.current_stream().cuda_stream), "deform_forward")
+        ctx.save_for_backward(tetpoints, tets, tetra_id, barys, canonical_gradient, scales, rotation)
+        ctx.set_materialize_grads(False)
+        return means3D, cov3D
+
+    @staticmethod
+    def backward(ctx, g_means, g_cov):
+        lib = _lib.load()
+        tetpoints, tets, tetra_id, barys, canonical_gradient, scales, rotation = ctx.saved_tensors
+        N, V, T, dev = int(tetra_id.shape[0]), int(tetpoints.shape[0]), int(tets.shape[0]), tetpoints.device
+        need = ctx.needs_input_grad
+        with torch.cuda.device(dev):
+            g_means = torch.zeros((N, 3), dtype=torch.float32, device=dev) if g_means is None else g_means.contiguous()
+            g_cov = torch.zeros((N, 6), dtype=torch.float32, device=dev) if g_cov is None else g_cov.contiguous()
+            g_tet = torch.zeros((V, 3), dtype=torch.float32, device=dev) if need[0] else None
+            g_bary = torch.empty((N, 4), dtype=torch.float32, device=dev) if need[3] else None
+            g_scales = torch.empty((N, 3), dtype=torch.float32, device=dev) if need[5] else None
+            g_rot = torch.empty((N, 4), dtype=torch.float32, device=dev) if need[6] else None
+            _lib.check(lib.d3ga_deform_backward(
+                N, V, T, tetpoints.data_ptr(), tets.data_ptr(), _lib.ptr(tetra_id), _lib.ptr(barys),
+                _lib.ptr(canonical_gradient), _lib.ptr(scales), _lib.ptr(rotation), _lib.ptr(g_means),
+                _lib.ptr(g_cov), _lib.ptr(g_tet), _lib.ptr(g_bary), _lib.ptr(g_scales), _lib.ptr(g_rot),
+                torch.cuda.current_stream().cuda_stream), "deform_backward")
+        return g_tet, None, None, g_bary, None, g_scales, g_rot
+
+
+def deform_gaussians(tetpoints, tets, tetra_id, barys, canonical_gradient, scales, rotation):
+    """Fused cage -> Gaussian deformation (models/cage_net.py:218-230).  Returns (means3D, cov3D_precomp)."""
+    return _DeformGaussians.apply(tetpoints, tets, tetra_id, barys, canonical_gradient, scales, rotation)

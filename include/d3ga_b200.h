@@ -1,0 +1,155 @@
+/*
+ * d3ga_b200.h -- C-ABI of libd3ga_b200.so: the B200 (sm_100a) render hot path of D3GA.
+ *
+ * Plain pointers and sizes only; no torch types.  All pointers are DEVICE pointers unless a parameter says
+ * "host".  Every entry point:
+ *   - returns 0 on success or a negative D3GA_E* code (d3ga_error_string() gives the text);
+ *   - enqueues its work on `stream` (a cudaStream_t passed as void*) and returns without synchronising;
+ *   - allocates nothing: the caller owns outputs and workspaces (sizes from the *_workspace_bytes queries);
+ *   - runs on the CURRENT device: the caller makes the buffers' device current first (the reference's own
+ *     extensions never did -- sampler_points.cpp:191 takes the current stream without a device guard).
+ *
+ * Each declaration cites the reference interface it replaces.  Citations are relative to the D3GA tree.
+ * The rasterizer's native source is a third-party dependency that is absent from that tree
+ * (graphdeco-inria/diff-gaussian-rasterization @ 9c5c2028, .SUBMODULES.json:16-22), so those entry points cite
+ * the reference's call site, which fixes names, argument meaning and layouts.
+ */
+#ifndef D3GA_B200_H
+#define D3GA_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define D3GA_OK 0
+#define D3GA_EINVAL (-1)    /* bad argument (null pointer, negative size, inconsistent option set) */
+#define D3GA_ECUDA (-2)     /* a CUDA runtime call failed; d3ga_last_cuda_error() has the cudaError_t */
+#define D3GA_ETOOBIG (-3)   /* size beyond what the 32-bit duplicate indices / look-back words can hold */
+#define D3GA_ENOTREADY (-4) /* staged call made out of order */
+
+typedef void *d3ga_stream_t; /* cudaStream_t */
+
+/* ---- library ------------------------------------------------------------------------------------------------ */
+int d3ga_version(void);
+const char *d3ga_error_string(int code);
+int d3ga_last_cuda_error(void);
+/* Number of kernels this library has launched in this process (the `gpu_launches` figure of bench.py). */
+uint64_t d3ga_launch_count(void);
+
+/* ---- rasterizer -------------------------------------------------------------
+ * Replaces: diff_gaussian_rasterization._C.rasterize_gaussians / rasterize_gaussians_backward as reached from
+ * renderer.py:130-141 (GaussianRasterizer.__call__) with the settings of renderer.py:79-93.
+ *
+ * Layouts (all fp32 row-major as the reference passes them): means3D [P,3]; cov3D_precomp [P,6] packed
+ * (xx,xy,xz,yy,yz,zz) (utils/general_utils.py:24-34) OR scales [P,3] + rotations [P,4] (r,x,y,z);
+ * opacities [P]; colors_precomp [P,3] OR shs [P,sh_coeffs,3]; viewmatrix / projmatrix [16] in the row-vector
+ * convention of lib/cameras.py:68-75; campos [3]; background [3]; out_color [3,H,W] planar; out_invdepth [H,W].
+ *
+ * Three workspaces, mirroring the upstream geomBuffer / binningBuffer / imgBuffer that the autograd function
+ * keeps alive between forward and backward:
+ *   geom    : per-Gaussian SoA (depth, xy, conic+opacity, rgb, cov3D, tiles_touched, offsets) + header + scan state
+ *   binning : (tile|depth) keys and Gaussian indices, double-buffered, + radix-sort state; sized by `capacity`
+ *   image   : per-tile ranges, per-pixel final transmittance and contributor count
+ * `capacity` is the number of (tile, Gaussian) duplicates the binning workspace can hold.  The true count
+ * ("num_rendered") is only known on the device; it is written to num_rendered_host (2 x uint32: count, overflow
+ * flag) by an async copy at the end of the geometry stage.  If it exceeds `capacity` the later stages do nothing
+ * and the caller re-runs BOTH stages with a larger capacity.  This replaces upstream's mid-pipeline host
+ * synchronisation: the caller may enqueue the render stage first and check the count afterwards.
+ */
+int d3ga_raster_workspace_bytes(int P, int W, int H, uint64_t capacity,
+                                uint64_t *geom_bytes, uint64_t *binning_bytes, uint64_t *image_bytes);
+
+/* Stage 1 = preprocess (R1) + scan (R2) + key duplication (R3), one fused kernel.
+ * Exactly one of {cov3D_precomp} / {scales, rotations} and one of {colors_precomp} / {shs} is non-null.
+ * radii [P] int32 is an output (the second element of the tuple GaussianRasterizer returns).
+ * num_rendered_host: pinned HOST memory, 2 x uint32, may be null. */
+int d3ga_raster_forward_geometry(int P, int sh_degree, int sh_coeffs,
+                                 const float *means3D, const float *scales, float scale_modifier,
+                                 const float *rotations, const float *opacities, const float *shs,
+                                 const float *cov3D_precomp, const float *colors_precomp,
+                                 const float *viewmatrix, const float *projmatrix, const float *campos,
+                                 int W, int H, float tanfovx, float tanfovy, int prefiltered, int antialiasing,
+                                 void *geom, void *binning, uint64_t capacity,
+                                 int32_t *radii, uint32_t *num_rendered_host, d3ga_stream_t stream);
+
+/* Stage 2 = radix sort (R4) + tile ranges (R5) + alpha blending (R6).  out_invdepth may be null. */
+int d3ga_raster_forward_render(int P, int W, int H, const float *background, const float *colors_precomp,
+                               void *geom, void *binning, uint64_t capacity, void *image,
+                               float *out_color, float *out_invdepth, d3ga_stream_t stream);
+
+/* Backward = blend backward (R7) + preprocess backward (R8).
+ * Inputs are the forward's inputs and workspaces plus dL_dout_color [3,H,W] (and optionally dL_dout_invdepth
+ * [H,W]).  Outputs (written, not accumulated): dL_dmeans3D [P,3], dL_dmeans2D [P,3], dL_dopacity [P],
+ * dL_dcolors [P,3] (when colors_precomp was given) or dL_dsh [P,sh_coeffs,3], dL_dcov3D [P,6] (when
+ * cov3D_precomp was given) or dL_dscales [P,3] + dL_drotations [P,4].
+ * grad_scratch: d3ga_raster_backward_scratch_bytes(P) bytes, contents undefined on entry. */
+uint64_t d3ga_raster_backward_scratch_bytes(int P);
+int d3ga_raster_backward(int P, int sh_degree, int sh_coeffs, int W, int H, const float *background,
+                         const float *means3D, const float *colors_precomp, const float *opacities,
+                         const float *scales, float scale_modifier, const float *rotations,
+                         const float *cov3D_precomp, const float *shs,
+                         const float *viewmatrix, const float *projmatrix, const float *campos,
+                         float tanfovx, float tanfovy, int antialiasing, const int32_t *radii,
+                         const void *geom, const void *binning, uint64_t capacity, const void *image,
+                         const float *dL_dout_color, const float *dL_dout_invdepth,
+                         void *grad_scratch,
+                         float *dL_dmeans2D, float *dL_dopacity, float *dL_dcolors, float *dL_dmeans3D,
+                         float *dL_dcov3D, float *dL_dsh, float *dL_dscales, float *dL_drotations,
+                         d3ga_stream_t stream);
+
+/* Byte offsets of the sections inside the three workspaces, for parity tests that compare key lists, sorted
+ * indices and ranges with the oracle.  out[] receives D3GA_LAYOUT_COUNT values, indexed by the enum. */
+enum {
+    D3GA_L_GEOM_HEADER = 0, /* uint32[64]: [0] num_rendered, [1] overflow, [3] final sort buffer (0/1)      */
+    D3GA_L_GEOM_DEPTH,      /* float  [P]                                                                  */
+    D3GA_L_GEOM_XY,         /* float2 [P]                                                                  */
+    D3GA_L_GEOM_CONIC_OPACITY, /* float4 [P]                                                               */
+    D3GA_L_GEOM_RGB,        /* float  [P,3] (SH path; the colors_precomp path reads the caller's tensor)   */
+    D3GA_L_GEOM_COV3D,      /* float  [P,6] (scales/rotations path)                                        */
+    D3GA_L_GEOM_TILES,      /* uint32 [P] tiles touched                                                    */
+    D3GA_L_GEOM_OFFSETS,    /* uint32 [P] inclusive prefix sum of tiles touched                            */
+    D3GA_L_GEOM_CLAMPED,    /* uint8  [P,3]                                                                */
+    D3GA_L_BIN_KEYS0,       /* uint64 [capacity]  unsorted keys after stage 1                              */
+    D3GA_L_BIN_KEYS1,       /* uint64 [capacity]                                                           */
+    D3GA_L_BIN_VALS0,       /* uint32 [capacity]  unsorted Gaussian indices after stage 1                  */
+    D3GA_L_BIN_VALS1,       /* uint32 [capacity]                                                           */
+    D3GA_L_IMG_RANGES,      /* uint2  [tiles]                                                              */
+    D3GA_L_IMG_FINAL_T,     /* float  [H*W]                                                                */
+    D3GA_L_IMG_N_CONTRIB,   /* uint32 [H*W]                                                                */
+    D3GA_LAYOUT_COUNT
+};
+int d3ga_raster_layout(int P, int W, int H, uint64_t capacity, uint64_t *out);
+
+/* ---- cage -> Gaussian deformation -------------------------------------------
+ * Replaces the torch op chain of models/cage_net.py:218-230 (+ lib/cage.py:339-342, tetra_sampler/tetra.py:74-80,
+ * utils/general_utils.py:24-34,58-90, models/cage_net.py:161-164) by one kernel each way.
+ * tetpoints [V,3] f32; tets [T,4] int64; tetra_id [N] int64; barys [N,4] f32 (not renormalised);
+ * canonical_gradient [N,3,3] f32; scales [N,3] f32 (post-exp); rotation [N,4] f32 (r,x,y,z; normalised inside).
+ * Outputs: means3D [N,3], cov3D [N,6].  A negative tetra_id wraps to T + id like torch indexing does. */
+int d3ga_deform_forward(int N, int V, int T, const float *tetpoints, const int64_t *tets, const int64_t *tetra_id,
+                        const float *barys, const float *canonical_gradient, const float *scales,
+                        const float *rotation, float *means3D, float *cov3D, d3ga_stream_t stream);
+/* dL_dtetpoints [V,3] is ACCUMULATED into (the caller zeroes it; several garments / views may add to it);
+ * dL_dbarys [N,4], dL_dscales [N,3], dL_drotation [N,4] are written.  Any output pointer may be null. */
+int d3ga_deform_backward(int N, int V, int T, const float *tetpoints, const int64_t *tets, const int64_t *tetra_id,
+                         const float *barys, const float *canonical_gradient, const float *scales,
+                         const float *rotation, const float *dL_dmeans3D, const float *dL_dcov3D,
+                         float *dL_dtetpoints, float *dL_dbarys, float *dL_dscales, float *dL_drotation,
+                         d3ga_stream_t stream);
+
+/* ---- barycentric embedding -------------------------------------------------------
+ * Replaces tetra_sampler.compute_bary (submodules/tetra-sampler/tetra_sampler/barys.py:9-33): the nearest-face
+ * query of bvh_distance_queries.BVH (bvh_cuda_op.cu:1065-1269) followed by barycentric_kernel
+ * (src/sampler_points_kernel.cu:279-313).  points [N,3]; tetras [T,4,3]; triangles [F,3,3]; tri_to_tetra [F,2]
+ * int32 (-1 = no neighbour).  Outputs: barys [N,4] f32, tetra_id [N] int32 (-1 on miss, barys 0),
+ * active [N] int32 (1 / -1), closest_face [N] int32 (may be null). */
+int d3ga_compute_bary(int N, int T, int F, const float *points, const float *tetras, const float *triangles,
+                      const int32_t *tri_to_tetra, float *barys, int32_t *tetra_id, int32_t *active,
+                      int32_t *closest_face, d3ga_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* D3GA_B200_H */

@@ -77,13 +77,20 @@ static inline real dot3(real a0, real b0, real a1, real b1, real a2, real b2) {
 /* upstream ndc2Pix: evaluated in double, rounded to float at the end (same formula as lib/cameras.py:77-78) */
 static inline real ndc2pix(real v, int S) { return (real)((((double)v + 1.0) * (double)S - 1.0) * 0.5); }
 
+/* float -> int like the device's cvt.rzi.s32.f32: truncate toward zero, saturate, NaN -> 0 */
+static inline int f2i(real v) {
+    if (v != v) return 0;
+    if (v >= R(2147483647.0)) return 2147483647;
+    if (v <= R(-2147483648.0)) return (-2147483647 - 1);
+    return (int)v;
+}
+static inline int clampi(int a, int hi) { return a < 0 ? 0 : (a > hi ? hi : a); }
 static inline void get_rect(real px, real py, int radius, int gx, int gy, int *x0, int *y0, int *x1, int *y1) {
     real r = (real)radius;
-    int a;
-    a = (int)((px - r) / R(TILE));            *x0 = a < 0 ? 0 : (a > gx ? gx : a);
-    a = (int)((py - r) / R(TILE));            *y0 = a < 0 ? 0 : (a > gy ? gy : a);
-    a = (int)((px + r + R(TILE - 1)) / R(TILE)); *x1 = a < 0 ? 0 : (a > gx ? gx : a);
-    a = (int)((py + r + R(TILE - 1)) / R(TILE)); *y1 = a < 0 ? 0 : (a > gy ? gy : a);
+    *x0 = clampi(f2i((px - r) / R(TILE)), gx);
+    *y0 = clampi(f2i((py - r) / R(TILE)), gy);
+    *x1 = clampi(f2i((px + r + R(TILE - 1)) / R(TILE)), gx);
+    *y1 = clampi(f2i((py + r + R(TILE - 1)) / R(TILE)), gy);
 }
 
 /* Sigma = R S^2 R^T with the raw (un-normalised) quaternion (r,x,y,z), packed (xx,xy,xz,yy,yz,zz) */
@@ -199,11 +206,11 @@ void orc_preprocess(int P, int deg, int M, const real *means, const real *scales
         real rad = CEIL(R(3) * SQRT(MAXR(l1, l2)));
         real pxi = ndc2pix(px_ndc, W), pyi = ndc2pix(py_ndc, H);
         int x0, y0, x1, y1;
-        get_rect(pxi, pyi, (int)rad, gx, gy, &x0, &y0, &x1, &y1);
+        get_rect(pxi, pyi, f2i(rad), gx, gy, &x0, &y0, &x1, &y1);
         if ((x1 - x0) * (y1 - y0) == 0) continue;
         if (!colors_precomp) sh_to_rgb(deg, M, m, campos, shs + (size_t)i * M * 3, rgb + 3 * i, clamped + 3 * i);
         depths[i] = zv;
-        radii[i] = (int)rad;
+        radii[i] = f2i(rad);
         xy[2 * i] = pxi; xy[2 * i + 1] = pyi;
         conic_opacity[4 * i + 0] = cyy * det_inv;
         conic_opacity[4 * i + 1] = -cxy * det_inv;
