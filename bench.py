@@ -1,0 +1,303 @@
+#!/usr/bin/env python
+"""bench.py -- fwd+bwd views/s of the D3GA render hot path on B200 (the metric of BASELINE.json).
+
+    python bench.py --gpus N --steps K --warmup W [--workload metric|c1|c2|c3|c4] [--views V]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N --steps K --warmup W
+    python bench.py --impl reference ...          # the CPU restatement of the reference path on the host cores
+
+A "step" is one multi-view training step on the hot path: every rank runs V camera views (cage deformation ->
+rasterizer forward -> loss -> rasterizer backward -> deformation backward, gradients accumulated) on replicated
+parameters, then ONE all-reduce of the flat gradient buffer (no collective when N = 1).  Cameras are sharded over
+ranks (camera c -> rank c mod N), per-rank work is fixed => weak scaling.  value = views of all ranks / max-over-ranks
+device time.  Prints ONE JSON line on rank 0.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import math
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+
+METRIC = "fwd+bwd views/s"
+UNIT = "views/s"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="metric")
+    ap.add_argument("--views", type=int, default=20, help="camera views per rank per step (C5: 160 cameras / 8 GPUs)")
+    ap.add_argument("--cameras", type=int, default=160)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+def measured_peak():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured"
+        except Exception:
+            pass
+    return 6650.0, "fallback"
+
+
+# ---- clocks ------------------------------------------------------------------------------------------------------------
+class ClockSampler:
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.idx, self.rows, self.proc = gpu_index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.idx}", f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm = [float(r[1]) for r in self.rows if len(r) >= 9 and r[1].replace(".", "").isdigit()]
+        mx = [float(r[2]) for r in self.rows if len(r) >= 9 and r[2].replace(".", "").isdigit()]
+        reasons = set()
+        for r in self.rows:
+            if len(r) >= 9:
+                for name, v in zip(["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"], r[5:9]):
+                    if v.lower().startswith("active"):
+                        reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ---- the CPU restatement of the reference path (cpu_baseline and --impl reference) -----------------------------------------
+def cpu_view(scene, cam, weights):
+    """One view fwd+bwd on the host: torch CPU deformation (the reference's own form, models/cage_net.py:213-230)
+    + the C rasterizer oracle (OpenMP).  Test infrastructure timed as the reported CPU baseline, never shipped."""
+    import torch as th
+
+    from oracle import deform_oracle
+    from oracle.raster_oracle import RasterOracle
+
+    t = th.from_numpy
+    leaves = [t(a).clone().requires_grad_(True) for a in (scene.tetpoints, scene.barys, scene.scales, scene.rotation)]
+    means, cov6 = deform_oracle.deform_gaussians(leaves[0], t(scene.tets), t(scene.tetra_id), leaves[1],
+                                                 t(scene.canonical_gradient), leaves[2], leaves[3])
+    orc = RasterOracle(np.float32)
+    st = orc.forward(means.detach().numpy(), scene.opacity, cam.viewmatrix, cam.projmatrix, cam.campos, scene.W,
+                     scene.H, cam.tanfovx, cam.tanfovy, [1, 1, 1], colors_precomp=scene.colors,
+                     cov3D_precomp=cov6.detach().numpy())
+    g = orc.backward(st, weights)
+    th.autograd.backward([means, cov6], [t(g["means3D"]), t(g["cov3D"])])
+    return st
+
+
+def time_cpu_views(scene, cams, weights, n_views, warm=0):
+    import torch as th
+
+    th.set_num_threads(os.cpu_count() or 1)
+    for i in range(warm):
+        cpu_view(scene, cams[i % len(cams)], weights)
+    t0 = time.perf_counter()
+    for i in range(n_views):
+        cpu_view(scene, cams[i % len(cams)], weights)
+    dt = time.perf_counter() - t0
+    return n_views / dt, dt
+
+
+def run_reference(args):
+    """`--impl reference`: the reference path's CPU implementation on the host cores, rank 0 only."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from d3ga_b200 import synth
+    from oracle import raster_oracle
+
+    raster_oracle.build()
+    scene = synth.make_workload(args.workload)
+    cams = synth.camera_ring(scene.W, scene.H, min(args.cameras, 16))
+    weights = np.random.default_rng(0).uniform(-1, 1, (3, scene.H, scene.W)).astype(np.float32)
+    cores = os.cpu_count() or 1
+    for i in range(args.warmup):
+        cpu_view(scene, cams[i % len(cams)], weights)
+    t0 = time.perf_counter()
+    for i in range(args.steps):     # each step = a bounded sample of the workload: ONE camera view
+        cpu_view(scene, cams[i % len(cams)], weights)
+    dt = time.perf_counter() - t0
+    v = args.steps / dt
+    sample = "1 camera view of the same scene per step (fwd+bwd), all host threads"
+    line = {"metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": 1e3 * dt / max(1, args.steps), "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic", "impl": "reference",
+            "config": workload_config(scene, args, 1),
+            "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+            "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def workload_config(scene, args, views):
+    return {"workload": f"{scene.name}: {scene.N} Gaussians in {scene.tets.shape[0]} tets over {len(scene.meta['garments'])} "
+                        f"cage(s), {scene.W}x{scene.H}, cov3D_precomp + colors_precomp path",
+            "views_per_rank_per_step": views, "cameras": args.cameras, "parallelism": f"camera-sharded dp{args.gpus}",
+            "l2": "working set (>= 150 MB of Gaussian state + binning buffers per view) exceeds the 126 MB L2; no flush"}
+
+
+# ---- the GPU arm -------------------------------------------------------------------------------------------------------------
+def run_ours(args):
+    import torch
+
+    from d3ga_b200 import _lib, dist as ddist, synth, training
+
+    rank, local, world = ddist.init_from_env()
+    assert torch.cuda.is_available(), "bench.py (impl ours) needs a GPU; there is no CPU fallback"
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    _lib.load()
+
+    scene = synth.make_workload(args.workload)
+    cams = synth.camera_ring(scene.W, scene.H, args.cameras)
+    mine = ddist.shard_cameras(len(cams), rank, world)
+    V = args.views
+    avatar = training.Avatar(scene, dev)
+    bank = training.CameraBank(cams, dev)
+    bg = torch.ones(3, device=dev)
+    rng = np.random.default_rng(0)
+    weights_h = torch.from_numpy(rng.uniform(-1, 1, (3, scene.H, scene.W)).astype(np.float32)).pin_memory()
+    weights = weights_h.to(dev)
+    loss_h = torch.zeros((), dtype=torch.float32).pin_memory()
+
+    def cam_ids(step):
+        return [mine[(step * V + v) % len(mine)] for v in range(V)]
+
+    def region(n_steps, first_step, **kw):
+        ddist.barrier()
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for s in range(n_steps):
+            training.multi_view_step(avatar, bank, cam_ids(first_step + s), weights, bg, **kw)
+        b.record()
+        torch.cuda.synchronize()
+        ddist.barrier()
+        return ddist.max_over_ranks(a.elapsed_time(b), dev)
+
+    # warm-up (also settles the workspace capacity hints)
+    region(args.warmup, 0)
+    clocks = ClockSampler(local) if rank == 0 else None
+    if clocks:
+        clocks.start()
+    l0 = _lib.launch_count()
+    ms = region(args.steps, args.warmup)
+    launches = _lib.launch_count() - l0
+    clk = clocks.stop() if clocks else None
+    views_total = world * V * args.steps
+    value = views_total / (ms * 1e-3)
+
+    # same region again with per-kernel CUDA events (kept out of `value`): per-kernel durations for the roofline
+    _lib.profile_enable(True)
+    region(args.steps, args.warmup)
+    prof = _lib.profile_collect()
+    _lib.profile_enable(False)
+
+    # scene statistics for the algorithmic-bytes model
+    from d3ga_b200 import diff_gaussian_rasterization as dgr
+    stats = dict(dgr.last_stats)
+    stats.update(dgr.sort_plan_of_last_forward())
+    D = int(stats.get("num_rendered", 0))
+    passes = int(stats.get("passes_executed", 6))
+    N, P, Tl = scene.N, scene.W * scene.H, ((scene.W + 15) // 16) * ((scene.H + 15) // 16)
+    bytes_per_launch = {
+        "deform_forward_kernel": 120 * N, "geometry_kernel": 84 * N + 12 * D, "sort_histogram_kernel": 8 * D,
+        "sort_pass_kernel": 24 * D, "tile_ranges_kernel": 8 * D + 8 * Tl, "blend_forward_kernel": 40 * D + 20 * P,
+        "blend_backward_kernel": 80 * D + 20 * P, "preprocess_backward_kernel": 104 * N,
+        "deform_backward_kernel": 212 * N}
+    peak, peak_kind = measured_peak()
+    kern = {}
+    for name, (tms, cnt) in prof.items():
+        if cnt:
+            avg = tms / cnt
+            kern[name] = {"launches_per_view": cnt / (V * args.steps), "avg_ms": avg, "total_ms": tms,
+                          "GBps": bytes_per_launch.get(name, 0) / (avg * 1e-3) / 1e9 if avg > 0 else None}
+    dominant = max(kern, key=lambda k: kern[k]["total_ms"]) if kern else None
+    view_bytes = 540 * N + (148 + 24 * passes) * D + 40 * P + 8 * Tl
+    roof = None
+    if dominant:
+        ach = kern[dominant]["GBps"]
+        roof = {"bound": "hbm", "kernel": dominant, "achieved": ach, "peak": peak, "unit": "GB/s",
+                "frac": ach / peak if ach else None, "traffic": None, "peak_kind": peak_kind,
+                "algorithmic_bytes_per_launch": bytes_per_launch.get(dominant),
+                "avg_launch_ms": kern[dominant]["avg_ms"],
+                "whole_view": {"bytes": view_bytes, "GBps": view_bytes * (V * args.steps) / (ms * 1e-3) / 1e9,
+                               "frac": view_bytes * (V * args.steps) / (ms * 1e-3) / 1e9 / peak,
+                               "frac_of_nominal_8000": view_bytes * (V * args.steps) / (ms * 1e-3) / 1e9 / 8000.0},
+                "kernels": kern, "num_rendered": D, "sort_passes_executed": passes}
+
+    # e2e: the same steps through the public API with this step's inputs in pinned HOST memory
+    e2e = None
+    if not args.no_e2e:
+        region(1, 0, from_host=True, weights_host=weights_h, loss_host=loss_h)
+        ms_e = region(args.steps, args.warmup, from_host=True, weights_host=weights_h, loss_host=loss_h)
+        h2d = 35 * 4 + avatar.tetpoints.numel() * 4 + weights.numel() * 4
+        e2e = {"value": views_total / (ms_e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d * V,
+               "d2h_bytes_per_step": 4 * V,
+               "inputs_from_host": "per view: camera (35 floats), cage vertices tetpoints [V,3], target/weight image [3,H,W]; "
+                                   "loss scalar read back per view; Gaussian parameters stay resident like nn.Parameters"}
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        n = 2 if scene.N >= 500_000 else 4
+        v_cpu, dt = time_cpu_views(scene, cams, weights_h.numpy(), n, warm=1)
+        cpu = {"value": v_cpu, "unit": UNIT, "cores": os.cpu_count() or 1, "kind": "port",
+               "sample": f"{n} camera views of the same scene (fwd+bwd) after 1 warm-up view, {dt:.1f} s: torch CPU "
+                         f"deformation + OpenMP C rasterizer oracle"}
+
+    if rank == 0:
+        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
+                "vs_baseline": None, "dtype": "f32", "data": "synthetic", "impl": "ours",
+                "config": workload_config(scene, args, V), "clocks": clk, "e2e": e2e, "gpu_launches": int(launches),
+                "roofline": roof, "cpu_baseline": cpu,
+                "allreduce_bytes_per_step": avatar.grads.nbytes() if world > 1 else 0}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        import torch.distributed as dist
+
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -14,6 +14,7 @@ LIB_PATH = os.path.join(_HERE, "libd3ga_b200.so")
 # every symbol include/d3ga_b200.h declares (tests/test_abi.py checks the header against this list)
 EXPORTS = [
     "d3ga_version", "d3ga_error_string", "d3ga_last_cuda_error", "d3ga_launch_count",
+    "d3ga_profile_enable", "d3ga_profile_kernel_count", "d3ga_profile_kernel_name", "d3ga_profile_collect",
     "d3ga_raster_workspace_bytes", "d3ga_raster_forward_geometry", "d3ga_raster_forward_render",
     "d3ga_raster_backward_scratch_bytes", "d3ga_raster_backward", "d3ga_raster_layout",
     "d3ga_deform_forward", "d3ga_deform_backward", "d3ga_compute_bary",
@@ -49,6 +50,10 @@ def load() -> C.CDLL:
     lib.d3ga_error_string.argtypes = [C.c_int]
     lib.d3ga_last_cuda_error.restype = C.c_int
     lib.d3ga_launch_count.restype = C.c_uint64
+    lib.d3ga_profile_enable.argtypes = [C.c_int]
+    lib.d3ga_profile_kernel_name.restype = C.c_char_p
+    lib.d3ga_profile_kernel_name.argtypes = [C.c_int]
+    lib.d3ga_profile_collect.argtypes = [C.POINTER(C.c_double), C.POINTER(C.c_uint64)]
     lib.d3ga_raster_workspace_bytes.argtypes = [i32, i32, i32, u64, C.POINTER(u64), C.POINTER(u64), C.POINTER(u64)]
     lib.d3ga_raster_layout.argtypes = [i32, i32, i32, u64, C.POINTER(u64)]
     lib.d3ga_raster_forward_geometry.argtypes = (
@@ -101,3 +106,17 @@ def raster_layout(P: int, W: int, H: int, capacity: int) -> dict:
 
 def launch_count() -> int:
     return int(load().d3ga_launch_count())
+
+
+def profile_enable(on: bool) -> None:
+    load().d3ga_profile_enable(1 if on else 0)
+
+
+def profile_collect() -> dict:
+    """{kernel name: (total ms, launches)} since the last collect."""
+    lib = load()
+    n = lib.d3ga_profile_kernel_count()
+    ms = (C.c_double * n)()
+    cnt = (C.c_uint64 * n)()
+    check(lib.d3ga_profile_collect(ms, cnt), "profile_collect")
+    return {lib.d3ga_profile_kernel_name(i).decode(): (float(ms[i]), int(cnt[i])) for i in range(n)}

@@ -1,6 +1,8 @@
 // api.cu -- the extern "C" surface of libd3ga_b200.so declared in include/d3ga_b200.h (rasterizer part; the
 // deformation and embedding entry points live beside their kernels in deform.cu / bary.cu).
 #include <atomic>
+#include <mutex>
+#include <vector>
 
 #include "common.cuh"
 
@@ -14,6 +16,33 @@ int set_cuda_error(cudaError_t e) {
     g_last_cuda_error.store((int)e);
     (void)cudaGetLastError();   // clear the sticky-free error state
     return D3GA_ECUDA;
+}
+
+// ---- per-kernel event timing -------------------------------------------------------------------------------------
+static std::atomic<int> g_prof_on{0};
+static std::mutex g_prof_mu;
+struct ProfRec { int id; cudaEvent_t a, b; };
+static std::vector<ProfRec> g_prof_recs;
+static const char *const g_kernel_names[K_COUNT] = {
+    "geometry_kernel", "sort_histogram_kernel", "sort_pass_kernel", "tile_ranges_kernel", "blend_forward_kernel",
+    "blend_backward_kernel", "preprocess_backward_kernel", "deform_forward_kernel", "deform_backward_kernel",
+    "compute_bary_kernel"};
+
+ProfScope::ProfScope(int id_, cudaStream_t s) : id(id_), stream(s), slot(nullptr) {
+    if (!g_prof_on.load(std::memory_order_relaxed)) return;
+    ProfRec *r = new ProfRec;
+    r->id = id;
+    if (cudaEventCreate(&r->a) != cudaSuccess || cudaEventCreate(&r->b) != cudaSuccess) { delete r; return; }
+    cudaEventRecord(r->a, stream);
+    slot = r;
+}
+ProfScope::~ProfScope() {
+    if (!slot) return;
+    ProfRec *r = (ProfRec *)slot;
+    cudaEventRecord(r->b, stream);
+    std::lock_guard<std::mutex> lk(g_prof_mu);
+    g_prof_recs.push_back(*r);
+    delete r;
 }
 
 // upstream getHigherMsb: number of bits needed for the tile id
@@ -47,6 +76,28 @@ const char *d3ga_error_string(int code) {
 }
 
 int d3ga_last_cuda_error(void) { return g_last_cuda_error.load(); }
+
+void d3ga_profile_enable(int on) { g_prof_on.store(on ? 1 : 0); }
+int d3ga_profile_kernel_count(void) { return K_COUNT; }
+const char *d3ga_profile_kernel_name(int id) { return id >= 0 && id < K_COUNT ? g_kernel_names[id] : ""; }
+int d3ga_profile_collect(double *ms, uint64_t *launches) {
+    std::vector<ProfRec> recs;
+    {
+        std::lock_guard<std::mutex> lk(g_prof_mu);
+        recs.swap(g_prof_recs);
+    }
+    for (int k = 0; k < K_COUNT; k++) { if (ms) ms[k] = 0.0; if (launches) launches[k] = 0; }
+    for (auto &r : recs) {
+        float t = 0.f;
+        D3GA_CUDA(cudaEventSynchronize(r.b));
+        D3GA_CUDA(cudaEventElapsedTime(&t, r.a, r.b));
+        if (ms) ms[r.id] += (double)t;
+        if (launches) launches[r.id] += 1;
+        cudaEventDestroy(r.a);
+        cudaEventDestroy(r.b);
+    }
+    return D3GA_OK;
+}
 uint64_t d3ga_launch_count(void) { return g_launches.load(); }
 
 int d3ga_raster_workspace_bytes(int P, int W, int H, uint64_t capacity, uint64_t *geom_bytes, uint64_t *binning_bytes,

@@ -140,6 +140,7 @@ extern "C" int d3ga_compute_bary(int N, int T, int F, const float *points, const
     if (N < 0 || T <= 0 || F <= 0) return D3GA_EINVAL;
     if (!points || !tetras || !triangles || !tri_to_tetra || !barys || !tetra_id || !active) return D3GA_EINVAL;
     if (N == 0) return D3GA_OK;
+    ProfScope prof(K_BARY, (cudaStream_t)stream);
     compute_bary_kernel<<<(N + BARY_THREADS - 1) / BARY_THREADS, BARY_THREADS, 0, (cudaStream_t)stream>>>(
         N, F, points, tetras, triangles, reinterpret_cast<const int2 *>(tri_to_tetra),
         reinterpret_cast<float4 *>(barys), tetra_id, active, closest_face);

@@ -95,6 +95,19 @@ inline ImgLayout img_layout(int W, int H) {
 constexpr int GRAD_ACC_FLOATS = 12;
 
 // ---- host-side helpers -----------------------------------------------------------------------------------------
+enum KernelId {
+    K_GEOMETRY = 0, K_SORT_HIST, K_SORT_PASS, K_RANGES, K_BLEND_FWD, K_BLEND_BWD, K_PRE_BWD, K_DEFORM_FWD, K_DEFORM_BWD,
+    K_BARY, K_COUNT
+};
+// Optional per-kernel CUDA-event timing (d3ga_profile_* in the C-ABI; bench.py's roofline figures come from it).
+// A no-op unless profiling is enabled.
+struct ProfScope {
+    int id;
+    cudaStream_t stream;
+    void *slot;
+    ProfScope(int id, cudaStream_t stream);
+    ~ProfScope();
+};
 void count_launch(int n = 1);
 int set_cuda_error(cudaError_t e);
 #define D3GA_CUDA(expr)                                         \

@@ -205,9 +205,10 @@ extern "C" int d3ga_deform_forward(int N, int V, int T, const float *tetpoints, 
                                    const float *scales, const float *rotation, float *means3D, float *cov3D,
                                    d3ga_stream_t stream) {
     if (N < 0 || V <= 0 || T <= 0) return D3GA_EINVAL;
+    if (N == 0) return D3GA_OK;
     if (!tetpoints || !tets || !tetra_id || !barys || !canonical_gradient || !scales || !rotation || !means3D || !cov3D)
         return D3GA_EINVAL;
-    if (N == 0) return D3GA_OK;
+    ProfScope prof(K_DEFORM_FWD, (cudaStream_t)stream);
     deform_forward_kernel<<<(N + GEO_THREADS - 1) / GEO_THREADS, GEO_THREADS, 0, (cudaStream_t)stream>>>(
         N, T, tetpoints, tets, tetra_id, barys, canonical_gradient, scales, rotation, means3D, cov3D);
     D3GA_LAUNCH_CHECK();
@@ -220,10 +221,11 @@ extern "C" int d3ga_deform_backward(int N, int V, int T, const float *tetpoints,
                                     const float *dL_dcov3D, float *dL_dtetpoints, float *dL_dbarys, float *dL_dscales,
                                     float *dL_drotation, d3ga_stream_t stream) {
     if (N < 0 || V <= 0 || T <= 0) return D3GA_EINVAL;
+    if (N == 0) return D3GA_OK;
     if (!tetpoints || !tets || !tetra_id || !barys || !canonical_gradient || !scales || !rotation || !dL_dmeans3D ||
         !dL_dcov3D)
         return D3GA_EINVAL;
-    if (N == 0) return D3GA_OK;
+    ProfScope prof(K_DEFORM_BWD, (cudaStream_t)stream);
     deform_backward_kernel<<<(N + GEO_THREADS - 1) / GEO_THREADS, GEO_THREADS, 0, (cudaStream_t)stream>>>(
         N, T, tetpoints, tets, tetra_id, barys, canonical_gradient, scales, rotation, dL_dmeans3D, dL_dcov3D,
         dL_dtetpoints, dL_dbarys, dL_dscales, dL_drotation);

@@ -281,6 +281,7 @@ int launch_preprocess_backward(int P, int sh_degree, int sh_coeffs, int W, int H
     p.clamped = geom + GL.clamped;
     p.dL_dmeans2D = dL_dmeans2D; p.dL_dopacity = dL_dopacity; p.dL_dcolors = dL_dcolors; p.dL_dmeans3D = dL_dmeans3D;
     p.dL_dcov3D = dL_dcov3D; p.dL_dsh = dL_dsh; p.dL_dscales = dL_dscales; p.dL_drotations = dL_drotations;
+    ProfScope prof(K_PRE_BWD, stream);
     preprocess_backward_kernel<<<(P + GEO_THREADS - 1) / GEO_THREADS, GEO_THREADS, 0, stream>>>(p);
     D3GA_LAUNCH_CHECK();
     return D3GA_OK;

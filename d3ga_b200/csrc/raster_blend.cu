@@ -274,6 +274,7 @@ int launch_blend_forward(int W, int H, const float *background, const float *col
     const float *depth = reinterpret_cast<const float *>(geom + GL.depth);
     float *final_T = reinterpret_cast<float *>(image + IL.final_T);
     uint32_t *n_contrib = reinterpret_cast<uint32_t *>(image + IL.n_contrib);
+    ProfScope prof(K_BLEND_FWD, stream);
     if (out_invdepth)
         blend_forward_kernel<true><<<grid, block, 0, stream>>>(hdr, ranges, v0, v1, W, H, xy, co, colors, depth,
                                                                background, final_T, n_contrib, out_color, out_invdepth);
@@ -298,6 +299,7 @@ int launch_blend_backward(int W, int H, const float *background, const float *co
     const float *depth = reinterpret_cast<const float *>(geom + GL.depth);
     const float *final_T = reinterpret_cast<const float *>(image + IL.final_T);
     const uint32_t *n_contrib = reinterpret_cast<const uint32_t *>(image + IL.n_contrib);
+    ProfScope prof(K_BLEND_BWD, stream);
     if (dL_dinvdepth_pix)
         blend_backward_kernel<true><<<grid, block, 0, stream>>>(hdr, ranges, v0, v1, W, H, background, xy, co, colors,
                                                                 depth, final_T, n_contrib, dL_dpix, dL_dinvdepth_pix,

@@ -353,6 +353,7 @@ int launch_geometry(int P, int sh_degree, int sh_coeffs, const float *means3D, c
     D3GA_CUDA(cudaMemsetAsync(geom + GL.header, 0, sizeof(RasterHeader), stream));
     D3GA_CUDA(cudaMemsetAsync(geom + GL.scan_state, 0, 8ull * (p.num_ctas + 1), stream));
     if (p.num_ctas > 0) {
+        ProfScope prof(K_GEOMETRY, stream);
         geometry_kernel<<<p.num_ctas, GEO_THREADS, 0, stream>>>(p);
         D3GA_LAUNCH_CHECK();
     }

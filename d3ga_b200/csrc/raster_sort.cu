@@ -288,19 +288,28 @@ int launch_sort_and_ranges(uint8_t *geom, uint8_t *binning, const BinLayout &BL,
     int hist_grid = (int)((capacity + per_cta - 1) / per_cta);
     if (hist_grid > 148 * 8) hist_grid = 148 * 8;
     if (hist_grid < 1) hist_grid = 1;
-    sort_histogram_kernel<<<hist_grid, HIST_THREADS, 0, stream>>>(hdr, keys0, ghist, bins, sort_bits, num_passes);
+    {
+        ProfScope prof(K_SORT_HIST, stream);
+        sort_histogram_kernel<<<hist_grid, HIST_THREADS, 0, stream>>>(hdr, keys0, ghist, bins, sort_bits, num_passes);
+    }
     D3GA_LAUNCH_CHECK();
     for (int p = 0; p < num_passes; p++) {
         const int shift = 8 * p;
         const int nb = sort_bits - shift < 8 ? sort_bits - shift : 8;
-        sort_pass_kernel<<<tiles_cap, SORT_THREADS, SORT_SMEM_BYTES, stream>>>(
-            hdr, keys0, keys1, vals0, vals1, bins, tile_state, tiles_cap, p, shift, (1u << nb) - 1u);
+        {
+            ProfScope prof(K_SORT_PASS, stream);
+            sort_pass_kernel<<<tiles_cap, SORT_THREADS, SORT_SMEM_BYTES, stream>>>(
+                hdr, keys0, keys1, vals0, vals1, bins, tile_state, tiles_cap, p, shift, (1u << nb) - 1u);
+        }
         D3GA_LAUNCH_CHECK();
     }
     int rg = (int)((capacity + 255) / 256);
     if (rg > 148 * 16) rg = 148 * 16;
     if (rg < 1) rg = 1;
-    tile_ranges_kernel<<<rg, 256, 0, stream>>>(hdr, keys0, keys1, ranges);
+    {
+        ProfScope prof(K_RANGES, stream);
+        tile_ranges_kernel<<<rg, 256, 0, stream>>>(hdr, keys0, keys1, ranges);
+    }
     D3GA_LAUNCH_CHECK();
     return D3GA_OK;
 }

@@ -47,6 +47,20 @@ class GaussianRasterizationSettings(NamedTuple):
 _capacity_hint: dict = {}
 _pinned_slots: dict = {}
 CAPACITY_SLACK = 1.25
+last_stats: dict = {}      # filled by every forward: {"num_rendered": D, "capacity": cap, "retries": n}
+_last_state = None
+
+
+def sort_plan_of_last_forward() -> dict:
+    """Reads the radix-sort plan of the most recent forward back from the device (synchronises; measurement only)."""
+    st = _last_state
+    if st is None:
+        return {}
+    hdr = st.geom[:256].cpu().numpy().view("uint32")
+    n = int(hdr[6])
+    skip = [int(x) for x in hdr[8:8 + n]]
+    return {"sort_bits": int(hdr[5]), "passes": n, "passes_executed": n - sum(skip), "skipped": skip,
+            "num_rendered": int(hdr[0])}
 
 
 def _pinned_counter(device):
@@ -125,6 +139,9 @@ def rasterize_forward(means3D, sh, colors_precomp, opacities, scales, rotations,
                 raise _lib.D3GAError(f"{D} (tile, Gaussian) duplicates exceed the 2^30-1 limit")
             cap = min((1 << 30) - 1, int(D * CAPACITY_SLACK) + 4096)
         _capacity_hint[key] = min((1 << 30) - 1, int(D * CAPACITY_SLACK) + 4096)
+    global _last_state
+    _last_state = st
+    last_stats.update(num_rendered=D, capacity=st.capacity)
     return color, radii, invdepth, st
 
 

@@ -1,0 +1,93 @@
+"""Host-side mirror of one D3GA optimisation step restricted to the hot path (models/trainer.py:91-140,186-192):
+cage deformation -> render -> loss -> backward, per camera, gradients accumulated; at the end of a multi-view step
+one all-reduce of the flat gradient buffer (d3ga_b200.dist).  Uses only the public drop-in API."""
+from __future__ import annotations
+
+import numpy as np
+import torch
+
+from d3ga_b200 import dist as ddist
+from d3ga_b200.diff_gaussian_rasterization import GaussianRasterizationSettings, GaussianRasterizer
+from d3ga_b200.tetra_sampler import deform_gaussians
+
+
+class CameraBank:
+    """Cameras as one packed pinned host array [n, 35] (view 16 | proj 16 | campos 3) and its device copy."""
+
+    def __init__(self, cams, device):
+        self.cams = cams
+        packed = np.stack([np.concatenate([c.viewmatrix.ravel(), c.projmatrix.ravel(), c.campos.ravel()]) for c in cams])
+        self.host = torch.from_numpy(packed.astype(np.float32))
+        if device.type == "cuda":
+            self.host = self.host.pin_memory()
+        self.dev = self.host.to(device)
+        self.slot = torch.empty(35, dtype=torch.float32, device=device)   # e2e: per-view upload target
+
+    def settings(self, i, W, H, bg, from_host=False):
+        c = self.cams[i]
+        if from_host:
+            self.slot.copy_(self.host[i], non_blocking=True)
+            row = self.slot
+        else:
+            row = self.dev[i]
+        return GaussianRasterizationSettings(
+            image_height=H, image_width=W, tanfovx=c.tanfovx, tanfovy=c.tanfovy, bg=bg, scale_modifier=1.0,
+            viewmatrix=row[0:16].view(4, 4), projmatrix=row[16:32].view(4, 4), sh_degree=0, campos=row[32:35],
+            prefiltered=False, debug=False, antialiasing=False)
+
+
+class Avatar:
+    """Resident parameters of the hot path (what nn.Parameters / buffers hold in models/cage_net.py)."""
+
+    def __init__(self, scene, device):
+        t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(device)  # noqa: E731
+        self.device = device
+        self.W, self.H, self.N = scene.W, scene.H, scene.N
+        self.tets, self.tetra_id, self.cg = t(scene.tets), t(scene.tetra_id), t(scene.canonical_gradient)
+        self.tetpoints = t(scene.tetpoints).requires_grad_(True)
+        self.barys = t(scene.barys).requires_grad_(True)
+        self.scales = t(scene.scales).requires_grad_(True)
+        self.rotation = t(scene.rotation).requires_grad_(True)
+        self.opacity = t(scene.opacity).requires_grad_(True)
+        self.colors = t(scene.colors).requires_grad_(True)
+        self.params = [self.tetpoints, self.barys, self.scales, self.rotation, self.opacity, self.colors]
+        self.grads = ddist.FlatGrads(self.params)
+        self.tetpoints_host = torch.from_numpy(scene.tetpoints.copy())
+        if device.type == "cuda":
+            self.tetpoints_host = self.tetpoints_host.pin_memory()
+
+    def render(self, rs):
+        """What GarmentNet.forward + render() do on the hot path (cage_net.py:218-230, renderer.py:122-141)."""
+        means3D, cov6 = deform_gaussians(self.tetpoints, self.tets, self.tetra_id, self.barys, self.cg, self.scales,
+                                         self.rotation)
+        means2D = torch.zeros_like(means3D, requires_grad=True) + 0
+        return GaussianRasterizer(raster_settings=rs)(
+            means3D=means3D, means2D=means2D, shs=None, colors_precomp=self.colors, opacities=self.opacity,
+            scales=None, rotations=None, cov3D_precomp=cov6)[0]
+
+
+def view_step(avatar, rs, weights):
+    """One view forward + backward; loss = sum(image * weights)."""
+    img = avatar.render(rs)
+    loss = (img * weights).sum()
+    loss.backward()
+    return loss
+
+
+def multi_view_step(avatar, bank, cam_ids, weights, bg, from_host=False, weights_host=None, loss_host=None):
+    """`cam_ids` views on this rank, then one all-reduce of the accumulated gradients."""
+    avatar.grads.zero_()
+    total = None
+    for i in cam_ids:
+        if from_host:   # e2e: this view's inputs arrive from pinned host memory, the loss goes back
+            with torch.no_grad():
+                avatar.tetpoints.copy_(avatar.tetpoints_host, non_blocking=True)
+                weights.copy_(weights_host, non_blocking=True)
+        rs = bank.settings(i, avatar.W, avatar.H, bg, from_host=from_host)
+        loss = view_step(avatar, rs, weights)
+        if from_host:
+            loss_host.copy_(loss.detach(), non_blocking=True)
+            torch.cuda.current_stream().synchronize()
+        total = loss.detach() if total is None else total + loss.detach()
+    avatar.grads.all_reduce()
+    return total

@@ -38,6 +38,14 @@ int d3ga_last_cuda_error(void);
 /* Number of kernels this library has launched in this process (the `gpu_launches` figure of bench.py). */
 uint64_t d3ga_launch_count(void);
 
+/* Measurement only (no counterpart in the reference; used by bench.py): when enabled, every kernel launch is
+ * bracketed by a pair of CUDA events on its stream.  d3ga_profile_collect() waits for the recorded events, adds up
+ * milliseconds and launches per kernel id (arrays of d3ga_profile_kernel_count() entries) and clears the record. */
+void d3ga_profile_enable(int on);
+int d3ga_profile_kernel_count(void);
+const char *d3ga_profile_kernel_name(int id);
+int d3ga_profile_collect(double *ms, uint64_t *launches);
+
 /* ---- rasterizer -------------------------------------------------------------
  * Replaces: diff_gaussian_rasterization._C.rasterize_gaussians / rasterize_gaussians_backward as reached from
  * renderer.py:130-141 (GaussianRasterizer.__call__) with the settings of renderer.py:79-93.

@@ -1,0 +1,85 @@
+"""-m gpu parity tests of rows A0/A1/A2: the fused deformation and the barycentric embedding, through the C-ABI."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import parity_util as util
+from d3ga_b200 import synth
+from d3ga_b200.tetra_sampler import Tetra, compute_bary, deform_gaussians
+from oracle import deform_oracle as do
+from oracle import tet_oracle
+from test_oracle_tet import lattice_case
+
+pytestmark = pytest.mark.gpu
+t = torch.from_numpy
+
+
+def test_deform_matches_reference_golden(cuda_lib):
+    G = np.load(os.path.join(util.GOLDEN, "deform_golden.npz"))
+    c = lambda k: t(G[k]).cuda()  # noqa: E731
+    means, cov6 = deform_gaussians(c("tetpoints"), c("tets"), c("tetra_id"), c("barys"), c("canonical_gradient"),
+                                   c("scales"), c("rotation"))
+    assert np.allclose(means.cpu().numpy(), G["means3D"], atol=1e-6)
+    assert util.rel_l2(cov6.cpu().numpy(), G["cov6"]) < 1e-5
+
+
+@pytest.mark.parametrize("workload", ["tiny", "c1"])
+def test_deform_forward_backward_vs_oracle(cuda_lib, workload):
+    sc = synth.make_workload(workload)
+    names = ["tetpoints", "barys", "scales", "rotation"]
+    cpu = {k: t(getattr(sc, k)).clone().requires_grad_(True) for k in names}
+    cpu["rotation"] = (t(sc.rotation) * 1.3).clone().requires_grad_(True)
+    gpu = {k: v.detach().cuda().requires_grad_(True) for k, v in cpu.items()}
+    fixed = dict(tets=t(sc.tets), tetra_id=t(sc.tetra_id), cg=t(sc.canonical_gradient))
+    m_ref, c_ref = do.deform_gaussians(cpu["tetpoints"], fixed["tets"], fixed["tetra_id"], cpu["barys"], fixed["cg"],
+                                       cpu["scales"], cpu["rotation"])
+    m, c = deform_gaussians(gpu["tetpoints"], fixed["tets"].cuda(), fixed["tetra_id"].cuda(), gpu["barys"],
+                            fixed["cg"].cuda(), gpu["scales"], gpu["rotation"])
+    assert np.allclose(m.detach().cpu().numpy(), m_ref.detach().numpy(), atol=2e-6)
+    assert util.rel_l2(c.detach().cpu().numpy(), c_ref.detach().numpy()) < 1e-5
+    rng = np.random.default_rng(0)
+    wm = t(rng.normal(size=m_ref.shape).astype(np.float32))
+    wc = t((rng.normal(size=c_ref.shape) * 1e3).astype(np.float32))
+    ((m_ref * wm).sum() + (c_ref * wc).sum()).backward()
+    ((m * wm.cuda()).sum() + (c * wc.cuda()).sum()).backward()
+    for k in names:
+        assert util.rel_l2(gpu[k].grad.cpu().numpy(), cpu[k].grad.numpy()) < 1e-3, k
+
+
+def test_deform_negative_tetra_id_wraps(cuda_lib):
+    sc = synth.make_workload("tiny")
+    tid = t(sc.tetra_id).clone()
+    tid[::10] = -1     # compute_bary's miss value; torch indexing wraps it to the last tet
+    args = [t(sc.tetpoints), t(sc.tets), tid, t(sc.barys), t(sc.canonical_gradient), t(sc.scales), t(sc.rotation)]
+    m_ref, c_ref = do.deform_gaussians(*args)
+    m, c = deform_gaussians(*[a.cuda() for a in args])
+    assert np.allclose(m.cpu().numpy(), m_ref.numpy(), atol=2e-6)
+    assert util.rel_l2(c.cpu().numpy(), c_ref.numpy()) < 1e-5
+
+
+def test_compute_bary_lattice(cuda_lib, oracle_libs):
+    pts, tets, faces, topo, tid, b, p = lattice_case(2000, seed=2)
+    cage = Tetra.from_tensors(t(pts), t(tets), device="cuda")
+    assert np.array_equal(cage.tetra_faces.cpu().numpy(), faces)
+    assert np.array_equal(cage.triangle_to_tetra.cpu().numpy(), topo)
+    barys, tetra_id, active = compute_bary(t(p).cuda(), cage.get_positions(), cage.get_triangles(),
+                                           cage.triangle_to_tetra, cage)
+    assert tetra_id.dtype == torch.int64 and active.dtype == torch.int32 and barys.shape == (len(p), 4)
+    ob, otid, oact, _ = tet_oracle.compute_bary(p, pts[tets], pts[faces], topo)
+    assert np.array_equal(tetra_id.cpu().numpy(), otid)
+    assert np.array_equal(active.cpu().numpy(), oact)
+    assert np.allclose(barys.cpu().numpy(), ob, atol=1e-5)
+    outside = np.zeros(len(p), bool)
+    outside[::50] = True
+    assert np.array_equal(otid[~outside], tid[~outside]) and np.all(otid[outside] == -1)
+
+
+def test_compute_bary_backward_raises(cuda_lib):
+    pts, tets, faces, topo, tid, b, p = lattice_case(16)
+    cage = Tetra.from_tensors(t(pts), t(tets), device="cuda")
+    x = t(p).cuda().requires_grad_(True)
+    barys, _, _ = compute_bary(x, cage.get_positions(), cage.get_triangles(), cage.triangle_to_tetra, cage)
+    with pytest.raises(NotImplementedError):
+        barys.sum().backward()
