@@ -23,6 +23,7 @@ SOURCES = [
     ("raster_sort.cu", []),
     ("raster_blend.cu", []),
     ("raster_backward.cu", []),
+    ("raster_backward_noalloc.cu", []),
     ("deform.cu", []),
     ("bary.cu", []),
 ]

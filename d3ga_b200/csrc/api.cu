@@ -28,6 +28,8 @@ static const char *const g_kernel_names[K_COUNT] = {
     "blend_backward_kernel", "preprocess_backward_kernel", "deform_forward_kernel", "deform_backward_kernel",
     "compute_bary_kernel"};
 
+bool profiling_enabled() { return g_prof_on.load(std::memory_order_relaxed) != 0; }
+
 ProfScope::ProfScope(int id_, cudaStream_t s) : id(id_), stream(s), slot(nullptr) {
     if (!g_prof_on.load(std::memory_order_relaxed)) return;
     ProfRec *r = new ProfRec;
@@ -70,7 +72,8 @@ const char *d3ga_error_string(int code) {
         case D3GA_EINVAL: return "invalid argument";
         case D3GA_ECUDA: return "CUDA runtime error (see d3ga_last_cuda_error)";
         case D3GA_ETOOBIG: return "size exceeds the 2^30-1 duplicate limit";
-        case D3GA_ENOTREADY: return "staged call out of order";
+        case D3GA_ENOTREADY: return "call not possible in the current state (staged call out of order, or profiling on)";
+        case D3GA_ELIMIT: return "more Gaussians than the fixed scratch of the allocation-free entry point holds";
         default: return "unknown error";
     }
 }

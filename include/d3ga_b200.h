@@ -27,7 +27,8 @@ extern "C" {
 #define D3GA_EINVAL (-1)    /* bad argument (null pointer, negative size, inconsistent option set) */
 #define D3GA_ECUDA (-2)     /* a CUDA runtime call failed; d3ga_last_cuda_error() has the cudaError_t */
 #define D3GA_ETOOBIG (-3)   /* size beyond what the 32-bit duplicate indices / look-back words can hold */
-#define D3GA_ENOTREADY (-4) /* staged call made out of order */
+#define D3GA_ENOTREADY (-4) /* call not possible in the current state */
+#define D3GA_ELIMIT (-5)    /* size beyond the fixed capacity of d3ga_raster_backward_noalloc */
 
 typedef void *d3ga_stream_t; /* cudaStream_t */
 
@@ -106,6 +107,32 @@ int d3ga_raster_backward(int P, int sh_degree, int sh_coeffs, int W, int H, cons
                          float *dL_dmeans2D, float *dL_dopacity, float *dL_dcolors, float *dL_dmeans3D,
                          float *dL_dcov3D, float *dL_dsh, float *dL_dscales, float *dL_drotations,
                          d3ga_stream_t stream);
+
+/* The same backward for hosts that cannot allocate device memory (no counterpart in the reference, whose Python
+ * glue always has torch's allocator): a C/C++ playback or fitting loop without a caching allocator, where
+ * cudaMalloc/cudaFree would stall the whole device and may fail once memory is committed, or a deployment that hands
+ * out all device memory at start-up.  Identical to d3ga_raster_backward() except that there is no grad_scratch
+ * argument: the 48-byte-per-Gaussian accumulator lives in a static __device__ array inside the library, which every
+ * GPU that loads the library holds (D3GA_NOALLOC_MAX_GAUSSIANS * 48 B = 12 MiB) until the process exits.
+ *   - P > D3GA_NOALLOC_MAX_GAUSSIANS returns D3GA_ELIMIT; nothing is launched.
+ *   - It calls no allocating routine; while d3ga_profile_enable(1) is in effect it returns D3GA_ENOTREADY, because
+ *     the timing hooks create CUDA events.
+ *   - The first call on a device looks the array's device address up (with that device current) and caches it; make
+ *     that call before any stream capture begins.
+ *   - Every call uses the same array and clears the part it needs first.  Two calls whose GPU work can overlap
+ *     (different streams, or different threads on one device) race on it: keep them on one stream, or serialise. */
+#define D3GA_NOALLOC_MAX_GAUSSIANS 262144
+int d3ga_raster_backward_noalloc(int P, int sh_degree, int sh_coeffs, int W, int H, const float *background,
+                                 const float *means3D, const float *colors_precomp, const float *opacities,
+                                 const float *scales, float scale_modifier, const float *rotations,
+                                 const float *cov3D_precomp, const float *shs,
+                                 const float *viewmatrix, const float *projmatrix, const float *campos,
+                                 float tanfovx, float tanfovy, int antialiasing, const int32_t *radii,
+                                 const void *geom, const void *binning, uint64_t capacity, const void *image,
+                                 const float *dL_dout_color, const float *dL_dout_invdepth,
+                                 float *dL_dmeans2D, float *dL_dopacity, float *dL_dcolors, float *dL_dmeans3D,
+                                 float *dL_dcov3D, float *dL_dsh, float *dL_dscales, float *dL_drotations,
+                                 d3ga_stream_t stream);
 
 /* Byte offsets of the sections inside the three workspaces, for parity tests that compare key lists, sorted
  * indices and ranges with the oracle.  out[] receives D3GA_LAYOUT_COUNT values, indexed by the enum. */
