@@ -25,6 +25,35 @@ namespace {
 
 constexpr int BATCH = TILE_PIX;   // Gaussians staged per round
 
+// Pixel footprint of one staged Gaussian: the axis-aligned box outside of which alpha = o * exp(power) is certainly
+// below the 1/255 cut (so the exact per-pixel test would skip it anyway).  power >= -tau with tau = ln(255 o) bounds
+// d^T C d <= 2 tau; the extents of that ellipse are sqrt(2 tau C^-1_xx), sqrt(2 tau C^-1_yy).  A relative and an
+// absolute margin keep the test conservative against rounding; degenerate conics are never culled.
+__device__ __forceinline__ float4 footprint_box(float2 c, float4 co) {
+    if (co.w < 1.f / 255.f) return make_float4(INFINITY, -INFINITY, INFINITY, -INFINITY);   // can never pass the cut
+    const float det = co.x * co.z - co.y * co.y;
+    const float tau = __logf(255.f * co.w);
+    if (!(det > 0.f) || !(tau >= 0.f)) return make_float4(-INFINITY, INFINITY, -INFINITY, INFINITY);
+    const float k = 2.f * tau / det;
+    const float hx = sqrtf(k * co.z) * 1.001f + 0.5f, hy = sqrtf(k * co.x) * 1.001f + 0.5f;
+    return make_float4(c.x - hx, c.x + hx, c.y - hy, c.y + hy);
+}
+
+// Each warp owns an 8x4 pixel block of the 16x16 tile (compact blocks cull better than 16x2 strips).
+struct WarpBlock {
+    int px, py;
+    float x0, x1, y0, y1;
+};
+__device__ __forceinline__ WarpBlock warp_block(int tid) {
+    const int warp = tid >> 5, lane = tid & 31;
+    const int bx = blockIdx.x * TILE + (warp & 1) * 8, by = blockIdx.y * TILE + (warp >> 1) * 4;
+    WarpBlock w;
+    w.px = bx + (lane & 7);
+    w.py = by + (lane >> 3);
+    w.x0 = (float)bx; w.x1 = (float)(bx + 7); w.y0 = (float)by; w.y1 = (float)(by + 3);
+    return w;
+}
+
 template <bool INVDEPTH>
 __global__ void __launch_bounds__(TILE_PIX) blend_forward_kernel(
     const RasterHeader *__restrict__ hdr, const uint2 *__restrict__ ranges, const uint32_t *__restrict__ vals0,
@@ -35,10 +64,14 @@ __global__ void __launch_bounds__(TILE_PIX) blend_forward_kernel(
     __shared__ float2 s_xy[BATCH];
     __shared__ float4 s_co[BATCH];
     __shared__ float4 s_feat[BATCH];   // r, g, b, 1/depth
+    __shared__ float4 s_box[BATCH];
+    __shared__ uint8_t s_list[TILE_PIX / 32][BATCH];
 
     const uint32_t tile = blockIdx.y * gridDim.x + blockIdx.x;
-    const int tid = threadIdx.y * TILE + threadIdx.x;
-    const int px = blockIdx.x * TILE + threadIdx.x, py = blockIdx.y * TILE + threadIdx.y;
+    const int tid = threadIdx.x;
+    const uint32_t lane = tid & 31, warp = tid >> 5;
+    const WarpBlock wb = warp_block(tid);
+    const int px = wb.px, py = wb.py;
     const bool inside = px < W && py < H;
     const float pxf = (float)px, pyf = (float)py;
     uint2 range = make_uint2(0, 0);
@@ -49,21 +82,40 @@ __global__ void __launch_bounds__(TILE_PIX) blend_forward_kernel(
 
     bool done = !inside;
     float T = 1.f, C0 = 0.f, C1 = 0.f, C2 = 0.f, invd = 0.f;
-    uint32_t contributor = 0, last = 0;
+    uint32_t last = 0;
     for (int i = 0; i < rounds; i++, todo -= BATCH) {
         if (__syncthreads_count(done) == TILE_PIX) break;
         const uint32_t progress = (uint32_t)i * BATCH + tid;
         if (range.x + progress < range.y) {
             const uint32_t id = point_list[range.x + progress];
-            s_xy[tid] = xy[id];
-            s_co[tid] = conic_opacity[id];
+            const float2 c = xy[id];
+            const float4 co = conic_opacity[id];
+            s_xy[tid] = c;
+            s_co[tid] = co;
+            s_box[tid] = footprint_box(c, co);
             s_feat[tid] = make_float4(colors[3 * (size_t)id], colors[3 * (size_t)id + 1], colors[3 * (size_t)id + 2],
                                       INVDEPTH ? __fdividef(1.f, depths[id]) : 0.f);
         }
         __syncthreads();
+        if (__all_sync(0xffffffffu, done)) continue;
         const int n = min(BATCH, todo);
-        for (int j = 0; !done && j < n; j++) {
-            contributor++;
+        // this warp's depth-ordered list of the staged Gaussians whose footprint reaches its pixel block
+        int cnt = 0;
+#pragma unroll
+        for (int r = 0; r < BATCH / 32; r++) {
+            const int g = r * 32 + (int)lane;
+            const float4 b = s_box[g];
+            const bool hit = g < n && b.y >= wb.x0 && b.x <= wb.x1 && b.w >= wb.y0 && b.z <= wb.y1;
+            const uint32_t m = __ballot_sync(0xffffffffu, hit);
+            if (hit) s_list[warp][cnt + __popc(m & lanemask_lt())] = (uint8_t)g;
+            cnt += __popc(m);
+        }
+        __syncwarp();
+        const uint32_t base = (uint32_t)i * BATCH;
+        for (int k = 0; k < cnt; k++) {
+            if (__all_sync(0xffffffffu, done)) break;
+            if (done) continue;
+            const int j = s_list[warp][k];
             const float2 c = s_xy[j];
             const float dx = c.x - pxf, dy = c.y - pyf;
             const float4 co = s_co[j];
@@ -78,7 +130,7 @@ __global__ void __launch_bounds__(TILE_PIX) blend_forward_kernel(
             C0 += f.x * w; C1 += f.y * w; C2 += f.z * w;
             if (INVDEPTH) invd += f.w * w;
             T = test_T;
-            last = contributor;
+            last = base + (uint32_t)j + 1u;
         }
     }
     if (inside) {
@@ -142,27 +194,40 @@ __global__ void __launch_bounds__(TILE_PIX) blend_backward_kernel(
     __shared__ float2 s_xy[BATCH];
     __shared__ float4 s_co[BATCH];
     __shared__ float4 s_feat[BATCH];
+    __shared__ float4 s_box[BATCH];
     __shared__ uint32_t s_id[BATCH];
+    __shared__ uint8_t s_list[TILE_PIX / 32][BATCH];
     __shared__ __align__(16) float s_acc[BATCH * GRAD_ACC_FLOATS];
+    __shared__ uint32_t s_max[TILE_PIX / 32];
 
     const uint32_t tile = blockIdx.y * gridDim.x + blockIdx.x;
-    const int tid = threadIdx.y * TILE + threadIdx.x;
-    const uint32_t lane = tid & 31;
-    const int px = blockIdx.x * TILE + threadIdx.x, py = blockIdx.y * TILE + threadIdx.y;
+    const int tid = threadIdx.x;
+    const uint32_t lane = tid & 31, warp = tid >> 5;
+    const WarpBlock wb = warp_block(tid);
+    const int px = wb.px, py = wb.py;
     const bool inside = px < W && py < H;
     const float pxf = (float)px, pyf = (float)py;
     uint2 range = make_uint2(0, 0);
     if (!hdr->overflow) range = ranges[tile];
     if (range.y <= range.x) return;
     const uint32_t *point_list = hdr->final_sel ? vals1 : vals0;
-    const int rounds = (int)((range.y - range.x + BATCH - 1) / BATCH);
-    int todo = (int)(range.y - range.x);
     const size_t pid = (size_t)py * W + px, plane = (size_t)H * W;
 
     const float T_final = inside ? final_T[pid] : 0.f;
     float T = T_final;
-    uint32_t contributor = (uint32_t)todo;
     const uint32_t last_contributor = inside ? n_contrib[pid] : 0u;
+    // Only the first n_proc Gaussians of the tile's list reached any pixel in the forward: nothing behind them is
+    // staged at all (the forward stops a pixel at T < 1e-4, typically after a small fraction of a deep list).
+    const uint32_t warp_last = __reduce_max_sync(0xffffffffu, last_contributor);
+    if (lane == 0) s_max[warp] = warp_last;
+    for (int k = tid; k < BATCH * GRAD_ACC_FLOATS; k += TILE_PIX) s_acc[k] = 0.f;
+    __syncthreads();
+    uint32_t n_proc = 0;
+#pragma unroll
+    for (int w = 0; w < TILE_PIX / 32; w++) n_proc = max(n_proc, s_max[w]);
+    if (n_proc == 0) return;
+    const int rounds = (int)((n_proc + BATCH - 1) / BATCH);
+
     float acc0 = 0.f, acc1 = 0.f, acc2 = 0.f, acci = 0.f;
     float lc0 = 0.f, lc1 = 0.f, lc2 = 0.f, lci = 0.f, last_alpha = 0.f;
     float g0 = 0.f, g1 = 0.f, g2 = 0.f, gi = 0.f;
@@ -173,33 +238,45 @@ __global__ void __launch_bounds__(TILE_PIX) blend_backward_kernel(
     const float bg_dot = bg[0] * g0 + bg[1] * g1 + bg[2] * g2;
     const float ddelx_dx = 0.5f * (float)W, ddely_dy = 0.5f * (float)H;
     const int slot = slot_of_lane(lane);
-    // the tile's deepest contributor bounds how far back any pixel has to look
-    const uint32_t cta_last = (uint32_t)__reduce_max_sync(0xffffffffu, last_contributor);
 
-    for (int k = tid; k < BATCH * GRAD_ACC_FLOATS; k += TILE_PIX) s_acc[k] = 0.f;
-
-    for (int i = 0; i < rounds; i++, todo -= BATCH) {
+    for (int i = 0; i < rounds; i++) {
         __syncthreads();
+        // staged slot t holds the Gaussian at forward position q = n_proc - 1 - (i * BATCH + t): back to front
         const uint32_t progress = (uint32_t)i * BATCH + tid;
-        if (range.x + progress < range.y) {
-            const uint32_t id = point_list[range.y - progress - 1];
+        if (progress < n_proc) {
+            const uint32_t id = point_list[range.x + (n_proc - 1u - progress)];
+            const float2 c = xy[id];
+            const float4 co = conic_opacity[id];
             s_id[tid] = id;
-            s_xy[tid] = xy[id];
-            s_co[tid] = conic_opacity[id];
+            s_xy[tid] = c;
+            s_co[tid] = co;
+            s_box[tid] = footprint_box(c, co);
             s_feat[tid] = make_float4(colors[3 * (size_t)id], colors[3 * (size_t)id + 1], colors[3 * (size_t)id + 2],
                                       INVDEPTH ? __fdividef(1.f, depths[id]) : 0.f);
         }
         __syncthreads();
-        const int n = min(BATCH, todo);
-        for (int j = 0; j < n; j++) {
-            contributor--;
-            // warp-uniform early-out: nobody in this warp got as far as this Gaussian in the forward
-            if (contributor >= cta_last) continue;
+        const int n = (int)min((uint32_t)BATCH, n_proc - (uint32_t)i * BATCH);
+        const uint32_t q_first = n_proc - 1u - (uint32_t)i * BATCH;   // forward position of staged slot 0
+        int cnt = 0;
+#pragma unroll
+        for (int r = 0; r < BATCH / 32; r++) {
+            const int g = r * 32 + (int)lane;
+            const float4 b = s_box[g];
+            const bool hit = g < n && (q_first - (uint32_t)g) < warp_last && b.y >= wb.x0 && b.x <= wb.x1 &&
+                             b.w >= wb.y0 && b.z <= wb.y1;
+            const uint32_t m = __ballot_sync(0xffffffffu, hit);
+            if (hit) s_list[warp][cnt + __popc(m & lanemask_lt())] = (uint8_t)g;
+            cnt += __popc(m);
+        }
+        __syncwarp();
+        for (int k = 0; k < cnt; k++) {
+            const int j = s_list[warp][k];
+            const uint32_t q = q_first - (uint32_t)j;
             float v[10];
 #pragma unroll
-            for (int k = 0; k < 10; k++) v[k] = 0.f;
+            for (int e = 0; e < 10; e++) v[e] = 0.f;
             bool hit = false;
-            if (contributor < last_contributor) {
+            if (q < last_contributor) {
                 const float2 c = s_xy[j];
                 const float dx = c.x - pxf, dy = c.y - pyf;
                 const float4 co = s_co[j];
@@ -264,7 +341,7 @@ __global__ void __launch_bounds__(TILE_PIX) blend_backward_kernel(
 int launch_blend_forward(int W, int H, const float *background, const float *colors, const uint8_t *geom,
                          const GeomLayout &GL, const uint8_t *binning, const BinLayout &BL, uint8_t *image,
                          const ImgLayout &IL, float *out_color, float *out_invdepth, cudaStream_t stream) {
-    const dim3 grid((W + TILE - 1) / TILE, (H + TILE - 1) / TILE), block(TILE, TILE);
+    const dim3 grid((W + TILE - 1) / TILE, (H + TILE - 1) / TILE), block(TILE_PIX);
     const RasterHeader *hdr = reinterpret_cast<const RasterHeader *>(geom + GL.header);
     const uint2 *ranges = reinterpret_cast<const uint2 *>(image + IL.ranges);
     const uint32_t *v0 = reinterpret_cast<const uint32_t *>(binning + BL.vals0);
@@ -289,7 +366,7 @@ int launch_blend_backward(int W, int H, const float *background, const float *co
                           const GeomLayout &GL, const uint8_t *binning, const BinLayout &BL, const uint8_t *image,
                           const ImgLayout &IL, const float *dL_dpix, const float *dL_dinvdepth_pix, float *grad_acc,
                           cudaStream_t stream) {
-    const dim3 grid((W + TILE - 1) / TILE, (H + TILE - 1) / TILE), block(TILE, TILE);
+    const dim3 grid((W + TILE - 1) / TILE, (H + TILE - 1) / TILE), block(TILE_PIX);
     const RasterHeader *hdr = reinterpret_cast<const RasterHeader *>(geom + GL.header);
     const uint2 *ranges = reinterpret_cast<const uint2 *>(image + IL.ranges);
     const uint32_t *v0 = reinterpret_cast<const uint32_t *>(binning + BL.vals0);
