@@ -25,11 +25,12 @@ struct RasterHeader {          // first 256 bytes of the geom workspace; zeroed 
     uint32_t hist_done;        // CTAs of the histogram kernel that have finished
     uint32_t sort_bits;        // 32 + bits(tile id)
     uint32_t num_passes;
-    uint32_t pad0;
+    uint32_t ranges_done;      // CTAs of the ranges kernel that have finished (last one orders the tiles)
     uint32_t pass_skip[SORT_MAX_PASSES];   // 1 = every key has the same digit in this pass
     uint32_t pass_src[SORT_MAX_PASSES];    // buffer (0/1) a pass reads from
     uint32_t pass_ticket[SORT_MAX_PASSES]; // dynamic tile id per pass
-    uint32_t pad1[64 - 8 - 3 * SORT_MAX_PASSES];
+    uint32_t blend_done;       // CTAs of the blend forward that have finished (last one orders the backward)
+    uint32_t pad1[64 - 9 - 3 * SORT_MAX_PASSES];
 };
 static_assert(sizeof(RasterHeader) == 256, "header is 256 bytes");
 
@@ -41,7 +42,7 @@ struct BinLayout {
     uint64_t tile_state_bytes;
 };
 struct ImgLayout {
-    uint64_t ranges, final_T, n_contrib, total;
+    uint64_t ranges, final_T, n_contrib, order_fwd, order_bwd, tile_nproc, total;
 };
 
 __host__ __device__ inline uint64_t align256(uint64_t x) { return (x + 255) & ~uint64_t(255); }
@@ -84,6 +85,9 @@ inline ImgLayout img_layout(int W, int H) {
     L.ranges = o;    o = align256(o + 8 * tiles);
     L.final_T = o;   o = align256(o + 4 * px);
     L.n_contrib = o; o = align256(o + 4 * px);
+    L.order_fwd = o;  o = align256(o + 4 * tiles);   // tiles, longest list first (blend forward launch order)
+    L.order_bwd = o;  o = align256(o + 4 * tiles);   // tiles, deepest contributor first (blend backward)
+    L.tile_nproc = o; o = align256(o + 4 * tiles);   // max over the tile's pixels of n_contrib
     L.total = o;
     return L;
 }
@@ -172,6 +176,50 @@ __device__ __forceinline__ void st_volatile_u32(uint32_t *p, uint32_t v) {
 __device__ __forceinline__ void st_volatile_u64(uint64_t *p, uint64_t v) {
     asm volatile("st.volatile.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
+// Longest-processing-time-first launch order: one CTA of 256 threads counting-sorts the tiles by key, descending
+// (256 buckets of width 32, saturating; order inside a bucket is arbitrary).  Two passes over the keys with the loads
+// batched eight deep (a single CTA is latency-bound on them).  s_bins needs 256 words.
+template <typename KeyFn>
+__device__ __forceinline__ void order_tiles_descending(int num_tiles, KeyFn key, uint32_t *order, uint32_t *s_bins) {
+    const int tid = threadIdx.x;
+    __shared__ uint32_t s_w[8];
+    s_bins[tid] = 0;
+    __syncthreads();
+    for (int t0 = 0; t0 < num_tiles; t0 += 256 * 8) {
+        uint32_t k[8];
+#pragma unroll
+        for (int u = 0; u < 8; u++) { const int t = t0 + u * 256 + tid; k[u] = t < num_tiles ? key(t) : 0u; }
+#pragma unroll
+        for (int u = 0; u < 8; u++)
+            if (t0 + u * 256 + tid < num_tiles) atomicAdd(&s_bins[255u - min(255u, k[u] >> 5)], 1u);
+    }
+    __syncthreads();
+    const uint32_t lane = tid & 31, warp = tid >> 5;
+    const uint32_t c = s_bins[tid];
+    uint32_t incl = c;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const uint32_t n = __shfl_up_sync(0xffffffffu, incl, d);
+        if (lane >= (uint32_t)d) incl += n;
+    }
+    if (lane == 31) s_w[warp] = incl;
+    __syncthreads();
+    uint32_t off = 0;
+    for (uint32_t w = 0; w < warp; w++) off += s_w[w];
+    s_bins[tid] = off + incl - c;
+    __syncthreads();
+    for (int t0 = 0; t0 < num_tiles; t0 += 256 * 8) {
+        uint32_t k[8];
+#pragma unroll
+        for (int u = 0; u < 8; u++) { const int t = t0 + u * 256 + tid; k[u] = t < num_tiles ? key(t) : 0u; }
+#pragma unroll
+        for (int u = 0; u < 8; u++) {
+            const int t = t0 + u * 256 + tid;
+            if (t < num_tiles) order[atomicAdd(&s_bins[255u - min(255u, k[u] >> 5)], 1u)] = (uint32_t)t;
+        }
+    }
+}
+
 __device__ __forceinline__ void red_add_v4(float *addr, float a, float b, float c, float d) {
     asm volatile("red.global.add.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
 }

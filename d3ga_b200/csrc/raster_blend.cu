@@ -10,11 +10,13 @@
 //
 // Backward: every (pixel, Gaussian) pair produces ten partial derivatives.  Instead of ten global atomics per pair
 // (upstream) they are reduced in three levels:
-//   warp   : butterfly transpose-reduction -- 12 shuffles bring the ten 32-lane sums to ten different lanes
-//            (a plain reduction would need 50), skipped entirely when no lane of the warp touches the Gaussian;
-//   CTA    : shared-memory accumulators, one row of 12 floats per staged Gaussian;
-//   global : three 16-byte vector reductions (REDG.E.ADD.F32x4) per (tile, Gaussian) into the packed accumulator
-//            that the preprocess backward (R8) then reads once.
+//   warp   : butterfly transpose-reduction over three Gaussians at a time -- 31 shuffles bring the 30 32-lane sums
+//            to 30 different lanes (a plain reduction would need 150), skipped entirely for Gaussians no lane of
+//            the warp touches;
+//   global : the 30 sums sit on 30 lanes, so ONE reduction instruction (RED.ADD.F32, <= 3 rows of 48 bytes, i.e. a
+//            handful of L2 sectors) adds them into the packed per-Gaussian accumulator that the preprocess backward
+//            (R8) then reads once -- one RED instruction per (warp, 3 Gaussians) instead of ten atomics per
+//            (pixel, Gaussian).
 // Algorithmic bytes: forward 40 B per duplicate + 20 B per pixel; backward 40 B read + 40 B gradient RMW per
 // duplicate + 20 B per pixel.  Both kernels are FP32/SFU bound rather than HBM bound.
 #include "common.cuh"
@@ -44,9 +46,9 @@ struct WarpBlock {
     int px, py;
     float x0, x1, y0, y1;
 };
-__device__ __forceinline__ WarpBlock warp_block(int tid) {
+__device__ __forceinline__ WarpBlock warp_block(int tid, int tile_x, int tile_y) {
     const int warp = tid >> 5, lane = tid & 31;
-    const int bx = blockIdx.x * TILE + (warp & 1) * 8, by = blockIdx.y * TILE + (warp >> 1) * 4;
+    const int bx = tile_x * TILE + (warp & 1) * 8, by = tile_y * TILE + (warp >> 1) * 4;
     WarpBlock w;
     w.px = bx + (lane & 7);
     w.py = by + (lane >> 3);
@@ -60,17 +62,22 @@ __global__ void __launch_bounds__(TILE_PIX) blend_forward_kernel(
     const uint32_t *__restrict__ vals1, int W, int H, const float2 *__restrict__ xy,
     const float4 *__restrict__ conic_opacity, const float *__restrict__ colors, const float *__restrict__ depths,
     const float *__restrict__ bg, float *__restrict__ final_T, uint32_t *__restrict__ n_contrib,
-    float *__restrict__ out_color, float *__restrict__ out_invdepth) {
+    float *__restrict__ out_color, float *__restrict__ out_invdepth, RasterHeader *__restrict__ hdr_rw, int grid_x,
+    int num_tiles, const uint32_t *__restrict__ order_fwd, uint32_t *__restrict__ tile_nproc,
+    uint32_t *__restrict__ order_bwd) {
     __shared__ float2 s_xy[BATCH];
     __shared__ float4 s_co[BATCH];
     __shared__ float4 s_feat[BATCH];   // r, g, b, 1/depth
     __shared__ float4 s_box[BATCH];
     __shared__ uint8_t s_list[TILE_PIX / 32][BATCH];
+    __shared__ uint32_t s_bins[257];
+    __shared__ uint32_t s_red[TILE_PIX / 32];
+    __shared__ uint32_t s_last;
 
-    const uint32_t tile = blockIdx.y * gridDim.x + blockIdx.x;
+    const uint32_t tile = order_fwd[blockIdx.x];   // longest Gaussian list first
     const int tid = threadIdx.x;
     const uint32_t lane = tid & 31, warp = tid >> 5;
-    const WarpBlock wb = warp_block(tid);
+    const WarpBlock wb = warp_block(tid, (int)(tile % (uint32_t)grid_x), (int)(tile / (uint32_t)grid_x));
     const int px = wb.px, py = wb.py;
     const bool inside = px < W && py < H;
     const float pxf = (float)px, pyf = (float)py;
@@ -83,19 +90,33 @@ __global__ void __launch_bounds__(TILE_PIX) blend_forward_kernel(
     bool done = !inside;
     float T = 1.f, C0 = 0.f, C1 = 0.f, C2 = 0.f, invd = 0.f;
     uint32_t last = 0;
+    // Software pipeline over batches: the Gaussian ids of batch i+2 and the gathered records of batch i+1 are in
+    // flight (in registers) while batch i is blended out of shared memory, so the dependent id -> record loads never
+    // sit on the critical path of a long tile.
+    const uint32_t count = range.y - range.x;
+    uint32_t id_next = 0;
+    float2 p_xy = make_float2(0.f, 0.f);
+    float4 p_co = make_float4(0.f, 0.f, 0.f, 0.f), p_feat = make_float4(0.f, 0.f, 0.f, 0.f);
+    auto gather = [&](uint32_t id) {
+        p_xy = xy[id];
+        p_co = conic_opacity[id];
+        p_feat = make_float4(colors[3 * (size_t)id], colors[3 * (size_t)id + 1], colors[3 * (size_t)id + 2],
+                             INVDEPTH ? depths[id] : 1.f);
+    };
+    if ((uint32_t)tid < count) gather(point_list[range.x + tid]);
+    if ((uint32_t)tid + BATCH < count) id_next = point_list[range.x + BATCH + tid];
     for (int i = 0; i < rounds; i++, todo -= BATCH) {
         if (__syncthreads_count(done) == TILE_PIX) break;
         const uint32_t progress = (uint32_t)i * BATCH + tid;
-        if (range.x + progress < range.y) {
-            const uint32_t id = point_list[range.x + progress];
-            const float2 c = xy[id];
-            const float4 co = conic_opacity[id];
-            s_xy[tid] = c;
-            s_co[tid] = co;
-            s_box[tid] = footprint_box(c, co);
-            s_feat[tid] = make_float4(colors[3 * (size_t)id], colors[3 * (size_t)id + 1], colors[3 * (size_t)id + 2],
-                                      INVDEPTH ? __fdividef(1.f, depths[id]) : 0.f);
+        if (progress < count) {
+            s_xy[tid] = p_xy;
+            s_co[tid] = p_co;
+            s_box[tid] = footprint_box(p_xy, p_co);
+            p_feat.w = INVDEPTH ? __fdividef(1.f, p_feat.w) : 0.f;
+            s_feat[tid] = p_feat;
         }
+        if (progress + BATCH < count) gather(id_next);
+        if (progress + 2 * BATCH < count) id_next = point_list[range.x + progress + 2 * BATCH];
         __syncthreads();
         if (__all_sync(0xffffffffu, done)) continue;
         const int n = min(BATCH, todo);
@@ -112,25 +133,36 @@ __global__ void __launch_bounds__(TILE_PIX) blend_forward_kernel(
         }
         __syncwarp();
         const uint32_t base = (uint32_t)i * BATCH;
-        for (int k = 0; k < cnt; k++) {
+        // four list entries at a time: their alphas are independent (instruction-level parallelism for the warp
+        // that sits on the tile's critical path); only the transmittance update is sequential
+        for (int k = 0; k < cnt; k += 4) {
             if (__all_sync(0xffffffffu, done)) break;
-            if (done) continue;
-            const int j = s_list[warp][k];
-            const float2 c = s_xy[j];
-            const float dx = c.x - pxf, dy = c.y - pyf;
-            const float4 co = s_co[j];
-            const float power = -0.5f * (co.x * dx * dx + co.z * dy * dy) - co.y * dx * dy;
-            if (power > 0.f) continue;
-            const float alpha = fminf(0.99f, co.w * __expf(power));
-            if (alpha < 1.f / 255.f) continue;
-            const float test_T = T * (1.f - alpha);
-            if (test_T < 0.0001f) { done = true; continue; }
-            const float4 f = s_feat[j];
-            const float w = alpha * T;
-            C0 += f.x * w; C1 += f.y * w; C2 += f.z * w;
-            if (INVDEPTH) invd += f.w * w;
-            T = test_T;
-            last = base + (uint32_t)j + 1u;
+            float a[4];
+            int jj[4];
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+                const bool valid = k + u < cnt;
+                const int j = valid ? (int)s_list[warp][k + u] : 0;
+                const float2 c = s_xy[j];
+                const float dx = c.x - pxf, dy = c.y - pyf;
+                const float4 co = s_co[j];
+                const float power = -0.5f * (co.x * dx * dx + co.z * dy * dy) - co.y * dx * dy;
+                const float alpha = fminf(0.99f, co.w * __expf(power));
+                a[u] = (valid && !(power > 0.f) && alpha >= 1.f / 255.f) ? alpha : 0.f;
+                jj[u] = j;
+            }
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+                if (done || a[u] == 0.f) continue;
+                const float test_T = T * (1.f - a[u]);
+                if (test_T < 0.0001f) { done = true; continue; }
+                const float4 f = s_feat[jj[u]];
+                const float w = a[u] * T;
+                C0 += f.x * w; C1 += f.y * w; C2 += f.z * w;
+                if (INVDEPTH) invd += f.w * w;
+                T = test_T;
+                last = base + (uint32_t)jj[u] + 1u;
+            }
         }
     }
     if (inside) {
@@ -142,46 +174,51 @@ __global__ void __launch_bounds__(TILE_PIX) blend_forward_kernel(
         out_color[2 * plane + pid] = C2 + T * bg[2];
         if (INVDEPTH) out_invdepth[pid] = invd;
     }
+    // deepest contributor of the tile = how far the backward has to go; the last CTA orders the backward's tiles
+    const uint32_t wmax = __reduce_max_sync(0xffffffffu, inside ? last : 0u);
+    if (lane == 0) s_red[warp] = wmax;
+    __syncthreads();
+    if (tid == 0) {
+        uint32_t m = 0;
+        for (int w = 0; w < TILE_PIX / 32; w++) m = max(m, s_red[w]);
+        tile_nproc[tile] = m;
+        __threadfence();
+        s_last = atomicAdd(&hdr_rw->blend_done, 1u) == (uint32_t)num_tiles - 1u;
+    }
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    const uint32_t *np = tile_nproc;
+    order_tiles_descending(num_tiles, [np](int t) { return __ldcg(np + t); }, order_bwd, s_bins);
 }
 
-// Ten values per lane, summed over the 32 lanes, end up in ten different lanes after 12 shuffles.
-//   stage xor16: 10 -> 5 values per lane   stage xor8: 5 -> 3   stage xor4: 3 -> 2   stage xor2: 2 -> 1   stage xor1
-// slot_of_lane() tells which of the ten sums a lane holds afterwards (-1: none; odd lanes duplicate the even ones).
-__device__ __forceinline__ int slot_of_lane(uint32_t lane) {
-    if (lane & 1u) return -1;
-    int base = (lane & 16u) ? 5 : 0, n = 5;
-    if (lane & 8u) { base += 3; n = 2; } else { n = 3; }
-    if (lane & 4u) { base += 2; n -= 2; } else { n = min(n, 2); }
-    if (lane & 2u) { base += 1; n -= 1; } else { n = min(n, 1); }
-    return n >= 1 ? base : -1;
-}
-__device__ __forceinline__ float butterfly10(const float (&v)[10], uint32_t lane) {
-    const bool b4 = lane & 16u, b3 = lane & 8u, b2 = lane & 4u, b1 = lane & 2u;
-    float a[5];
+// Three Gaussians at once: 3 x 10 partials (+2 zeros) per lane, summed over the 32 lanes, land on 32 DIFFERENT lanes
+// (lane l ends up holding the total of value l) after 16+8+4+2+1 = 31 shuffles -- 10.3 per Gaussian, and the shuffles
+// of a stage are independent, so their latency overlaps instead of adding up per Gaussian.
+__device__ __forceinline__ float butterfly32(float (&w)[32], uint32_t lane) {
+    const bool b4 = lane & 16u, b3 = lane & 8u, b2 = lane & 4u, b1 = lane & 2u, b0 = lane & 1u;
 #pragma unroll
-    for (int k = 0; k < 5; k++) {
-        const float send = b4 ? v[k] : v[k + 5], keep = b4 ? v[k + 5] : v[k];
-        a[k] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
+    for (int k = 0; k < 16; k++) {
+        const float send = b4 ? w[k] : w[k + 16], keep = b4 ? w[k + 16] : w[k];
+        w[k] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
     }
-    float b[3];
-    {
-        const float r0 = __shfl_xor_sync(0xffffffffu, b3 ? a[0] : a[3], 8);
-        const float r1 = __shfl_xor_sync(0xffffffffu, b3 ? a[1] : a[4], 8);
-        const float r2 = __shfl_xor_sync(0xffffffffu, b3 ? a[2] : 0.f, 8);
-        b[0] = (b3 ? a[3] : a[0]) + r0;
-        b[1] = (b3 ? a[4] : a[1]) + r1;
-        b[2] = b3 ? 0.f : a[2] + r2;
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+        const float send = b3 ? w[k] : w[k + 8], keep = b3 ? w[k + 8] : w[k];
+        w[k] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
     }
-    float c[2];
-    {
-        const float r0 = __shfl_xor_sync(0xffffffffu, b2 ? b[0] : b[2], 4);
-        const float r1 = __shfl_xor_sync(0xffffffffu, b2 ? b[1] : 0.f, 4);
-        c[0] = (b2 ? b[2] : b[0]) + r0;
-        c[1] = b2 ? 0.f : b[1] + r1;
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        const float send = b2 ? w[k] : w[k + 4], keep = b2 ? w[k + 4] : w[k];
+        w[k] = keep + __shfl_xor_sync(0xffffffffu, send, 4);
     }
-    float d = (b1 ? c[1] : c[0]) + __shfl_xor_sync(0xffffffffu, b1 ? c[0] : c[1], 2);
-    d += __shfl_xor_sync(0xffffffffu, d, 1);
-    return d;
+#pragma unroll
+    for (int k = 0; k < 2; k++) {
+        const float send = b1 ? w[k] : w[k + 2], keep = b1 ? w[k + 2] : w[k];
+        w[k] = keep + __shfl_xor_sync(0xffffffffu, send, 2);
+    }
+    const float send = b0 ? w[0] : w[1], keep = b0 ? w[1] : w[0];
+    return keep + __shfl_xor_sync(0xffffffffu, send, 1);
 }
 
 template <bool INVDEPTH>
@@ -190,20 +227,22 @@ __global__ void __launch_bounds__(TILE_PIX) blend_backward_kernel(
     const uint32_t *__restrict__ vals1, int W, int H, const float *__restrict__ bg, const float2 *__restrict__ xy,
     const float4 *__restrict__ conic_opacity, const float *__restrict__ colors, const float *__restrict__ depths,
     const float *__restrict__ final_T, const uint32_t *__restrict__ n_contrib, const float *__restrict__ dL_dpix,
-    const float *__restrict__ dL_dinvdepth_pix, float *__restrict__ grad_acc) {
-    __shared__ float2 s_xy[BATCH];
-    __shared__ float4 s_co[BATCH];
-    __shared__ float4 s_feat[BATCH];
-    __shared__ float4 s_box[BATCH];
-    __shared__ uint32_t s_id[BATCH];
+    const float *__restrict__ dL_dinvdepth_pix, float *__restrict__ grad_acc, int grid_x,
+    const uint32_t *__restrict__ order_bwd) {
+    // double-buffered staging: batch i+1 is gathered into registers while batch i is processed, then parked in the
+    // other buffer -- one CTA barrier per batch
+    __shared__ float2 s_xy[2][BATCH];
+    __shared__ float4 s_co[2][BATCH];
+    __shared__ float4 s_feat[2][BATCH];
+    __shared__ float4 s_box[2][BATCH];
+    __shared__ uint32_t s_id[2][BATCH];
     __shared__ uint8_t s_list[TILE_PIX / 32][BATCH];
-    __shared__ __align__(16) float s_acc[BATCH * GRAD_ACC_FLOATS];
     __shared__ uint32_t s_max[TILE_PIX / 32];
 
-    const uint32_t tile = blockIdx.y * gridDim.x + blockIdx.x;
+    const uint32_t tile = order_bwd[blockIdx.x];   // deepest contributor first
     const int tid = threadIdx.x;
     const uint32_t lane = tid & 31, warp = tid >> 5;
-    const WarpBlock wb = warp_block(tid);
+    const WarpBlock wb = warp_block(tid, (int)(tile % (uint32_t)grid_x), (int)(tile / (uint32_t)grid_x));
     const int px = wb.px, py = wb.py;
     const bool inside = px < W && py < H;
     const float pxf = (float)px, pyf = (float)py;
@@ -220,7 +259,6 @@ __global__ void __launch_bounds__(TILE_PIX) blend_backward_kernel(
     // staged at all (the forward stops a pixel at T < 1e-4, typically after a small fraction of a deep list).
     const uint32_t warp_last = __reduce_max_sync(0xffffffffu, last_contributor);
     if (lane == 0) s_max[warp] = warp_last;
-    for (int k = tid; k < BATCH * GRAD_ACC_FLOATS; k += TILE_PIX) s_acc[k] = 0.f;
     __syncthreads();
     uint32_t n_proc = 0;
 #pragma unroll
@@ -237,31 +275,40 @@ __global__ void __launch_bounds__(TILE_PIX) blend_backward_kernel(
     }
     const float bg_dot = bg[0] * g0 + bg[1] * g1 + bg[2] * g2;
     const float ddelx_dx = 0.5f * (float)W, ddely_dy = 0.5f * (float)H;
-    const int slot = slot_of_lane(lane);
+    const uint32_t slot = lane % 10u, group = lane / 10u;   // lane l (< 30) ends up with sum `slot` of Gaussian `group`
+
+    uint32_t p_id = 0;
+    float2 p_xy = make_float2(0.f, 0.f);
+    float4 p_co = make_float4(0.f, 0.f, 0.f, 0.f), p_feat = make_float4(0.f, 0.f, 0.f, 0.f);
+    // staged slot t of batch i holds the Gaussian at forward position q = n_proc - 1 - (i * BATCH + t): back to front
+    auto gather = [&](uint32_t progress) {
+        p_id = point_list[range.x + (n_proc - 1u - progress)];
+        p_xy = xy[p_id];
+        p_co = conic_opacity[p_id];
+        p_feat = make_float4(colors[3 * (size_t)p_id], colors[3 * (size_t)p_id + 1], colors[3 * (size_t)p_id + 2],
+                             INVDEPTH ? __fdividef(1.f, depths[p_id]) : 0.f);
+    };
+    auto park = [&](int buf) {
+        s_id[buf][tid] = p_id;
+        s_xy[buf][tid] = p_xy;
+        s_co[buf][tid] = p_co;
+        s_box[buf][tid] = footprint_box(p_xy, p_co);
+        s_feat[buf][tid] = p_feat;
+    };
+    if ((uint32_t)tid < n_proc) { gather(tid); park(0); }
+    __syncthreads();
 
     for (int i = 0; i < rounds; i++) {
-        __syncthreads();
-        // staged slot t holds the Gaussian at forward position q = n_proc - 1 - (i * BATCH + t): back to front
-        const uint32_t progress = (uint32_t)i * BATCH + tid;
-        if (progress < n_proc) {
-            const uint32_t id = point_list[range.x + (n_proc - 1u - progress)];
-            const float2 c = xy[id];
-            const float4 co = conic_opacity[id];
-            s_id[tid] = id;
-            s_xy[tid] = c;
-            s_co[tid] = co;
-            s_box[tid] = footprint_box(c, co);
-            s_feat[tid] = make_float4(colors[3 * (size_t)id], colors[3 * (size_t)id + 1], colors[3 * (size_t)id + 2],
-                                      INVDEPTH ? __fdividef(1.f, depths[id]) : 0.f);
-        }
-        __syncthreads();
+        const int buf = i & 1;
+        const uint32_t next = (uint32_t)(i + 1) * BATCH + tid;
+        if (next < n_proc) gather(next);   // in flight while this batch is processed
         const int n = (int)min((uint32_t)BATCH, n_proc - (uint32_t)i * BATCH);
         const uint32_t q_first = n_proc - 1u - (uint32_t)i * BATCH;   // forward position of staged slot 0
         int cnt = 0;
 #pragma unroll
         for (int r = 0; r < BATCH / 32; r++) {
             const int g = r * 32 + (int)lane;
-            const float4 b = s_box[g];
+            const float4 b = s_box[buf][g];
             const bool hit = g < n && (q_first - (uint32_t)g) < warp_last && b.y >= wb.x0 && b.x <= wb.x1 &&
                              b.w >= wb.y0 && b.z <= wb.y1;
             const uint32_t m = __ballot_sync(0xffffffffu, hit);
@@ -269,70 +316,70 @@ __global__ void __launch_bounds__(TILE_PIX) blend_backward_kernel(
             cnt += __popc(m);
         }
         __syncwarp();
-        for (int k = 0; k < cnt; k++) {
-            const int j = s_list[warp][k];
-            const uint32_t q = q_first - (uint32_t)j;
-            float v[10];
+        // three list entries at a time: independent alpha evaluation, sequential transmittance recurrence, then ONE
+        // 32-value butterfly for the 3 x 10 partial derivatives and one RED instruction (30 lanes, <= 3 rows)
+        for (int k = 0; k < cnt; k += 3) {
+            int jj[3];
+            float G_[3], al[3], dx_[3], dy_[3];
+            bool ok[3];
 #pragma unroll
-            for (int e = 0; e < 10; e++) v[e] = 0.f;
-            bool hit = false;
-            if (q < last_contributor) {
-                const float2 c = s_xy[j];
+            for (int u = 0; u < 3; u++) {
+                const bool valid = k + u < cnt;
+                const int j = valid ? (int)s_list[warp][k + u] : 0;
+                const float2 c = s_xy[buf][j];
                 const float dx = c.x - pxf, dy = c.y - pyf;
-                const float4 co = s_co[j];
+                const float4 co = s_co[buf][j];
                 const float power = -0.5f * (co.x * dx * dx + co.z * dy * dy) - co.y * dx * dy;
-                if (power <= 0.f) {
-                    const float G = __expf(power);
-                    const float alpha = fminf(0.99f, co.w * G);
-                    if (alpha >= 1.f / 255.f) {
-                        hit = true;
-                        const float inv_1ma = __fdividef(1.f, 1.f - alpha);
-                        T = T * inv_1ma;
-                        const float dchannel_dcolor = alpha * T;
-                        const float4 f = s_feat[j];
-                        acc0 = last_alpha * lc0 + (1.f - last_alpha) * acc0; lc0 = f.x;
-                        acc1 = last_alpha * lc1 + (1.f - last_alpha) * acc1; lc1 = f.y;
-                        acc2 = last_alpha * lc2 + (1.f - last_alpha) * acc2; lc2 = f.z;
-                        float dL_dalpha = (f.x - acc0) * g0 + (f.y - acc1) * g1 + (f.z - acc2) * g2;
-                        v[6] = dchannel_dcolor * g0; v[7] = dchannel_dcolor * g1; v[8] = dchannel_dcolor * g2;
-                        if (INVDEPTH) {
-                            acci = last_alpha * lci + (1.f - last_alpha) * acci; lci = f.w;
-                            dL_dalpha += (f.w - acci) * gi;
-                            v[9] = dchannel_dcolor * gi;
-                        }
-                        dL_dalpha *= T;
-                        last_alpha = alpha;
-                        dL_dalpha += (-T_final * inv_1ma) * bg_dot;
-                        const float dL_dG = co.w * dL_dalpha;
-                        const float gdx = G * dx, gdy = G * dy;
-                        const float dG_ddelx = -gdx * co.x - gdy * co.y;
-                        const float dG_ddely = -gdy * co.z - gdx * co.y;
-                        v[0] = dL_dG * dG_ddelx * ddelx_dx;
-                        v[1] = dL_dG * dG_ddely * ddely_dy;
-                        v[2] = -0.5f * gdx * dx * dL_dG;
-                        v[3] = -0.5f * gdx * dy * dL_dG;
-                        v[4] = -0.5f * gdy * dy * dL_dG;
-                        v[5] = G * dL_dalpha;
-                    }
-                }
+                const float G = __expf(power);
+                const float alpha = fminf(0.99f, co.w * G);
+                ok[u] = valid && (q_first - (uint32_t)j) < last_contributor && !(power > 0.f) && alpha >= 1.f / 255.f;
+                jj[u] = j; G_[u] = G; al[u] = alpha; dx_[u] = dx; dy_[u] = dy;
             }
-            if (!__any_sync(0xffffffffu, hit)) continue;
-            const float sum = butterfly10(v, lane);
-            if (slot >= 0 && sum != 0.f) atomicAdd(&s_acc[j * GRAD_ACC_FLOATS + slot], sum);
+            if (!__any_sync(0xffffffffu, ok[0] || ok[1] || ok[2])) continue;
+            float w[32];
+#pragma unroll
+            for (int e = 0; e < 32; e++) w[e] = 0.f;
+#pragma unroll
+            for (int u = 0; u < 3; u++) {
+                if (!ok[u]) continue;
+                const float alpha = al[u], G = G_[u], dx = dx_[u], dy = dy_[u];
+                const float4 co = s_co[buf][jj[u]];
+                const float4 f = s_feat[buf][jj[u]];
+                const float inv_1ma = __fdividef(1.f, 1.f - alpha);
+                T = T * inv_1ma;
+                const float dchannel_dcolor = alpha * T;
+                acc0 = last_alpha * lc0 + (1.f - last_alpha) * acc0; lc0 = f.x;
+                acc1 = last_alpha * lc1 + (1.f - last_alpha) * acc1; lc1 = f.y;
+                acc2 = last_alpha * lc2 + (1.f - last_alpha) * acc2; lc2 = f.z;
+                float dL_dalpha = (f.x - acc0) * g0 + (f.y - acc1) * g1 + (f.z - acc2) * g2;
+                w[10 * u + 6] = dchannel_dcolor * g0;
+                w[10 * u + 7] = dchannel_dcolor * g1;
+                w[10 * u + 8] = dchannel_dcolor * g2;
+                if (INVDEPTH) {
+                    acci = last_alpha * lci + (1.f - last_alpha) * acci; lci = f.w;
+                    dL_dalpha += (f.w - acci) * gi;
+                    w[10 * u + 9] = dchannel_dcolor * gi;
+                }
+                dL_dalpha *= T;
+                last_alpha = alpha;
+                dL_dalpha += (-T_final * inv_1ma) * bg_dot;
+                const float dL_dG = co.w * dL_dalpha;
+                const float gdx = G * dx, gdy = G * dy;
+                w[10 * u + 0] = dL_dG * (-gdx * co.x - gdy * co.y) * ddelx_dx;
+                w[10 * u + 1] = dL_dG * (-gdy * co.z - gdx * co.y) * ddely_dy;
+                w[10 * u + 2] = -0.5f * gdx * dx * dL_dG;
+                w[10 * u + 3] = -0.5f * gdx * dy * dL_dG;
+                w[10 * u + 4] = -0.5f * gdy * dy * dL_dG;
+                w[10 * u + 5] = G * dL_dalpha;
+            }
+            const float sum = butterfly32(w, lane);
+            if (lane < 30u && sum != 0.f) {
+                const int j = group == 0u ? jj[0] : (group == 1u ? jj[1] : jj[2]);
+                atomicAdd(grad_acc + (size_t)s_id[buf][j] * GRAD_ACC_FLOATS + slot, sum);
+            }
         }
+        if (next < n_proc) park(buf ^ 1);
         __syncthreads();
-        // flush this batch: one row of 12 floats per staged Gaussian -> three vector reductions
-        if (tid < n) {
-            float4 *row = reinterpret_cast<float4 *>(s_acc + tid * GRAD_ACC_FLOATS);
-            const float4 r0 = row[0], r1 = row[1], r2 = row[2];
-            float *dst = grad_acc + (size_t)s_id[tid] * GRAD_ACC_FLOATS;
-            if (r0.x != 0.f || r0.y != 0.f || r0.z != 0.f || r0.w != 0.f) red_add_v4(dst, r0.x, r0.y, r0.z, r0.w);
-            if (r1.x != 0.f || r1.y != 0.f || r1.z != 0.f || r1.w != 0.f) red_add_v4(dst + 4, r1.x, r1.y, r1.z, r1.w);
-            if (r2.x != 0.f || r2.y != 0.f) red_add_v2(dst + 8, r2.x, r2.y);
-            row[0] = make_float4(0.f, 0.f, 0.f, 0.f);
-            row[1] = make_float4(0.f, 0.f, 0.f, 0.f);
-            row[2] = make_float4(0.f, 0.f, 0.f, 0.f);
-        }
     }
 }
 
@@ -341,8 +388,9 @@ __global__ void __launch_bounds__(TILE_PIX) blend_backward_kernel(
 int launch_blend_forward(int W, int H, const float *background, const float *colors, const uint8_t *geom,
                          const GeomLayout &GL, const uint8_t *binning, const BinLayout &BL, uint8_t *image,
                          const ImgLayout &IL, float *out_color, float *out_invdepth, cudaStream_t stream) {
-    const dim3 grid((W + TILE - 1) / TILE, (H + TILE - 1) / TILE), block(TILE_PIX);
+    const int gx = (W + TILE - 1) / TILE, gy = (H + TILE - 1) / TILE, num_tiles = gx * gy;
     const RasterHeader *hdr = reinterpret_cast<const RasterHeader *>(geom + GL.header);
+    RasterHeader *hdr_rw = const_cast<RasterHeader *>(hdr);
     const uint2 *ranges = reinterpret_cast<const uint2 *>(image + IL.ranges);
     const uint32_t *v0 = reinterpret_cast<const uint32_t *>(binning + BL.vals0);
     const uint32_t *v1 = reinterpret_cast<const uint32_t *>(binning + BL.vals1);
@@ -351,13 +399,18 @@ int launch_blend_forward(int W, int H, const float *background, const float *col
     const float *depth = reinterpret_cast<const float *>(geom + GL.depth);
     float *final_T = reinterpret_cast<float *>(image + IL.final_T);
     uint32_t *n_contrib = reinterpret_cast<uint32_t *>(image + IL.n_contrib);
+    const uint32_t *order_fwd = reinterpret_cast<const uint32_t *>(image + IL.order_fwd);
+    uint32_t *order_bwd = reinterpret_cast<uint32_t *>(image + IL.order_bwd);
+    uint32_t *tile_nproc = reinterpret_cast<uint32_t *>(image + IL.tile_nproc);
     ProfScope prof(K_BLEND_FWD, stream);
     if (out_invdepth)
-        blend_forward_kernel<true><<<grid, block, 0, stream>>>(hdr, ranges, v0, v1, W, H, xy, co, colors, depth,
-                                                               background, final_T, n_contrib, out_color, out_invdepth);
+        blend_forward_kernel<true><<<num_tiles, TILE_PIX, 0, stream>>>(
+            hdr, ranges, v0, v1, W, H, xy, co, colors, depth, background, final_T, n_contrib, out_color, out_invdepth,
+            hdr_rw, gx, num_tiles, order_fwd, tile_nproc, order_bwd);
     else
-        blend_forward_kernel<false><<<grid, block, 0, stream>>>(hdr, ranges, v0, v1, W, H, xy, co, colors, depth,
-                                                                background, final_T, n_contrib, out_color, nullptr);
+        blend_forward_kernel<false><<<num_tiles, TILE_PIX, 0, stream>>>(
+            hdr, ranges, v0, v1, W, H, xy, co, colors, depth, background, final_T, n_contrib, out_color, nullptr,
+            hdr_rw, gx, num_tiles, order_fwd, tile_nproc, order_bwd);
     D3GA_LAUNCH_CHECK();
     return D3GA_OK;
 }
@@ -366,7 +419,7 @@ int launch_blend_backward(int W, int H, const float *background, const float *co
                           const GeomLayout &GL, const uint8_t *binning, const BinLayout &BL, const uint8_t *image,
                           const ImgLayout &IL, const float *dL_dpix, const float *dL_dinvdepth_pix, float *grad_acc,
                           cudaStream_t stream) {
-    const dim3 grid((W + TILE - 1) / TILE, (H + TILE - 1) / TILE), block(TILE_PIX);
+    const int gx = (W + TILE - 1) / TILE, gy = (H + TILE - 1) / TILE, num_tiles = gx * gy;
     const RasterHeader *hdr = reinterpret_cast<const RasterHeader *>(geom + GL.header);
     const uint2 *ranges = reinterpret_cast<const uint2 *>(image + IL.ranges);
     const uint32_t *v0 = reinterpret_cast<const uint32_t *>(binning + BL.vals0);
@@ -376,14 +429,16 @@ int launch_blend_backward(int W, int H, const float *background, const float *co
     const float *depth = reinterpret_cast<const float *>(geom + GL.depth);
     const float *final_T = reinterpret_cast<const float *>(image + IL.final_T);
     const uint32_t *n_contrib = reinterpret_cast<const uint32_t *>(image + IL.n_contrib);
+    const uint32_t *order_bwd = reinterpret_cast<const uint32_t *>(image + IL.order_bwd);
     ProfScope prof(K_BLEND_BWD, stream);
     if (dL_dinvdepth_pix)
-        blend_backward_kernel<true><<<grid, block, 0, stream>>>(hdr, ranges, v0, v1, W, H, background, xy, co, colors,
-                                                                depth, final_T, n_contrib, dL_dpix, dL_dinvdepth_pix,
-                                                                grad_acc);
+        blend_backward_kernel<true><<<num_tiles, TILE_PIX, 0, stream>>>(
+            hdr, ranges, v0, v1, W, H, background, xy, co, colors, depth, final_T, n_contrib, dL_dpix, dL_dinvdepth_pix,
+            grad_acc, gx, order_bwd);
     else
-        blend_backward_kernel<false><<<grid, block, 0, stream>>>(hdr, ranges, v0, v1, W, H, background, xy, co, colors,
-                                                                 depth, final_T, n_contrib, dL_dpix, nullptr, grad_acc);
+        blend_backward_kernel<false><<<num_tiles, TILE_PIX, 0, stream>>>(
+            hdr, ranges, v0, v1, W, H, background, xy, co, colors, depth, final_T, n_contrib, dL_dpix, nullptr, grad_acc,
+            gx, order_bwd);
     D3GA_LAUNCH_CHECK();
     return D3GA_OK;
 }

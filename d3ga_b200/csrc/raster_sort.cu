@@ -236,10 +236,13 @@ __global__ void __launch_bounds__(SORT_THREADS) sort_pass_kernel(RasterHeader *h
     }
 }
 
-__global__ void __launch_bounds__(256) tile_ranges_kernel(const RasterHeader *hdr, const uint64_t *keys0,
-                                                          const uint64_t *keys1, uint2 *ranges) {
-    if (hdr->overflow) return;
-    const uint32_t D = hdr->num_rendered;
+__global__ void __launch_bounds__(256) tile_ranges_kernel(RasterHeader *hdr, const uint64_t *keys0,
+                                                          const uint64_t *keys1, uint2 *ranges, int num_tiles,
+                                                          uint32_t *order_fwd) {
+    __shared__ uint32_t s_bins[257];
+    __shared__ uint32_t s_last;
+    const bool live = !hdr->overflow;
+    const uint32_t D = live ? hdr->num_rendered : 0u;
     const uint64_t *keys = hdr->final_sel ? keys1 : keys0;
     const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
     for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < D; i += stride) {
@@ -255,6 +258,15 @@ __global__ void __launch_bounds__(256) tile_ranges_kernel(const RasterHeader *hd
         }
         if (i == D - 1) ranges[cur].y = D;
     }
+    // the last CTA to finish orders the tiles by list length for the blend forward (longest first)
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) s_last = atomicAdd(&hdr->ranges_done, 1u) == gridDim.x - 1;
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    const uint2 *r = ranges;
+    order_tiles_descending(num_tiles, [r](int t) { const uint2 v = __ldcg(r + t); return v.y - v.x; }, order_fwd, s_bins);
 }
 
 }  // namespace
@@ -308,7 +320,8 @@ int launch_sort_and_ranges(uint8_t *geom, uint8_t *binning, const BinLayout &BL,
     if (rg < 1) rg = 1;
     {
         ProfScope prof(K_RANGES, stream);
-        tile_ranges_kernel<<<rg, 256, 0, stream>>>(hdr, keys0, keys1, ranges);
+        tile_ranges_kernel<<<rg, 256, 0, stream>>>(hdr, keys0, keys1, ranges, num_tiles,
+                                                   reinterpret_cast<uint32_t *>(image + IL.order_fwd));
     }
     D3GA_LAUNCH_CHECK();
     return D3GA_OK;
