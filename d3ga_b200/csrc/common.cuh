@@ -10,8 +10,8 @@ namespace d3ga {
 constexpr int TILE = 16;           // 16x16 pixel tiles (upstream BLOCK_X / BLOCK_Y)
 constexpr int TILE_PIX = TILE * TILE;
 constexpr int GEO_THREADS = 256;   // Gaussians per CTA in the per-Gaussian kernels
-constexpr int SORT_THREADS = 256;
-constexpr int SORT_ITEMS = 16;     // keys per thread per onesweep tile
+constexpr int SORT_THREADS = 512;
+constexpr int SORT_ITEMS = 8;      // keys per thread per onesweep tile
 constexpr int SORT_TILE = SORT_THREADS * SORT_ITEMS;  // 4096 pairs = 48 KB of payload per CTA
 constexpr int SORT_MAX_PASSES = 8;
 constexpr uint32_t MAX_DUPLICATES = (1u << 30) - 1;  // look-back words keep 2 flag bits

@@ -65,10 +65,12 @@ __global__ void __launch_bounds__(TILE_PIX) blend_forward_kernel(
     float *__restrict__ out_color, float *__restrict__ out_invdepth, RasterHeader *__restrict__ hdr_rw, int grid_x,
     int num_tiles, const uint32_t *__restrict__ order_fwd, uint32_t *__restrict__ tile_nproc,
     uint32_t *__restrict__ order_bwd) {
-    __shared__ float2 s_xy[BATCH];
-    __shared__ float4 s_co[BATCH];
-    __shared__ float4 s_feat[BATCH];   // r, g, b, 1/depth
-    __shared__ float4 s_box[BATCH];
+    // double-buffered staging: batch i+1 is gathered into registers while batch i is blended, then parked in the
+    // other buffer -- one CTA barrier per batch (the "is every pixel done" vote)
+    __shared__ float2 s_xy[2][BATCH];
+    __shared__ float4 s_co[2][BATCH];
+    __shared__ float4 s_feat[2][BATCH];   // r, g, b, 1/depth
+    __shared__ float4 s_box[2][BATCH];
     __shared__ uint8_t s_list[TILE_PIX / 32][BATCH];
     __shared__ uint32_t s_bins[257];
     __shared__ uint32_t s_red[TILE_PIX / 32];
@@ -84,48 +86,45 @@ __global__ void __launch_bounds__(TILE_PIX) blend_forward_kernel(
     uint2 range = make_uint2(0, 0);
     if (!hdr->overflow) range = ranges[tile];
     const uint32_t *point_list = hdr->final_sel ? vals1 : vals0;
-    const int rounds = (int)((range.y - range.x + BATCH - 1) / BATCH);
-    int todo = (int)(range.y - range.x);
+    const uint32_t count = range.y - range.x;
+    const int rounds = (int)((count + BATCH - 1) / BATCH);
+    int todo = (int)count;
 
     bool done = !inside;
     float T = 1.f, C0 = 0.f, C1 = 0.f, C2 = 0.f, invd = 0.f;
     uint32_t last = 0;
-    // Software pipeline over batches: the Gaussian ids of batch i+2 and the gathered records of batch i+1 are in
-    // flight (in registers) while batch i is blended out of shared memory, so the dependent id -> record loads never
-    // sit on the critical path of a long tile.
-    const uint32_t count = range.y - range.x;
-    uint32_t id_next = 0;
     float2 p_xy = make_float2(0.f, 0.f);
     float4 p_co = make_float4(0.f, 0.f, 0.f, 0.f), p_feat = make_float4(0.f, 0.f, 0.f, 0.f);
-    auto gather = [&](uint32_t id) {
+    auto gather = [&](uint32_t progress) {
+        const uint32_t id = point_list[range.x + progress];
         p_xy = xy[id];
         p_co = conic_opacity[id];
         p_feat = make_float4(colors[3 * (size_t)id], colors[3 * (size_t)id + 1], colors[3 * (size_t)id + 2],
-                             INVDEPTH ? depths[id] : 1.f);
+                             INVDEPTH ? __fdividef(1.f, depths[id]) : 0.f);
     };
-    if ((uint32_t)tid < count) gather(point_list[range.x + tid]);
-    if ((uint32_t)tid + BATCH < count) id_next = point_list[range.x + BATCH + tid];
+    auto park = [&](int buf) {
+        s_xy[buf][tid] = p_xy;
+        s_co[buf][tid] = p_co;
+        s_box[buf][tid] = footprint_box(p_xy, p_co);
+        s_feat[buf][tid] = p_feat;
+    };
+    if ((uint32_t)tid < count) { gather(tid); park(0); }
     for (int i = 0; i < rounds; i++, todo -= BATCH) {
         if (__syncthreads_count(done) == TILE_PIX) break;
-        const uint32_t progress = (uint32_t)i * BATCH + tid;
-        if (progress < count) {
-            s_xy[tid] = p_xy;
-            s_co[tid] = p_co;
-            s_box[tid] = footprint_box(p_xy, p_co);
-            p_feat.w = INVDEPTH ? __fdividef(1.f, p_feat.w) : 0.f;
-            s_feat[tid] = p_feat;
+        const int buf = i & 1;
+        const uint32_t next = (uint32_t)(i + 1) * BATCH + tid;
+        if (next < count) gather(next);   // in flight while this batch is blended
+        if (__all_sync(0xffffffffu, done)) {
+            if (next < count) park(buf ^ 1);
+            continue;
         }
-        if (progress + BATCH < count) gather(id_next);
-        if (progress + 2 * BATCH < count) id_next = point_list[range.x + progress + 2 * BATCH];
-        __syncthreads();
-        if (__all_sync(0xffffffffu, done)) continue;
         const int n = min(BATCH, todo);
         // this warp's depth-ordered list of the staged Gaussians whose footprint reaches its pixel block
         int cnt = 0;
 #pragma unroll
         for (int r = 0; r < BATCH / 32; r++) {
             const int g = r * 32 + (int)lane;
-            const float4 b = s_box[g];
+            const float4 b = s_box[buf][g];
             const bool hit = g < n && b.y >= wb.x0 && b.x <= wb.x1 && b.w >= wb.y0 && b.z <= wb.y1;
             const uint32_t m = __ballot_sync(0xffffffffu, hit);
             if (hit) s_list[warp][cnt + __popc(m & lanemask_lt())] = (uint8_t)g;
@@ -143,9 +142,9 @@ __global__ void __launch_bounds__(TILE_PIX) blend_forward_kernel(
             for (int u = 0; u < 4; u++) {
                 const bool valid = k + u < cnt;
                 const int j = valid ? (int)s_list[warp][k + u] : 0;
-                const float2 c = s_xy[j];
+                const float2 c = s_xy[buf][j];
                 const float dx = c.x - pxf, dy = c.y - pyf;
-                const float4 co = s_co[j];
+                const float4 co = s_co[buf][j];
                 const float power = -0.5f * (co.x * dx * dx + co.z * dy * dy) - co.y * dx * dy;
                 const float alpha = fminf(0.99f, co.w * __expf(power));
                 a[u] = (valid && !(power > 0.f) && alpha >= 1.f / 255.f) ? alpha : 0.f;
@@ -156,7 +155,7 @@ __global__ void __launch_bounds__(TILE_PIX) blend_forward_kernel(
                 if (done || a[u] == 0.f) continue;
                 const float test_T = T * (1.f - a[u]);
                 if (test_T < 0.0001f) { done = true; continue; }
-                const float4 f = s_feat[jj[u]];
+                const float4 f = s_feat[buf][jj[u]];
                 const float w = a[u] * T;
                 C0 += f.x * w; C1 += f.y * w; C2 += f.z * w;
                 if (INVDEPTH) invd += f.w * w;
@@ -164,6 +163,7 @@ __global__ void __launch_bounds__(TILE_PIX) blend_forward_kernel(
                 last = base + (uint32_t)jj[u] + 1u;
             }
         }
+        if (next < count) park(buf ^ 1);
     }
     if (inside) {
         const size_t pid = (size_t)py * W + px, plane = (size_t)H * W;

@@ -25,7 +25,8 @@ constexpr uint32_t ST_AGG = 1u << 30, ST_INC = 2u << 30, ST_FLAGS = 3u << 30, ST
 constexpr int HIST_THREADS = 256;
 constexpr int HIST_ITEMS = 8;
 
-// exclusive scan of one value per thread over a 256-thread CTA; s_tmp needs 8 words
+// exclusive scan of one value per thread over the FIRST 256 threads of a CTA (every thread of the CTA must call it:
+// it contains barriers); s_tmp needs 8 words
 __device__ __forceinline__ uint32_t block_excl_scan_256(uint32_t v, uint32_t *s_tmp, uint32_t *total) {
     const uint32_t lane = lane_id(), warp = threadIdx.x >> 5;
     uint32_t incl = v;
@@ -35,7 +36,7 @@ __device__ __forceinline__ uint32_t block_excl_scan_256(uint32_t v, uint32_t *s_
         if (lane >= (uint32_t)d) incl += n;
     }
     __syncthreads();   // s_tmp may still be in use by a previous call
-    if (lane == 31) s_tmp[warp] = incl;
+    if (lane == 31 && warp < 8) s_tmp[warp] = incl;
     __syncthreads();
     uint32_t off = 0, tot = 0;
 #pragma unroll
@@ -73,15 +74,28 @@ __global__ void __launch_bounds__(HIST_THREADS) sort_histogram_kernel(RasterHead
         for (int i = 0; i < HIST_ITEMS; i++) {
             const uint32_t active = __ballot_sync(0xffffffffu, ok[i]);
             if (!active) continue;
+            const uint32_t lane = lane_id();
+            // Depth digits (low 32 bits): consecutive keys of one Gaussian share the depth, so only the first lane of
+            // each run counts, with the run length -- a fifth of the shared-memory atomics on typical scenes.
+            const uint32_t depth = (uint32_t)k[i];
+            const uint32_t prev = __shfl_up_sync(0xffffffffu, depth, 1);
+            const bool head = ok[i] && (lane == 0 || prev != depth);
+            const uint32_t heads = __ballot_sync(0xffffffffu, head);
+            const uint32_t above = lane == 31 ? 0u : (heads & ~((2u << lane) - 1u));
+            const uint32_t run = (above ? (uint32_t)(__ffs(above) - 1) : (uint32_t)__popc(active)) - lane;
             for (int p = 0; p < num_passes; p++) {
                 const int shift = 8 * p;
+                if (shift < 32) {
+                    if (head) atomicAdd(&s_hist[p][(depth >> shift) & 0xffu], run);
+                    continue;
+                }
+                // tile digits: neighbouring lanes hit neighbouring bins; a whole warp in one bin adds once
                 const uint32_t nb = min(8, sort_bits - shift);
                 const uint32_t d = (uint32_t)(k[i] >> shift) & ((1u << nb) - 1u);
-                // neighbouring keys often share a digit (constant exponent byte, same tile): one add per warp then
                 const uint32_t d0 = __shfl_sync(0xffffffffu, d, __ffs(active) - 1);
                 const bool uniform = __all_sync(0xffffffffu, !ok[i] || d == d0);
                 if (uniform) {
-                    if (lane_id() == (uint32_t)(__ffs(active) - 1)) atomicAdd(&s_hist[p][d0], __popc(active));
+                    if (lane == (uint32_t)(__ffs(active) - 1)) atomicAdd(&s_hist[p][d0], __popc(active));
                 } else if (ok[i]) {
                     atomicAdd(&s_hist[p][d], 1u);
                 }
@@ -184,36 +198,52 @@ __global__ void __launch_bounds__(SORT_THREADS) sort_pass_kernel(RasterHeader *h
     }
     __syncthreads();
 
-    // thread d: exclusive prefix of digit d over the warps, tile total, look-back for the global offset
+    // thread d (< 256): exclusive prefix of digit d over the warps, tile total, look-back for the global offset
     const uint32_t d = tid;
-    uint32_t total = 0;
+    uint32_t total = 0, excl = 0;
+    if (tid < 256) {
 #pragma unroll
-    for (int w = 0; w < SORT_WARPS; w++) {
-        const uint32_t c = s_whist[w * 256 + d];
-        s_whist[w * 256 + d] = total;
-        total += c;
-    }
-    const uint32_t n_invalid = SORT_TILE - n_valid;
-    const uint32_t count = total - (d == 255u ? n_invalid : 0u);   // padding sorts to the very end of digit 255
-    uint32_t *state = tile_state + ((size_t)pass * tiles_cap + tile) * 256;
-    uint32_t excl = 0;
-    if (tile == 0) {
-        st_volatile_u32(state + d, ST_INC | count);
-    } else {
-        st_volatile_u32(state + d, ST_AGG | count);
-        const uint32_t *prev = state + d - 256;
-        while (true) {
-            const uint32_t s = ld_volatile_u32(prev);
-            if ((s & ST_FLAGS) == 0) continue;
-            excl += s & ST_VALUE;
-            if ((s & ST_FLAGS) == ST_INC) break;
-            prev -= 256;
+        for (int w = 0; w < SORT_WARPS; w++) {
+            const uint32_t c = s_whist[w * 256 + d];
+            s_whist[w * 256 + d] = total;
+            total += c;
         }
-        st_volatile_u32(state + d, ST_INC | (excl + count));
+        const uint32_t n_invalid = SORT_TILE - n_valid;
+        const uint32_t count = total - (d == 255u ? n_invalid : 0u);   // padding sorts to the very end of digit 255
+        uint32_t *state = tile_state + ((size_t)pass * tiles_cap + tile) * 256;
+        if (tile == 0) {
+            st_volatile_u32(state + d, ST_INC | count);
+        } else {
+            st_volatile_u32(state + d, ST_AGG | count);
+            // Look-back, eight predecessors per round trip: all CTAs of the first wave reach this point together, so
+            // a one-at-a-time walk would be a chain of (resident CTAs) dependent L2 reads.
+            int p = (int)tile - 1;
+            bool resolved = false;
+            while (!resolved) {
+                uint32_t sv[8];
+#pragma unroll
+                for (int u = 0; u < 8; u++)
+                    sv[u] = p - u >= 0 ? ld_volatile_u32(state + d - (size_t)256 * (tile - (uint32_t)(p - u))) : ST_INC;
+                int used = 0;
+#pragma unroll
+                for (int u = 0; u < 8; u++) {
+                    if (resolved || used != u) continue;       // stop at the first inclusive word or unready word
+                    const uint32_t f = sv[u] & ST_FLAGS;
+                    if (f == 0) continue;                       // not published yet: retry from here
+                    excl += sv[u] & ST_VALUE;
+                    used = u + 1;
+                    if (f == ST_INC) resolved = true;
+                }
+                p -= used;
+            }
+            st_volatile_u32(state + d, ST_INC | (excl + count));
+        }
     }
     const uint32_t start = block_excl_scan_256(total, s_misc, nullptr);
-    s_start[d] = start;
-    s_gbase[d] = bins[pass * 256 + d] + excl - start;
+    if (tid < 256) {
+        s_start[d] = start;
+        s_gbase[d] = bins[pass * 256 + d] + excl - start;
+    }
     __syncthreads();
 
     // reorder inside the tile
