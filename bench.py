@@ -26,6 +26,12 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
+os.environ["NCCL_DEBUG"] = os.environ.get("D3GA_NCCL_DEBUG", "WARN")   # keep NCCL's banner off stdout: ONE JSON line
+if "reference" in sys.argv:
+    # the CPU arm uses every host thread it can (torchrun exports OMP_NUM_THREADS=1 for its workers); must be set
+    # before numpy / torch / the oracle's libgomp are loaded
+    os.environ["OMP_NUM_THREADS"] = str(os.cpu_count() or 1)
+
 import numpy as np  # noqa: E402
 
 METRIC = "fwd+bwd views/s"
