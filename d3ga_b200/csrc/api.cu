@@ -26,7 +26,7 @@ static std::vector<ProfRec> g_prof_recs;
 static const char *const g_kernel_names[K_COUNT] = {
     "geometry_kernel", "sort_histogram_kernel", "sort_pass_kernel", "tile_ranges_kernel", "blend_forward_kernel",
     "blend_backward_kernel", "preprocess_backward_kernel", "deform_forward_kernel", "deform_backward_kernel",
-    "compute_bary_kernel"};
+    "compute_bary_kernel", "segment_sort_kernel"};
 
 bool profiling_enabled() { return g_prof_on.load(std::memory_order_relaxed) != 0; }
 

@@ -101,7 +101,7 @@ constexpr int GRAD_ACC_FLOATS = 12;
 // ---- host-side helpers -----------------------------------------------------------------------------------------
 enum KernelId {
     K_GEOMETRY = 0, K_SORT_HIST, K_SORT_PASS, K_RANGES, K_BLEND_FWD, K_BLEND_BWD, K_PRE_BWD, K_DEFORM_FWD, K_DEFORM_BWD,
-    K_BARY, K_COUNT
+    K_BARY, K_SEG_SORT, K_COUNT
 };
 // Optional per-kernel CUDA-event timing (d3ga_profile_* in the C-ABI; bench.py's roofline figures come from it).
 // A no-op unless profiling is enabled.
@@ -135,6 +135,8 @@ int launch_geometry(int P, int sh_degree, int sh_coeffs, const float *means3D, c
                     uint64_t capacity, int32_t *radii, cudaStream_t stream);
 int launch_sort_and_ranges(uint8_t *geom, uint8_t *binning, const BinLayout &BL, uint64_t capacity, int sort_bits,
                            uint8_t *image, const ImgLayout &IL, int num_tiles, cudaStream_t stream);
+int launch_segment_sort(uint8_t *geom, uint8_t *binning, const BinLayout &BL, uint8_t *image, const ImgLayout &IL,
+                        int num_tiles, cudaStream_t stream);
 int launch_blend_forward(int W, int H, const float *background, const float *colors, const uint8_t *geom,
                          const GeomLayout &GL, const uint8_t *binning, const BinLayout &BL, uint8_t *image,
                          const ImgLayout &IL, float *out_color, float *out_invdepth, cudaStream_t stream);
@@ -159,6 +161,19 @@ __device__ __forceinline__ uint32_t lanemask_lt() {
     uint32_t m;
     asm("mov.u32 %0, %%lanemask_lt;" : "=r"(m));
     return m;
+}
+// Lanes holding the same 8-bit digit.  Eight ballots + logic instead of MATCH.ANY: on sm_100 the match instruction is
+// issued through the MIO queue and throttles a ranking loop (ncu: stall_mio on every MATCH.ANY), ballots are plain
+// ALU-side votes.
+__device__ __forceinline__ uint32_t match_digit8(uint32_t d) {
+    uint32_t peers = 0xffffffffu;
+#pragma unroll
+    for (int b = 0; b < 8; b++) {
+        const bool bit = (d >> b) & 1u;
+        const uint32_t m = __ballot_sync(0xffffffffu, bit);
+        peers &= bit ? m : ~m;
+    }
+    return peers;
 }
 __device__ __forceinline__ uint32_t ld_volatile_u32(const uint32_t *p) {
     uint32_t v;

@@ -16,6 +16,10 @@ namespace d3ga {
 
 namespace {
 
+#ifndef DEFORM_BWD_MIN_CTAS
+#define DEFORM_BWD_MIN_CTAS 3
+#endif
+
 struct Tet4 {
     float v[4][3];
 };
@@ -83,115 +87,156 @@ __global__ void __launch_bounds__(GEO_THREADS) deform_forward_kernel(
             cov3D[6 * (size_t)n + o++] = B[i][0] * B[j][0] + B[i][1] * B[j][1] + B[i][2] * B[j][2];
 }
 
-__global__ void __launch_bounds__(GEO_THREADS) deform_backward_kernel(
+// Warp-level segmented sum over runs of equal tet id (lanes are tet-sorted), then one set of 12 atomics per run.
+// Every lane of the warp calls it from the same place (full-mask shuffles); lanes without a contribution pass zeros.
+__device__ __forceinline__ void segmented_vertex_scatter(int64_t t, const int64_t (&vid)[4], float (&v)[12],
+                                                         float *__restrict__ dL_dtetpoints) {
+    const uint32_t lane = threadIdx.x & 31;
+    const int64_t tprev = __shfl_up_sync(0xffffffffu, t, 1);
+    const bool head = lane == 0 || t != tprev;
+    const uint32_t heads = __ballot_sync(0xffffffffu, head);
+#pragma unroll
+    for (int off = 1; off < 32; off <<= 1) {
+        // lane may absorb lane+off iff no run starts in (lane, lane+off]
+        const bool take = lane + off < 32 && ((heads >> (lane + 1)) & ((1u << off) - 1u)) == 0u;
+#pragma unroll
+        for (int k = 0; k < 12; k++) {
+            const float o = __shfl_down_sync(0xffffffffu, v[k], off);
+            if (take) v[k] += o;
+        }
+    }
+    if (head) {
+#pragma unroll
+        for (int k = 0; k < 4; k++)
+#pragma unroll
+            for (int c = 0; c < 3; c++)
+                if (v[3 * k + c] != 0.f) atomicAdd(dL_dtetpoints + 3 * vid[k] + c, v[3 * k + c]);
+    }
+}
+
+__global__ void __launch_bounds__(GEO_THREADS, DEFORM_BWD_MIN_CTAS) deform_backward_kernel(
     int N, int T, const float *__restrict__ tetpoints, const int64_t *__restrict__ tets,
     const int64_t *__restrict__ tetra_id, const float *__restrict__ barys, const float *__restrict__ cgrad,
     const float *__restrict__ scales, const float *__restrict__ rotation, const float *__restrict__ dL_dmeans,
     const float *__restrict__ dL_dcov, float *__restrict__ dL_dtetpoints, float *__restrict__ dL_dbarys,
-    float *__restrict__ dL_dscales, float *__restrict__ dL_drotation) {
-    const int n = blockIdx.x * GEO_THREADS + threadIdx.x;
-    if (n >= N) return;
-    int64_t t = tetra_id[n];
-    if (t < 0) t += T;
-    int64_t vid[4];
-    Tet4 X;
-    load_tet(tetpoints, tets, t, vid, X);
-    const float4 b = *reinterpret_cast<const float4 *>(barys + 4 * (size_t)n);
-    const float bw[4] = {b.x, b.y, b.z, b.w};
-    const float dm[3] = {dL_dmeans[3 * (size_t)n], dL_dmeans[3 * (size_t)n + 1], dL_dmeans[3 * (size_t)n + 2]};
-    float g6[6];
+    float *__restrict__ dL_dscales, float *__restrict__ dL_drotation, const int32_t *__restrict__ order) {
+    const int i = blockIdx.x * GEO_THREADS + threadIdx.x;
+    const bool live = i < N;
+    // With `order` (a permutation that sorts tetra_id) neighbouring lanes share tets: their cage-vertex gradients are
+    // summed inside the warp and one lane per tet issues the atomics (~N/T times fewer L2 atomics).
+    const int n = live ? (order ? order[i] : i) : 0;
+    int64_t t = -1 - (int64_t)(threadIdx.x & 31);   // dead lanes: distinct keys, never merged with anything
+    int64_t vid[4] = {0, 0, 0, 0};
+    float dvf[12];
 #pragma unroll
-    for (int k = 0; k < 6; k++) g6[k] = dL_dcov[6 * (size_t)n + k];
+    for (int k = 0; k < 12; k++) dvf[k] = 0.f;
 
-    // recompute the forward
-    float G[3][3], Cg[3][3], J[3][3];
+    if (live) {
+        t = tetra_id[n];
+        if (t < 0) t += T;
+        Tet4 X;
+        load_tet(tetpoints, tets, t, vid, X);
+        const float4 b = *reinterpret_cast<const float4 *>(barys + 4 * (size_t)n);
+        const float bw[4] = {b.x, b.y, b.z, b.w};
+        const float dm[3] = {dL_dmeans[3 * (size_t)n], dL_dmeans[3 * (size_t)n + 1], dL_dmeans[3 * (size_t)n + 2]};
+        float g6[6];
 #pragma unroll
-    for (int i = 0; i < 3; i++) {
-        G[i][0] = X.v[3][i] - X.v[0][i]; G[i][1] = X.v[2][i] - X.v[0][i]; G[i][2] = X.v[1][i] - X.v[0][i];
-    }
+        for (int k = 0; k < 6; k++) g6[k] = dL_dcov[6 * (size_t)n + k];
+
+        // recompute the forward
+        float G[3][3], Cg[3][3], J[3][3];
 #pragma unroll
-    for (int k = 0; k < 9; k++) Cg[k / 3][k % 3] = cgrad[9 * (size_t)n + k];
+        for (int r = 0; r < 3; r++) {
+            G[r][0] = X.v[3][r] - X.v[0][r]; G[r][1] = X.v[2][r] - X.v[0][r]; G[r][2] = X.v[1][r] - X.v[0][r];
+        }
 #pragma unroll
-    for (int i = 0; i < 3; i++)
+        for (int k = 0; k < 9; k++) Cg[k / 3][k % 3] = cgrad[9 * (size_t)n + k];
 #pragma unroll
-        for (int j = 0; j < 3; j++) J[i][j] = G[i][0] * Cg[0][j] + G[i][1] * Cg[1][j] + G[i][2] * Cg[2][j];
-    const float4 q = *reinterpret_cast<const float4 *>(rotation + 4 * (size_t)n);
-    const float inv = 1.f / sqrtf(q.x * q.x + q.y * q.y + q.z * q.z + q.w * q.w);
-    const float qr = q.x * inv, qx = q.y * inv, qy = q.z * inv, qz = q.w * inv;
-    float Rm[3][3];
-    rotation_from_unit_quat(qr, qx, qy, qz, Rm);
-    const float s[3] = {scales[3 * (size_t)n], scales[3 * (size_t)n + 1], scales[3 * (size_t)n + 2]};
-    float JR[3][3], B[3][3];
+        for (int r = 0; r < 3; r++)
 #pragma unroll
-    for (int i = 0; i < 3; i++)
+            for (int j = 0; j < 3; j++) J[r][j] = G[r][0] * Cg[0][j] + G[r][1] * Cg[1][j] + G[r][2] * Cg[2][j];
+        const float4 q = *reinterpret_cast<const float4 *>(rotation + 4 * (size_t)n);
+        const float inv = 1.f / sqrtf(q.x * q.x + q.y * q.y + q.z * q.z + q.w * q.w);
+        const float qr = q.x * inv, qx = q.y * inv, qy = q.z * inv, qz = q.w * inv;
+        float Rm[3][3];
+        rotation_from_unit_quat(qr, qx, qy, qz, Rm);
+        const float s[3] = {scales[3 * (size_t)n], scales[3 * (size_t)n + 1], scales[3 * (size_t)n + 2]};
+        float JR[3][3], B[3][3];
+#pragma unroll
+        for (int r = 0; r < 3; r++)
+#pragma unroll
+            for (int k = 0; k < 3; k++) {
+                JR[r][k] = J[r][0] * Rm[0][k] + J[r][1] * Rm[1][k] + J[r][2] * Rm[2][k];
+                B[r][k] = JR[r][k] * s[k];
+            }
+        // cov = B B^T, only the upper triangle is an output: dB = (D + D^T) B with D the upper-triangular gradient
+        const float Ds[3][3] = {{2.f * g6[0], g6[1], g6[2]}, {g6[1], 2.f * g6[3], g6[4]}, {g6[2], g6[4], 2.f * g6[5]}};
+        float dB[3][3];
+#pragma unroll
+        for (int r = 0; r < 3; r++)
+#pragma unroll
+            for (int k = 0; k < 3; k++) dB[r][k] = Ds[r][0] * B[0][k] + Ds[r][1] * B[1][k] + Ds[r][2] * B[2][k];
+        // B = (J R) diag(s)
+        float ds[3], dJR[3][3];
 #pragma unroll
         for (int k = 0; k < 3; k++) {
-            JR[i][k] = J[i][0] * Rm[0][k] + J[i][1] * Rm[1][k] + J[i][2] * Rm[2][k];
-            B[i][k] = JR[i][k] * s[k];
+            ds[k] = dB[0][k] * JR[0][k] + dB[1][k] * JR[1][k] + dB[2][k] * JR[2][k];
+#pragma unroll
+            for (int r = 0; r < 3; r++) dJR[r][k] = dB[r][k] * s[k];
         }
-    // cov = B B^T, only the upper triangle is an output: dB = (D + D^T) B with D the upper-triangular gradient
-    const float Ds[3][3] = {{2.f * g6[0], g6[1], g6[2]}, {g6[1], 2.f * g6[3], g6[4]}, {g6[2], g6[4], 2.f * g6[5]}};
-    float dB[3][3];
+        // JR = J R : dJ = dJR R^T, dR = J^T dJR
+        float dJ[3][3], A[3][3];
 #pragma unroll
-    for (int i = 0; i < 3; i++)
+        for (int r = 0; r < 3; r++)
 #pragma unroll
-        for (int k = 0; k < 3; k++) dB[i][k] = Ds[i][0] * B[0][k] + Ds[i][1] * B[1][k] + Ds[i][2] * B[2][k];
-    // B = (J R) diag(s)
-    float ds[3], dJR[3][3];
+            for (int j = 0; j < 3; j++) {
+                dJ[r][j] = dJR[r][0] * Rm[j][0] + dJR[r][1] * Rm[j][1] + dJR[r][2] * Rm[j][2];
+                A[r][j] = J[0][r] * dJR[0][j] + J[1][r] * dJR[1][j] + J[2][r] * dJR[2][j];
+            }
+        if (dL_dscales) {
 #pragma unroll
-    for (int k = 0; k < 3; k++) {
-        ds[k] = dB[0][k] * JR[0][k] + dB[1][k] * JR[1][k] + dB[2][k] * JR[2][k];
-#pragma unroll
-        for (int i = 0; i < 3; i++) dJR[i][k] = dB[i][k] * s[k];
-    }
-    // JR = J R : dJ = dJR R^T, dR = J^T dJR
-    float dJ[3][3], A[3][3];
-#pragma unroll
-    for (int i = 0; i < 3; i++)
-#pragma unroll
-        for (int j = 0; j < 3; j++) {
-            dJ[i][j] = dJR[i][0] * Rm[j][0] + dJR[i][1] * Rm[j][1] + dJR[i][2] * Rm[j][2];
-            A[i][j] = J[0][i] * dJR[0][j] + J[1][i] * dJR[1][j] + J[2][i] * dJR[2][j];
+            for (int k = 0; k < 3; k++) dL_dscales[3 * (size_t)n + k] = ds[k];
         }
-    if (dL_dscales) {
-#pragma unroll
-        for (int k = 0; k < 3; k++) dL_dscales[3 * (size_t)n + k] = ds[k];
-    }
-    if (dL_drotation) {
-        const float r = qr, x = qx, y = qy, z = qz;
-        float dq[4];
-        dq[0] = 2.f * (-z * A[0][1] + y * A[0][2] + z * A[1][0] - x * A[1][2] - y * A[2][0] + x * A[2][1]);
-        dq[1] = 2.f * (y * A[0][1] + z * A[0][2] + y * A[1][0] - 2.f * x * A[1][1] - r * A[1][2] + z * A[2][0] + r * A[2][1] - 2.f * x * A[2][2]);
-        dq[2] = 2.f * (-2.f * y * A[0][0] + x * A[0][1] + r * A[0][2] + x * A[1][0] + z * A[1][2] - r * A[2][0] + z * A[2][1] - 2.f * y * A[2][2]);
-        dq[3] = 2.f * (-2.f * z * A[0][0] - r * A[0][1] + x * A[0][2] + r * A[1][0] - 2.f * z * A[1][1] + y * A[1][2] + x * A[2][0] + y * A[2][1]);
-        // through q / |q|
-        const float dotp = r * dq[0] + x * dq[1] + y * dq[2] + z * dq[3];
-        *reinterpret_cast<float4 *>(dL_drotation + 4 * (size_t)n) =
-            make_float4((dq[0] - r * dotp) * inv, (dq[1] - x * dotp) * inv, (dq[2] - y * dotp) * inv, (dq[3] - z * dotp) * inv);
-    }
-    if (dL_dbarys) {
-        float db[4];
-#pragma unroll
-        for (int k = 0; k < 4; k++) db[k] = X.v[k][0] * dm[0] + X.v[k][1] * dm[1] + X.v[k][2] * dm[2];
-        *reinterpret_cast<float4 *>(dL_dbarys + 4 * (size_t)n) = make_float4(db[0], db[1], db[2], db[3]);
-    }
-    if (dL_dtetpoints) {
-        // J = G Cg : dG = dJ Cg^T ; columns of G are (v3-v0, v2-v0, v1-v0)
-        float dv[4][3];
-#pragma unroll
-        for (int i = 0; i < 3; i++) {
-            const float g0 = dJ[i][0] * Cg[0][0] + dJ[i][1] * Cg[0][1] + dJ[i][2] * Cg[0][2];
-            const float g1 = dJ[i][0] * Cg[1][0] + dJ[i][1] * Cg[1][1] + dJ[i][2] * Cg[1][2];
-            const float g2 = dJ[i][0] * Cg[2][0] + dJ[i][1] * Cg[2][1] + dJ[i][2] * Cg[2][2];
-            dv[3][i] = g0 + bw[3] * dm[i];
-            dv[2][i] = g1 + bw[2] * dm[i];
-            dv[1][i] = g2 + bw[1] * dm[i];
-            dv[0][i] = -(g0 + g1 + g2) + bw[0] * dm[i];
+        if (dL_drotation) {
+            const float r = qr, x = qx, y = qy, z = qz;
+            float dq[4];
+            dq[0] = 2.f * (-z * A[0][1] + y * A[0][2] + z * A[1][0] - x * A[1][2] - y * A[2][0] + x * A[2][1]);
+            dq[1] = 2.f * (y * A[0][1] + z * A[0][2] + y * A[1][0] - 2.f * x * A[1][1] - r * A[1][2] + z * A[2][0] + r * A[2][1] - 2.f * x * A[2][2]);
+            dq[2] = 2.f * (-2.f * y * A[0][0] + x * A[0][1] + r * A[0][2] + x * A[1][0] + z * A[1][2] - r * A[2][0] + z * A[2][1] - 2.f * y * A[2][2]);
+            dq[3] = 2.f * (-2.f * z * A[0][0] - r * A[0][1] + x * A[0][2] + r * A[1][0] - 2.f * z * A[1][1] + y * A[1][2] + x * A[2][0] + y * A[2][1]);
+            // through q / |q|
+            const float dotp = r * dq[0] + x * dq[1] + y * dq[2] + z * dq[3];
+            *reinterpret_cast<float4 *>(dL_drotation + 4 * (size_t)n) =
+                make_float4((dq[0] - r * dotp) * inv, (dq[1] - x * dotp) * inv, (dq[2] - y * dotp) * inv, (dq[3] - z * dotp) * inv);
         }
+        if (dL_dbarys) {
+            float db[4];
+#pragma unroll
+            for (int k = 0; k < 4; k++) db[k] = X.v[k][0] * dm[0] + X.v[k][1] * dm[1] + X.v[k][2] * dm[2];
+            *reinterpret_cast<float4 *>(dL_dbarys + 4 * (size_t)n) = make_float4(db[0], db[1], db[2], db[3]);
+        }
+        if (dL_dtetpoints) {
+            // J = G Cg : dG = dJ Cg^T ; columns of G are (v3-v0, v2-v0, v1-v0)
+#pragma unroll
+            for (int r = 0; r < 3; r++) {
+                const float g0 = dJ[r][0] * Cg[0][0] + dJ[r][1] * Cg[0][1] + dJ[r][2] * Cg[0][2];
+                const float g1 = dJ[r][0] * Cg[1][0] + dJ[r][1] * Cg[1][1] + dJ[r][2] * Cg[1][2];
+                const float g2 = dJ[r][0] * Cg[2][0] + dJ[r][1] * Cg[2][1] + dJ[r][2] * Cg[2][2];
+                dvf[9 + r] = g0 + bw[3] * dm[r];
+                dvf[6 + r] = g1 + bw[2] * dm[r];
+                dvf[3 + r] = g2 + bw[1] * dm[r];
+                dvf[0 + r] = -(g0 + g1 + g2) + bw[0] * dm[r];
+            }
+        }
+    }
+    if (!dL_dtetpoints) return;
+    if (order) {
+        segmented_vertex_scatter(t, vid, dvf, dL_dtetpoints);   // every lane, one call site
+    } else if (live) {
 #pragma unroll
         for (int k = 0; k < 4; k++)
 #pragma unroll
-            for (int c = 0; c < 3; c++) atomicAdd(dL_dtetpoints + 3 * vid[k] + c, dv[k][c]);
+            for (int c = 0; c < 3; c++) atomicAdd(dL_dtetpoints + 3 * vid[k] + c, dvf[3 * k + c]);
     }
 }
 
@@ -215,11 +260,11 @@ extern "C" int d3ga_deform_forward(int N, int V, int T, const float *tetpoints, 
     return D3GA_OK;
 }
 
-extern "C" int d3ga_deform_backward(int N, int V, int T, const float *tetpoints, const int64_t *tets,
-                                    const int64_t *tetra_id, const float *barys, const float *canonical_gradient,
-                                    const float *scales, const float *rotation, const float *dL_dmeans3D,
-                                    const float *dL_dcov3D, float *dL_dtetpoints, float *dL_dbarys, float *dL_dscales,
-                                    float *dL_drotation, d3ga_stream_t stream) {
+static int deform_backward_impl(int N, int V, int T, const float *tetpoints, const int64_t *tets,
+                                const int64_t *tetra_id, const float *barys, const float *canonical_gradient,
+                                const float *scales, const float *rotation, const float *dL_dmeans3D,
+                                const float *dL_dcov3D, float *dL_dtetpoints, float *dL_dbarys, float *dL_dscales,
+                                float *dL_drotation, const int32_t *order, d3ga_stream_t stream) {
     if (N < 0 || V <= 0 || T <= 0) return D3GA_EINVAL;
     if (N == 0) return D3GA_OK;
     if (!tetpoints || !tets || !tetra_id || !barys || !canonical_gradient || !scales || !rotation || !dL_dmeans3D ||
@@ -228,7 +273,29 @@ extern "C" int d3ga_deform_backward(int N, int V, int T, const float *tetpoints,
     ProfScope prof(K_DEFORM_BWD, (cudaStream_t)stream);
     deform_backward_kernel<<<(N + GEO_THREADS - 1) / GEO_THREADS, GEO_THREADS, 0, (cudaStream_t)stream>>>(
         N, T, tetpoints, tets, tetra_id, barys, canonical_gradient, scales, rotation, dL_dmeans3D, dL_dcov3D,
-        dL_dtetpoints, dL_dbarys, dL_dscales, dL_drotation);
+        dL_dtetpoints, dL_dbarys, dL_dscales, dL_drotation, order);
     D3GA_LAUNCH_CHECK();
     return D3GA_OK;
+}
+
+extern "C" int d3ga_deform_backward(int N, int V, int T, const float *tetpoints, const int64_t *tets,
+                                    const int64_t *tetra_id, const float *barys, const float *canonical_gradient,
+                                    const float *scales, const float *rotation, const float *dL_dmeans3D,
+                                    const float *dL_dcov3D, float *dL_dtetpoints, float *dL_dbarys, float *dL_dscales,
+                                    float *dL_drotation, d3ga_stream_t stream) {
+    return deform_backward_impl(N, V, T, tetpoints, tets, tetra_id, barys, canonical_gradient, scales, rotation,
+                                dL_dmeans3D, dL_dcov3D, dL_dtetpoints, dL_dbarys, dL_dscales, dL_drotation, nullptr,
+                                stream);
+}
+
+extern "C" int d3ga_deform_backward_ordered(int N, int V, int T, const float *tetpoints, const int64_t *tets,
+                                            const int64_t *tetra_id, const float *barys,
+                                            const float *canonical_gradient, const float *scales,
+                                            const float *rotation, const float *dL_dmeans3D, const float *dL_dcov3D,
+                                            float *dL_dtetpoints, float *dL_dbarys, float *dL_dscales,
+                                            float *dL_drotation, const int32_t *order, d3ga_stream_t stream) {
+    if (!order) return D3GA_EINVAL;
+    return deform_backward_impl(N, V, T, tetpoints, tets, tetra_id, barys, canonical_gradient, scales, rotation,
+                                dL_dmeans3D, dL_dcov3D, dL_dtetpoints, dL_dbarys, dL_dscales, dL_drotation, order,
+                                stream);
 }

@@ -19,9 +19,15 @@
 //            (pixel, Gaussian).
 // Algorithmic bytes: forward 40 B per duplicate + 20 B per pixel; backward 40 B read + 40 B gradient RMW per
 // duplicate + 20 B per pixel.  Both kernels are FP32/SFU bound rather than HBM bound.
+#include <cstdlib>
+
 #include "common.cuh"
 
 namespace d3ga {
+
+#ifdef D3GA_DEBUG_TIMING
+__device__ unsigned long long *g_dbg_buf = nullptr;   // [tiles][4]: tile, cycles, smid, max warp entries
+#endif
 
 namespace {
 
@@ -78,6 +84,10 @@ __global__ void __launch_bounds__(TILE_PIX) blend_forward_kernel(
 
     const uint32_t tile = order_fwd[blockIdx.x];   // longest Gaussian list first
     const int tid = threadIdx.x;
+#ifdef D3GA_DEBUG_TIMING
+    const long long dbg_t0 = clock64();
+    unsigned dbg_entries = 0, dbg_batches = 0;
+#endif
     const uint32_t lane = tid & 31, warp = tid >> 5;
     const WarpBlock wb = warp_block(tid, (int)(tile % (uint32_t)grid_x), (int)(tile / (uint32_t)grid_x));
     const int px = wb.px, py = wb.py;
@@ -131,6 +141,9 @@ __global__ void __launch_bounds__(TILE_PIX) blend_forward_kernel(
             cnt += __popc(m);
         }
         __syncwarp();
+#ifdef D3GA_DEBUG_TIMING
+        dbg_entries += cnt; dbg_batches++;
+#endif
         const uint32_t base = (uint32_t)i * BATCH;
         // four list entries at a time: their alphas are independent (instruction-level parallelism for the warp
         // that sits on the tile's critical path); only the transmittance update is sequential
@@ -174,6 +187,21 @@ __global__ void __launch_bounds__(TILE_PIX) blend_forward_kernel(
         out_color[2 * plane + pid] = C2 + T * bg[2];
         if (INVDEPTH) out_invdepth[pid] = invd;
     }
+#ifdef D3GA_DEBUG_TIMING
+    if (g_dbg_buf) {
+        const unsigned emax = __reduce_max_sync(0xffffffffu, dbg_entries);
+        __shared__ unsigned s_dbg[8];
+        if (lane == 0) s_dbg[warp] = emax;
+        __syncthreads();
+        if (tid == 0) {
+            unsigned m = 0, sm;
+            for (int w = 0; w < 8; w++) m = max(m, s_dbg[w]);
+            asm("mov.u32 %0, %%smid;" : "=r"(sm));
+            unsigned long long *o = g_dbg_buf + 6 * (size_t)blockIdx.x;
+            o[0] = tile; o[1] = (unsigned long long)(clock64() - dbg_t0); o[2] = sm; o[3] = m; o[4] = count; o[5] = dbg_batches;
+        }
+    }
+#endif
     // deepest contributor of the tile = how far the backward has to go; the last CTA orders the backward's tiles
     const uint32_t wmax = __reduce_max_sync(0xffffffffu, inside ? last : 0u);
     if (lane == 0) s_red[warp] = wmax;
@@ -385,6 +413,24 @@ __global__ void __launch_bounds__(TILE_PIX) blend_backward_kernel(
 
 }  // namespace
 
+#ifdef D3GA_DEBUG_TIMING
+extern "C" int d3ga_debug_set_buffer(void *p) {
+    unsigned long long *v = (unsigned long long *)p;
+    return cudaMemcpyToSymbol(g_dbg_buf, &v, sizeof(v)) == cudaSuccess ? 0 : -2;
+}
+#endif
+
+// Residency limiter (tuning knob): extra dynamic shared memory so that at most `ctas_per_sm` CTAs share an SM.
+static int dyn_smem_for_residency(int ctas_per_sm, int static_bytes) {
+    if (ctas_per_sm <= 0) return 0;
+    const int budget = 227 * 1024 / ctas_per_sm - static_bytes - 1024;
+    return budget > 0 ? budget : 0;
+}
+static int env_int(const char *name, int dflt) {
+    const char *v = getenv(name);
+    return v ? atoi(v) : dflt;
+}
+
 int launch_blend_forward(int W, int H, const float *background, const float *colors, const uint8_t *geom,
                          const GeomLayout &GL, const uint8_t *binning, const BinLayout &BL, uint8_t *image,
                          const ImgLayout &IL, float *out_color, float *out_invdepth, cudaStream_t stream) {
@@ -402,13 +448,20 @@ int launch_blend_forward(int W, int H, const float *background, const float *col
     const uint32_t *order_fwd = reinterpret_cast<const uint32_t *>(image + IL.order_fwd);
     uint32_t *order_bwd = reinterpret_cast<uint32_t *>(image + IL.order_bwd);
     uint32_t *tile_nproc = reinterpret_cast<uint32_t *>(image + IL.tile_nproc);
+    static const int dyn = dyn_smem_for_residency(env_int("D3GA_BLEND_FWD_CTAS", 0), 32 * 1024);
+    static bool attr_set = false;
+    if (dyn > 0 && !attr_set) {
+        cudaFuncSetAttribute(blend_forward_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn);
+        cudaFuncSetAttribute(blend_forward_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn);
+        attr_set = true;
+    }
     ProfScope prof(K_BLEND_FWD, stream);
     if (out_invdepth)
-        blend_forward_kernel<true><<<num_tiles, TILE_PIX, 0, stream>>>(
+        blend_forward_kernel<true><<<num_tiles, TILE_PIX, dyn, stream>>>(
             hdr, ranges, v0, v1, W, H, xy, co, colors, depth, background, final_T, n_contrib, out_color, out_invdepth,
             hdr_rw, gx, num_tiles, order_fwd, tile_nproc, order_bwd);
     else
-        blend_forward_kernel<false><<<num_tiles, TILE_PIX, 0, stream>>>(
+        blend_forward_kernel<false><<<num_tiles, TILE_PIX, dyn, stream>>>(
             hdr, ranges, v0, v1, W, H, xy, co, colors, depth, background, final_T, n_contrib, out_color, nullptr,
             hdr_rw, gx, num_tiles, order_fwd, tile_nproc, order_bwd);
     D3GA_LAUNCH_CHECK();
@@ -430,13 +483,20 @@ int launch_blend_backward(int W, int H, const float *background, const float *co
     const float *final_T = reinterpret_cast<const float *>(image + IL.final_T);
     const uint32_t *n_contrib = reinterpret_cast<const uint32_t *>(image + IL.n_contrib);
     const uint32_t *order_bwd = reinterpret_cast<const uint32_t *>(image + IL.order_bwd);
+    static const int dyn = dyn_smem_for_residency(env_int("D3GA_BLEND_BWD_CTAS", 0), 33 * 1024);
+    static bool attr_set = false;
+    if (dyn > 0 && !attr_set) {
+        cudaFuncSetAttribute(blend_backward_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn);
+        cudaFuncSetAttribute(blend_backward_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn);
+        attr_set = true;
+    }
     ProfScope prof(K_BLEND_BWD, stream);
     if (dL_dinvdepth_pix)
-        blend_backward_kernel<true><<<num_tiles, TILE_PIX, 0, stream>>>(
+        blend_backward_kernel<true><<<num_tiles, TILE_PIX, dyn, stream>>>(
             hdr, ranges, v0, v1, W, H, background, xy, co, colors, depth, final_T, n_contrib, dL_dpix, dL_dinvdepth_pix,
             grad_acc, gx, order_bwd);
     else
-        blend_backward_kernel<false><<<num_tiles, TILE_PIX, 0, stream>>>(
+        blend_backward_kernel<false><<<num_tiles, TILE_PIX, dyn, stream>>>(
             hdr, ranges, v0, v1, W, H, background, xy, co, colors, depth, final_T, n_contrib, dL_dpix, nullptr, grad_acc,
             gx, order_bwd);
     D3GA_LAUNCH_CHECK();

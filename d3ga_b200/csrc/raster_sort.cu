@@ -15,6 +15,9 @@
 //      equal digits with coalesced stores.  HBM traffic per pass: 12 B read + 12 B written per pair.
 //   3. ranges: neighbour compare of key >> 32 on the sorted list.
 // Algorithmic bytes: 8 D (histogram) + 24 D per executed pass + 8 D + 8 Tl (ranges).
+#include <cstdlib>
+#include <cstring>
+
 #include "common.cuh"
 
 namespace d3ga {
@@ -51,7 +54,7 @@ __device__ __forceinline__ uint32_t block_excl_scan_256(uint32_t v, uint32_t *s_
 
 __global__ void __launch_bounds__(HIST_THREADS) sort_histogram_kernel(RasterHeader *hdr, const uint64_t *keys,
                                                                       uint32_t *ghist, uint32_t *bins, int sort_bits,
-                                                                      int num_passes) {
+                                                                      int num_passes, int first_pass) {
     __shared__ uint32_t s_hist[SORT_MAX_PASSES][256];
     __shared__ uint32_t s_tmp[8];
     __shared__ uint32_t s_flag;
@@ -83,7 +86,7 @@ __global__ void __launch_bounds__(HIST_THREADS) sort_histogram_kernel(RasterHead
             const uint32_t heads = __ballot_sync(0xffffffffu, head);
             const uint32_t above = lane == 31 ? 0u : (heads & ~((2u << lane) - 1u));
             const uint32_t run = (above ? (uint32_t)(__ffs(above) - 1) : (uint32_t)__popc(active)) - lane;
-            for (int p = 0; p < num_passes; p++) {
+            for (int p = first_pass; p < num_passes; p++) {
                 const int shift = 8 * p;
                 if (shift < 32) {
                     if (head) atomicAdd(&s_hist[p][(depth >> shift) & 0xffu], run);
@@ -117,7 +120,8 @@ __global__ void __launch_bounds__(HIST_THREADS) sort_histogram_kernel(RasterHead
     uint32_t src = 0;
     for (int p = 0; p < num_passes; p++) {
         const uint32_t c = __ldcg(ghist + p * 256 + tid);
-        const int all_in_one = __syncthreads_or(D == 0 || c == D);
+        // passes below first_pass (the depth digits) are left to the per-tile shared-memory sort
+        const int all_in_one = __syncthreads_or(D == 0 || c == D || p < first_pass);
         const uint32_t ex = block_excl_scan_256(c, s_tmp, nullptr);
         bins[p * 256 + tid] = ex;
         if (tid == 0) {
@@ -184,16 +188,24 @@ __global__ void __launch_bounds__(SORT_THREADS) sort_pass_kernel(RasterHeader *h
         val[r] = ok ? __ldcs(vin + tile_base + local) : 0u;
     }
     __syncwarp();
-    uint32_t rank[SORT_ITEMS];
+    uint32_t rank[SORT_ITEMS];   // holds the peer mask between the two phases
+    // phase 1: digit groups per round (independent across rounds: the match latencies overlap)
 #pragma unroll
     for (int r = 0; r < SORT_ITEMS; r++) {
         const uint32_t local = chunk + r * 32 + lane;
         const uint32_t d = local < n_valid ? ((uint32_t)(key[r] >> shift) & mask) : 255u;
-        const uint32_t peers = __match_any_sync(0xffffffffu, d);
-        const uint32_t pre = wh[d];
-        __syncwarp();
-        if (lane == 31u - (uint32_t)__clz(peers)) wh[d] = pre + __popc(peers);
-        __syncwarp();
+        rank[r] = __match_any_sync(0xffffffffu, d);   // peer mask for now
+    }
+    // phase 2: one shared-memory atomic per digit group and round, in round order (stable), broadcast to the group
+#pragma unroll
+    for (int r = 0; r < SORT_ITEMS; r++) {
+        const uint32_t local = chunk + r * 32 + lane;
+        const uint32_t d = local < n_valid ? ((uint32_t)(key[r] >> shift) & mask) : 255u;
+        const uint32_t peers = rank[r];
+        const uint32_t leader = 31u - (uint32_t)__clz(peers);
+        uint32_t pre = 0;
+        if (lane == leader) pre = atomicAdd(&wh[d], (uint32_t)__popc(peers));
+        pre = __shfl_sync(0xffffffffu, pre, leader);
         rank[r] = pre + __popc(peers & lanemask_lt());
     }
     __syncthreads();
@@ -317,6 +329,11 @@ int launch_sort_and_ranges(uint8_t *geom, uint8_t *binning, const BinLayout &BL,
     const int num_passes = (sort_bits + 7) / 8;
     if (num_passes > SORT_MAX_PASSES) return D3GA_EINVAL;
     const uint32_t tiles_cap = (uint32_t)sort_tiles(capacity);
+    // Default: the full 64-bit LSD sort (depth digits first, constant digits skipped).  D3GA_SORT_MODE=segmented runs
+    // the global passes on the tile digits only and sorts each tile's depths in shared memory (raster_segsort.cu);
+    // measured equal on B200 (profiles/), kept for A/B measurements.
+    static const bool segmented = getenv("D3GA_SORT_MODE") && strcmp(getenv("D3GA_SORT_MODE"), "segmented") == 0;
+    const int first_pass = segmented ? 4 : 0;
 
     if (!g_sort_attr_set) {
         D3GA_CUDA(cudaFuncSetAttribute(sort_pass_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SORT_SMEM_BYTES));
@@ -332,10 +349,11 @@ int launch_sort_and_ranges(uint8_t *geom, uint8_t *binning, const BinLayout &BL,
     if (hist_grid < 1) hist_grid = 1;
     {
         ProfScope prof(K_SORT_HIST, stream);
-        sort_histogram_kernel<<<hist_grid, HIST_THREADS, 0, stream>>>(hdr, keys0, ghist, bins, sort_bits, num_passes);
+        sort_histogram_kernel<<<hist_grid, HIST_THREADS, 0, stream>>>(hdr, keys0, ghist, bins, sort_bits, num_passes,
+                                                                      first_pass);
     }
     D3GA_LAUNCH_CHECK();
-    for (int p = 0; p < num_passes; p++) {
+    for (int p = first_pass; p < num_passes; p++) {
         const int shift = 8 * p;
         const int nb = sort_bits - shift < 8 ? sort_bits - shift : 8;
         {
@@ -354,6 +372,7 @@ int launch_sort_and_ranges(uint8_t *geom, uint8_t *binning, const BinLayout &BL,
                                                    reinterpret_cast<uint32_t *>(image + IL.order_fwd));
     }
     D3GA_LAUNCH_CHECK();
+    if (segmented) return launch_segment_sort(geom, binning, BL, image, IL, num_tiles, stream);
     return D3GA_OK;
 }
 

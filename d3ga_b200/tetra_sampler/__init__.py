@@ -15,10 +15,15 @@ The ray/segment samplers and the bundled SMPL layer of the reference package are
 """
 from __future__ import annotations
 
+import os
+
 import numpy as np
 import torch
 
 from d3ga_b200 import _lib
+
+
+USE_TET_ORDER = os.environ.get("D3GA_DEFORM_ORDERED", "1") != "0"
 
 
 def _check(t, name, dtype):
@@ -137,6 +142,22 @@ def compute_bary(points, tetras, triangles, tri_to_tetra, tetra_model):
     return BarycentricCuda.apply(points, tetras, triangles, tri_to_tetra, tetra_model)
 
 
+# tetra_id is a constant buffer of the model (lib/cage.py:331-337): its sort permutation is computed once and reused by
+# every backward (d3ga_deform_backward_ordered sums a tet's vertex gradients in the warp before the atomics).
+_order_cache: dict = {}
+
+
+def _tet_order(tetra_id):
+    key = (tetra_id.data_ptr(), tetra_id._version, int(tetra_id.shape[0]), tetra_id.device)
+    order = _order_cache.get(key)
+    if order is None:
+        if len(_order_cache) > 16:
+            _order_cache.clear()
+        order = torch.argsort(tetra_id, stable=True).to(torch.int32).contiguous()
+        _order_cache[key] = order
+    return order
+
+
 class _DeformGaussians(torch.autograd.Function):
     @staticmethod
     def forward(ctx, tetpoints, tets, tetra_id, barys, canonical_gradient, scales, rotation):
@@ -173,11 +194,18 @@ class _DeformGaussians(torch.autograd.Function):
             g_bary = torch.empty((N, 4), dtype=torch.float32, device=dev) if need[3] else None
             g_scales = torch.empty((N, 3), dtype=torch.float32, device=dev) if need[5] else None
             g_rot = torch.empty((N, 4), dtype=torch.float32, device=dev) if need[6] else None
-            _lib.check(lib.d3ga_deform_backward(
-                N, V, T, tetpoints.data_ptr(), tets.data_ptr(), _lib.ptr(tetra_id), _lib.ptr(barys),
-                _lib.ptr(canonical_gradient), _lib.ptr(scales), _lib.ptr(rotation), _lib.ptr(g_means),
-                _lib.ptr(g_cov), _lib.ptr(g_tet), _lib.ptr(g_bary), _lib.ptr(g_scales), _lib.ptr(g_rot),
-                torch.cuda.current_stream().cuda_stream), "deform_backward")
+            if N > 0 and g_tet is not None and USE_TET_ORDER:
+                _lib.check(lib.d3ga_deform_backward_ordered(
+                    N, V, T, tetpoints.data_ptr(), tets.data_ptr(), _lib.ptr(tetra_id), _lib.ptr(barys),
+                    _lib.ptr(canonical_gradient), _lib.ptr(scales), _lib.ptr(rotation), _lib.ptr(g_means),
+                    _lib.ptr(g_cov), _lib.ptr(g_tet), _lib.ptr(g_bary), _lib.ptr(g_scales), _lib.ptr(g_rot),
+                    _tet_order(tetra_id).data_ptr(), torch.cuda.current_stream().cuda_stream), "deform_backward_ordered")
+            else:
+                _lib.check(lib.d3ga_deform_backward(
+                    N, V, T, tetpoints.data_ptr(), tets.data_ptr(), _lib.ptr(tetra_id), _lib.ptr(barys),
+                    _lib.ptr(canonical_gradient), _lib.ptr(scales), _lib.ptr(rotation), _lib.ptr(g_means),
+                    _lib.ptr(g_cov), _lib.ptr(g_tet), _lib.ptr(g_bary), _lib.ptr(g_scales), _lib.ptr(g_rot),
+                    torch.cuda.current_stream().cuda_stream), "deform_backward")
         return g_tet, None, None, g_bary, None, g_scales, g_rot
 
 

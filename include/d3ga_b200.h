@@ -174,6 +174,16 @@ int d3ga_deform_backward(int N, int V, int T, const float *tetpoints, const int6
                          float *dL_dtetpoints, float *dL_dbarys, float *dL_dscales, float *dL_drotation,
                          d3ga_stream_t stream);
 
+/* Same backward with the Gaussians visited in the order `order` [N] int32 gives (a permutation of 0..N-1, normally
+ * argsort(tetra_id), which the caller computes once -- tetra_id is a constant buffer, lib/cage.py:331-337).  Any
+ * permutation is valid; when it groups equal tetra_id together the cage-vertex gradients of a tet are summed inside
+ * the warp and one lane per tet issues the atomics (~N/T times fewer than d3ga_deform_backward). */
+int d3ga_deform_backward_ordered(int N, int V, int T, const float *tetpoints, const int64_t *tets,
+                                 const int64_t *tetra_id, const float *barys, const float *canonical_gradient,
+                                 const float *scales, const float *rotation, const float *dL_dmeans3D,
+                                 const float *dL_dcov3D, float *dL_dtetpoints, float *dL_dbarys, float *dL_dscales,
+                                 float *dL_drotation, const int32_t *order, d3ga_stream_t stream);
+
 /* ---- barycentric embedding -------------------------------------------------------
  * Replaces tetra_sampler.compute_bary (submodules/tetra-sampler/tetra_sampler/barys.py:9-33): the nearest-face
  * query of bvh_distance_queries.BVH (bvh_cuda_op.cu:1065-1269) followed by barycentric_kernel

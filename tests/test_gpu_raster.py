@@ -216,3 +216,18 @@ def test_full_size_properties(cuda_lib, oracle_libs, workload):
     rg = orc.backward(ref, w)
     for k in ("means3D", "cov3D", "opacity", "colors"):
         assert util.rel_l2(g1[k], rg[k]) < GRAD_TOL, (k, util.rel_l2(g1[k], rg[k]))
+
+
+def test_segmented_sort_mode_is_bit_exact_too(cuda_lib, oracle_libs):
+    """D3GA_SORT_MODE=segmented (global passes on the tile digits + per-tile depth sort in shared memory) is read when
+    the library first sorts, so it is exercised in a fresh process; it must give the same lists as the default."""
+    import os
+    import subprocess
+    import sys
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = dict(os.environ, D3GA_SORT_MODE="segmented")
+    r = subprocess.run([sys.executable, "-m", "pytest", "-q", "-x", "-m", "gpu", os.path.join(root, "tests", "test_gpu_raster.py"),
+                        "-k", "test_sort_and_ranges_bit_exact or (test_full_size_properties and c2)"],
+                       env=env, cwd=root, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
