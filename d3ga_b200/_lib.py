@@ -125,3 +125,35 @@ def profile_collect() -> dict:
     cnt = (C.c_uint64 * n)()
     check(lib.d3ga_profile_collect(ms, cnt), "profile_collect")
     return {lib.d3ga_profile_kernel_name(i).decode(): (float(ms[i]), int(cnt[i])) for i in range(n)}
+
+
+# ---- cheap device / stream plumbing (torch.cuda.current_stream() and torch.cuda.device() cost ~20 us each) ------------
+import torch as _torch
+
+
+def raw_stream(device) -> int:
+    """cudaStream_t of torch's current stream on `device`, as an integer."""
+    return _torch._C._cuda_getCurrentRawStream(device.index if device.index is not None else _torch.cuda.current_device())
+
+
+class device_guard:
+    """Makes `device` current for the duration of a call (the C-ABI runs on the current device); no-op when it is."""
+
+    __slots__ = ("idx", "prev")
+
+    def __init__(self, device):
+        self.idx = device.index if device.index is not None else -1
+        self.prev = -1
+
+    def __enter__(self):
+        if self.idx >= 0:
+            cur = _torch._C._cuda_getDevice()
+            if cur != self.idx:
+                self.prev = cur
+                _torch._C._cuda_setDevice(self.idx)
+        return self
+
+    def __exit__(self, *exc):
+        if self.prev >= 0:
+            _torch._C._cuda_setDevice(self.prev)
+        return False

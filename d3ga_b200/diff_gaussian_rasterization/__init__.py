@@ -63,6 +63,19 @@ def sort_plan_of_last_forward() -> dict:
             "num_rendered": int(hdr[0])}
 
 
+_ws_cache: dict = {}
+
+
+def _workspace_bytes(P, W, H, cap):
+    key = (P, W, H, cap)
+    v = _ws_cache.get(key)
+    if v is None:
+        if len(_ws_cache) > 256:
+            _ws_cache.clear()
+        v = _ws_cache[key] = _lib.workspace_bytes(P, W, H, cap)
+    return v
+
+
 def _pinned_counter(device):
     slot = _pinned_slots.get(device)
     if slot is None:
@@ -102,20 +115,21 @@ def rasterize_forward(means3D, sh, colors_precomp, opacities, scales, rotations,
     view = _f32c(rs.viewmatrix, "viewmatrix")
     proj = _f32c(rs.projmatrix, "projmatrix")
     campos = _f32c(rs.campos, "campos")
-    with torch.cuda.device(dev):
-        stream = torch.cuda.current_stream().cuda_stream
+    with _lib.device_guard(dev):
+        stream = _lib.raw_stream(dev)
         color = torch.empty((3, H, W), dtype=torch.float32, device=dev)
         invdepth = torch.empty((1, H, W), dtype=torch.float32, device=dev) if want_invdepth else None
         radii = torch.empty((P,), dtype=torch.int32, device=dev)
         st = RasterState()
         st.P, st.W, st.H = P, W, H
-        gb, _, ib = _lib.workspace_bytes(P, W, H, 0)
+        gb, _, ib = _workspace_bytes(P, W, H, 0)
         st.geom = torch.empty(gb, dtype=torch.uint8, device=dev)
         st.image = torch.empty(ib, dtype=torch.uint8, device=dev)
         host = _pinned_counter(dev)
+        host_np = host.numpy()
         ev = torch.cuda.Event()
         while True:
-            _, bb, _ = _lib.workspace_bytes(P, W, H, cap)
+            _, bb, _ = _workspace_bytes(P, W, H, cap)
             st.binning = torch.empty(bb, dtype=torch.uint8, device=dev)
             st.capacity = cap
             _lib.check(lib.d3ga_raster_forward_geometry(
@@ -130,8 +144,8 @@ def rasterize_forward(means3D, sh, colors_precomp, opacities, scales, rotations,
                 P, W, H, bg.data_ptr(), _lib.ptr(colors_precomp), st.geom.data_ptr(), st.binning.data_ptr(), cap,
                 st.image.data_ptr(), color.data_ptr(), _lib.ptr(invdepth), stream), "raster_forward_render")
             ev.synchronize()   # waits for stage 1 only; stage 2 keeps running
-            D = int(host[0].item()) & 0xFFFFFFFF
-            overflow = int(host[1].item())
+            D, overflow = int(host_np[0]) & 0xFFFFFFFF, int(host_np[1])
+            D, overflow = int(D), int(overflow)
             st.num_rendered = D
             if not overflow:
                 break
@@ -151,8 +165,8 @@ def rasterize_backward(st, grad_color, grad_invdepth, means3D, sh, colors_precom
     dev = means3D.device
     P, W, H = st.P, st.W, st.H
     M = 0 if sh is None else int(sh.shape[1])
-    with torch.cuda.device(dev):
-        stream = torch.cuda.current_stream().cuda_stream
+    with _lib.device_guard(dev):
+        stream = _lib.raw_stream(dev)
         grad_color = _f32c(grad_color, "grad_color")
         grad_invdepth = _f32c(grad_invdepth, "grad_invdepth")
         scratch = torch.empty(int(lib.d3ga_raster_backward_scratch_bytes(P)), dtype=torch.uint8, device=dev)

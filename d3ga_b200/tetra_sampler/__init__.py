@@ -123,14 +123,14 @@ class BarycentricCuda(torch.autograd.Function):
         triangles = _check(triangles, "triangles", torch.float32)
         tri_to_tetra = _check(tri_to_tetra, "tri_to_tetra", torch.int32)
         n, dev = points.size(0), points.device
-        with torch.cuda.device(dev):
+        with _lib.device_guard(dev):
             barys = torch.zeros(n, 4, dtype=torch.float32, device=dev)
             tetra_id = torch.zeros(n, dtype=torch.int32, device=dev)
             active_points = torch.zeros(n, dtype=torch.int32, device=dev)
             _lib.check(lib.d3ga_compute_bary(
                 n, int(tetras.shape[0]), int(triangles.shape[0]), _lib.ptr(points), tetras.data_ptr(),
                 triangles.data_ptr(), tri_to_tetra.data_ptr(), _lib.ptr(barys), _lib.ptr(tetra_id),
-                _lib.ptr(active_points), None, torch.cuda.current_stream().cuda_stream), "compute_bary")
+                _lib.ptr(active_points), None, _lib.raw_stream(dev)), "compute_bary")
         return barys, tetra_id.long(), active_points
 
     @staticmethod
@@ -170,13 +170,13 @@ class _DeformGaussians(torch.autograd.Function):
         scales = _check(scales, "scales", torch.float32)
         rotation = _check(rotation, "rotation", torch.float32)
         N, V, T, dev = int(tetra_id.shape[0]), int(tetpoints.shape[0]), int(tets.shape[0]), tetpoints.device
-        with torch.cuda.device(dev):
+        with _lib.device_guard(dev):
             means3D = torch.empty((N, 3), dtype=torch.float32, device=dev)
             cov3D = torch.empty((N, 6), dtype=torch.float32, device=dev)
             _lib.check(lib.d3ga_deform_forward(
                 N, V, T, tetpoints.data_ptr(), tets.data_ptr(), _lib.ptr(tetra_id), _lib.ptr(barys),
                 _lib.ptr(canonical_gradient), _lib.ptr(scales), _lib.ptr(rotation), _lib.ptr(means3D),
-                _lib.ptr(cov3D), torch.cuda.current_stream().cuda_stream), "deform_forward")
+                _lib.ptr(cov3D), _lib.raw_stream(dev)), "deform_forward")
         ctx.save_for_backward(tetpoints, tets, tetra_id, barys, canonical_gradient, scales, rotation)
         ctx.set_materialize_grads(False)
         return means3D, cov3D
@@ -187,7 +187,7 @@ class _DeformGaussians(torch.autograd.Function):
         tetpoints, tets, tetra_id, barys, canonical_gradient, scales, rotation = ctx.saved_tensors
         N, V, T, dev = int(tetra_id.shape[0]), int(tetpoints.shape[0]), int(tets.shape[0]), tetpoints.device
         need = ctx.needs_input_grad
-        with torch.cuda.device(dev):
+        with _lib.device_guard(dev):
             g_means = torch.zeros((N, 3), dtype=torch.float32, device=dev) if g_means is None else g_means.contiguous()
             g_cov = torch.zeros((N, 6), dtype=torch.float32, device=dev) if g_cov is None else g_cov.contiguous()
             g_tet = torch.zeros((V, 3), dtype=torch.float32, device=dev) if need[0] else None
@@ -199,13 +199,13 @@ class _DeformGaussians(torch.autograd.Function):
                     N, V, T, tetpoints.data_ptr(), tets.data_ptr(), _lib.ptr(tetra_id), _lib.ptr(barys),
                     _lib.ptr(canonical_gradient), _lib.ptr(scales), _lib.ptr(rotation), _lib.ptr(g_means),
                     _lib.ptr(g_cov), _lib.ptr(g_tet), _lib.ptr(g_bary), _lib.ptr(g_scales), _lib.ptr(g_rot),
-                    _tet_order(tetra_id).data_ptr(), torch.cuda.current_stream().cuda_stream), "deform_backward_ordered")
+                    _tet_order(tetra_id).data_ptr(), _lib.raw_stream(dev)), "deform_backward_ordered")
             else:
                 _lib.check(lib.d3ga_deform_backward(
                     N, V, T, tetpoints.data_ptr(), tets.data_ptr(), _lib.ptr(tetra_id), _lib.ptr(barys),
                     _lib.ptr(canonical_gradient), _lib.ptr(scales), _lib.ptr(rotation), _lib.ptr(g_means),
                     _lib.ptr(g_cov), _lib.ptr(g_tet), _lib.ptr(g_bary), _lib.ptr(g_scales), _lib.ptr(g_rot),
-                    torch.cuda.current_stream().cuda_stream), "deform_backward")
+                    _lib.raw_stream(dev)), "deform_backward")
         return g_tet, None, None, g_bary, None, g_scales, g_rot
 
 
