@@ -19,8 +19,6 @@
 //            (pixel, Gaussian).
 // Algorithmic bytes: forward 40 B per duplicate + 20 B per pixel; backward 40 B read + 40 B gradient RMW per
 // duplicate + 20 B per pixel.  Both kernels are FP32/SFU bound rather than HBM bound.
-#include <cstdlib>
-
 #include "common.cuh"
 
 namespace d3ga {
@@ -45,6 +43,18 @@ __device__ __forceinline__ float4 footprint_box(float2 c, float4 co) {
     const float k = 2.f * tau / det;
     const float hx = sqrtf(k * co.z) * 1.001f + 0.5f, hy = sqrtf(k * co.x) * 1.001f + 0.5f;
     return make_float4(c.x - hx, c.x + hx, c.y - hy, c.y + hy);
+}
+
+// Conic pre-scaled for the inner loop: log2(G) = A dx^2 + B dx dy + C dy^2 with A = -0.5 log2(e) conic.xx, B = -log2(e)
+// conic.xy, C = -0.5 log2(e) conic.yy, so G = exp2(.) costs one MUFU and no extra multiply.
+constexpr float LOG2E = 1.4426950408889634f;
+__device__ __forceinline__ float4 prescale_conic(float4 co) {
+    return make_float4(-0.5f * LOG2E * co.x, -LOG2E * co.y, -0.5f * LOG2E * co.z, co.w);
+}
+__device__ __forceinline__ float fast_exp2(float x) {
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
 }
 
 // Each warp owns an 8x4 pixel block of the 16x16 tile (compact blocks cull better than 16x2 strips).
@@ -114,7 +124,7 @@ __global__ void __launch_bounds__(TILE_PIX) blend_forward_kernel(
     };
     auto park = [&](int buf) {
         s_xy[buf][tid] = p_xy;
-        s_co[buf][tid] = p_co;
+        s_co[buf][tid] = prescale_conic(p_co);
         s_box[buf][tid] = footprint_box(p_xy, p_co);
         s_feat[buf][tid] = p_feat;
     };
@@ -157,9 +167,9 @@ __global__ void __launch_bounds__(TILE_PIX) blend_forward_kernel(
                 const int j = valid ? (int)s_list[warp][k + u] : 0;
                 const float2 c = s_xy[buf][j];
                 const float dx = c.x - pxf, dy = c.y - pyf;
-                const float4 co = s_co[buf][j];
-                const float power = -0.5f * (co.x * dx * dx + co.z * dy * dy) - co.y * dx * dy;
-                const float alpha = fminf(0.99f, co.w * __expf(power));
+                const float4 co = s_co[buf][j];   // pre-scaled: log2 domain
+                const float power = dx * (co.x * dx + co.y * dy) + co.z * dy * dy;
+                const float alpha = fminf(0.99f, co.w * fast_exp2(power));
                 a[u] = (valid && !(power > 0.f) && alpha >= 1.f / 255.f) ? alpha : 0.f;
                 jj[u] = j;
             }
@@ -420,17 +430,6 @@ extern "C" int d3ga_debug_set_buffer(void *p) {
 }
 #endif
 
-// Residency limiter (tuning knob): extra dynamic shared memory so that at most `ctas_per_sm` CTAs share an SM.
-static int dyn_smem_for_residency(int ctas_per_sm, int static_bytes) {
-    if (ctas_per_sm <= 0) return 0;
-    const int budget = 227 * 1024 / ctas_per_sm - static_bytes - 1024;
-    return budget > 0 ? budget : 0;
-}
-static int env_int(const char *name, int dflt) {
-    const char *v = getenv(name);
-    return v ? atoi(v) : dflt;
-}
-
 int launch_blend_forward(int W, int H, const float *background, const float *colors, const uint8_t *geom,
                          const GeomLayout &GL, const uint8_t *binning, const BinLayout &BL, uint8_t *image,
                          const ImgLayout &IL, float *out_color, float *out_invdepth, cudaStream_t stream) {
@@ -448,20 +447,13 @@ int launch_blend_forward(int W, int H, const float *background, const float *col
     const uint32_t *order_fwd = reinterpret_cast<const uint32_t *>(image + IL.order_fwd);
     uint32_t *order_bwd = reinterpret_cast<uint32_t *>(image + IL.order_bwd);
     uint32_t *tile_nproc = reinterpret_cast<uint32_t *>(image + IL.tile_nproc);
-    static const int dyn = dyn_smem_for_residency(env_int("D3GA_BLEND_FWD_CTAS", 0), 32 * 1024);
-    static bool attr_set = false;
-    if (dyn > 0 && !attr_set) {
-        cudaFuncSetAttribute(blend_forward_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn);
-        cudaFuncSetAttribute(blend_forward_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn);
-        attr_set = true;
-    }
     ProfScope prof(K_BLEND_FWD, stream);
     if (out_invdepth)
-        blend_forward_kernel<true><<<num_tiles, TILE_PIX, dyn, stream>>>(
+        blend_forward_kernel<true><<<num_tiles, TILE_PIX, 0, stream>>>(
             hdr, ranges, v0, v1, W, H, xy, co, colors, depth, background, final_T, n_contrib, out_color, out_invdepth,
             hdr_rw, gx, num_tiles, order_fwd, tile_nproc, order_bwd);
     else
-        blend_forward_kernel<false><<<num_tiles, TILE_PIX, dyn, stream>>>(
+        blend_forward_kernel<false><<<num_tiles, TILE_PIX, 0, stream>>>(
             hdr, ranges, v0, v1, W, H, xy, co, colors, depth, background, final_T, n_contrib, out_color, nullptr,
             hdr_rw, gx, num_tiles, order_fwd, tile_nproc, order_bwd);
     D3GA_LAUNCH_CHECK();
@@ -483,20 +475,13 @@ int launch_blend_backward(int W, int H, const float *background, const float *co
     const float *final_T = reinterpret_cast<const float *>(image + IL.final_T);
     const uint32_t *n_contrib = reinterpret_cast<const uint32_t *>(image + IL.n_contrib);
     const uint32_t *order_bwd = reinterpret_cast<const uint32_t *>(image + IL.order_bwd);
-    static const int dyn = dyn_smem_for_residency(env_int("D3GA_BLEND_BWD_CTAS", 0), 33 * 1024);
-    static bool attr_set = false;
-    if (dyn > 0 && !attr_set) {
-        cudaFuncSetAttribute(blend_backward_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn);
-        cudaFuncSetAttribute(blend_backward_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn);
-        attr_set = true;
-    }
     ProfScope prof(K_BLEND_BWD, stream);
     if (dL_dinvdepth_pix)
-        blend_backward_kernel<true><<<num_tiles, TILE_PIX, dyn, stream>>>(
+        blend_backward_kernel<true><<<num_tiles, TILE_PIX, 0, stream>>>(
             hdr, ranges, v0, v1, W, H, background, xy, co, colors, depth, final_T, n_contrib, dL_dpix, dL_dinvdepth_pix,
             grad_acc, gx, order_bwd);
     else
-        blend_backward_kernel<false><<<num_tiles, TILE_PIX, dyn, stream>>>(
+        blend_backward_kernel<false><<<num_tiles, TILE_PIX, 0, stream>>>(
             hdr, ranges, v0, v1, W, H, background, xy, co, colors, depth, final_T, n_contrib, dL_dpix, nullptr, grad_acc,
             gx, order_bwd);
     D3GA_LAUNCH_CHECK();
