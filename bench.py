@@ -255,10 +255,17 @@ def run_ours(args):
     dominant = max(kern, key=lambda k: kern[k]["total_ms"]) if kern else None
     view_bytes = 540 * N + (148 + 24 * passes) * D + 40 * P + 8 * Tl
     roof = None
+    traffic = None
+    try:   # DRAM bytes per launch of the dominant kernel from the committed `ncu --set full` capture (profiles/)
+        tj = json.load(open(os.path.join(ROOT, "profiles", "r1_traffic.json")))
+        if args.workload == "metric" and dominant in tj["kernels"]:
+            traffic = tj["kernels"][dominant]["dram_bytes"]
+    except Exception:
+        traffic = None
     if dominant:
         ach = kern[dominant]["GBps"]
         roof = {"bound": "hbm", "kernel": dominant, "achieved": ach, "peak": peak, "unit": "GB/s",
-                "frac": ach / peak if ach else None, "traffic": None, "peak_kind": peak_kind,
+                "frac": ach / peak if ach else None, "traffic": traffic, "peak_kind": peak_kind,
                 "algorithmic_bytes_per_launch": bytes_per_launch.get(dominant),
                 "avg_launch_ms": kern[dominant]["avg_ms"],
                 "whole_view": {"bytes": view_bytes, "GBps": view_bytes * (V * args.steps) / (ms * 1e-3) / 1e9,
