@@ -71,7 +71,7 @@ const char *d3ga_error_string(int code) {
         case D3GA_OK: return "ok";
         case D3GA_EINVAL: return "invalid argument";
         case D3GA_ECUDA: return "CUDA runtime error (see d3ga_last_cuda_error)";
-        case D3GA_ETOOBIG: return "size exceeds the 2^30-1 duplicate limit";
+        case D3GA_ETOOBIG: return "size exceeds the 2^31-1 duplicate limit";
         case D3GA_ENOTREADY: return "call not possible in the current state (staged call out of order, or profiling on)";
         case D3GA_ELIMIT: return "more Gaussians than the fixed scratch of the allocation-free entry point holds";
         default: return "unknown error";

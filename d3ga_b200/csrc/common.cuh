@@ -14,7 +14,7 @@ constexpr int SORT_THREADS = 512;
 constexpr int SORT_ITEMS = 8;      // keys per thread per onesweep tile
 constexpr int SORT_TILE = SORT_THREADS * SORT_ITEMS;  // 4096 pairs = 48 KB of payload per CTA
 constexpr int SORT_MAX_PASSES = 8;
-constexpr uint32_t MAX_DUPLICATES = (1u << 30) - 1;  // look-back words keep 2 flag bits
+constexpr uint32_t MAX_DUPLICATES = (1u << 31) - 1;  // an inclusive look-back word keeps 1 flag bit
 
 // ---- workspace layouts ------------------------------------------------------------------------------------------
 struct RasterHeader {          // first 256 bytes of the geom workspace; zeroed at the start of every forward

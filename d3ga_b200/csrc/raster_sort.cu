@@ -24,7 +24,12 @@ namespace d3ga {
 
 namespace {
 
-constexpr uint32_t ST_AGG = 1u << 30, ST_INC = 2u << 30, ST_FLAGS = 3u << 30, ST_VALUE = ~ST_FLAGS;
+// look-back word: bit 31 set = inclusive prefix in the low 31 bits; else bit 30 set = tile aggregate (<= SORT_TILE) in
+// the low 30 bits; 0 = not published yet
+constexpr uint32_t ST_INC = 1u << 31, ST_AGG = 1u << 30;
+__device__ __forceinline__ bool st_ready(uint32_t s) { return (s & (ST_INC | ST_AGG)) != 0u; }
+__device__ __forceinline__ bool st_inclusive(uint32_t s) { return (s & ST_INC) != 0u; }
+__device__ __forceinline__ uint32_t st_value(uint32_t s) { return (s & ST_INC) ? (s & ~ST_INC) : (s & ~ST_AGG); }
 constexpr int HIST_THREADS = 256;
 constexpr int HIST_ITEMS = 8;
 
@@ -240,11 +245,10 @@ __global__ void __launch_bounds__(SORT_THREADS) sort_pass_kernel(RasterHeader *h
 #pragma unroll
                 for (int u = 0; u < 8; u++) {
                     if (resolved || used != u) continue;       // stop at the first inclusive word or unready word
-                    const uint32_t f = sv[u] & ST_FLAGS;
-                    if (f == 0) continue;                       // not published yet: retry from here
-                    excl += sv[u] & ST_VALUE;
+                    if (!st_ready(sv[u])) continue;             // not published yet: retry from here
+                    excl += st_value(sv[u]);
                     used = u + 1;
-                    if (f == ST_INC) resolved = true;
+                    if (st_inclusive(sv[u])) resolved = true;
                 }
                 p -= used;
             }

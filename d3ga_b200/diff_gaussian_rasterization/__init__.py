@@ -149,10 +149,10 @@ def rasterize_forward(means3D, sh, colors_precomp, opacities, scales, rotations,
             st.num_rendered = D
             if not overflow:
                 break
-            if D >= (1 << 30) - 1:
-                raise _lib.D3GAError(f"{D} (tile, Gaussian) duplicates exceed the 2^30-1 limit")
-            cap = min((1 << 30) - 1, int(D * CAPACITY_SLACK) + 4096)
-        _capacity_hint[key] = min((1 << 30) - 1, int(D * CAPACITY_SLACK) + 4096)
+            if D >= (1 << 31) - 1:
+                raise _lib.D3GAError(f"{D} (tile, Gaussian) duplicates exceed the 2^31-1 limit")
+            cap = min((1 << 31) - 1, int(D * CAPACITY_SLACK) + 4096)
+        _capacity_hint[key] = min((1 << 31) - 1, int(D * CAPACITY_SLACK) + 4096)
     global _last_state
     _last_state = st
     last_stats.update(num_rendered=D, capacity=st.capacity)

@@ -38,7 +38,7 @@ def test_size_queries_need_no_gpu():
     lay = _lib.raster_layout(1000, 64, 48, 5000)
     assert lay["geom_header"] == 0 and lay["bin_keys1"] - lay["bin_keys0"] >= 5000 * 8
     with pytest.raises(_lib.D3GAError):
-        _lib.workspace_bytes(10, 64, 48, 1 << 31)
+        _lib.workspace_bytes(10, 64, 48, 1 << 32)
 
 
 def test_settings_and_rasterizer_interface():

@@ -231,3 +231,48 @@ def test_segmented_sort_mode_is_bit_exact_too(cuda_lib, oracle_libs):
                         "-k", "test_sort_and_ranges_bit_exact or (test_full_size_properties and c2)"],
                        env=env, cwd=root, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+
+
+def test_c4_stress_billion_duplicates(cuda_lib):
+    """BASELINE.json config 4 (4 M Gaussians, scales x4, 3840x2160): ~1.3e9 (tile, Gaussian) duplicates -- beyond 2^30,
+    far beyond what the CPU oracle can check in seconds, so only size-independent properties are verified, on the
+    device: sortedness, ranges partition the list, every Gaussian appears tiles_touched times, capacity retry path."""
+    from d3ga_b200 import diff_gaussian_rasterization as dgr
+    from d3ga_b200.tetra_sampler import deform_gaussians
+
+    sc = synth.make_workload("c4")
+    cam = synth.make_camera(sc.W, sc.H, 20, 10)
+    t = lambda a: torch.from_numpy(a).cuda()  # noqa: E731
+    means, cov6 = deform_gaussians(t(sc.tetpoints), t(sc.tets), t(sc.tetra_id), t(sc.barys), t(sc.canonical_gradient),
+                                   t(sc.scales), t(sc.rotation))
+    rs = dgr.GaussianRasterizationSettings(
+        image_height=sc.H, image_width=sc.W, tanfovx=cam.tanfovx, tanfovy=cam.tanfovy, bg=torch.ones(3, device="cuda"),
+        scale_modifier=1.0, viewmatrix=t(cam.viewmatrix), projmatrix=t(cam.projmatrix), sh_degree=0, campos=t(cam.campos),
+        prefiltered=False, debug=False, antialiasing=False)
+    color, radii, _, st = dgr.rasterize_forward(means, None, t(sc.colors), t(sc.opacity), None, None, cov6, rs,
+                                                want_invdepth=False)
+    torch.cuda.synchronize()
+    D = st.num_rendered
+    assert D > (1 << 30) and torch.isfinite(color).all()
+    lay = dgr._lib.raster_layout(sc.N, sc.W, sc.H, st.capacity)
+    hdr = st.geom[:256].cpu().numpy().view(np.uint32)
+    assert int(hdr[0]) == D and int(hdr[1]) == 0
+    sel = int(hdr[3])
+    koff, voff = lay["bin_keys1" if sel else "bin_keys0"], lay["bin_vals1" if sel else "bin_vals0"]
+    keys = st.binning[koff:koff + 8 * D].view(torch.int64)
+    tiles_of_key = keys >> 32
+    assert bool((tiles_of_key[1:] >= tiles_of_key[:-1]).all())
+    depth_of_key = keys & 0xFFFFFFFF
+    same_tile = tiles_of_key[1:] == tiles_of_key[:-1]
+    assert bool((depth_of_key[1:][same_tile] >= depth_of_key[:-1][same_tile]).all())
+    del same_tile, depth_of_key
+    vals = st.binning[voff:voff + 4 * D].view(torch.int32)
+    tiles = st.geom[lay["geom_tiles"]:lay["geom_tiles"] + 4 * sc.N].view(torch.int32)
+    assert int(tiles.sum(dtype=torch.int64)) == D
+    assert bool((torch.bincount(vals, minlength=sc.N) == tiles).all())
+    ntiles = ((sc.W + 15) // 16) * ((sc.H + 15) // 16)
+    ranges = st.image[lay["img_ranges"]:lay["img_ranges"] + 8 * ntiles].view(torch.int32).view(ntiles, 2).long() & 0xFFFFFFFF
+    lens = ranges[:, 1] - ranges[:, 0]
+    assert int(lens.sum()) == D and bool((lens >= 0).all())
+    nz = torch.nonzero(lens).flatten()
+    assert bool((tiles_of_key[ranges[nz, 0]] == nz).all())
