@@ -26,7 +26,8 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
-os.environ["NCCL_DEBUG"] = os.environ.get("D3GA_NCCL_DEBUG", "WARN")   # keep NCCL's banner off stdout: ONE JSON line
+# stdout carries ONE JSON line: NCCL's version banner / warnings go to stderr
+os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
 if "reference" in sys.argv:
     # the CPU arm uses every host thread it can (torchrun exports OMP_NUM_THREADS=1 for its workers); must be set
     # before numpy / torch / the oracle's libgomp are loaded
