@@ -276,3 +276,104 @@ def test_c4_stress_billion_duplicates(cuda_lib):
     assert int(lens.sum()) == D and bool((lens >= 0).all())
     nz = torch.nonzero(lens).flatten()
     assert bool((tiles_of_key[ranges[nz, 0]] == nz).all())
+
+
+def edge_cases():
+    rng = np.random.default_rng(21)
+    out = {}
+    # opacity 1 at pixel centres: alpha hits the 0.99 clamp (gradient flows through it like upstream)
+    g = util.random_gaussians(64, rng, sigma=0.08, with_behind=False)
+    g["opacity"][:] = 1.0
+    out["alpha_clamp"] = (g, synth.make_camera(48, 48, 0, 0), 48, 48)
+    # one Gaussian far larger than the image, one sub-pixel, one exactly on a tile corner
+    g = util.random_gaussians(3, rng, with_behind=False)
+    g["means"][:] = [[0, 0, 0], [0.05, 0.02, 0], [0, 0, 0]]
+    g["cov6"][:] = 0
+    g["cov6"][0, [0, 3, 5]] = 4.0
+    g["cov6"][1, [0, 3, 5]] = 1e-10
+    g["cov6"][2, [0, 3, 5]] = 1e-3
+    g["scales"][:] = [[2, 2, 2], [1e-5, 1e-5, 1e-5], [0.03, 0.03, 0.03]]
+    out["huge_and_tiny"] = (g, synth.make_camera(64, 64, 0, 0), 64, 64)
+    # indefinite / zero covariance inputs, a point far off screen and one behind the camera
+    g = util.random_gaussians(16, rng, with_behind=True)
+    g["cov6"][0] = 0
+    g["cov6"][1] = [1e-3, 2e-3, 0, 1e-3, 0, 1e-3]   # not positive definite
+    g["means"][2] = [50, 0, 0]
+    out["degenerate"] = (g, synth.make_camera(40, 24, 5, 5), 40, 24)
+    for (w, h) in [(1, 1), (16, 16), (17, 33)]:
+        out[f"size_{w}x{h}"] = (util.random_gaussians(257, rng, sigma=0.2, with_behind=False), synth.make_camera(w, h, 10, -10), w, h)
+    out["single"] = (util.random_gaussians(1, rng, sigma=0.1, with_behind=False), synth.make_camera(32, 32), 32, 32)
+    return out
+
+
+EDGE = edge_cases()
+
+
+@pytest.mark.parametrize("name", list(EDGE))
+@pytest.mark.parametrize("path", ["precomp", "sh"])
+def test_edge_cases_match_oracle(cuda_lib, oracle_libs, name, path):
+    g, cam, W, H = EDGE[name]
+    orc, ref = util.oracle_forward(g, cam, W, H, BG, path)
+    got = gpu_util.forward_stages(g, cam, W, H, BG, path)
+    assert np.array_equal(got["radii"], ref["radii"])
+    assert np.array_equal(got["keys"], ref["keys"]) and np.array_equal(got["point_list"], ref["point_list"])
+    assert np.array_equal(got["ranges"], ref["ranges"])
+    assert_image_close(got["color"], ref["color"])
+    assert np.array_equal(got["n_contrib"], ref["n_contrib"])
+    w = np.random.default_rng(5).uniform(-1, 1, size=(3, H, W)).astype(np.float32)
+    rg = orc.backward(ref, w)
+    gg = gpu_util.backward(got, W, H, cam, w)
+    names = ["means3D", "means2D", "opacity"] + (["colors", "cov3D"] if path == "precomp" else ["sh", "scales", "rotations"])
+    for k in names:
+        r = rg["mean2D" if k == "means2D" else k]
+        assert np.isfinite(gg[k]).all(), k
+        if np.linalg.norm(r) > 0:
+            assert util.rel_l2(gg[k], r) < GRAD_TOL, (k, util.rel_l2(gg[k], r))
+        else:
+            assert np.abs(gg[k]).max() == 0, k
+
+
+@pytest.mark.parametrize("deg,M", [(0, 1), (1, 4), (2, 9), (2, 16), (3, 16)])
+def test_sh_degrees(cuda_lib, oracle_libs, deg, M):
+    """Active SH degree below the stored coefficient count (D3GA raises sh_degree during training)."""
+    from d3ga_b200 import _lib
+
+    rng = np.random.default_rng(deg * 10 + M)
+    g = util.random_gaussians(300, rng, sigma=0.06, with_behind=False)
+    g["shs"] = np.ascontiguousarray(g["shs"][:, :M])
+    cam = synth.make_camera(64, 48, 15, 5)
+    orc, ref = util.oracle_forward(g, cam, 64, 48, BG, "sh", sh_degree=deg)
+    lib = _lib.load()
+    d = gpu_util.dev
+    t = dict(means=d(g["means"]), op=d(g["opacity"]), sh=d(g["shs"]), sc=d(g["scales"]), rot=d(g["rot"]))
+    P, W, H = 300, 64, 48
+    cap = 1 << 16
+    gb, bb, ib = _lib.workspace_bytes(P, W, H, cap)
+    geom, binning, image = (torch.zeros(n, dtype=torch.uint8, device="cuda") for n in (gb, bb, ib))
+    radii = torch.zeros(P, dtype=torch.int32, device="cuda")
+    color = torch.zeros(3, H, W, device="cuda")
+    view, proj, campos, bg = d(cam.viewmatrix), d(cam.projmatrix), d(cam.campos), d(np.asarray(BG, np.float32))
+    s = torch.cuda.current_stream().cuda_stream
+    _lib.check(lib.d3ga_raster_forward_geometry(P, deg, M, t["means"].data_ptr(), t["sc"].data_ptr(), 1.0, t["rot"].data_ptr(),
+                                                t["op"].data_ptr(), t["sh"].data_ptr(), None, None, view.data_ptr(),
+                                                proj.data_ptr(), campos.data_ptr(), W, H, cam.tanfovx, cam.tanfovy, 0, 0,
+                                                geom.data_ptr(), binning.data_ptr(), cap, radii.data_ptr(), None, s), "geometry")
+    _lib.check(lib.d3ga_raster_forward_render(P, W, H, bg.data_ptr(), None, geom.data_ptr(), binning.data_ptr(), cap,
+                                              image.data_ptr(), color.data_ptr(), None, s), "render")
+    torch.cuda.synchronize()
+    assert_image_close(color.cpu().numpy(), ref["color"])
+    w = rng.uniform(-1, 1, size=(3, H, W)).astype(np.float32)
+    rg = orc.backward(ref, w)
+    scratch = torch.empty(int(lib.d3ga_raster_backward_scratch_bytes(P)), dtype=torch.uint8, device="cuda")
+    z = lambda *sh: torch.full(sh, float("nan"), device="cuda")  # noqa: E731
+    gm2, gop, gm3, gsh, gsc, grot = z(P, 3), z(P), z(P, 3), z(P, M, 3), z(P, 3), z(P, 4)
+    _lib.check(lib.d3ga_raster_backward(P, deg, M, W, H, bg.data_ptr(), t["means"].data_ptr(), None, t["op"].data_ptr(),
+                                        t["sc"].data_ptr(), 1.0, t["rot"].data_ptr(), None, t["sh"].data_ptr(),
+                                        view.data_ptr(), proj.data_ptr(), campos.data_ptr(), cam.tanfovx, cam.tanfovy, 0,
+                                        radii.data_ptr(), geom.data_ptr(), binning.data_ptr(), cap, image.data_ptr(),
+                                        d(w).data_ptr(), None, scratch.data_ptr(), gm2.data_ptr(), gop.data_ptr(), None,
+                                        gm3.data_ptr(), None, gsh.data_ptr(), gsc.data_ptr(), grot.data_ptr(), s), "backward")
+    torch.cuda.synchronize()
+    assert util.rel_l2(gsh.cpu().numpy(), rg["sh"]) < GRAD_TOL
+    assert util.rel_l2(gm3.cpu().numpy(), rg["means3D"]) < GRAD_TOL
+    assert np.all(gsh.cpu().numpy()[:, (deg + 1) ** 2:] == 0)
