@@ -1,6 +1,8 @@
 // api.cu -- the extern "C" surface of libd3ga_b200.so declared in include/d3ga_b200.h (rasterizer part; the
 // deformation and embedding entry points live beside their kernels in deform.cu / bary.cu).
 #include <atomic>
+#include <cstdlib>
+#include <cstring>
 #include <mutex>
 #include <vector>
 
@@ -26,7 +28,8 @@ static std::vector<ProfRec> g_prof_recs;
 static const char *const g_kernel_names[K_COUNT] = {
     "geometry_kernel", "sort_histogram_kernel", "sort_pass_kernel", "tile_ranges_kernel", "blend_forward_kernel",
     "blend_backward_kernel", "preprocess_backward_kernel", "deform_forward_kernel", "deform_backward_kernel",
-    "compute_bary_kernel", "segment_sort_kernel"};
+    "compute_bary_kernel", "segment_sort_kernel", "preprocess_kernel", "emit_sorted_kernel", "depth_histogram_kernel",
+    "depth_sort_pass_kernel"};
 
 bool profiling_enabled() { return g_prof_on.load(std::memory_order_relaxed) != 0; }
 
@@ -45,6 +48,16 @@ ProfScope::~ProfScope() {
     std::lock_guard<std::mutex> lk(g_prof_mu);
     g_prof_recs.push_back(*r);
     delete r;
+}
+
+int sort_mode() {
+    static const int mode = [] {
+        const char *v = getenv("D3GA_SORT_MODE");
+        if (v && strcmp(v, "global") == 0) return (int)SORT_GLOBAL;
+        if (v && strcmp(v, "segmented") == 0) return (int)SORT_SEGMENTED;
+        return (int)SORT_DEPTH_FIRST;
+    }();
+    return mode;
 }
 
 // upstream getHigherMsb: number of bits needed for the tile id

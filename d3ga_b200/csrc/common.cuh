@@ -30,12 +30,21 @@ struct RasterHeader {          // first 256 bytes of the geom workspace; zeroed 
     uint32_t pass_src[SORT_MAX_PASSES];    // buffer (0/1) a pass reads from
     uint32_t pass_ticket[SORT_MAX_PASSES]; // dynamic tile id per pass
     uint32_t blend_done;       // CTAs of the blend forward that have finished (last one orders the backward)
-    uint32_t pad1[64 - 9 - 3 * SORT_MAX_PASSES];
+    // plan of the 32-bit depth sort over the Gaussians (depth-first binning)
+    uint32_t dep_final_sel;    // which depth key/value buffer (0/1) holds the depth-sorted Gaussian list
+    uint32_t dep_hist_done;
+    uint32_t dep_culled;       // Gaussians with no tile (their key is 0xffffffff)
+    uint32_t dep_skip[4];
+    uint32_t dep_src[4];
+    uint32_t dep_ticket[4];
+    uint32_t pad1[64 - 9 - 3 * SORT_MAX_PASSES - 3 - 12];
 };
 static_assert(sizeof(RasterHeader) == 256, "header is 256 bytes");
 
 struct GeomLayout {
-    uint64_t header, depth, xy, conic_opacity, rgb, cov3D, tiles, offsets, clamped, scan_state, total;
+    uint64_t header, depth, xy, conic_opacity, rgb, cov3D, tiles, offsets, clamped, scan_state;
+    uint64_t rect_pack, dkeys, dvals, dep_hist, dep_bins, dep_state, total;   // depth-first binning
+    uint64_t p_pad;
 };
 struct BinLayout {
     uint64_t keys0, keys1, vals0, vals1, hist, bins, tile_state, total;
@@ -60,6 +69,13 @@ inline GeomLayout geom_layout(int P) {
     L.offsets = o;       o = align256(o + 4 * p);
     L.clamped = o;       o = align256(o + 3 * p);
     L.scan_state = o;    o = align256(o + 8 * ((p + GEO_THREADS - 1) / GEO_THREADS + 1));
+    L.p_pad = align256(p < 1 ? 1 : p);   // element stride between the two halves of the depth-sort ping-pong
+    L.rect_pack = o;     o = align256(o + 8 * p);
+    L.dkeys = o;         o = align256(o + 8 * L.p_pad);
+    L.dvals = o;         o = align256(o + 8 * L.p_pad);
+    L.dep_hist = o;      o = align256(o + 4 * 256 * 4);
+    L.dep_bins = o;      o = align256(o + 4 * 256 * 4);
+    L.dep_state = o;     o = align256(o + 4ull * 256 * 4 * ((p + SORT_TILE - 1) / SORT_TILE + 1));
     L.total = o;
     return L;
 }
@@ -101,7 +117,7 @@ constexpr int GRAD_ACC_FLOATS = 12;
 // ---- host-side helpers -----------------------------------------------------------------------------------------
 enum KernelId {
     K_GEOMETRY = 0, K_SORT_HIST, K_SORT_PASS, K_RANGES, K_BLEND_FWD, K_BLEND_BWD, K_PRE_BWD, K_DEFORM_FWD, K_DEFORM_BWD,
-    K_BARY, K_SEG_SORT, K_COUNT
+    K_BARY, K_SEG_SORT, K_PREPROCESS, K_EMIT, K_DEPTH_HIST, K_DEPTH_PASS, K_COUNT
 };
 // Optional per-kernel CUDA-event timing (d3ga_profile_* in the C-ABI; bench.py's roofline figures come from it).
 // A no-op unless profiling is enabled.
@@ -135,6 +151,9 @@ int launch_geometry(int P, int sh_degree, int sh_coeffs, const float *means3D, c
                     uint64_t capacity, int32_t *radii, cudaStream_t stream);
 int launch_sort_and_ranges(uint8_t *geom, uint8_t *binning, const BinLayout &BL, uint64_t capacity, int sort_bits,
                            uint8_t *image, const ImgLayout &IL, int num_tiles, cudaStream_t stream);
+int launch_depth_sort(int P, uint8_t *geom, const GeomLayout &GL, cudaStream_t stream);
+enum SortMode { SORT_DEPTH_FIRST = 0, SORT_GLOBAL = 1, SORT_SEGMENTED = 2 };
+int sort_mode();   // D3GA_SORT_MODE = depthfirst (default) | global | segmented
 int launch_segment_sort(uint8_t *geom, uint8_t *binning, const BinLayout &BL, uint8_t *image, const ImgLayout &IL,
                         int num_tiles, cudaStream_t stream);
 int launch_blend_forward(int W, int H, const float *background, const float *colors, const uint8_t *geom,

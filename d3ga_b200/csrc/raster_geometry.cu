@@ -66,6 +66,10 @@ struct GeoParams {
     uint64_t capacity;
     int32_t *radii;
     uint32_t num_ctas;
+    // depth-first binning
+    uint2 *rect_pack;      // [P] (x0 | y0 << 16, width) of the tile rect
+    uint32_t *dkeys, *dvals;   // [2][P_pad] ping-pong of the 32-bit depth sort
+    uint32_t P_pad;
 };
 
 constexpr uint64_t FLAG_AGG = 1ull << 62, FLAG_INC = 2ull << 62, FLAG_MASK = 3ull << 62;
@@ -101,27 +105,12 @@ __device__ void sh_to_rgb(int deg, const float *sh, float3 dir, float *rgb, uint
     }
 }
 
-__global__ void __launch_bounds__(GEO_THREADS) geometry_kernel(const GeoParams p) {
-    __shared__ float s_view[16], s_proj[16], s_cam[3];
-    __shared__ uint32_t s_excl[GEO_THREADS];
-    __shared__ uint32_t s_rect[GEO_THREADS];   // x0 | y0 << 16
-    __shared__ uint32_t s_width[GEO_THREADS];
-    __shared__ uint32_t s_depth[GEO_THREADS];
-    __shared__ uint32_t s_warp[GEO_THREADS / 32];
-    __shared__ uint32_t s_bid;
-    __shared__ uint64_t s_base;
-
-    const int tid = threadIdx.x;
-    if (tid == 0) s_bid = atomicAdd(&p.hdr->geo_ticket, 1u);
-    if (tid < 16) { s_view[tid] = p.view[tid]; s_proj[tid] = p.proj[tid]; }
-    if (tid < 3) s_cam[tid] = p.campos[tid];
-    __syncthreads();
-    const uint32_t bid = s_bid;
-    const int idx = (int)(bid * GEO_THREADS + tid);
-
-    // ---- R1: preprocess ------------------------------------------------------------------------------------------
-    uint32_t count = 0, rect = 0, width = 0, dbits = 0;
-    if (idx < p.P) {
+// ---- R1: preprocess one Gaussian; returns its tile count, rect (x0 | y0 << 16), rect width and depth bits ------------
+__device__ __forceinline__ void preprocess_one(const GeoParams &p, int idx, const float *s_view, const float *s_proj,
+                                               const float *s_cam, uint32_t &count, uint32_t &rect, uint32_t &width,
+                                               uint32_t &dbits) {
+    count = 0; rect = 0; width = 0; dbits = 0;
+    {
         int radius = 0;
         float depth = 0.f, pxi = 0.f, pyi = 0.f;
         float4 co = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -239,6 +228,14 @@ __global__ void __launch_bounds__(GEO_THREADS) geometry_kernel(const GeoParams p
         p.tiles[idx] = count;
     }
 
+}
+
+// ---- R2 + R3: CTA scan, decoupled look-back over CTAs, cooperative key emission ------------------------------------
+// `slot` is this thread's position in the scan order (bid * GEO_THREADS + tid), `gidx` the Gaussian it stands for.
+__device__ __forceinline__ void scan_and_emit(const GeoParams &p, uint32_t bid, int tid, bool in_range, uint32_t gidx,
+                                              uint32_t count, uint32_t rect, uint32_t width, uint32_t dbits,
+                                              uint32_t *s_excl, uint32_t *s_rect, uint32_t *s_width, uint32_t *s_depth,
+                                              uint32_t *s_gidx, uint32_t *s_warp, uint64_t *s_base_p) {
     // ---- R2: CTA-local exclusive scan, then decoupled look-back across CTAs ---------------------------------------
     const uint32_t lane = lane_id(), warp = tid >> 5;
     uint32_t incl = count;
@@ -251,6 +248,7 @@ __global__ void __launch_bounds__(GEO_THREADS) geometry_kernel(const GeoParams p
     s_rect[tid] = rect;
     s_width[tid] = width;
     s_depth[tid] = dbits;
+    s_gidx[tid] = gidx;
     __syncthreads();
     uint32_t warp_off = 0, cta_total = 0;
 #pragma unroll
@@ -288,7 +286,7 @@ __global__ void __launch_bounds__(GEO_THREADS) geometry_kernel(const GeoParams p
         }
         if (lane == 0) {
             st_volatile_u64(p.scan_state + bid, FLAG_INC | (base + cta_total));
-            s_base = base;
+            *s_base_p = base;
             if (bid == p.num_ctas - 1) {
                 const uint64_t total = base + cta_total;
                 p.hdr->num_rendered = total > 0xffffffffull ? 0xffffffffu : (uint32_t)total;
@@ -297,8 +295,8 @@ __global__ void __launch_bounds__(GEO_THREADS) geometry_kernel(const GeoParams p
         }
     }
     __syncthreads();
-    const uint64_t base = s_base;
-    if (idx < p.P) p.offsets[idx] = (uint32_t)(base + excl + count);   // inclusive, like upstream's point_offsets
+    const uint64_t base = *s_base_p;
+    if (in_range) p.offsets[bid * GEO_THREADS + tid] = (uint32_t)(base + excl + count);   // inclusive prefix in scan order
 
     // ---- R3: emit (key, value) pairs over the CTA's flattened output range ------------------------------------------
     for (uint32_t o = tid; o < cta_total; o += GEO_THREADS) {
@@ -311,9 +309,74 @@ __global__ void __launch_bounds__(GEO_THREADS) geometry_kernel(const GeoParams p
         const uint64_t dst = base + o;
         if (dst < p.capacity) {
             p.keys[dst] = ((uint64_t)(ty * (uint32_t)p.gx + tx) << 32) | s_depth[g];
-            p.vals[dst] = bid * GEO_THREADS + g;
+            p.vals[dst] = s_gidx[g];
         }
     }
+}
+
+#define GEO_SMEM_DECL                                                                  \
+    __shared__ uint32_t s_excl[GEO_THREADS], s_rect[GEO_THREADS], s_width[GEO_THREADS]; \
+    __shared__ uint32_t s_depth[GEO_THREADS], s_gidx[GEO_THREADS];                    \
+    __shared__ uint32_t s_warp[GEO_THREADS / 32];                                     \
+    __shared__ uint32_t s_bid;                                                        \
+    __shared__ uint64_t s_base;
+
+// Fused R1 + R2 + R3: keys are emitted in Gaussian-index order (the order upstream's duplicateWithKeys produces).
+__global__ void __launch_bounds__(GEO_THREADS) geometry_kernel(const GeoParams p) {
+    __shared__ float s_view[16], s_proj[16], s_cam[3];
+    GEO_SMEM_DECL
+    const int tid = threadIdx.x;
+    if (tid == 0) s_bid = atomicAdd(&p.hdr->geo_ticket, 1u);
+    if (tid < 16) { s_view[tid] = p.view[tid]; s_proj[tid] = p.proj[tid]; }
+    if (tid < 3) s_cam[tid] = p.campos[tid];
+    __syncthreads();
+    const uint32_t bid = s_bid;
+    const int idx = (int)(bid * GEO_THREADS + tid);
+    uint32_t count = 0, rect = 0, width = 0, dbits = 0;
+    if (idx < p.P) preprocess_one(p, idx, s_view, s_proj, s_cam, count, rect, width, dbits);
+    scan_and_emit(p, bid, tid, idx < p.P, (uint32_t)idx, count, rect, width, dbits, s_excl, s_rect, s_width, s_depth,
+                  s_gidx, s_warp, &s_base);
+}
+
+// Depth-first binning, step 1: R1 only.  Also writes the 32-bit sort key of every Gaussian (its depth bits; culled
+// Gaussians get 0xffffffff) and its rect, so that the emission can run later in depth order.
+__global__ void __launch_bounds__(GEO_THREADS) preprocess_kernel(const GeoParams p) {
+    __shared__ float s_view[16], s_proj[16], s_cam[3];
+    const int tid = threadIdx.x;
+    if (tid < 16) { s_view[tid] = p.view[tid]; s_proj[tid] = p.proj[tid]; }
+    if (tid < 3) s_cam[tid] = p.campos[tid];
+    __syncthreads();
+    const int idx = (int)(blockIdx.x * GEO_THREADS + tid);
+    if (idx >= p.P) return;
+    uint32_t count, rect, width, dbits;
+    preprocess_one(p, idx, s_view, s_proj, s_cam, count, rect, width, dbits);
+    p.rect_pack[idx] = make_uint2(rect, width);
+    p.dkeys[idx] = count ? dbits : 0xffffffffu;
+    p.dvals[idx] = (uint32_t)idx;
+}
+
+// Depth-first binning, step 3: R2 + R3 over the Gaussians in depth order (`order` = values of the depth sort).  The
+// duplicate list comes out ordered by (depth, Gaussian), so the global sort only has to run on the tile digits.
+__global__ void __launch_bounds__(GEO_THREADS) emit_sorted_kernel(const GeoParams p) {
+    GEO_SMEM_DECL
+    const int tid = threadIdx.x;
+    if (tid == 0) s_bid = atomicAdd(&p.hdr->geo_ticket, 1u);
+    __syncthreads();
+    const uint32_t bid = s_bid;
+    const int slot = (int)(bid * GEO_THREADS + tid);
+    uint32_t count = 0, rect = 0, width = 0, dbits = 0, g = 0;
+    if (slot < p.P) {
+        const uint32_t *order = p.hdr->dep_final_sel ? p.dvals + p.P_pad : p.dvals;
+        g = order[slot];
+        count = p.tiles[g];
+        if (count) {
+            const uint2 rw = p.rect_pack[g];
+            rect = rw.x; width = rw.y;
+            dbits = __float_as_uint(p.depth[g]);
+        }
+    }
+    scan_and_emit(p, bid, tid, slot < p.P, g, count, rect, width, dbits, s_excl, s_rect, s_width, s_depth, s_gidx, s_warp,
+                  &s_base);
 }
 
 }  // namespace
@@ -352,11 +415,30 @@ int launch_geometry(int P, int sh_degree, int sh_coeffs, const float *means3D, c
     // header + look-back words start at zero
     D3GA_CUDA(cudaMemsetAsync(geom + GL.header, 0, sizeof(RasterHeader), stream));
     D3GA_CUDA(cudaMemsetAsync(geom + GL.scan_state, 0, 8ull * (p.num_ctas + 1), stream));
-    if (p.num_ctas > 0) {
+    p.rect_pack = reinterpret_cast<uint2 *>(geom + GL.rect_pack);
+    p.dkeys = reinterpret_cast<uint32_t *>(geom + GL.dkeys);
+    p.dvals = reinterpret_cast<uint32_t *>(geom + GL.dvals);
+    p.P_pad = (uint32_t)GL.p_pad;
+    if (p.num_ctas == 0) return D3GA_OK;
+    if (sort_mode() != SORT_DEPTH_FIRST) {
         ProfScope prof(K_GEOMETRY, stream);
         geometry_kernel<<<p.num_ctas, GEO_THREADS, 0, stream>>>(p);
         D3GA_LAUNCH_CHECK();
+        return D3GA_OK;
     }
+    // depth-first binning: preprocess -> sort the Gaussians by depth (N elements) -> emit the duplicates in that order
+    {
+        ProfScope prof(K_PREPROCESS, stream);
+        preprocess_kernel<<<p.num_ctas, GEO_THREADS, 0, stream>>>(p);
+    }
+    D3GA_LAUNCH_CHECK();
+    int rc = launch_depth_sort(P, geom, GL, stream);
+    if (rc) return rc;
+    {
+        ProfScope prof(K_EMIT, stream);
+        emit_sorted_kernel<<<p.num_ctas, GEO_THREADS, 0, stream>>>(p);
+    }
+    D3GA_LAUNCH_CHECK();
     return D3GA_OK;
 }
 

@@ -142,38 +142,43 @@ __global__ void __launch_bounds__(HIST_THREADS) sort_histogram_kernel(RasterHead
     }
 }
 
-constexpr int SORT_SMEM_KEYS = SORT_TILE * 8;
-constexpr int SORT_SMEM_VALS = SORT_TILE * 4;
 constexpr int SORT_WARPS = SORT_THREADS / 32;
-constexpr int SORT_SMEM_BYTES = SORT_SMEM_KEYS + SORT_SMEM_VALS + 4 * (SORT_WARPS * 256 + 256 + 256 + 16);
+template <typename KeyT>
+constexpr int sort_smem_bytes() {
+    return SORT_TILE * (int)sizeof(KeyT) + SORT_TILE * 4 + 4 * (SORT_WARPS * 256 + 256 + 256 + 16);
+}
 
-__global__ void __launch_bounds__(SORT_THREADS) sort_pass_kernel(RasterHeader *hdr, uint64_t *keys0, uint64_t *keys1,
+// PLAN 0: the (tile|depth) duplicate list, count and plan from the header (num_rendered, pass_*).
+// PLAN 1: the 32-bit depth keys of the Gaussians (depth-first binning), count = n_fixed, plan in dep_*.
+template <typename KeyT, int PLAN>
+__global__ void __launch_bounds__(SORT_THREADS) sort_pass_kernel(RasterHeader *hdr, KeyT *keys0, KeyT *keys1,
                                                                  uint32_t *vals0, uint32_t *vals1,
                                                                  const uint32_t *bins, uint32_t *tile_state,
                                                                  uint32_t tiles_cap, int pass, int shift,
-                                                                 uint32_t mask) {
+                                                                 uint32_t mask, uint32_t n_fixed) {
     extern __shared__ __align__(16) uint8_t smem[];
-    uint64_t *s_keys = reinterpret_cast<uint64_t *>(smem);
-    uint32_t *s_vals = reinterpret_cast<uint32_t *>(smem + SORT_SMEM_KEYS);
+    KeyT *s_keys = reinterpret_cast<KeyT *>(smem);
+    uint32_t *s_vals = reinterpret_cast<uint32_t *>(smem + SORT_TILE * sizeof(KeyT));
     uint32_t *s_whist = s_vals + SORT_TILE;         // [warps][256] per-warp digit counts -> exclusive over warps
     uint32_t *s_start = s_whist + SORT_WARPS * 256; // [256] first slot of each digit inside the tile
     uint32_t *s_gbase = s_start + 256;              // [256] global slot of s_start[d] minus s_start[d]
     uint32_t *s_misc = s_gbase + 256;               // [0..7] scan scratch, [8] tile id
 
-    if (hdr->overflow || hdr->pass_skip[pass]) return;
-    const uint32_t D = hdr->num_rendered;
+    if (PLAN == 0 ? (hdr->overflow || hdr->pass_skip[pass]) : hdr->dep_skip[pass]) return;
+    const uint32_t D = PLAN == 0 ? hdr->num_rendered : n_fixed;
+    uint32_t *ticket = PLAN == 0 ? &hdr->pass_ticket[pass] : &hdr->dep_ticket[pass];
+    const uint32_t src = PLAN == 0 ? hdr->pass_src[pass] : hdr->dep_src[pass];
     const int tid = threadIdx.x;
     const uint32_t lane = lane_id(), warp = tid >> 5;
-    if (tid == 0) s_misc[8] = atomicAdd(&hdr->pass_ticket[pass], 1u);
+    if (tid == 0) s_misc[8] = atomicAdd(ticket, 1u);
     __syncthreads();
     const uint32_t tile = s_misc[8];
     const uint64_t tile_base = (uint64_t)tile * SORT_TILE;
     if (tile_base >= D) return;
     const uint32_t n_valid = (uint32_t)min((uint64_t)SORT_TILE, (uint64_t)D - tile_base);
-    const uint32_t src = hdr->pass_src[pass];
-    const uint64_t *kin = src ? keys1 : keys0;
+    const KeyT *kin = src ? keys1 : keys0;
     const uint32_t *vin = src ? vals1 : vals0;
-    uint64_t *kout = src ? keys0 : keys1;
+    KeyT *kout = src ? keys0 : keys1;
     uint32_t *vout = src ? vals0 : vals1;
 
     uint32_t *wh = s_whist + warp * 256;
@@ -182,14 +187,14 @@ __global__ void __launch_bounds__(SORT_THREADS) sort_pass_kernel(RasterHeader *h
 
     // warp w owns the contiguous chunk [w*512, (w+1)*512) of the tile, read 32 consecutive pairs at a time, so
     // (warp, round, lane) order is the input order -- which is what makes the ranking stable.
-    uint64_t key[SORT_ITEMS];
+    KeyT key[SORT_ITEMS];
     uint32_t val[SORT_ITEMS];
     const uint32_t chunk = warp * (32 * SORT_ITEMS);
 #pragma unroll
     for (int r = 0; r < SORT_ITEMS; r++) {
         const uint32_t local = chunk + r * 32 + lane;
         const bool ok = local < n_valid;
-        key[r] = ok ? __ldcs(kin + tile_base + local) : ~0ull;
+        key[r] = ok ? __ldcs(kin + tile_base + local) : (KeyT)~(KeyT)0;
         val[r] = ok ? __ldcs(vin + tile_base + local) : 0u;
     }
     __syncwarp();
@@ -274,12 +279,63 @@ __global__ void __launch_bounds__(SORT_THREADS) sort_pass_kernel(RasterHeader *h
     __syncthreads();
     // runs of equal digits go to consecutive global slots
     for (uint32_t i = tid; i < n_valid; i += SORT_THREADS) {
-        const uint64_t k = s_keys[i];
+        const KeyT k = s_keys[i];
         const uint32_t dg = (uint32_t)(k >> shift) & mask;
         const uint32_t dst = s_gbase[dg] + i;
         kout[dst] = k;
         vout[dst] = s_vals[i];
     }
+}
+
+// Digit counts of the Gaussians' 32-bit depth keys (depth-first binning) and the plan of that sort.  Culled Gaussians
+// carry the key 0xffffffff: they are counted (they move in every executed pass) but do not stop a pass from being
+// skipped -- a pass in which every VISIBLE key has the same digit is the identity for the visible keys.
+__global__ void __launch_bounds__(HIST_THREADS) depth_histogram_kernel(RasterHeader *hdr, const uint32_t *keys,
+                                                                       uint32_t n, uint32_t *ghist, uint32_t *bins) {
+    __shared__ uint32_t s_hist[4][256];
+    __shared__ uint32_t s_tmp[8];
+    __shared__ uint32_t s_culled, s_flag;
+    const int tid = threadIdx.x;
+    for (int p = 0; p < 4; p++) s_hist[p][tid] = 0;
+    if (tid == 0) s_culled = 0;
+    __syncthreads();
+    uint32_t culled = 0;
+    for (uint32_t i = blockIdx.x * HIST_THREADS + tid; i < n; i += gridDim.x * HIST_THREADS) {
+        const uint32_t k = __ldcs(keys + i);
+        culled += k == 0xffffffffu;
+#pragma unroll
+        for (int p = 0; p < 4; p++) atomicAdd(&s_hist[p][(k >> (8 * p)) & 255u], 1u);
+    }
+    culled = __reduce_add_sync(0xffffffffu, culled);
+    if ((tid & 31) == 0 && culled) atomicAdd(&s_culled, culled);
+    __syncthreads();
+    for (int p = 0; p < 4; p++) {
+        const uint32_t c = s_hist[p][tid];
+        if (c) atomicAdd(&ghist[p * 256 + tid], c);
+    }
+    if (tid == 0 && s_culled) atomicAdd(&hdr->dep_culled, s_culled);
+    __threadfence();
+    __syncthreads();
+    if (tid == 0) s_flag = atomicAdd(&hdr->dep_hist_done, 1u) == gridDim.x - 1;
+    __syncthreads();
+    if (!s_flag) return;
+    __threadfence();
+    const uint32_t n_culled = *((volatile uint32_t *)&hdr->dep_culled);
+    const uint32_t n_visible = n - n_culled;
+    uint32_t src = 0;
+    for (int p = 0; p < 4; p++) {
+        const uint32_t c = __ldcg(ghist + p * 256 + tid);
+        const uint32_t cv = c - (tid == 255 ? n_culled : 0u);
+        const int all_in_one = __syncthreads_or(n_visible == 0 || cv == n_visible);
+        const uint32_t ex = block_excl_scan_256(c, s_tmp, nullptr);
+        bins[p * 256 + tid] = ex;
+        if (tid == 0) {
+            hdr->dep_skip[p] = all_in_one ? 1u : 0u;
+            hdr->dep_src[p] = src;
+        }
+        if (!all_in_one) src ^= 1u;
+    }
+    if (tid == 0) hdr->dep_final_sel = src;
 }
 
 __global__ void __launch_bounds__(256) tile_ranges_kernel(RasterHeader *hdr, const uint64_t *keys0,
@@ -333,14 +389,18 @@ int launch_sort_and_ranges(uint8_t *geom, uint8_t *binning, const BinLayout &BL,
     const int num_passes = (sort_bits + 7) / 8;
     if (num_passes > SORT_MAX_PASSES) return D3GA_EINVAL;
     const uint32_t tiles_cap = (uint32_t)sort_tiles(capacity);
-    // Default: the full 64-bit LSD sort (depth digits first, constant digits skipped).  D3GA_SORT_MODE=segmented runs
-    // the global passes on the tile digits only and sorts each tile's depths in shared memory (raster_segsort.cu);
-    // measured equal on B200 (profiles/), kept for A/B measurements.
-    static const bool segmented = getenv("D3GA_SORT_MODE") && strcmp(getenv("D3GA_SORT_MODE"), "segmented") == 0;
-    const int first_pass = segmented ? 4 : 0;
+    // depth-first (default): the duplicate list was emitted in depth order, only the tile digits are left to sort.
+    // global   : the full 64-bit LSD sort (depth digits first, constant digits skipped).
+    // segmented: tile digits globally, then each tile's depths in shared memory (raster_segsort.cu).
+    const int mode = sort_mode();
+    const bool segmented = mode == SORT_SEGMENTED;
+    const int first_pass = mode == SORT_GLOBAL ? 0 : 4;
 
     if (!g_sort_attr_set) {
-        D3GA_CUDA(cudaFuncSetAttribute(sort_pass_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SORT_SMEM_BYTES));
+        D3GA_CUDA(cudaFuncSetAttribute(sort_pass_kernel<uint64_t, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       sort_smem_bytes<uint64_t>()));
+        D3GA_CUDA(cudaFuncSetAttribute(sort_pass_kernel<uint32_t, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       sort_smem_bytes<uint32_t>()));
         g_sort_attr_set = 1;
     }
     D3GA_CUDA(cudaMemsetAsync(ghist, 0, 4 * 256 * SORT_MAX_PASSES, stream));
@@ -362,8 +422,8 @@ int launch_sort_and_ranges(uint8_t *geom, uint8_t *binning, const BinLayout &BL,
         const int nb = sort_bits - shift < 8 ? sort_bits - shift : 8;
         {
             ProfScope prof(K_SORT_PASS, stream);
-            sort_pass_kernel<<<tiles_cap, SORT_THREADS, SORT_SMEM_BYTES, stream>>>(
-                hdr, keys0, keys1, vals0, vals1, bins, tile_state, tiles_cap, p, shift, (1u << nb) - 1u);
+            sort_pass_kernel<uint64_t, 0><<<tiles_cap, SORT_THREADS, sort_smem_bytes<uint64_t>(), stream>>>(
+                hdr, keys0, keys1, vals0, vals1, bins, tile_state, tiles_cap, p, shift, (1u << nb) - 1u, 0u);
         }
         D3GA_LAUNCH_CHECK();
     }
@@ -377,6 +437,43 @@ int launch_sort_and_ranges(uint8_t *geom, uint8_t *binning, const BinLayout &BL,
     }
     D3GA_LAUNCH_CHECK();
     if (segmented) return launch_segment_sort(geom, binning, BL, image, IL, num_tiles, stream);
+    return D3GA_OK;
+}
+
+// The 32-bit depth sort of the Gaussians that precedes the key emission in depth-first mode.
+int launch_depth_sort(int P, uint8_t *geom, const GeomLayout &GL, cudaStream_t stream) {
+    RasterHeader *hdr = reinterpret_cast<RasterHeader *>(geom + GL.header);
+    uint32_t *dkeys = reinterpret_cast<uint32_t *>(geom + GL.dkeys);
+    uint32_t *dvals = reinterpret_cast<uint32_t *>(geom + GL.dvals);
+    uint32_t *ghist = reinterpret_cast<uint32_t *>(geom + GL.dep_hist);
+    uint32_t *bins = reinterpret_cast<uint32_t *>(geom + GL.dep_bins);
+    uint32_t *state = reinterpret_cast<uint32_t *>(geom + GL.dep_state);
+    const uint32_t tiles = (uint32_t)((P + SORT_TILE - 1) / SORT_TILE);
+    if (!g_sort_attr_set) {
+        D3GA_CUDA(cudaFuncSetAttribute(sort_pass_kernel<uint64_t, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       sort_smem_bytes<uint64_t>()));
+        D3GA_CUDA(cudaFuncSetAttribute(sort_pass_kernel<uint32_t, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       sort_smem_bytes<uint32_t>()));
+        g_sort_attr_set = 1;
+    }
+    D3GA_CUDA(cudaMemsetAsync(ghist, 0, 4 * 256 * 4, stream));
+    D3GA_CUDA(cudaMemsetAsync(state, 0, 4ull * 256 * 4 * (tiles + 1), stream));
+    int grid = (P + HIST_THREADS * 4 - 1) / (HIST_THREADS * 4);
+    if (grid > 148 * 8) grid = 148 * 8;
+    if (grid < 1) grid = 1;
+    {
+        ProfScope prof(K_DEPTH_HIST, stream);
+        depth_histogram_kernel<<<grid, HIST_THREADS, 0, stream>>>(hdr, dkeys, (uint32_t)P, ghist, bins);
+    }
+    D3GA_LAUNCH_CHECK();
+    for (int p = 0; p < 4; p++) {
+        {
+            ProfScope prof(K_DEPTH_PASS, stream);
+            sort_pass_kernel<uint32_t, 1><<<tiles, SORT_THREADS, sort_smem_bytes<uint32_t>(), stream>>>(
+                hdr, dkeys, dkeys + GL.p_pad, dvals, dvals + GL.p_pad, bins, state, tiles, p, 8 * p, 255u, (uint32_t)P);
+        }
+        D3GA_LAUNCH_CHECK();
+    }
     return D3GA_OK;
 }
 

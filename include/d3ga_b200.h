@@ -144,9 +144,10 @@ enum {
     D3GA_L_GEOM_RGB,        /* float  [P,3] (SH path; the colors_precomp path reads the caller's tensor)   */
     D3GA_L_GEOM_COV3D,      /* float  [P,6] (scales/rotations path)                                        */
     D3GA_L_GEOM_TILES,      /* uint32 [P] tiles touched                                                    */
-    D3GA_L_GEOM_OFFSETS,    /* uint32 [P] inclusive prefix sum of tiles touched                            */
+    D3GA_L_GEOM_OFFSETS,    /* uint32 [P] inclusive prefix sum of tiles touched, in emission order         */
     D3GA_L_GEOM_CLAMPED,    /* uint8  [P,3]                                                                */
-    D3GA_L_BIN_KEYS0,       /* uint64 [capacity]  unsorted keys after stage 1                              */
+    D3GA_L_BIN_KEYS0,       /* uint64 [capacity]  unsorted keys after stage 1 (emission order: by depth in the
+                             * default depth-first binning, by Gaussian index with D3GA_SORT_MODE=global)   */
     D3GA_L_BIN_KEYS1,       /* uint64 [capacity]                                                           */
     D3GA_L_BIN_VALS0,       /* uint32 [capacity]  unsorted Gaussian indices after stage 1                  */
     D3GA_L_BIN_VALS1,       /* uint32 [capacity]                                                           */
