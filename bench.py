@@ -287,6 +287,30 @@ def run_ours(args):
                "inputs_from_host": "per view: camera (35 floats), cage vertices tetpoints [V,3], target/weight image [3,H,W]; "
                                    "loss scalar read back per view; Gaussian parameters stay resident like nn.Parameters"}
 
+    # a D3GA training FRAME renders the same Gaussians twice (RGB + silhouette); frames/s with and
+    # without sharing R1-R5 between the two renders (extra information, not the headline metric)
+    pair = None
+    if rank == 0 and world == 1 and not args.no_e2e:
+        from d3ga_b200 import diff_gaussian_rasterization as dgr
+        pair = {}
+        for share in (True, False):
+            dgr.SHARE_GEOMETRY = share
+            dgr._geom_cache.clear()
+            for i in range(3):
+                avatar.grads.zero_()
+                training.frame_step(avatar, bank, mine[i % len(mine)], weights, bg)
+            torch.cuda.synchronize()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            nfr = 2 * V
+            a.record()
+            for i in range(nfr):
+                training.frame_step(avatar, bank, mine[(3 + i) % len(mine)], weights, bg)
+            b.record()
+            torch.cuda.synchronize()
+            pair["frames_per_s_shared_geometry" if share else "frames_per_s_independent_renders"] = nfr / (a.elapsed_time(b) * 1e-3)
+        dgr.SHARE_GEOMETRY = True
+        pair["note"] = "1 frame = deformation + RGB render + silhouette render + backward of both (models/trainer.py:91-140)"
+
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         n = 2 if scene.N >= 500_000 else 4
@@ -300,7 +324,7 @@ def run_ours(args):
                 "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
                 "vs_baseline": None, "dtype": "f32", "data": "synthetic", "impl": "ours",
                 "config": workload_config(scene, args, V), "clocks": clk, "e2e": e2e, "gpu_launches": int(launches),
-                "roofline": roof, "cpu_baseline": cpu,
+                "roofline": roof, "cpu_baseline": cpu, "training_frame_pair": pair,
                 "allreduce_bytes_per_step": avatar.grads.nbytes() if world > 1 else 0}
         print(json.dumps(line), flush=True)
     if world > 1:

@@ -185,6 +185,29 @@ int d3ga_raster_forward_render(int P, int W, int H, const float *background, con
                                 (uint8_t *)image, IL, out_color, out_invdepth, stream);
 }
 
+int d3ga_raster_forward_blend(int P, int W, int H, const float *background, const float *colors_precomp, void *geom,
+                              const void *binning, uint64_t capacity, const void *tile_src_image, void *image,
+                              float *out_color, float *out_invdepth, d3ga_stream_t stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    if (P < 0 || W <= 0 || H <= 0 || !geom || !binning || !image || !tile_src_image || !background || !out_color)
+        return D3GA_EINVAL;
+    if (capacity > MAX_DUPLICATES) return D3GA_ETOOBIG;
+    const GeomLayout GL = geom_layout(P);
+    const BinLayout BL = bin_layout(capacity);
+    const ImgLayout IL = img_layout(W, H);
+    const uint64_t tiles = (uint64_t)((W + TILE - 1) / TILE) * ((H + TILE - 1) / TILE);
+    // per-tile ranges and the forward launch order come from the render that did the binning
+    D3GA_CUDA(cudaMemcpyAsync((uint8_t *)image + IL.ranges, (const uint8_t *)tile_src_image + IL.ranges, 8 * tiles,
+                              cudaMemcpyDeviceToDevice, stream));
+    D3GA_CUDA(cudaMemcpyAsync((uint8_t *)image + IL.order_fwd, (const uint8_t *)tile_src_image + IL.order_fwd,
+                              4 * tiles, cudaMemcpyDeviceToDevice, stream));
+    RasterHeader *hdr = reinterpret_cast<RasterHeader *>((uint8_t *)geom + GL.header);
+    D3GA_CUDA(cudaMemsetAsync(&hdr->blend_done, 0, sizeof(uint32_t), stream));
+    const float *colors = colors_precomp ? colors_precomp : reinterpret_cast<const float *>((uint8_t *)geom + GL.rgb);
+    return launch_blend_forward(W, H, background, colors, (const uint8_t *)geom, GL, (const uint8_t *)binning, BL,
+                                (uint8_t *)image, IL, out_color, out_invdepth, stream);
+}
+
 uint64_t d3ga_raster_backward_scratch_bytes(int P) { return align256((uint64_t)(P > 0 ? P : 1) * GRAD_ACC_FLOATS * 4); }
 
 int d3ga_raster_backward(int P, int sh_degree, int sh_coeffs, int W, int H, const float *background,

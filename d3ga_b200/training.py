@@ -50,6 +50,7 @@ class Avatar:
         self.rotation = t(scene.rotation).requires_grad_(True)
         self.opacity = t(scene.opacity).requires_grad_(True)
         self.colors = t(scene.colors).requires_grad_(True)
+        self.silhouette = torch.ones_like(self.colors)   # models/cage_net.py:249 silhouette_rgb
         self.params = [self.tetpoints, self.barys, self.scales, self.rotation, self.opacity, self.colors]
         self.grads = ddist.FlatGrads(self.params)
         self.tetpoints_host = torch.from_numpy(scene.tetpoints.copy())
@@ -91,3 +92,22 @@ def multi_view_step(avatar, bank, cam_ids, weights, bg, from_host=False, weights
         total = loss.detach() if total is None else total + loss.detach()
     avatar.grads.all_reduce()
     return total
+
+
+def frame_step(avatar, bank, cam_id, weights, bg):
+    """One D3GA training frame on the hot path (models/trainer.py:91-140): the deformation once, then TWO renders of the
+    same Gaussians -- RGB on a random background and the silhouette (constant colour, black background), each through
+    its own render() call with its own Camera object -- and one backward through both."""
+    means3D, cov6 = deform_gaussians(avatar.tetpoints, avatar.tets, avatar.tetra_id, avatar.barys, avatar.cg,
+                                     avatar.scales, avatar.rotation)
+    imgs = []
+    for colors, background in ((avatar.colors, bg), (avatar.silhouette, torch.zeros_like(bg))):
+        rs = bank.settings(cam_id, avatar.W, avatar.H, background)
+        rs = rs._replace(viewmatrix=rs.viewmatrix.clone(), projmatrix=rs.projmatrix.clone(), campos=rs.campos.clone())
+        means2D = torch.zeros_like(means3D, requires_grad=True) + 0
+        imgs.append(GaussianRasterizer(raster_settings=rs)(
+            means3D=means3D, means2D=means2D, shs=None, colors_precomp=colors, opacities=avatar.opacity, scales=None,
+            rotations=None, cov3D_precomp=cov6)[0])
+    loss = (imgs[0] * weights).sum() + (imgs[1] * weights).sum()
+    loss.backward()
+    return loss

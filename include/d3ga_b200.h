@@ -88,6 +88,17 @@ int d3ga_raster_forward_render(int P, int W, int H, const float *background, con
                                void *geom, void *binning, uint64_t capacity, void *image,
                                float *out_color, float *out_invdepth, d3ga_stream_t stream);
 
+/* Alpha blending (R6) alone, on the geometry and binning state an earlier d3ga_raster_forward_geometry +
+ * d3ga_raster_forward_render pair left in `geom` / `binning` -- for a second render of the SAME Gaussians from the SAME
+ * camera with other colours / background.  D3GA does exactly that every training frame: the RGB and the silhouette
+ * render of models/trainer.py:102-110 share means, covariances and opacities, so R1-R5 need to run once
+ * (SURVEY.md 8(f) rank 1).  `tile_src_image` is the image workspace of the render that did the binning (its per-tile
+ * ranges and launch order are copied into `image`, which must be a different buffer).  The two renders then have
+ * separate image workspaces and may be differentiated independently with d3ga_raster_backward. */
+int d3ga_raster_forward_blend(int P, int W, int H, const float *background, const float *colors_precomp, void *geom,
+                              const void *binning, uint64_t capacity, const void *tile_src_image, void *image,
+                              float *out_color, float *out_invdepth, d3ga_stream_t stream);
+
 /* Backward = blend backward (R7) + preprocess backward (R8).
  * Inputs are the forward's inputs and workspaces plus dL_dout_color [3,H,W] (and optionally dL_dout_invdepth
  * [H,W]).  Outputs (written, not accumulated): dL_dmeans3D [P,3], dL_dmeans2D [P,3], dL_dopacity [P],

@@ -385,3 +385,62 @@ def test_sh_degrees(cuda_lib, oracle_libs, deg, M):
     assert util.rel_l2(gsh.cpu().numpy(), rg["sh"]) < GRAD_TOL
     assert util.rel_l2(gm3.cpu().numpy(), rg["means3D"]) < GRAD_TOL
     assert np.all(gsh.cpu().numpy()[:, (deg + 1) ** 2:] == 0)
+
+
+def test_shared_geometry_second_render(cuda_lib, oracle_libs):
+    """models/trainer.py:102-110: the RGB render and the silhouette render of a frame pass the SAME means / covariance /
+    opacity tensors and an equal camera; the second call must re-use the first call's binning and still give exactly
+    the image and gradients of an independent render."""
+    from d3ga_b200 import diff_gaussian_rasterization as dgr
+    from d3ga_b200.diff_gaussian_rasterization import GaussianRasterizationSettings, GaussianRasterizer
+
+    g, cam, W, H = CASES["tiny_avatar"]
+    d = gpu_util.dev
+
+    def settings(bg):   # a fresh Camera per render() call, like renderer.py:70
+        return GaussianRasterizationSettings(
+            image_height=H, image_width=W, tanfovx=cam.tanfovx, tanfovy=cam.tanfovy, bg=d(np.asarray(bg, np.float32)),
+            scale_modifier=1.0, viewmatrix=d(cam.viewmatrix), projmatrix=d(cam.projmatrix), sh_degree=0,
+            campos=d(cam.campos), prefiltered=False, debug=False, antialiasing=False)
+
+    means = d(g["means"]).requires_grad_(True)
+    cov = d(g["cov6"]).requires_grad_(True)
+    op = d(g["opacity"]).requires_grad_(True)
+    rgb = d(g["colors"]).requires_grad_(True)
+    sil = torch.ones_like(rgb).requires_grad_(True)
+    dgr._geom_cache.clear()
+    h0, m0 = dgr.share_stats["hits"], dgr.share_stats["misses"]
+    img1 = GaussianRasterizer(settings([0.3, 0.6, 0.9]))(means3D=means, means2D=torch.zeros_like(means), opacities=op,
+                                                        colors_precomp=rgb, cov3D_precomp=cov)[0]
+    img2 = GaussianRasterizer(settings([0, 0, 0]))(means3D=means, means2D=torch.zeros_like(means), opacities=op,
+                                                  colors_precomp=sil, cov3D_precomp=cov)[0]
+    assert dgr.share_stats["hits"] == h0 + 1 and dgr.share_stats["misses"] == m0 + 1
+    rng = np.random.default_rng(8)
+    w1, w2 = (d(rng.uniform(-1, 1, (3, H, W)).astype(np.float32)) for _ in range(2))
+    ((img1 * w1).sum() + (img2 * w2).sum()).backward()
+    # oracle: two independent renders
+    g2 = dict(g, colors=np.ones_like(g["colors"]))
+    o1, r1 = util.oracle_forward(g, cam, W, H, [0.3, 0.6, 0.9])
+    o2, r2 = util.oracle_forward(g2, cam, W, H, [0, 0, 0])
+    assert_image_close(img1.detach().cpu().numpy(), r1["color"])
+    assert_image_close(img2.detach().cpu().numpy(), r2["color"])
+    ga, gb = o1.backward(r1, w1.cpu().numpy()), o2.backward(r2, w2.cpu().numpy())
+    assert util.rel_l2(means.grad.cpu().numpy(), ga["means3D"] + gb["means3D"]) < GRAD_TOL
+    assert util.rel_l2(cov.grad.cpu().numpy(), ga["cov3D"] + gb["cov3D"]) < GRAD_TOL
+    assert util.rel_l2(op.grad.cpu().numpy().ravel(), ga["opacity"] + gb["opacity"]) < GRAD_TOL
+    assert util.rel_l2(rgb.grad.cpu().numpy(), ga["colors"]) < GRAD_TOL
+    assert util.rel_l2(sil.grad.cpu().numpy(), gb["colors"]) < GRAD_TOL
+    # an in-place update of the geometry (optimizer step) or another camera must miss
+    with torch.no_grad():
+        means.add_(0.0)
+    h1 = dgr.share_stats["hits"]
+    GaussianRasterizer(settings([0, 0, 0]))(means3D=means, means2D=torch.zeros_like(means), opacities=op,
+                                           colors_precomp=sil, cov3D_precomp=cov)
+    assert dgr.share_stats["hits"] == h1
+    cam2 = synth.make_camera(W, H, 80, 0)
+    rs2 = settings([0, 0, 0])._replace(viewmatrix=d(cam2.viewmatrix), projmatrix=d(cam2.projmatrix), campos=d(cam2.campos))
+    img3 = GaussianRasterizer(rs2)(means3D=means, means2D=torch.zeros_like(means), opacities=op, colors_precomp=sil,
+                                   cov3D_precomp=cov)[0]
+    assert dgr.share_stats["hits"] == h1
+    _, r3 = util.oracle_forward(g2, cam2, W, H, [0, 0, 0])
+    assert_image_close(img3.detach().cpu().numpy(), r3["color"])
