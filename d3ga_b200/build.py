@@ -26,6 +26,7 @@ SOURCES = [
     ("raster_backward.cu", []),
     ("raster_backward_noalloc.cu", []),
     ("deform.cu", []),
+    ("fem.cu", []),
     ("bary.cu", []),
 ]
 COMMON = [

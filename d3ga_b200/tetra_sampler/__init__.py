@@ -212,3 +212,37 @@ class _DeformGaussians(torch.autograd.Function):
 def deform_gaussians(tetpoints, tets, tetra_id, barys, canonical_gradient, scales, rotation):
     """Fused cage -> Gaussian deformation (models/cage_net.py:218-230).  Returns (means3D, cov3D_precomp)."""
     return _DeformGaussians.apply(tetpoints, tets, tetra_id, barys, canonical_gradient, scales, rotation)
+
+
+class _FemEnergy(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, tetpoints, tets, dn_inv):
+        lib = _lib.load()
+        tetpoints = _check(tetpoints, "tetpoints", torch.float32)
+        tets = _check(tets, "tets", torch.int64)
+        dn_inv = _check(dn_inv, "dn_inv", torch.float32)
+        T, V, dev = int(tets.shape[0]), int(tetpoints.shape[0]), tetpoints.device
+        with _lib.device_guard(dev):
+            energy = torch.empty((T,), dtype=torch.float32, device=dev)
+            _lib.check(lib.d3ga_fem_energy_forward(T, V, tetpoints.data_ptr(), _lib.ptr(tets), _lib.ptr(dn_inv),
+                                                   _lib.ptr(energy), _lib.raw_stream(dev)), "fem_energy_forward")
+        ctx.save_for_backward(tetpoints, tets, dn_inv)
+        return energy
+
+    @staticmethod
+    def backward(ctx, g):
+        lib = _lib.load()
+        tetpoints, tets, dn_inv = ctx.saved_tensors
+        T, V, dev = int(tets.shape[0]), int(tetpoints.shape[0]), tetpoints.device
+        with _lib.device_guard(dev):
+            g_tet = torch.zeros((V, 3), dtype=torch.float32, device=dev)
+            _lib.check(lib.d3ga_fem_energy_backward(T, V, tetpoints.data_ptr(), _lib.ptr(tets), _lib.ptr(dn_inv),
+                                                    _lib.ptr(g.contiguous()), g_tet.data_ptr(), _lib.raw_stream(dev)),
+                       "fem_energy_backward")
+        return g_tet, None, None
+
+
+def fem_energy(tetpoints, tets, dn_inv):
+    """Per-tet stable neo-Hookean energy of CageBase.fem_energy (lib/cage.py:349-361), fused forward and backward.
+    ``dn_inv`` = inverse rest-pose edge matrices ``inv(G(rest_points[tets]))`` (lib/cage.py:312-313).  Returns [T]."""
+    return _FemEnergy.apply(tetpoints, tets, dn_inv)

@@ -196,6 +196,16 @@ int d3ga_deform_backward_ordered(int N, int V, int T, const float *tetpoints, co
                                  const float *dL_dcov3D, float *dL_dtetpoints, float *dL_dbarys, float *dL_dscales,
                                  float *dL_drotation, const int32_t *order, d3ga_stream_t stream);
 
+/* ---- cage FEM energy ------------------------------------------------------------
+ * Replaces CageBase.fem_energy (lib/cage.py:349-361, called at models/cage_net.py:225) and its autograd backward:
+ * per tet, F = G(tetpoints[tets]) @ dn_inv, energy = 0.5 (det F - 1)^2 + 0.5 (tr(F^T F) - 3).
+ * tetpoints [V,3] f32; tets [T,4] int64; dn_inv [T,3,3] f32 (inverse rest-pose edge matrices, lib/cage.py:312-313);
+ * energy [T] f32.  The backward ACCUMULATES into dL_dtetpoints [V,3] (caller zeroes it). */
+int d3ga_fem_energy_forward(int T, int V, const float *tetpoints, const int64_t *tets, const float *dn_inv,
+                            float *energy, d3ga_stream_t stream);
+int d3ga_fem_energy_backward(int T, int V, const float *tetpoints, const int64_t *tets, const float *dn_inv,
+                             const float *dL_denergy, float *dL_dtetpoints, d3ga_stream_t stream);
+
 /* ---- barycentric embedding -------------------------------------------------------
  * Replaces tetra_sampler.compute_bary (submodules/tetra-sampler/tetra_sampler/barys.py:9-33): the nearest-face
  * query of bvh_distance_queries.BVH (bvh_cuda_op.cu:1065-1269) followed by barycentric_kernel

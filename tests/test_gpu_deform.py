@@ -83,3 +83,26 @@ def test_compute_bary_backward_raises(cuda_lib):
     barys, _, _ = compute_bary(x, cage.get_positions(), cage.get_triangles(), cage.triangle_to_tetra, cage)
     with pytest.raises(NotImplementedError):
         barys.sum().backward()
+
+
+def test_fem_energy_forward_backward_vs_oracle(cuda_lib):
+    """the fused neo-Hookean cage energy (lib/cage.py:349-361) against its torch restatement."""
+    from d3ga_b200.tetra_sampler import fem_energy
+
+    sc = synth.make_workload("c1")
+    rest = t(sc.canon_points)
+    tets = t(sc.tets)
+    dn_inv = torch.linalg.inv(do.tet_gradient(rest[tets]))
+    x_cpu = t(sc.tetpoints).clone().requires_grad_(True)
+    e_ref = do.fem_energy(x_cpu, tets, dn_inv)
+    x_gpu = t(sc.tetpoints).cuda().requires_grad_(True)
+    e = fem_energy(x_gpu, tets.cuda(), dn_inv.cuda())
+    assert e.shape == e_ref.shape
+    assert np.allclose(e.detach().cpu().numpy(), e_ref.detach().numpy(), rtol=1e-4, atol=1e-5)
+    w = t(np.random.default_rng(1).uniform(0.5, 1.5, size=e_ref.shape).astype(np.float32))
+    (e_ref * w).mean().backward()
+    (e * w.cuda()).mean().backward()
+    assert util.rel_l2(x_gpu.grad.cpu().numpy(), x_cpu.grad.numpy()) < 1e-4
+    # rest pose: zero energy (its gradient is NOT zero there: dE/dF = F at F = I, it only cancels at interior vertices)
+    e0 = fem_energy(rest.cuda(), tets.cuda(), dn_inv.cuda())
+    assert float(e0.abs().max()) < 1e-4
