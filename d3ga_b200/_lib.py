@@ -19,7 +19,7 @@ EXPORTS = [
     "d3ga_raster_forward_blend",
     "d3ga_raster_backward_scratch_bytes", "d3ga_raster_backward", "d3ga_raster_backward_noalloc", "d3ga_raster_layout",
     "d3ga_deform_forward", "d3ga_deform_backward", "d3ga_deform_backward_ordered", "d3ga_compute_bary",
-    "d3ga_fem_energy_forward", "d3ga_fem_energy_backward",
+    "d3ga_fem_energy_forward", "d3ga_fem_energy_backward", "d3ga_ssim_l1_forward", "d3ga_ssim_l1_backward",
 ]
 
 LAYOUT_NAMES = [
@@ -78,6 +78,8 @@ def load() -> C.CDLL:
     lib.d3ga_deform_backward_ordered.argtypes = [i32, i32, i32] + [vp] * 15
     lib.d3ga_fem_energy_forward.argtypes = [i32, i32, vp, vp, vp, vp, vp]
     lib.d3ga_fem_energy_backward.argtypes = [i32, i32, vp, vp, vp, vp, vp, vp]
+    lib.d3ga_ssim_l1_forward.argtypes = [i32, i32, i32, vp, vp, vp, vp, vp, vp, vp]
+    lib.d3ga_ssim_l1_backward.argtypes = [i32, i32, i32, vp, vp, vp, vp, vp, f32, f32, vp, vp]
     lib.d3ga_compute_bary.argtypes = [i32, i32, i32, vp, vp, vp, vp, vp, vp, vp, vp, vp]
     for name in EXPORTS:
         getattr(lib, name)   # AttributeError if the build is stale

@@ -27,6 +27,7 @@ SOURCES = [
     ("raster_backward_noalloc.cu", []),
     ("deform.cu", []),
     ("fem.cu", []),
+    ("ssim.cu", []),
     ("bary.cu", []),
 ]
 COMMON = [

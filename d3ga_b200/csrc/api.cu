@@ -29,7 +29,8 @@ static const char *const g_kernel_names[K_COUNT] = {
     "geometry_kernel", "sort_histogram_kernel", "sort_pass_kernel", "tile_ranges_kernel", "blend_forward_kernel",
     "blend_backward_kernel", "preprocess_backward_kernel", "deform_forward_kernel", "deform_backward_kernel",
     "compute_bary_kernel", "segment_sort_kernel", "preprocess_kernel", "emit_sorted_kernel", "depth_histogram_kernel",
-    "depth_sort_pass_kernel", "fem_energy_forward_kernel", "fem_energy_backward_kernel"};
+    "depth_sort_pass_kernel", "fem_energy_forward_kernel", "fem_energy_backward_kernel",
+    "ssim_forward_kernel", "ssim_backward_kernel"};
 
 bool profiling_enabled() { return g_prof_on.load(std::memory_order_relaxed) != 0; }
 

@@ -206,6 +206,18 @@ int d3ga_fem_energy_forward(int T, int V, const float *tetpoints, const int64_t 
 int d3ga_fem_energy_backward(int T, int V, const float *tetpoints, const int64_t *tets, const float *dn_inv,
                              const float *dL_denergy, float *dL_dtetpoints, d3ga_stream_t stream);
 
+/* ---- fused L1 + SSIM image loss -------------------------------------------------
+ * Replaces utils/loss_utils.py:29-30 (l1_loss) and :59-90 (ssim, window 11, sigma 1.5, zero padding) with their
+ * autograd backward, as combined at train.py:190-193.  img1 (prediction), img2 (target): [C,H,W] f32.
+ * Forward: sums[0] = sum of the SSIM map, sums[1] = sum of |img1 - img2| (device, 2 floats, overwritten); the three
+ * derivative maps [C,H,W] are optional (all or none) and only needed for the backward.
+ * Backward: dL_dimg1 = g_ssim * dSSIMsum/dimg1 + g_l1 * sign(img1 - img2)  (written). */
+int d3ga_ssim_l1_forward(int C, int H, int W, const float *img1, const float *img2, float *sums, float *dm_dmu1,
+                         float *dm_dE11, float *dm_dE12, d3ga_stream_t stream);
+int d3ga_ssim_l1_backward(int C, int H, int W, const float *img1, const float *img2, const float *dm_dmu1,
+                          const float *dm_dE11, const float *dm_dE12, float g_ssim, float g_l1, float *dL_dimg1,
+                          d3ga_stream_t stream);
+
 /* ---- barycentric embedding -------------------------------------------------------
  * Replaces tetra_sampler.compute_bary (submodules/tetra-sampler/tetra_sampler/barys.py:9-33): the nearest-face
  * query of bvh_distance_queries.BVH (bvh_cuda_op.cu:1065-1269) followed by barycentric_kernel
