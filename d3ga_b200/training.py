@@ -75,22 +75,61 @@ def view_step(avatar, rs, weights):
     return loss
 
 
-def multi_view_step(avatar, bank, cam_ids, weights, bg, from_host=False, weights_host=None, loss_host=None):
-    """`cam_ids` views on this rank, then one all-reduce of the accumulated gradients."""
+class HostFeed:
+    """Per-view inputs that arrive from pinned host memory (the e2e arm of bench.py): the target / weight image is
+    copied on a side stream one view ahead into a double buffer, so the 3*H*W*4-byte upload overlaps the previous
+    view's kernels -- what a data loader with a prefetch queue does (train.py:426-434 uses pinned DataLoader memory)."""
+
+    def __init__(self, weights_host, device):
+        self.host = weights_host
+        self.stream = torch.cuda.Stream(device=device)
+        self.bufs = [torch.empty_like(weights_host, device=device) for _ in range(2)]
+        self.ready = [torch.cuda.Event() for _ in range(2)]
+        self.free = [torch.cuda.Event() for _ in range(2)]
+        for e in self.free:
+            e.record()
+        self.k = 0
+
+    def prefetch(self):
+        """Enqueue the upload of the next view's image; returns the slot it will land in."""
+        slot = self.k % 2
+        self.k += 1
+        with torch.cuda.stream(self.stream):
+            self.stream.wait_event(self.free[slot])      # the view that used this buffer has finished with it
+            self.bufs[slot].copy_(self.host, non_blocking=True)
+            self.ready[slot].record(self.stream)
+        return slot
+
+    def acquire(self, slot):
+        torch.cuda.current_stream().wait_event(self.ready[slot])
+        return self.bufs[slot]
+
+    def release(self, slot):
+        self.free[slot].record()
+
+
+def multi_view_step(avatar, bank, cam_ids, weights, bg, from_host=False, feed=None, loss_host=None):
+    """`cam_ids` views on this rank, then one all-reduce of the accumulated gradients.  With from_host, every view's
+    camera, cage vertices and target image come from pinned host memory and the step's loss is read back at the end."""
     avatar.grads.zero_()
     total = None
-    for i in cam_ids:
-        if from_host:   # e2e: this view's inputs arrive from pinned host memory, the loss goes back
+    slot = feed.prefetch() if from_host else None
+    for n, i in enumerate(cam_ids):
+        if from_host:
             with torch.no_grad():
                 avatar.tetpoints.copy_(avatar.tetpoints_host, non_blocking=True)
-                weights.copy_(weights_host, non_blocking=True)
+            weights = feed.acquire(slot)
+            nxt = feed.prefetch() if n + 1 < len(cam_ids) else None
         rs = bank.settings(i, avatar.W, avatar.H, bg, from_host=from_host)
         loss = view_step(avatar, rs, weights)
         if from_host:
-            loss_host.copy_(loss.detach(), non_blocking=True)
-            torch.cuda.current_stream().synchronize()
+            feed.release(slot)
+            slot = nxt
         total = loss.detach() if total is None else total + loss.detach()
     avatar.grads.all_reduce()
+    if from_host:
+        loss_host.copy_(total, non_blocking=True)     # the step's result goes back to the host
+        torch.cuda.current_stream().synchronize()
     return total
 
 
