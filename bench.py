@@ -216,10 +216,9 @@ def run_ours(args):
 
     # warm-up: W steps as asked (this also settles the workspace capacity hints and the allocator), then keep the
     # same work running until the GPU has been busy for about a second so clocks and power state have ramped
-    region(args.warmup, 0)
-    t_warm = time.perf_counter()
-    while time.perf_counter() - t_warm < 1.0:
-        region(1, 0)
+    ms_w = region(args.warmup, 0)                     # max over ranks: the same number on every rank
+    extra = min(200, int(1000.0 / max(1e-3, ms_w / max(1, args.warmup))) + 1)
+    region(extra, 0)
     clocks = ClockSampler(local) if rank == 0 else None
     if clocks:
         clocks.start()
