@@ -200,3 +200,126 @@ WORKLOADS = {
 def make_workload(name: str, seed=0, with_sh=False) -> Scene:
     N, T, W, H, sm, g = WORKLOADS[name]
     return make_scene(name, N, T, W, H, seed=seed, scale_mul=sm, garments=g, with_sh=with_sh)
+
+
+# ---- synthetic skinned skeleton (cage-vertex LBS) --------------------------------------
+def make_skeleton(n_vertices: int = 2197, seed: int = 0, fingers: int = 5, finger_len: int = 4,
+                  max_influences: int = 8, box=(600.0, 1800.0, 400.0)):
+    """A humanoid-shaped joint tree plus skinned vertices, in the dictionary formats the reference's constructors read.
+
+    Returns (model_json, lbs_config_dict, lbs_scale[1,NS], motion[1,NP]):
+      * model_json["Skeleton"]["Bones"][j] = {Name, Parent, PreRotation (x,y,z,w), TranslationOffset};
+        model_json["SkinnedModel"] = {RestPositions, RestVertexNormals, SkinningWeights [(joint, w)...],
+        SkinningOffsets [V+1], Faces{Indices, TextureIndices}, TextureCoordinates}  (lbsmodel/body_model.py:62-101);
+      * lbs_config_dict = {channel_names, transform [7*NJ, NP+NS], transform_offsets [1, 7*NJ], limits,
+        nr_scaling_params, nr_position_params}  (lbsmodel/body_model.py:24-38, :562-576).
+    Joint 0 is a world joint (Parent beyond the bone count -> -1), joint 1 the body root the reference reads its
+    root transform from (body_model.py:190).  Units are millimetres like the reference's body model
+    (lib/blueman.py:150 divides by 1000).  ~160 joints with the defaults, 6 global + one parameter per rotating
+    channel, scale parameters shared per limb.
+    """
+    rng = np.random.default_rng(seed)
+    names, parents, offs = [], [], []
+
+    def add(name, parent, off):
+        names.append(name)
+        parents.append(parent)
+        offs.append(off)
+        return len(names) - 1
+
+    world = add("world", 10 ** 6, (0.0, 0.0, 0.0))
+    root = add("b_root", world, (0.0, 900.0, 0.0))
+    spine = root
+    for i in range(4):
+        spine = add(f"b_spine{i}", spine, (0.0, 120.0, 5.0))
+    neck = add("b_neck", spine, (0.0, 90.0, 0.0))
+    head = add("b_head", neck, (0.0, 110.0, 10.0))
+    for e in ("l", "r"):
+        add(f"b_{e}_eye", head, (30.0 if e == "l" else -30.0, 40.0, 70.0))
+    for side, sx in (("l", 1.0), ("r", -1.0)):
+        clav = add(f"b_{side}_clav", spine, (sx * 60.0, 60.0, 0.0))
+        arm = add(f"b_{side}_arm", clav, (sx * 130.0, 0.0, 0.0))
+        twist = add(f"b_{side}_arm_twist", arm, (sx * 130.0, 0.0, 0.0))
+        fore = add(f"b_{side}_forearm", twist, (sx * 130.0, 0.0, 0.0))
+        ftw = add(f"b_{side}_forearm_twist", fore, (sx * 120.0, 0.0, 0.0))
+        wrist = add(f"b_{side}_wrist", ftw, (sx * 120.0, 0.0, 0.0))
+        for f in range(fingers):
+            j = wrist
+            for k in range(finger_len):
+                j = add(f"b_{side}_f{f}_{k}", j, (sx * (40.0 - 5 * k), 0.0, 12.0 * (f - 2) if k == 0 else 0.0))
+        up = add(f"b_{side}_upleg", root, (sx * 90.0, -60.0, 0.0))
+        uptw = add(f"b_{side}_upleg_twist", up, (0.0, -200.0, 0.0))
+        leg = add(f"b_{side}_leg", uptw, (0.0, -220.0, 0.0))
+        legtw = add(f"b_{side}_leg_twist", leg, (0.0, -200.0, 0.0))
+        foot = add(f"b_{side}_foot", legtw, (0.0, -210.0, -20.0))
+        ball = add(f"b_{side}_ball", foot, (0.0, -50.0, 120.0))
+        for t in range(5):
+            toe = add(f"b_{side}_toe{t}_0", ball, (sx * 12.0 * (t - 2), 0.0, 30.0))
+            add(f"b_{side}_toe{t}_1", toe, (0.0, 0.0, 20.0))
+    nj = len(names)
+    pre = rng.normal(size=(nj, 4)) * np.array([0.15, 0.15, 0.15, 0.0]) + np.array([0.0, 0.0, 0.0, 1.0])
+    pre /= np.linalg.norm(pre, axis=1, keepdims=True)
+    pre[0] = (0.0, 0.0, 0.0, 1.0)
+    offs = np.asarray(offs, np.float64) + rng.normal(size=(nj, 3)) * 2.0
+    offs[0] = 0.0
+    bones = [{"Name": names[j], "Parent": int(parents[j]), "PreRotation": [float(x) for x in pre[j]],
+              "TranslationOffset": [float(x) for x in offs[j]]} for j in range(nj)]
+
+    # rest-pose joint positions (pre-rotations ignored: only used to place vertices and pick influences)
+    pos = np.zeros((nj, 3))
+    for j in range(1, nj):
+        pos[j] = pos[parents[j]] + offs[j] if parents[j] < nj else offs[j]
+    lo, hi = pos.min(0) - 60.0, pos.max(0) + 60.0
+    verts = rng.uniform(lo, hi, size=(n_vertices, 3))
+    weights_flat, offsets = [], [0]
+    for v in range(n_vertices):
+        d = np.linalg.norm(pos[1:] - verts[v], axis=1)
+        k = int(rng.integers(1, max_influences + 1))
+        nearest = np.argsort(d, kind="stable")[:k] + 1
+        w = np.exp(-d[nearest - 1] / 80.0) + 1e-3
+        w /= w.sum()
+        weights_flat += [[int(j), float(x)] for j, x in zip(nearest, w)]
+        offsets.append(len(weights_flat))
+    model_json = {
+        "Skeleton": {"Bones": bones},
+        "SkinnedModel": {
+            "RestPositions": verts.astype(np.float32).tolist(),
+            "RestVertexNormals": np.tile(np.array([[0.0, 0.0, 1.0]], np.float32), (n_vertices, 1)).tolist(),
+            "SkinningWeights": weights_flat, "SkinningOffsets": offsets,
+            "Faces": {"Indices": [0, 1, 2], "TextureIndices": [0, 1, 2]},
+            "TextureCoordinates": [0.0, 0.0, 1.0, 0.0, 0.0, 1.0],
+        },
+    }
+
+    # parameter transform: 6 global parameters drive the root's tx..rz; every other joint gets rx/ry/rz parameters
+    # (twist joints only rx); scale parameters are shared by limb and feed the "sc" channel.
+    triplets, n_pos = [], 0
+    for c in range(6):
+        triplets.append((7 * root + c, n_pos, 1.0))
+        n_pos += 1
+    for j in range(2, nj):
+        chans = (3,) if "twist" in names[j] else (3, 4, 5)
+        for c in chans:
+            triplets.append((7 * j + c, n_pos, 1.0))
+            if "twist" in names[j] and n_pos > 6:                # twist joints also follow their parent's parameter
+                triplets.append((7 * j + c, n_pos - 1, 0.5))
+            n_pos += 1
+    groups = ["spine", "neck", "head", "eye", "l_clav", "r_clav", "l_arm", "r_arm", "l_forearm", "r_forearm", "l_wrist",
+              "r_wrist", "l_f", "r_f", "l_upleg", "r_upleg", "l_leg", "r_leg", "l_foot", "r_foot", "l_ball", "r_ball",
+              "l_toe", "r_toe", "root"]
+    n_scale = len(groups)
+    for j in range(1, nj):
+        for gi, gname in enumerate(groups):
+            if gname in names[j]:
+                triplets.append((7 * j + 6, n_pos + gi, 1.0))
+                break
+    transform = np.zeros((7 * nj, n_pos + n_scale), np.float32)
+    for r, c, v in triplets:
+        transform[r, c] = v
+    cfg = {"channel_names": ["tx", "ty", "tz", "rx", "ry", "rz", "sc"], "transform": transform,
+           "transform_offsets": np.zeros((1, 7 * nj), np.float32), "limits": [],
+           "nr_scaling_params": n_scale, "nr_position_params": n_pos}
+    lbs_scale = (rng.normal(size=(1, n_scale)) * 0.05).astype(np.float32)
+    motion = (rng.normal(size=(1, n_pos)) * 0.35).astype(np.float32)
+    motion[0, :3] = (30.0, -20.0, 45.0)
+    return model_json, cfg, lbs_scale, motion

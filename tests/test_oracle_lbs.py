@@ -1,0 +1,80 @@
+"""CPU tests pinning oracle/lbs_oracle.py against vectors produced by the REFERENCE's own lbsmodel/body_model.py,
+lib/blueman.py (Blueman.get) and lib/smplman.py (Smplman.deform) -- tests/golden/lbs_golden.npz, see
+tests/golden/make_lbs_golden.py.  The reference computes in float32; the oracle is run in float64 (tolerance = float32
+round-off through a ~12-joint chain on millimetre-scale coordinates) and in float32."""
+import os
+
+import numpy as np
+import pytest
+
+import parity_util as util
+from d3ga_b200 import synth
+from oracle import lbs_oracle as lo
+
+G = np.load(os.path.join(util.GOLDEN, "lbs_golden.npz"))
+
+
+def skeleton(dtype):
+    model_json, cfg, _, _ = synth.make_skeleton(int(G["V"]), seed=int(G["seed"]))
+    return lo.Skeleton(model_json, cfg, dtype=dtype)
+
+
+@pytest.mark.parametrize("dtype", [np.float64, np.float32])
+def test_skeleton_states_and_matrices(dtype):
+    sk = skeleton(dtype)
+    assert np.array_equal(sk.parents, G["joint_parents"].reshape(-1))
+    assert np.array_equal(sk.skin_indices, G["skin_indices"])
+    assert np.array_equal(sk.skin_weights.astype(np.float32), G["skin_weights"])
+    params = np.concatenate([G["motion"], G["scales"]], 1)
+    jp = lo.param_transform(sk.transform, sk.transform_offsets, params.astype(dtype))
+    assert np.abs(jp - G["joint_params"]).max() < 1e-5
+    assert np.abs(sk.bind_state - G["bind_state"]).max() < 2e-3          # millimetres; |t| ~ 2000
+    st = sk.states(params)
+    assert np.abs(st[..., :3] - G["states"][..., :3]).max() < 2e-3
+    assert np.abs(st[..., 3:] - G["states"][..., 3:]).max() < 1e-5
+    mats = sk.matrices(params)
+    assert np.abs(mats[..., :3] - G["mats"][..., :3]).max() < 1e-5
+    assert np.abs(mats[..., 3] - G["mats"][..., 3]).max() < 5e-3
+
+
+@pytest.mark.parametrize("dtype", [np.float64, np.float32])
+def test_skinning_unposing_root(dtype):
+    sk = skeleton(dtype)
+    m, s = G["motion"].astype(dtype), G["scales"].astype(dtype)
+    assert np.abs(sk.forward(m, s) - G["posed"]).max() < 5e-3
+    assert np.abs(sk.forward(m, s, G["verts_in"]) - G["posed_in"]).max() < 5e-3
+    assert np.abs(sk.unpose(m, s, G["posed_in"]) - G["unposed"]).max() < 1e-2
+    assert np.abs(sk.unpose(m, s, G["posed_in"]) - G["verts_in"]).max() < 2e-2    # round trip
+    t_root, R_root = sk.root_rigid_transform(m)
+    assert np.abs(t_root - G["t_root"]).max() < 2e-3
+    assert np.abs(R_root - G["R_root"]).max() < 1e-5
+
+
+@pytest.mark.parametrize("dtype", [np.float64, np.float32])
+def test_cage_pose_matches_blueman_get(dtype):
+    sk = skeleton(dtype)
+    assert np.array_equal(lo.rot180(), G["blue_rot180"][0])
+    g0, RT0, cm = lo.cage_pose(sk, G["motion"][:1], G["scales"][:1], G["global_scaling"], G["template"][None])
+    assert np.abs(RT0 - G["blue_RT0"]).max() < 1e-5
+    assert np.abs(cm - G["blue_center_mass"]).max() < 1e-5               # metres
+    assert np.abs(g0 - G["blue_geom0"]).max() < 1e-5
+    g1, _, _ = lo.cage_pose(sk, G["motion"][1:2], G["scales"][:1], G["global_scaling"], G["template"][None],
+                            delta=G["blue_delta"], center_mass=G["blue_center_mass"])
+    assert np.abs(g1 - G["blue_geom1"]).max() < 1e-5
+    if dtype == np.float64:                                             # gradient wrt delta by central differences
+        rng = np.random.default_rng(0)
+        d = rng.normal(size=G["blue_delta"].shape)
+        h = 1e-4
+        f = lambda x: (lo.cage_pose(sk, G["motion"][1:2], G["scales"][:1], G["global_scaling"], G["template"][None],
+                                    delta=x, center_mass=G["blue_center_mass"])[0] * G["blue_weight"]).sum()
+        fd = (f(G["blue_delta"] + h * d) - f(G["blue_delta"] - h * d)) / (2 * h)
+        assert np.isclose(fd, (G["blue_grad_delta"] * d).sum(), rtol=1e-4)
+
+
+@pytest.mark.parametrize("dtype", [np.float64, np.float32])
+def test_smpl_deform_matches_smplman(dtype):
+    c = lambda k: G[k].astype(dtype)
+    assert np.abs(lo.batch_rodrigues(c("smpl_Rh")) - G["rodrigues"]).max() < 1e-6
+    g = lo.smpl_deform(c("smpl_weights"), G["smpl_nn_ids"], c("smpl_vertices"), c("smpl_A"), c("smpl_Bs"), c("smpl_Rh"),
+                       c("smpl_Th"), c("smpl_delta"))
+    assert np.abs(g - G["smpl_geom"]).max() < 1e-5
