@@ -20,6 +20,8 @@ EXPORTS = [
     "d3ga_raster_backward_scratch_bytes", "d3ga_raster_backward", "d3ga_raster_backward_noalloc", "d3ga_raster_layout",
     "d3ga_deform_forward", "d3ga_deform_backward", "d3ga_deform_backward_ordered", "d3ga_compute_bary",
     "d3ga_fem_energy_forward", "d3ga_fem_energy_backward", "d3ga_ssim_l1_forward", "d3ga_ssim_l1_backward",
+    "d3ga_lbs_skeleton_forward", "d3ga_lbs_states_to_matrix", "d3ga_lbs_skin_forward", "d3ga_lbs_skin_backward", "d3ga_lbs_unskin_forward",
+    "d3ga_lbs_skin_dense_forward", "d3ga_lbs_skin_dense_backward",
 ]
 
 LAYOUT_NAMES = [
@@ -81,6 +83,15 @@ def load() -> C.CDLL:
     lib.d3ga_ssim_l1_forward.argtypes = [i32, i32, i32, vp, vp, vp, vp, vp, vp, vp]
     lib.d3ga_ssim_l1_backward.argtypes = [i32, i32, i32, vp, vp, vp, vp, vp, f32, f32, vp, vp]
     lib.d3ga_compute_bary.argtypes = [i32, i32, i32, vp, vp, vp, vp, vp, vp, vp, vp, vp]
+    i64 = C.c_int64
+    lib.d3ga_lbs_skeleton_forward.argtypes = [i32, i32, i32, i32, vp, vp, i64, i32] + [vp] * 11
+    lib.d3ga_lbs_states_to_matrix.argtypes = [i32, i32, vp, vp, vp, vp]
+    lib.d3ga_lbs_skin_forward.argtypes = [i32, i32, i32, i32, vp, i64, vp, i64, f32, vp, vp, vp, vp, vp, i32, vp, f32, vp,
+                                          vp, vp, vp]
+    lib.d3ga_lbs_skin_backward.argtypes = [i32, i32, i32, i32, vp, vp, vp, vp, vp, i32, vp, f32, vp, f32, vp, vp]
+    lib.d3ga_lbs_unskin_forward.argtypes = [i32, i32, i32, i32, vp, vp, vp, vp, vp, vp]
+    lib.d3ga_lbs_skin_dense_forward.argtypes = [i32, i32, i32, i32] + [vp] * 10
+    lib.d3ga_lbs_skin_dense_backward.argtypes = [i32, i32, i32, i32] + [vp] * 7
     for name in EXPORTS:
         getattr(lib, name)   # AttributeError if the build is stale
     _lib = lib

@@ -29,6 +29,7 @@ SOURCES = [
     ("fem.cu", []),
     ("ssim.cu", []),
     ("bary.cu", []),
+    ("lbs.cu", []),
 ]
 COMMON = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",

@@ -30,7 +30,8 @@ static const char *const g_kernel_names[K_COUNT] = {
     "blend_backward_kernel", "preprocess_backward_kernel", "deform_forward_kernel", "deform_backward_kernel",
     "compute_bary_kernel", "segment_sort_kernel", "preprocess_kernel", "emit_sorted_kernel", "depth_histogram_kernel",
     "depth_sort_pass_kernel", "fem_energy_forward_kernel", "fem_energy_backward_kernel",
-    "ssim_forward_kernel", "ssim_backward_kernel"};
+    "ssim_forward_kernel", "ssim_backward_kernel", "lbs_skeleton_kernel", "lbs_skin_forward_kernel",
+    "lbs_skin_backward_kernel", "lbs_unskin_kernel", "lbs_skin_dense_forward_kernel", "lbs_skin_dense_backward_kernel"};
 
 bool profiling_enabled() { return g_prof_on.load(std::memory_order_relaxed) != 0; }
 
@@ -87,7 +88,7 @@ const char *d3ga_error_string(int code) {
         case D3GA_ECUDA: return "CUDA runtime error (see d3ga_last_cuda_error)";
         case D3GA_ETOOBIG: return "size exceeds the 2^31-1 duplicate limit";
         case D3GA_ENOTREADY: return "call not possible in the current state (staged call out of order, or profiling on)";
-        case D3GA_ELIMIT: return "more Gaussians than the fixed scratch of the allocation-free entry point holds";
+        case D3GA_ELIMIT: return "size beyond a fixed capacity (the fixed scratch of the allocation-free entry point; 1024 joints of the skeleton kernel)";
         default: return "unknown error";
     }
 }

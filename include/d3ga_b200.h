@@ -28,7 +28,7 @@ extern "C" {
 #define D3GA_ECUDA (-2)     /* a CUDA runtime call failed; d3ga_last_cuda_error() has the cudaError_t */
 #define D3GA_ETOOBIG (-3)   /* size beyond what the 32-bit duplicate indices / look-back words can hold */
 #define D3GA_ENOTREADY (-4) /* call not possible in the current state */
-#define D3GA_ELIMIT (-5)    /* size beyond the fixed capacity of d3ga_raster_backward_noalloc */
+#define D3GA_ELIMIT (-5)    /* size beyond a fixed capacity (d3ga_raster_backward_noalloc, d3ga_lbs_skeleton_forward) */
 
 typedef void *d3ga_stream_t; /* cudaStream_t */
 
@@ -217,6 +217,66 @@ int d3ga_ssim_l1_forward(int C, int H, int W, const float *img1, const float *im
 int d3ga_ssim_l1_backward(int C, int H, int W, const float *img1, const float *img2, const float *dm_dmu1,
                           const float *dm_dE11, const float *dm_dE12, float g_ssim, float g_l1, float *dL_dimg1,
                           d3ga_stream_t stream);
+
+/* ---- cage-vertex linear blend skinning -------------------------------------------
+ * The step that produces `tetpoints` right before the deformation.  Quaternions are (x, y, z, w); joint matrices
+ * are row-major [3][4] (rotation*scale | translation), the layout of states_to_matrix (lbsmodel/body_model.py:350-387).
+ *
+ * d3ga_lbs_skeleton_forward replaces ParameterTransform.forward (body_model.py:39-47), solve_skeleton_state
+ * (:311-347) and states_to_matrix (:350-387): one kernel, one CTA per pose.  The raw model parameters are
+ * (pose [batch, n_pose] | scales [n_scale]); scales_stride = floats between poses (0 = one scale vector for all,
+ * the lbs_scale.expand of body_model.py:670); scales may be null (all zero).  with_zero_scale_copy != 0 appends
+ * `batch` more solves of the same poses with every scale parameter zero -- the solve
+ * compute_root_rigid_transform (body_model.py:176-190) needs -- so states / mats then hold 2*batch poses.
+ * The parameter transform [7*n_joints, n_pose+n_scale] is passed as CSR (row_ptr [7*NJ+1], col_idx, vals) plus
+ * offsets [7*NJ]; joint_offset [NJ,3]; joint_rotation [NJ,4] pre-rotations; joint_parents [NJ] int32 (negative =
+ * root; any index order works); bind_state [NJ,8] (required for mats).  Outputs (either may be null):
+ * states [*,NJ,8] = (t, q, scale), mats [*,NJ,3,4].  At most 1024 joints (D3GA_ELIMIT beyond).
+ * d3ga_lbs_states_to_matrix is states_to_matrix alone, for callers that hold skeleton states. */
+int d3ga_lbs_skeleton_forward(int batch, int n_joints, int n_pose, int n_scale, const float *pose, const float *scales,
+                              int64_t scales_stride, int with_zero_scale_copy, const int32_t *row_ptr,
+                              const int32_t *col_idx, const float *vals, const float *offsets,
+                              const float *joint_offset, const float *joint_rotation, const int32_t *joint_parents,
+                              const float *bind_state, float *states, float *mats, d3ga_stream_t stream);
+int d3ga_lbs_states_to_matrix(int batch, int n_joints, const float *bind_state, const float *states, float *mats,
+                              d3ga_stream_t stream);
+
+/* d3ga_lbs_skin_forward replaces LinearBlendSkinning.skinning (body_model.py:208-234), LBSModule.pose's global
+ * scaling (:669-675) and the tail of Blueman.get (lib/blueman.py:101-116,139-158; CageBase.transform lib/cage.py:54-58):
+ *   v   = delta ? (verts / delta_unit + delta) * delta_unit : verts                         [V,3] per pose
+ *   g   = global_scaling * sum_k skin_weights[v,k] * (mats[skin_indices[v,k]] @ [v;1])      K influences
+ *   out = Rinv (g / unit_div) + tinv + shift,   [Rinv|tinv] = inverse([R|t/unit_div](root_mats[root_joint]) @ pre_mul)
+ * verts_stride / delta_stride: floats between poses (0 = one array shared by all poses).  global_scaling [3],
+ * root_mats [batch,NJ,3,4] (the zero-scale solve, body_model.py:176-190), pre_mul [4,4] row-major, shift [3] and
+ * rt_out [batch,4,4] (the inverse transform, blueman.py:148) may each be null (identity / none).
+ * d3ga_lbs_skin_backward writes dL_dverts [batch,V,3] = grad_scale * d out / d v ^T dL_dout (pass delta_unit as
+ * grad_scale to differentiate with respect to delta).  Gradients to the pose parameters are not provided: the
+ * reference never optimises them (models/cage_net.py:186-189 feed dataset motion). */
+int d3ga_lbs_skin_forward(int batch, int V, int K, int n_joints, const float *verts, int64_t verts_stride,
+                          const float *delta, int64_t delta_stride, float delta_unit, const int64_t *skin_indices,
+                          const float *skin_weights, const float *mats, const float *global_scaling,
+                          const float *root_mats, int root_joint, const float *pre_mul, float unit_div,
+                          const float *shift, float *out, float *rt_out, d3ga_stream_t stream);
+int d3ga_lbs_skin_backward(int batch, int V, int K, int n_joints, const int64_t *skin_indices,
+                           const float *skin_weights, const float *mats, const float *global_scaling,
+                           const float *root_mats, int root_joint, const float *pre_mul, float unit_div,
+                           const float *dL_dout, float grad_scale, float *dL_dverts, d3ga_stream_t stream);
+
+/* LinearBlendSkinning.unskinning (body_model.py:248-283, init only): blend each vertex's matrices, invert, apply.
+ * verts, out [batch,V,3]. */
+int d3ga_lbs_unskin_forward(int batch, int V, int K, int n_joints, const float *verts, const int64_t *skin_indices,
+                            const float *skin_weights, const float *mats, float *out, d3ga_stream_t stream);
+
+/* Smplman.deform (lib/smplman.py:155-171): out = Rodrigues(Rh) (T [v + delta + Bs[nn]; 1]) + Th with
+ * T = sum_j weights[nn, j] A[j], nn = nn_ids[v].  verts, delta (nullable) [V,3]; weights [Vd,J]; nn_ids [V] int64;
+ * A [batch,J,4,4]; Bs [batch,Vd,3]; Rh, Th [batch,3]; out [batch,V,3].  Backward: dL_dverts [batch,V,3]
+ * (= gradient to delta as well). */
+int d3ga_lbs_skin_dense_forward(int batch, int V, int Vd, int J, const float *verts, const float *delta,
+                                const float *weights, const int64_t *nn_ids, const float *A, const float *Bs,
+                                const float *Rh, const float *Th, float *out, d3ga_stream_t stream);
+int d3ga_lbs_skin_dense_backward(int batch, int V, int Vd, int J, const float *weights, const int64_t *nn_ids,
+                                 const float *A, const float *Rh, const float *dL_dout, float *dL_dverts,
+                                 d3ga_stream_t stream);
 
 /* ---- barycentric embedding -------------------------------------------------------
  * Replaces tetra_sampler.compute_bary (submodules/tetra-sampler/tetra_sampler/barys.py:9-33): the nearest-face

@@ -125,6 +125,27 @@ try:
                smpl_Bs=Bs, smpl_Rh=Rh, smpl_Th=Th, smpl_delta=sdelta.detach().numpy(), smpl_geom=sg.detach().numpy(),
                smpl_weight=swgt.numpy(), smpl_grad_delta=sg_delta.numpy(),
                rodrigues=ref_lbs.batch_rodrigues(t(Rh)).numpy())
+
+    # load_momentum_cfg (body_model.py:390-578) on a parameter file written from the synthetic transform
+    import io
+    import json
+    names = [b["Name"] for b in model_json["Skeleton"]["Bones"]]
+    chans = cfg["channel_names"]
+    npos = cfg["nr_position_params"]
+    pname = lambda c: (f"p{c}" if c < npos else f"scale_{c - npos}")
+    lines = ["# synthetic skeleton parameters", "parameterset all p0 p1"]
+    for r in range(cfg["transform"].shape[0]):
+        cols = np.nonzero(cfg["transform"][r])[0]
+        if len(cols):
+            terms = " + ".join(f"{cfg['transform'][r, c]:.3f} * {pname(c)}" for c in cols)
+            lines.append(f"{names[r // 7]}.{chans[r % 7]} = {terms}   # row {r}")
+    lines += ["limit p7 minmax [-1.5, 0.75] 2.0 #", "limit b_head.rx minmax_passive [ -0.3 , 0.4 ] #",
+              "limit nothing minmax [0, 1]", "limit scale_3 minmax [-0.2,0.2] #", ""]
+    text = "\n".join(lines)
+    parsed = body_model.load_momentum_cfg(model_json, io.StringIO(text))
+    out.update(cfg_text=np.array(text), cfg_transform=parsed["transform"], cfg_param_names=np.array(parsed["model_param_names"]),
+               cfg_limits=np.array(json.dumps(parsed["limits"])), cfg_nr_scaling=parsed["nr_scaling_params"],
+               cfg_nr_position=parsed["nr_position_params"])
 finally:
     torch.Tensor.cuda = _cuda
 np.savez_compressed(os.path.join(ROOT, "tests", "golden", "lbs_golden.npz"), **out)

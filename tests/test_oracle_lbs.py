@@ -78,3 +78,37 @@ def test_smpl_deform_matches_smplman(dtype):
     g = lo.smpl_deform(c("smpl_weights"), G["smpl_nn_ids"], c("smpl_vertices"), c("smpl_A"), c("smpl_Bs"), c("smpl_Rh"),
                        c("smpl_Th"), c("smpl_delta"))
     assert np.abs(g - G["smpl_geom"]).max() < 1e-5
+
+
+def test_parameter_file_parser_matches_reference():
+    """d3ga_b200.lbsmodel.load_momentum_cfg (host logic, no GPU) against the reference's parser on the same text."""
+    import io
+    import json
+
+    from d3ga_b200.lbsmodel import load_momentum_cfg
+
+    model_json, cfg, _, _ = synth.make_skeleton(int(G["V"]), seed=int(G["seed"]))
+    out = load_momentum_cfg(model_json, io.StringIO(str(G["cfg_text"])))
+    assert np.array_equal(out["transform"], G["cfg_transform"])
+    assert out["model_param_names"] == list(G["cfg_param_names"])
+    assert out["limits"] == json.loads(str(G["cfg_limits"]))
+    assert out["nr_scaling_params"] == int(G["cfg_nr_scaling"]) and out["nr_position_params"] == int(G["cfg_nr_position"])
+    assert out["transform_offsets"].shape == (1, out["transform"].shape[0])
+
+
+def test_skin_tables_match_reference():
+    """LinearBlendSkinning.__init__'s ragged -> [V, 8] tables (host logic) against the reference's buffers."""
+    from d3ga_b200.lbsmodel import LinearBlendSkinning
+
+    model_json, cfg, _, _ = synth.make_skeleton(int(G["V"]), seed=int(G["seed"]))
+    fn = LinearBlendSkinning(model_json, cfg)
+    assert np.array_equal(fn.skin_indices.numpy(), G["skin_indices"])
+    assert np.array_equal(fn.skin_weights.numpy(), G["skin_weights"])
+    assert np.array_equal(fn.joint_parents.numpy(), G["joint_parents"])
+    dense = fn.param_transform.transform.numpy()
+    pt = fn.param_transform
+    rebuilt = np.zeros_like(dense)
+    rp = pt.csr_row_ptr.numpy()
+    for r in range(dense.shape[0]):
+        rebuilt[r, pt.csr_col_idx.numpy()[rp[r]:rp[r + 1]]] = pt.csr_vals.numpy()[rp[r]:rp[r + 1]]
+    assert np.array_equal(rebuilt, dense)
