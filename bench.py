@@ -316,6 +316,49 @@ def run_ours(args):
         dgr.SHARE_GEOMETRY = True
         pair["note"] = "1 frame = deformation + RGB render + silhouette render + backward of both (models/trainer.py:91-140)"
 
+    # the cage-vertex skinning that produces tetpoints (Blueman.get), forward + backward to delta
+    lbs = None
+    if rank == 0 and world == 1 and not args.no_e2e:
+        from d3ga_b200 import lbsmodel
+        n_cage = int(avatar.tetpoints.shape[0])
+        model_json, cfg, lbs_scale, motion = synth.make_skeleton(n_cage, seed=0)
+        tmpl = np.asarray(model_json["SkinnedModel"]["RestPositions"], np.float32)
+        mod = lbsmodel.LBSModule(model_json, cfg, tmpl, lbs_scale, np.float32(1.0)).to(dev)
+        mot = torch.from_numpy(motion).to(dev)
+        delta = torch.zeros(1, n_cage, 3, device=dev, requires_grad=True)
+        rot180 = torch.diag(torch.tensor([-1.0, 1.0, -1.0, 1.0], device=dev))
+        g_out = torch.randn(1, n_cage, 3, device=dev)
+
+        def lbs_iter():
+            delta.grad = None
+            mod.cage_pose(mot, delta=delta, pre_mul=rot180).backward(g_out)
+
+        for _ in range(5):
+            lbs_iter()
+        l0 = _lib.launch_count()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(200):
+            lbs_iter()
+        b.record()
+        torch.cuda.synchronize()
+        _lib.profile_enable(True)
+        for _ in range(20):
+            lbs_iter()
+        kprof = {k: round(v[0] / v[1] * 1e3, 2) for k, v in _lib.profile_collect().items() if v[1] and k.startswith("lbs_")}
+        _lib.profile_enable(False)
+        lbs = {"us_per_pose_fwd_bwd": a.elapsed_time(b) * 1e3 / 200, "kernel_us": kprof, "kernel_launches_per_pose": (_lib.launch_count() - l0) / 200,
+               "joints": len(model_json["Skeleton"]["Bones"]), "cage_vertices": n_cage,
+               "note": "Blueman.get (lib/blueman.py:139-167) + gradient to delta; the reference's joint loop alone is "
+                       "~10 torch launches per joint (lbsmodel/body_model.py:327-345)"}
+        if not args.no_cpu_baseline:
+            from oracle import lbs_oracle
+            sk = lbs_oracle.Skeleton(model_json, cfg, dtype=np.float32)
+            t0 = time.perf_counter()
+            for _ in range(3):
+                lbs_oracle.cage_pose(sk, motion, lbs_scale, np.float32(1.0), tmpl[None], delta=np.zeros((1, n_cage, 3), np.float32))
+            lbs["cpu_port_us_per_pose_fwd"] = (time.perf_counter() - t0) / 3 * 1e6
+
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         n = 2 if scene.N >= 500_000 else 4
@@ -329,7 +372,7 @@ def run_ours(args):
                 "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
                 "vs_baseline": None, "dtype": "f32", "data": "synthetic", "impl": "ours",
                 "config": workload_config(scene, args, V), "clocks": clk, "e2e": e2e, "gpu_launches": int(launches),
-                "roofline": roof, "cpu_baseline": cpu, "training_frame_pair": pair,
+                "roofline": roof, "cpu_baseline": cpu, "training_frame_pair": pair, "cage_lbs": lbs,
                 "allreduce_bytes_per_step": avatar.grads.nbytes() if world > 1 else 0}
         print(json.dumps(line), flush=True)
     if world > 1:

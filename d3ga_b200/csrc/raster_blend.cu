@@ -421,6 +421,311 @@ __global__ void __launch_bounds__(TILE_PIX) blend_backward_kernel(
     }
 }
 
+
+// ---- warp-autonomous variants ------------------------------------------------------------------------------------------
+// Same arithmetic as the kernels above, different staging: the CTA still owns a tile, but each warp walks the tile's
+// list ON ITS OWN -- 32 Gaussians per step, one per lane, gathered a step ahead in registers, tested against the warp's
+// 8x4 pixel block, and only the survivors are parked (compacted, in list order) in a per-warp ring in shared memory from
+// which the blend loop takes them in groups.  There is no CTA barrier in the loop: in the CTA-staged kernels a third of
+// all warp-stall samples sit on that barrier (profiles/r1_ncu_full_final.csv), because per-warp culling gives the eight
+// warps of a tile very different amounts of work.  A warp whose pixels are all finished simply stops.  The price is that
+// the eight warps each read the tile's list (L1 hits for seven of them) and each evaluate the footprint test.
+constexpr int RING = 64;                     // per-warp ring of staged survivors (>= group - 1 + 32)
+
+// Exact version of the footprint test for one warp's pixel block: does the ellipse d^T C d <= 2 tau (outside of which
+// alpha < 1/255, see footprint_box) reach any pixel centre of the block?  The quadratic is convex with its minimum at
+// the Gaussian centre, so when the centre lies outside the block its minimum over the block sits on the edge(s) facing
+// the centre; on an edge it is a 1-D quadratic, minimised in closed form and clamped.  A relative and an absolute
+// margin keep the test conservative against rounding (a false "hit" only costs time, the per-pixel test decides);
+// degenerate conics are never culled.  Rejects the diagonal, elongated splats the bounding box lets through.
+__device__ __forceinline__ bool footprint_hit(float2 c, float4 co, const WarpBlock &wb) {
+    if (co.w < 1.f / 255.f) return false;   // can never pass the cut
+    const float det = co.x * co.z - co.y * co.y;
+    const float tau = __logf(255.f * co.w);
+    if (!(det > 0.f) || !(tau >= 0.f) || !(co.x > 0.f) || !(co.z > 0.f)) return true;
+    const float lim = 2.f * tau * 1.002f + 0.01f;
+    const float xl = wb.x0 - c.x, xh = wb.x1 - c.x, yl = wb.y0 - c.y, yh = wb.y1 - c.y;
+    const bool in_x = xl <= 0.f && xh >= 0.f, in_y = yl <= 0.f && yh >= 0.f;
+    if (in_x && in_y) return true;
+    float qmin = INFINITY;
+    if (!in_x) {
+        const float dx = xl > 0.f ? xl : xh;
+        const float dy = fminf(fmaxf(__fdividef(-co.y * dx, co.z), yl), yh);
+        qmin = co.x * dx * dx + 2.f * co.y * dx * dy + co.z * dy * dy;
+    }
+    if (!in_y) {
+        const float dy = yl > 0.f ? yl : yh;
+        const float dx = fminf(fmaxf(__fdividef(-co.y * dy, co.x), xl), xh);
+        qmin = fminf(qmin, co.x * dx * dx + 2.f * co.y * dx * dy + co.z * dy * dy);
+    }
+    return qmin <= lim;
+}
+
+template <bool INVDEPTH>
+__global__ void __launch_bounds__(TILE_PIX, 4) blend_forward_warp_kernel(
+    const RasterHeader *__restrict__ hdr, const uint2 *__restrict__ ranges, const uint32_t *__restrict__ vals0,
+    const uint32_t *__restrict__ vals1, int W, int H, const float2 *__restrict__ xy,
+    const float4 *__restrict__ conic_opacity, const float *__restrict__ colors, const float *__restrict__ depths,
+    const float *__restrict__ bg, float *__restrict__ final_T, uint32_t *__restrict__ n_contrib,
+    float *__restrict__ out_color, float *__restrict__ out_invdepth, RasterHeader *__restrict__ hdr_rw, int grid_x,
+    int num_tiles, const uint32_t *__restrict__ order_fwd, uint32_t *__restrict__ tile_nproc,
+    uint32_t *__restrict__ order_bwd) {
+    __shared__ float4 s_a[TILE_PIX / 32][RING];      // x, y, list position + 1 (bits), unused
+    __shared__ float4 s_co[TILE_PIX / 32][RING];     // pre-scaled conic, opacity
+    __shared__ float4 s_feat[TILE_PIX / 32][RING];   // r, g, b, 1/depth
+    __shared__ uint32_t s_bins[257];
+    __shared__ uint32_t s_red[TILE_PIX / 32];
+    __shared__ uint32_t s_last;
+
+    const uint32_t tile = order_fwd[blockIdx.x];   // longest Gaussian list first
+    const int tid = threadIdx.x;
+    const uint32_t lane = tid & 31, warp = tid >> 5;
+    const WarpBlock wb = warp_block(tid, (int)(tile % (uint32_t)grid_x), (int)(tile / (uint32_t)grid_x));
+    const int px = wb.px, py = wb.py;
+    const bool inside = px < W && py < H;
+    const float pxf = (float)px, pyf = (float)py;
+    uint2 range = make_uint2(0, 0);
+    if (!hdr->overflow) range = ranges[tile];
+    const uint32_t *point_list = (hdr->final_sel ? vals1 : vals0) + range.x;
+    const uint32_t count = range.y - range.x;
+    const uint32_t nchunks = (count + 31u) / 32u;
+
+    bool done = !inside;
+    float T = 1.f, C0 = 0.f, C1 = 0.f, C2 = 0.f, invd = 0.f;
+    uint32_t last = 0;
+    float4(*ra)[RING] = s_a, (*rco)[RING] = s_co, (*rfeat)[RING] = s_feat;
+
+    float2 p_xy = make_float2(0.f, 0.f);
+    float4 p_co = make_float4(0.f, 0.f, 0.f, 0.f), p_feat = make_float4(0.f, 0.f, 0.f, 0.f);
+    auto gather = [&](uint32_t id) {
+        p_xy = xy[id];
+        p_co = conic_opacity[id];
+        p_feat = make_float4(colors[3 * (size_t)id], colors[3 * (size_t)id + 1], colors[3 * (size_t)id + 2],
+                             INVDEPTH ? __fdividef(1.f, depths[id]) : 0.f);
+    };
+    // ids run two steps ahead of the blend, the Gaussians themselves one step
+    uint32_t id_next = 0;
+    if (lane < count) gather(point_list[lane]);
+    if (32u + lane < count) id_next = point_list[32u + lane];
+    uint32_t head = 0, tail = 0;
+    const bool warp_active = !__all_sync(0xffffffffu, done);
+    for (uint32_t c = 0; c < nchunks && warp_active; c++) {
+        const uint32_t pos = c * 32u + lane;
+        bool hit = false;
+        if (pos < count) hit = footprint_hit(p_xy, p_co, wb);
+        const uint32_t m = __ballot_sync(0xffffffffu, hit);
+        if (hit) {
+            const uint32_t slot = (tail + __popc(m & lanemask_lt())) & (RING - 1);
+            ra[warp][slot] = make_float4(p_xy.x, p_xy.y, __uint_as_float(pos + 1u), 0.f);
+            rco[warp][slot] = prescale_conic(p_co);
+            rfeat[warp][slot] = p_feat;
+        }
+        tail += __popc(m);
+        if (pos + 32u < count) gather(id_next);                      // in flight while the ring is blended
+        if (pos + 64u < count) id_next = point_list[pos + 64u];
+        __syncwarp();
+        const bool flush = c + 1u == nchunks;
+        bool all_done = false;
+        while (tail - head >= 4u || (flush && tail != head)) {
+            const uint32_t avail = min(4u, tail - head);
+            float a[4];
+            uint32_t ss[4];
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+                const uint32_t s = (head + (uint32_t)u) & (RING - 1);
+                const float4 e = ra[warp][s];
+                const float dx = e.x - pxf, dy = e.y - pyf;
+                const float4 co = rco[warp][s];   // pre-scaled: log2 domain
+                const float power = dx * (co.x * dx + co.y * dy) + co.z * dy * dy;
+                const float alpha = fminf(0.99f, co.w * fast_exp2(power));
+                a[u] = ((uint32_t)u < avail && !(power > 0.f) && alpha >= 1.f / 255.f) ? alpha : 0.f;
+                ss[u] = s;
+            }
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+                if (done || a[u] == 0.f) continue;
+                const float test_T = T * (1.f - a[u]);
+                if (test_T < 0.0001f) { done = true; continue; }
+                const float4 f = rfeat[warp][ss[u]];
+                const float w = a[u] * T;
+                C0 += f.x * w; C1 += f.y * w; C2 += f.z * w;
+                if (INVDEPTH) invd += f.w * w;
+                T = test_T;
+                last = __float_as_uint(ra[warp][ss[u]].z);
+            }
+            head += avail;
+            if (__all_sync(0xffffffffu, done)) { all_done = true; break; }
+        }
+        if (all_done) break;
+    }
+    if (inside) {
+        const size_t pid = (size_t)py * W + px, plane = (size_t)H * W;
+        final_T[pid] = T;
+        n_contrib[pid] = last;
+        out_color[pid] = C0 + T * bg[0];
+        out_color[plane + pid] = C1 + T * bg[1];
+        out_color[2 * plane + pid] = C2 + T * bg[2];
+        if (INVDEPTH) out_invdepth[pid] = invd;
+    }
+    // deepest contributor of the tile = how far the backward has to go; the last CTA orders the backward's tiles
+    const uint32_t wmax = __reduce_max_sync(0xffffffffu, inside ? last : 0u);
+    if (lane == 0) s_red[warp] = wmax;
+    __syncthreads();
+    if (tid == 0) {
+        uint32_t mx = 0;
+        for (int w = 0; w < TILE_PIX / 32; w++) mx = max(mx, s_red[w]);
+        tile_nproc[tile] = mx;
+        __threadfence();
+        s_last = atomicAdd(&hdr_rw->blend_done, 1u) == (uint32_t)num_tiles - 1u;
+    }
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    const uint32_t *np = tile_nproc;
+    order_tiles_descending(num_tiles, [np](int t) { return __ldcg(np + t); }, order_bwd, s_bins);
+}
+
+template <bool INVDEPTH>
+__global__ void __launch_bounds__(TILE_PIX) blend_backward_warp_kernel(
+    const RasterHeader *__restrict__ hdr, const uint2 *__restrict__ ranges, const uint32_t *__restrict__ vals0,
+    const uint32_t *__restrict__ vals1, int W, int H, const float *__restrict__ bg, const float2 *__restrict__ xy,
+    const float4 *__restrict__ conic_opacity, const float *__restrict__ colors, const float *__restrict__ depths,
+    const float *__restrict__ final_T, const uint32_t *__restrict__ n_contrib, const float *__restrict__ dL_dpix,
+    const float *__restrict__ dL_dinvdepth_pix, float *__restrict__ grad_acc, int grid_x,
+    const uint32_t *__restrict__ order_bwd) {
+    __shared__ float4 s_a[TILE_PIX / 32][RING];      // x, y, Gaussian id (bits), forward list position (bits)
+    __shared__ float4 s_co[TILE_PIX / 32][RING];
+    __shared__ float4 s_feat[TILE_PIX / 32][RING];
+
+    const uint32_t tile = order_bwd[blockIdx.x];   // deepest contributor first
+    const int tid = threadIdx.x;
+    const uint32_t lane = tid & 31, warp = tid >> 5;
+    const WarpBlock wb = warp_block(tid, (int)(tile % (uint32_t)grid_x), (int)(tile / (uint32_t)grid_x));
+    const int px = wb.px, py = wb.py;
+    const bool inside = px < W && py < H;
+    const float pxf = (float)px, pyf = (float)py;
+    uint2 range = make_uint2(0, 0);
+    if (!hdr->overflow) range = ranges[tile];
+    if (range.y <= range.x) return;
+    const uint32_t *point_list = (hdr->final_sel ? vals1 : vals0) + range.x;
+    const size_t pid = (size_t)py * W + px, plane = (size_t)H * W;
+
+    const float T_final = inside ? final_T[pid] : 0.f;
+    float T = T_final;
+    const uint32_t last_contributor = inside ? n_contrib[pid] : 0u;
+    // this warp only walks the prefix of the list that reached one of ITS pixels in the forward, back to front
+    const uint32_t n_proc = __reduce_max_sync(0xffffffffu, last_contributor);
+    if (n_proc == 0) return;
+    const uint32_t nchunks = (n_proc + 31u) / 32u;
+
+    float acc0 = 0.f, acc1 = 0.f, acc2 = 0.f, acci = 0.f;
+    float lc0 = 0.f, lc1 = 0.f, lc2 = 0.f, lci = 0.f, last_alpha = 0.f;
+    float g0 = 0.f, g1 = 0.f, g2 = 0.f, gi = 0.f;
+    if (inside) {
+        g0 = dL_dpix[pid]; g1 = dL_dpix[plane + pid]; g2 = dL_dpix[2 * plane + pid];
+        if (INVDEPTH) gi = dL_dinvdepth_pix[pid];
+    }
+    const float bg_dot = bg[0] * g0 + bg[1] * g1 + bg[2] * g2;
+    const float ddelx_dx = 0.5f * (float)W, ddely_dy = 0.5f * (float)H;
+    const uint32_t slot10 = lane % 10u, group = lane / 10u;   // lane l (< 30) ends up with sum `slot10` of Gaussian `group`
+
+    uint32_t p_id = 0, id_next = 0;
+    float2 p_xy = make_float2(0.f, 0.f);
+    float4 p_co = make_float4(0.f, 0.f, 0.f, 0.f), p_feat = make_float4(0.f, 0.f, 0.f, 0.f);
+    auto gather = [&](uint32_t id) {
+        p_id = id;
+        p_xy = xy[id];
+        p_co = conic_opacity[id];
+        p_feat = make_float4(colors[3 * (size_t)id], colors[3 * (size_t)id + 1], colors[3 * (size_t)id + 2],
+                             INVDEPTH ? __fdividef(1.f, depths[id]) : 0.f);
+    };
+    // lane l of step c looks at forward position q = n_proc - 1 - (32 c + l)
+    if (lane < n_proc) gather(point_list[n_proc - 1u - lane]);
+    if (32u + lane < n_proc) id_next = point_list[n_proc - 33u - lane];
+    uint32_t head = 0, tail = 0;
+    for (uint32_t c = 0; c < nchunks; c++) {
+        const uint32_t back = c * 32u + lane;
+        bool hit = false;
+        if (back < n_proc) hit = footprint_hit(p_xy, p_co, wb);
+        const uint32_t m = __ballot_sync(0xffffffffu, hit);
+        if (hit) {
+            const uint32_t s = (tail + __popc(m & lanemask_lt())) & (RING - 1);
+            s_a[warp][s] = make_float4(p_xy.x, p_xy.y, __uint_as_float(p_id), __uint_as_float(n_proc - 1u - back));
+            s_co[warp][s] = p_co;
+            s_feat[warp][s] = p_feat;
+        }
+        tail += __popc(m);
+        if (back + 32u < n_proc) gather(id_next);
+        if (back + 64u < n_proc) id_next = point_list[n_proc - 65u - back];
+        __syncwarp();
+        const bool flush = c + 1u == nchunks;
+        // three ring entries at a time: independent alpha evaluation, sequential transmittance recurrence, then ONE
+        // 32-value butterfly for the 3 x 10 partial derivatives and one RED instruction (30 lanes, <= 3 rows)
+        while (tail - head >= 3u || (flush && tail != head)) {
+            const uint32_t avail = min(3u, tail - head);
+            uint32_t ss[3];
+            float G_[3], al[3], dx_[3], dy_[3];
+            bool ok[3];
+#pragma unroll
+            for (int u = 0; u < 3; u++) {
+                const uint32_t s = (head + (uint32_t)u) & (RING - 1);
+                const float4 e = s_a[warp][s];
+                const float dx = e.x - pxf, dy = e.y - pyf;
+                const float4 co = s_co[warp][s];
+                const float power = -0.5f * (co.x * dx * dx + co.z * dy * dy) - co.y * dx * dy;
+                const float G = __expf(power);
+                const float alpha = fminf(0.99f, co.w * G);
+                ok[u] = (uint32_t)u < avail && __float_as_uint(e.w) < last_contributor && !(power > 0.f) &&
+                        alpha >= 1.f / 255.f;
+                ss[u] = s; G_[u] = G; al[u] = alpha; dx_[u] = dx; dy_[u] = dy;
+            }
+            head += avail;
+            if (!__any_sync(0xffffffffu, ok[0] || ok[1] || ok[2])) continue;
+            float w[32];
+#pragma unroll
+            for (int e = 0; e < 32; e++) w[e] = 0.f;
+#pragma unroll
+            for (int u = 0; u < 3; u++) {
+                if (!ok[u]) continue;
+                const float alpha = al[u], G = G_[u], dx = dx_[u], dy = dy_[u];
+                const float4 co = s_co[warp][ss[u]];
+                const float4 f = s_feat[warp][ss[u]];
+                const float inv_1ma = __fdividef(1.f, 1.f - alpha);
+                T = T * inv_1ma;
+                const float dchannel_dcolor = alpha * T;
+                acc0 = last_alpha * lc0 + (1.f - last_alpha) * acc0; lc0 = f.x;
+                acc1 = last_alpha * lc1 + (1.f - last_alpha) * acc1; lc1 = f.y;
+                acc2 = last_alpha * lc2 + (1.f - last_alpha) * acc2; lc2 = f.z;
+                float dL_dalpha = (f.x - acc0) * g0 + (f.y - acc1) * g1 + (f.z - acc2) * g2;
+                w[10 * u + 6] = dchannel_dcolor * g0;
+                w[10 * u + 7] = dchannel_dcolor * g1;
+                w[10 * u + 8] = dchannel_dcolor * g2;
+                if (INVDEPTH) {
+                    acci = last_alpha * lci + (1.f - last_alpha) * acci; lci = f.w;
+                    dL_dalpha += (f.w - acci) * gi;
+                    w[10 * u + 9] = dchannel_dcolor * gi;
+                }
+                dL_dalpha *= T;
+                last_alpha = alpha;
+                dL_dalpha += (-T_final * inv_1ma) * bg_dot;
+                const float dL_dG = co.w * dL_dalpha;
+                const float gdx = G * dx, gdy = G * dy;
+                w[10 * u + 0] = dL_dG * (-gdx * co.x - gdy * co.y) * ddelx_dx;
+                w[10 * u + 1] = dL_dG * (-gdy * co.z - gdx * co.y) * ddely_dy;
+                w[10 * u + 2] = -0.5f * gdx * dx * dL_dG;
+                w[10 * u + 3] = -0.5f * gdx * dy * dL_dG;
+                w[10 * u + 4] = -0.5f * gdy * dy * dL_dG;
+                w[10 * u + 5] = G * dL_dalpha;
+            }
+            const float sum = butterfly32(w, lane);
+            if (lane < 30u && sum != 0.f) {
+                const uint32_t s = group == 0u ? ss[0] : (group == 1u ? ss[1] : ss[2]);
+                atomicAdd(grad_acc + (size_t)__float_as_uint(s_a[warp][s].z) * GRAD_ACC_FLOATS + slot10, sum);
+            }
+        }
+    }
+}
+
 }  // namespace
 
 #ifdef D3GA_DEBUG_TIMING
@@ -448,7 +753,16 @@ int launch_blend_forward(int W, int H, const float *background, const float *col
     uint32_t *order_bwd = reinterpret_cast<uint32_t *>(image + IL.order_bwd);
     uint32_t *tile_nproc = reinterpret_cast<uint32_t *>(image + IL.tile_nproc);
     ProfScope prof(K_BLEND_FWD, stream);
-    if (out_invdepth)
+    if (blend_mode() == BLEND_WARP) {
+        if (out_invdepth)
+            blend_forward_warp_kernel<true><<<num_tiles, TILE_PIX, 0, stream>>>(
+                hdr, ranges, v0, v1, W, H, xy, co, colors, depth, background, final_T, n_contrib, out_color, out_invdepth,
+                hdr_rw, gx, num_tiles, order_fwd, tile_nproc, order_bwd);
+        else
+            blend_forward_warp_kernel<false><<<num_tiles, TILE_PIX, 0, stream>>>(
+                hdr, ranges, v0, v1, W, H, xy, co, colors, depth, background, final_T, n_contrib, out_color, nullptr,
+                hdr_rw, gx, num_tiles, order_fwd, tile_nproc, order_bwd);
+    } else if (out_invdepth)
         blend_forward_kernel<true><<<num_tiles, TILE_PIX, 0, stream>>>(
             hdr, ranges, v0, v1, W, H, xy, co, colors, depth, background, final_T, n_contrib, out_color, out_invdepth,
             hdr_rw, gx, num_tiles, order_fwd, tile_nproc, order_bwd);
@@ -476,7 +790,16 @@ int launch_blend_backward(int W, int H, const float *background, const float *co
     const uint32_t *n_contrib = reinterpret_cast<const uint32_t *>(image + IL.n_contrib);
     const uint32_t *order_bwd = reinterpret_cast<const uint32_t *>(image + IL.order_bwd);
     ProfScope prof(K_BLEND_BWD, stream);
-    if (dL_dinvdepth_pix)
+    if (blend_mode() == BLEND_WARP) {
+        if (dL_dinvdepth_pix)
+            blend_backward_warp_kernel<true><<<num_tiles, TILE_PIX, 0, stream>>>(
+                hdr, ranges, v0, v1, W, H, background, xy, co, colors, depth, final_T, n_contrib, dL_dpix,
+                dL_dinvdepth_pix, grad_acc, gx, order_bwd);
+        else
+            blend_backward_warp_kernel<false><<<num_tiles, TILE_PIX, 0, stream>>>(
+                hdr, ranges, v0, v1, W, H, background, xy, co, colors, depth, final_T, n_contrib, dL_dpix, nullptr,
+                grad_acc, gx, order_bwd);
+    } else if (dL_dinvdepth_pix)
         blend_backward_kernel<true><<<num_tiles, TILE_PIX, 0, stream>>>(
             hdr, ranges, v0, v1, W, H, background, xy, co, colors, depth, final_T, n_contrib, dL_dpix, dL_dinvdepth_pix,
             grad_acc, gx, order_bwd);
