@@ -618,15 +618,13 @@ __global__ void __launch_bounds__(TILE_PIX) blend_backward_warp_kernel(
     if (n_proc == 0) return;
     const uint32_t nchunks = (n_proc + 31u) / 32u;
 
-    float acc0 = 0.f, acc1 = 0.f, acc2 = 0.f, acci = 0.f;
-    float lc0 = 0.f, lc1 = 0.f, lc2 = 0.f, lci = 0.f, last_alpha = 0.f;
+    float behind = 0.f;
     float g0 = 0.f, g1 = 0.f, g2 = 0.f, gi = 0.f;
     if (inside) {
         g0 = dL_dpix[pid]; g1 = dL_dpix[plane + pid]; g2 = dL_dpix[2 * plane + pid];
         if (INVDEPTH) gi = dL_dinvdepth_pix[pid];
     }
     const float bg_dot = bg[0] * g0 + bg[1] * g1 + bg[2] * g2;
-    const float ddelx_dx = 0.5f * (float)W, ddely_dy = 0.5f * (float)H;
     const uint32_t slot10 = lane % 10u, group = lane / 10u;   // lane l (< 30) ends up with sum `slot10` of Gaussian `group`
 
     uint32_t p_id = 0, id_next = 0;
@@ -651,7 +649,7 @@ __global__ void __launch_bounds__(TILE_PIX) blend_backward_warp_kernel(
         if (hit) {
             const uint32_t s = (tail + __popc(m & lanemask_lt())) & (RING - 1);
             s_a[warp][s] = make_float4(p_xy.x, p_xy.y, __uint_as_float(p_id), __uint_as_float(n_proc - 1u - back));
-            s_co[warp][s] = p_co;
+            s_co[warp][s] = prescale_conic(p_co);
             s_feat[warp][s] = p_feat;
         }
         tail += __popc(m);
@@ -671,9 +669,9 @@ __global__ void __launch_bounds__(TILE_PIX) blend_backward_warp_kernel(
                 const uint32_t s = (head + (uint32_t)u) & (RING - 1);
                 const float4 e = s_a[warp][s];
                 const float dx = e.x - pxf, dy = e.y - pyf;
-                const float4 co = s_co[warp][s];
-                const float power = -0.5f * (co.x * dx * dx + co.z * dy * dy) - co.y * dx * dy;
-                const float G = __expf(power);
+                const float4 co = s_co[warp][s];   // pre-scaled (log2 domain): exactly the forward's alpha
+                const float power = dx * (co.x * dx + co.y * dy) + co.z * dy * dy;
+                const float G = fast_exp2(power);
                 const float alpha = fminf(0.99f, co.w * G);
                 ok[u] = (uint32_t)u < avail && __float_as_uint(e.w) < last_contributor && !(power > 0.f) &&
                         alpha >= 1.f / 255.f;
@@ -687,35 +685,34 @@ __global__ void __launch_bounds__(TILE_PIX) blend_backward_warp_kernel(
 #pragma unroll
             for (int u = 0; u < 3; u++) {
                 if (!ok[u]) continue;
-                const float alpha = al[u], G = G_[u], dx = dx_[u], dy = dy_[u];
-                const float4 co = s_co[warp][ss[u]];
+                const float alpha = al[u], dx = dx_[u], dy = dy_[u];
                 const float4 f = s_feat[warp][ss[u]];
-                const float inv_1ma = __fdividef(1.f, 1.f - alpha);
-                T = T * inv_1ma;
-                const float dchannel_dcolor = alpha * T;
-                acc0 = last_alpha * lc0 + (1.f - last_alpha) * acc0; lc0 = f.x;
-                acc1 = last_alpha * lc1 + (1.f - last_alpha) * acc1; lc1 = f.y;
-                acc2 = last_alpha * lc2 + (1.f - last_alpha) * acc2; lc2 = f.z;
-                float dL_dalpha = (f.x - acc0) * g0 + (f.y - acc1) * g1 + (f.z - acc2) * g2;
-                w[10 * u + 6] = dchannel_dcolor * g0;
-                w[10 * u + 7] = dchannel_dcolor * g1;
-                w[10 * u + 8] = dchannel_dcolor * g2;
+                const float ra = __fdividef(1.f, 1.f - alpha);
+                T = T * ra;                                   // transmittance in front of this Gaussian
+                const float aT = alpha * T;
+                float cg = f.x * g0 + f.y * g1 + f.z * g2;    // (colour . dL/dpixel)
+                w[10 * u + 6] = aT * g0;
+                w[10 * u + 7] = aT * g1;
+                w[10 * u + 8] = aT * g2;
                 if (INVDEPTH) {
-                    acci = last_alpha * lci + (1.f - last_alpha) * acci; lci = f.w;
-                    dL_dalpha += (f.w - acci) * gi;
-                    w[10 * u + 9] = dchannel_dcolor * gi;
+                    cg += f.w * gi;
+                    w[10 * u + 9] = aT * gi;
                 }
-                dL_dalpha *= T;
-                last_alpha = alpha;
-                dL_dalpha += (-T_final * inv_1ma) * bg_dot;
-                const float dL_dG = co.w * dL_dalpha;
-                const float gdx = G * dx, gdy = G * dy;
-                w[10 * u + 0] = dL_dG * (-gdx * co.x - gdy * co.y) * ddelx_dx;
-                w[10 * u + 1] = dL_dG * (-gdy * co.z - gdx * co.y) * ddely_dy;
-                w[10 * u + 2] = -0.5f * gdx * dx * dL_dG;
-                w[10 * u + 3] = -0.5f * gdx * dy * dL_dG;
-                w[10 * u + 4] = -0.5f * gdy * dy * dL_dG;
-                w[10 * u + 5] = G * dL_dalpha;
+                // dL/dalpha = (c - accum_rec) . g T - T_final/(1-alpha) (bg . g) with accum_rec T = behind / (1 - alpha),
+                // behind = sum over the contributors behind this one of (c . g) alpha T  (the upstream recurrence,
+                // contracted with g before instead of after)
+                const float dL_dalpha = cg * T - (behind + T_final * bg_dot) * ra;
+                behind += cg * aT;
+                // raw moments of p = G dL/dalpha about the Gaussian centre; the preprocess backward turns them into
+                // dL/dmean2D, dL/dconic and dL/dopacity with the per-Gaussian conic (raster_backward.cu)
+                const float pw = G_[u] * dL_dalpha;
+                const float pdx = pw * dx, pdy = pw * dy;
+                w[10 * u + 0] = pdx;
+                w[10 * u + 1] = pdy;
+                w[10 * u + 2] = pdx * dx;
+                w[10 * u + 3] = pdx * dy;
+                w[10 * u + 4] = pdy * dy;
+                w[10 * u + 5] = pw;
             }
             const float sum = butterfly32(w, lane);
             if (lane < 30u && sum != 0.f) {
