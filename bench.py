@@ -50,6 +50,7 @@ def parse():
     ap.add_argument("--cameras", type=int, default=160)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-graph", action="store_true", help="eager per-view launches instead of the captured CUDA graph")
     return ap.parse_args()
 
 
@@ -172,6 +173,7 @@ def workload_config(scene, args, views):
     return {"workload": f"{scene.name}: {scene.N} Gaussians in {scene.tets.shape[0]} tets over {len(scene.meta['garments'])} "
                         f"cage(s), {scene.W}x{scene.H}, cov3D_precomp + colors_precomp path",
             "views_per_rank_per_step": views, "cameras": args.cameras, "parallelism": f"camera-sharded dp{args.gpus}",
+            "launch": "eager" if args.no_graph else "one CUDA-graph replay per view",
             "l2": "working set (>= 150 MB of Gaussian state + binning buffers per view) exceeds the 126 MB L2; no flush"}
 
 
@@ -202,13 +204,21 @@ def run_ours(args):
     def cam_ids(step):
         return [mine[(step * V + v) % len(mine)] for v in range(V)]
 
-    def region(n_steps, first_step, **kw):
+    # one view = one replay of the captured graph (training.GraphedViewStep); --no-graph launches every view eagerly
+    gv = None if args.no_graph else training.GraphedViewStep(avatar, cams[0], bg)
+
+    def region(n_steps, first_step, eager=False, **kw):
         ddist.barrier()
         torch.cuda.synchronize()
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         a.record()
         for s in range(n_steps):
-            training.multi_view_step(avatar, bank, cam_ids(first_step + s), weights, bg, **kw)
+            if gv is not None and not eager:
+                kw2 = {k: v for k, v in kw.items() if k != "from_host"}
+                training.multi_view_step_graphed(avatar, bank, cam_ids(first_step + s), gv, weights=weights,
+                                                 from_host=kw.get("from_host", False), **kw2)
+            else:
+                training.multi_view_step(avatar, bank, cam_ids(first_step + s), weights, bg, **kw)
         b.record()
         torch.cuda.synchronize()
         ddist.barrier()
@@ -231,7 +241,7 @@ def run_ours(args):
 
     # same region again with per-kernel CUDA events (kept out of `value`): per-kernel durations for the roofline
     _lib.profile_enable(True)
-    region(args.steps, args.warmup)
+    region(args.steps, args.warmup, eager=True)
     prof = _lib.profile_collect()
     _lib.profile_enable(False)
 
@@ -282,14 +292,14 @@ def run_ours(args):
     # e2e: the same steps through the public API with this step's inputs in pinned HOST memory
     e2e = None
     if not args.no_e2e:
-        feed = training.HostFeed(weights_h, dev)
+        feed = training.HostFeed(weights_h, dev, cam_host=bank.host, tetpoints_host=avatar.tetpoints_host)
         region(1, 0, from_host=True, feed=feed, loss_host=loss_h)
         ms_e = region(args.steps, args.warmup, from_host=True, feed=feed, loss_host=loss_h)
         h2d = 35 * 4 + avatar.tetpoints.numel() * 4 + weights.numel() * 4
         e2e = {"value": views_total / (ms_e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d * V,
                "d2h_bytes_per_step": 4,
                "inputs_from_host": "per view: camera (35 floats), cage vertices tetpoints [V,3], target/weight image [3,H,W] "
-                                   "(uploaded one view ahead on a side stream); the step's loss is read back once per step; "
+                                   "(all uploaded one view ahead on a side stream); the step's loss is read back once per step; "
                                    "Gaussian parameters stay resident like nn.Parameters"}
 
     # a D3GA training FRAME renders the same Gaussians twice (RGB + silhouette); frames/s with and
@@ -342,12 +352,13 @@ def run_ours(args):
             lbs_iter()
         b.record()
         torch.cuda.synchronize()
+        lbs_launches = (_lib.launch_count() - l0) / 200
         _lib.profile_enable(True)
         for _ in range(20):
             lbs_iter()
         kprof = {k: round(v[0] / v[1] * 1e3, 2) for k, v in _lib.profile_collect().items() if v[1] and k.startswith("lbs_")}
         _lib.profile_enable(False)
-        lbs = {"us_per_pose_fwd_bwd": a.elapsed_time(b) * 1e3 / 200, "kernel_us": kprof, "kernel_launches_per_pose": (_lib.launch_count() - l0) / 200,
+        lbs = {"us_per_pose_fwd_bwd": a.elapsed_time(b) * 1e3 / 200, "kernel_us": kprof, "kernel_launches_per_pose": lbs_launches,
                "joints": len(model_json["Skeleton"]["Bones"]), "cage_vertices": n_cage,
                "note": "Blueman.get (lib/blueman.py:139-167) + gradient to delta; the reference's joint loop alone is "
                        "~10 torch launches per joint (lbsmodel/body_model.py:327-345)"}

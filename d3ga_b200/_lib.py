@@ -9,7 +9,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libd3ga_b200.so")
+LIB_PATH = os.environ.get("D3GA_LIB") or os.path.join(_HERE, "libd3ga_b200.so")   # D3GA_LIB: development builds
 
 # every symbol include/d3ga_b200.h declares (tests/test_abi.py checks the header against this list)
 EXPORTS = [
@@ -127,8 +127,19 @@ def raster_layout(P: int, W: int, H: int, capacity: int) -> dict:
     return dict(zip(LAYOUT_NAMES, [int(v) for v in out]))
 
 
+_graph_launches = 0
+
+
+def note_graph_launches(n: int) -> None:
+    """Kernels of this library that a CUDA-graph replay launched (the C counter only sees launches made through the
+    entry points, i.e. at capture time)."""
+    global _graph_launches
+    _graph_launches += int(n)
+
+
 def launch_count() -> int:
-    return int(load().d3ga_launch_count())
+    """Kernels launched by this library: through its entry points plus those replayed from captured graphs."""
+    return int(load().d3ga_launch_count()) + _graph_launches
 
 
 def profile_enable(on: bool) -> None:

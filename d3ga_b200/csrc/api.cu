@@ -62,15 +62,6 @@ int sort_mode() {
     return mode;
 }
 
-int blend_mode() {
-    static const int mode = [] {
-        const char *v = getenv("D3GA_BLEND_MODE");
-        if (v && strcmp(v, "warp") == 0) return (int)BLEND_WARP;
-        return (int)BLEND_CTA;
-    }();
-    return mode;
-}
-
 // upstream getHigherMsb: number of bits needed for the tile id
 static int higher_msb(uint32_t n) {
     uint32_t msb = sizeof(n) * 4, step = msb;

@@ -155,8 +155,6 @@ int launch_sort_and_ranges(uint8_t *geom, uint8_t *binning, const BinLayout &BL,
 int launch_depth_sort(int P, uint8_t *geom, const GeomLayout &GL, cudaStream_t stream);
 enum SortMode { SORT_DEPTH_FIRST = 0, SORT_GLOBAL = 1, SORT_SEGMENTED = 2 };
 int sort_mode();   // D3GA_SORT_MODE = depthfirst (default) | global | segmented
-enum BlendMode { BLEND_CTA = 0, BLEND_WARP = 1 };
-int blend_mode();  // D3GA_BLEND_MODE = cta (CTA-staged batches) | warp (warp-autonomous staging)
 int launch_segment_sort(uint8_t *geom, uint8_t *binning, const BinLayout &BL, uint8_t *image, const ImgLayout &IL,
                         int num_tiles, cudaStream_t stream);
 int launch_blend_forward(int W, int H, const float *background, const float *colors, const uint8_t *geom,

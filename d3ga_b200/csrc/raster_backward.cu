@@ -15,7 +15,7 @@ namespace d3ga {
 namespace {
 
 struct BwdParams {
-    int P, sh_degree, sh_coeffs, W, H, antialiasing, has_invdepth, moments;
+    int P, sh_degree, sh_coeffs, W, H, antialiasing, has_invdepth;
     float scale_modifier, tanfovx, tanfovy, focal_x, focal_y;
     const float *means3D, *opacities, *scales, *rotations, *cov3D, *shs, *view, *proj, *campos, *grad_acc;
     const int32_t *radii;
@@ -46,8 +46,8 @@ __global__ void __launch_bounds__(GEO_THREADS) preprocess_backward_kernel(const 
         acc[4] = b.x; acc[5] = b.y; acc[6] = b.z; acc[7] = b.w;
         acc[8] = c.x; acc[9] = c.y; acc[10] = c.z; acc[11] = c.w;
     }
-    if (p.moments) {
-        // the warp-autonomous blend backward accumulates raw moments of p = G dL/dalpha about the 2-D centre:
+    {
+        // the blend backward accumulates raw moments of p = G dL/dalpha about the 2-D centre:
         // (sum p dx, sum p dy, sum p dx^2, sum p dx dy, sum p dy^2, sum p); with dL/dG = opacity dL/dalpha they give
         // the six derivatives upstream accumulates per pixel
         const float4 co = p.conic_opacity[i];
@@ -284,7 +284,6 @@ int launch_preprocess_backward(int P, int sh_degree, int sh_coeffs, int W, int H
     BwdParams p;
     p.P = P; p.sh_degree = sh_degree; p.sh_coeffs = sh_coeffs; p.W = W; p.H = H; p.antialiasing = antialiasing;
     p.has_invdepth = has_invdepth_grad;
-    p.moments = blend_mode() == BLEND_WARP;
     p.conic_opacity = reinterpret_cast<const float4 *>(geom + GL.conic_opacity);
     p.scale_modifier = scale_modifier; p.tanfovx = tanfovx; p.tanfovy = tanfovy;
     p.focal_y = (float)H / (2.0f * tanfovy);

@@ -3,13 +3,23 @@
 // Replaces renderCUDA forward / backward inside diff_gaussian_rasterization._C (reached from renderer.py:130-141
 // and from autograd when models/trainer.py:186-192 calls loss.backward()).
 //
-// One CTA per 16x16 tile, one thread per pixel.  The tile's depth-sorted Gaussians are staged through shared
-// memory in batches of 256 (id, pixel centre, conic + opacity, colour, 1/depth), front to back in the forward and
-// back to front in the backward.  Forward semantics (same order of tests as upstream): skip power > 0, alpha =
-// min(.99, o * exp(power)), skip alpha < 1/255, stop the pixel when T * (1 - alpha) < 1e-4, out = C + T * bg.
+// One CTA per 16x16 tile (longest list first), one thread per pixel, one warp per 8x4 pixel block.  Each warp walks the
+// tile's depth-sorted list ON ITS OWN -- 32 Gaussians per step, one per lane, gathered a step ahead in registers (ids two
+// steps ahead), tested exactly against the warp's pixel block (footprint_hit), and only the survivors are parked
+// (compacted, in list order) in a per-warp ring in shared memory from which the blend loop takes them in groups.  There
+// is no CTA barrier in the loop: with batches staged by the whole CTA a third of all warp-stall samples sat on that
+// barrier, because per-warp culling gives the eight warps of a tile very different amounts of work.  A warp whose pixels
+// are all finished simply stops.  The price is that the eight warps each read the tile's list (they run close enough
+// together that seven of them hit in L1) and each evaluate the footprint test.  Front to back in the forward, back to
+// front over the prefix its own pixels reached in the backward.
+// Forward semantics (same order of tests as upstream): skip power > 0, alpha = min(.99, o * exp(power)), skip
+// alpha < 1/255, stop the pixel when T * (1 - alpha) < 1e-4, out = C + T * bg.
 //
-// Backward: every (pixel, Gaussian) pair produces ten partial derivatives.  Instead of ten global atomics per pair
-// (upstream) they are reduced in three levels:
+// Backward: every (pixel, Gaussian) pair produces nine or ten partial sums: the six raw moments of p = G dL/dalpha about
+// the Gaussian's 2-D centre (sum p dx, p dy, p dx^2, p dx dy, p dy^2, p -- the preprocess backward turns them into
+// dL/dmean2D, dL/dconic, dL/dopacity with the per-Gaussian conic, so the pixel loop never touches the conic again), the
+// three colour derivatives and the inverse-depth one.  Instead of ten global atomics per pair (upstream) they are reduced
+// in two levels:
 //   warp   : butterfly transpose-reduction over three Gaussians at a time -- 31 shuffles bring the 30 32-lane sums
 //            to 30 different lanes (a plain reduction would need 150), skipped entirely for Gaussians no lane of
 //            the warp touches;
@@ -17,33 +27,17 @@
 //            handful of L2 sectors) adds them into the packed per-Gaussian accumulator that the preprocess backward
 //            (R8) then reads once -- one RED instruction per (warp, 3 Gaussians) instead of ten atomics per
 //            (pixel, Gaussian).
+// dL/dalpha uses upstream's recurrence contracted with dL/dpixel BEFORE the loop instead of after (one scalar "behind"
+// = sum over the contributors behind of (c . g) alpha T instead of a running colour per channel).
 // Algorithmic bytes: forward 40 B per duplicate + 20 B per pixel; backward 40 B read + 40 B gradient RMW per
-// duplicate + 20 B per pixel.  Both kernels are FP32/SFU bound rather than HBM bound.
+// duplicate + 20 B per pixel.  Both kernels are issue / latency bound rather than HBM bound.
+// Measured and dropped: persistent CTAs with a per-CTA tile queue or a per-CTA block dispenser (the warps of a tile drift
+// apart, the list no longer hits in L1: 273 -> 333-386 us backward), 2 or 4 warps per CTA, 4 CTAs/SM in the backward.
 #include "common.cuh"
 
 namespace d3ga {
 
-#ifdef D3GA_DEBUG_TIMING
-__device__ unsigned long long *g_dbg_buf = nullptr;   // [tiles][4]: tile, cycles, smid, max warp entries
-#endif
-
 namespace {
-
-constexpr int BATCH = TILE_PIX;   // Gaussians staged per round
-
-// Pixel footprint of one staged Gaussian: the axis-aligned box outside of which alpha = o * exp(power) is certainly
-// below the 1/255 cut (so the exact per-pixel test would skip it anyway).  power >= -tau with tau = ln(255 o) bounds
-// d^T C d <= 2 tau; the extents of that ellipse are sqrt(2 tau C^-1_xx), sqrt(2 tau C^-1_yy).  A relative and an
-// absolute margin keep the test conservative against rounding; degenerate conics are never culled.
-__device__ __forceinline__ float4 footprint_box(float2 c, float4 co) {
-    if (co.w < 1.f / 255.f) return make_float4(INFINITY, -INFINITY, INFINITY, -INFINITY);   // can never pass the cut
-    const float det = co.x * co.z - co.y * co.y;
-    const float tau = __logf(255.f * co.w);
-    if (!(det > 0.f) || !(tau >= 0.f)) return make_float4(-INFINITY, INFINITY, -INFINITY, INFINITY);
-    const float k = 2.f * tau / det;
-    const float hx = sqrtf(k * co.z) * 1.001f + 0.5f, hy = sqrtf(k * co.x) * 1.001f + 0.5f;
-    return make_float4(c.x - hx, c.x + hx, c.y - hy, c.y + hy);
-}
 
 // Conic pre-scaled for the inner loop: log2(G) = A dx^2 + B dx dy + C dy^2 with A = -0.5 log2(e) conic.xx, B = -log2(e)
 // conic.xy, C = -0.5 log2(e) conic.yy, so G = exp2(.) costs one MUFU and no extra multiply.
@@ -62,8 +56,7 @@ struct WarpBlock {
     int px, py;
     float x0, x1, y0, y1;
 };
-__device__ __forceinline__ WarpBlock warp_block(int tid, int tile_x, int tile_y) {
-    const int warp = tid >> 5, lane = tid & 31;
+__device__ __forceinline__ WarpBlock warp_block(int warp, int lane, int tile_x, int tile_y) {
     const int bx = tile_x * TILE + (warp & 1) * 8, by = tile_y * TILE + (warp >> 1) * 4;
     WarpBlock w;
     w.px = bx + (lane & 7);
@@ -71,163 +64,8 @@ __device__ __forceinline__ WarpBlock warp_block(int tid, int tile_x, int tile_y)
     w.x0 = (float)bx; w.x1 = (float)(bx + 7); w.y0 = (float)by; w.y1 = (float)(by + 3);
     return w;
 }
-
-template <bool INVDEPTH>
-__global__ void __launch_bounds__(TILE_PIX) blend_forward_kernel(
-    const RasterHeader *__restrict__ hdr, const uint2 *__restrict__ ranges, const uint32_t *__restrict__ vals0,
-    const uint32_t *__restrict__ vals1, int W, int H, const float2 *__restrict__ xy,
-    const float4 *__restrict__ conic_opacity, const float *__restrict__ colors, const float *__restrict__ depths,
-    const float *__restrict__ bg, float *__restrict__ final_T, uint32_t *__restrict__ n_contrib,
-    float *__restrict__ out_color, float *__restrict__ out_invdepth, RasterHeader *__restrict__ hdr_rw, int grid_x,
-    int num_tiles, const uint32_t *__restrict__ order_fwd, uint32_t *__restrict__ tile_nproc,
-    uint32_t *__restrict__ order_bwd) {
-    // double-buffered staging: batch i+1 is gathered into registers while batch i is blended, then parked in the
-    // other buffer -- one CTA barrier per batch (the "is every pixel done" vote)
-    __shared__ float2 s_xy[2][BATCH];
-    __shared__ float4 s_co[2][BATCH];
-    __shared__ float4 s_feat[2][BATCH];   // r, g, b, 1/depth
-    __shared__ float4 s_box[2][BATCH];
-    __shared__ uint8_t s_list[TILE_PIX / 32][BATCH];
-    __shared__ uint32_t s_bins[257];
-    __shared__ uint32_t s_red[TILE_PIX / 32];
-    __shared__ uint32_t s_last;
-
-    const uint32_t tile = order_fwd[blockIdx.x];   // longest Gaussian list first
-    const int tid = threadIdx.x;
-#ifdef D3GA_DEBUG_TIMING
-    const long long dbg_t0 = clock64();
-    unsigned dbg_entries = 0, dbg_batches = 0;
-#endif
-    const uint32_t lane = tid & 31, warp = tid >> 5;
-    const WarpBlock wb = warp_block(tid, (int)(tile % (uint32_t)grid_x), (int)(tile / (uint32_t)grid_x));
-    const int px = wb.px, py = wb.py;
-    const bool inside = px < W && py < H;
-    const float pxf = (float)px, pyf = (float)py;
-    uint2 range = make_uint2(0, 0);
-    if (!hdr->overflow) range = ranges[tile];
-    const uint32_t *point_list = hdr->final_sel ? vals1 : vals0;
-    const uint32_t count = range.y - range.x;
-    const int rounds = (int)((count + BATCH - 1) / BATCH);
-    int todo = (int)count;
-
-    bool done = !inside;
-    float T = 1.f, C0 = 0.f, C1 = 0.f, C2 = 0.f, invd = 0.f;
-    uint32_t last = 0;
-    float2 p_xy = make_float2(0.f, 0.f);
-    float4 p_co = make_float4(0.f, 0.f, 0.f, 0.f), p_feat = make_float4(0.f, 0.f, 0.f, 0.f);
-    auto gather = [&](uint32_t progress) {
-        const uint32_t id = point_list[range.x + progress];
-        p_xy = xy[id];
-        p_co = conic_opacity[id];
-        p_feat = make_float4(colors[3 * (size_t)id], colors[3 * (size_t)id + 1], colors[3 * (size_t)id + 2],
-                             INVDEPTH ? __fdividef(1.f, depths[id]) : 0.f);
-    };
-    auto park = [&](int buf) {
-        s_xy[buf][tid] = p_xy;
-        s_co[buf][tid] = prescale_conic(p_co);
-        s_box[buf][tid] = footprint_box(p_xy, p_co);
-        s_feat[buf][tid] = p_feat;
-    };
-    if ((uint32_t)tid < count) { gather(tid); park(0); }
-    for (int i = 0; i < rounds; i++, todo -= BATCH) {
-        if (__syncthreads_count(done) == TILE_PIX) break;
-        const int buf = i & 1;
-        const uint32_t next = (uint32_t)(i + 1) * BATCH + tid;
-        if (next < count) gather(next);   // in flight while this batch is blended
-        if (__all_sync(0xffffffffu, done)) {
-            if (next < count) park(buf ^ 1);
-            continue;
-        }
-        const int n = min(BATCH, todo);
-        // this warp's depth-ordered list of the staged Gaussians whose footprint reaches its pixel block
-        int cnt = 0;
-#pragma unroll
-        for (int r = 0; r < BATCH / 32; r++) {
-            const int g = r * 32 + (int)lane;
-            const float4 b = s_box[buf][g];
-            const bool hit = g < n && b.y >= wb.x0 && b.x <= wb.x1 && b.w >= wb.y0 && b.z <= wb.y1;
-            const uint32_t m = __ballot_sync(0xffffffffu, hit);
-            if (hit) s_list[warp][cnt + __popc(m & lanemask_lt())] = (uint8_t)g;
-            cnt += __popc(m);
-        }
-        __syncwarp();
-#ifdef D3GA_DEBUG_TIMING
-        dbg_entries += cnt; dbg_batches++;
-#endif
-        const uint32_t base = (uint32_t)i * BATCH;
-        // four list entries at a time: their alphas are independent (instruction-level parallelism for the warp
-        // that sits on the tile's critical path); only the transmittance update is sequential
-        for (int k = 0; k < cnt; k += 4) {
-            if (__all_sync(0xffffffffu, done)) break;
-            float a[4];
-            int jj[4];
-#pragma unroll
-            for (int u = 0; u < 4; u++) {
-                const bool valid = k + u < cnt;
-                const int j = valid ? (int)s_list[warp][k + u] : 0;
-                const float2 c = s_xy[buf][j];
-                const float dx = c.x - pxf, dy = c.y - pyf;
-                const float4 co = s_co[buf][j];   // pre-scaled: log2 domain
-                const float power = dx * (co.x * dx + co.y * dy) + co.z * dy * dy;
-                const float alpha = fminf(0.99f, co.w * fast_exp2(power));
-                a[u] = (valid && !(power > 0.f) && alpha >= 1.f / 255.f) ? alpha : 0.f;
-                jj[u] = j;
-            }
-#pragma unroll
-            for (int u = 0; u < 4; u++) {
-                if (done || a[u] == 0.f) continue;
-                const float test_T = T * (1.f - a[u]);
-                if (test_T < 0.0001f) { done = true; continue; }
-                const float4 f = s_feat[buf][jj[u]];
-                const float w = a[u] * T;
-                C0 += f.x * w; C1 += f.y * w; C2 += f.z * w;
-                if (INVDEPTH) invd += f.w * w;
-                T = test_T;
-                last = base + (uint32_t)jj[u] + 1u;
-            }
-        }
-        if (next < count) park(buf ^ 1);
-    }
-    if (inside) {
-        const size_t pid = (size_t)py * W + px, plane = (size_t)H * W;
-        final_T[pid] = T;
-        n_contrib[pid] = last;
-        out_color[pid] = C0 + T * bg[0];
-        out_color[plane + pid] = C1 + T * bg[1];
-        out_color[2 * plane + pid] = C2 + T * bg[2];
-        if (INVDEPTH) out_invdepth[pid] = invd;
-    }
-#ifdef D3GA_DEBUG_TIMING
-    if (g_dbg_buf) {
-        const unsigned emax = __reduce_max_sync(0xffffffffu, dbg_entries);
-        __shared__ unsigned s_dbg[8];
-        if (lane == 0) s_dbg[warp] = emax;
-        __syncthreads();
-        if (tid == 0) {
-            unsigned m = 0, sm;
-            for (int w = 0; w < 8; w++) m = max(m, s_dbg[w]);
-            asm("mov.u32 %0, %%smid;" : "=r"(sm));
-            unsigned long long *o = g_dbg_buf + 6 * (size_t)blockIdx.x;
-            o[0] = tile; o[1] = (unsigned long long)(clock64() - dbg_t0); o[2] = sm; o[3] = m; o[4] = count; o[5] = dbg_batches;
-        }
-    }
-#endif
-    // deepest contributor of the tile = how far the backward has to go; the last CTA orders the backward's tiles
-    const uint32_t wmax = __reduce_max_sync(0xffffffffu, inside ? last : 0u);
-    if (lane == 0) s_red[warp] = wmax;
-    __syncthreads();
-    if (tid == 0) {
-        uint32_t m = 0;
-        for (int w = 0; w < TILE_PIX / 32; w++) m = max(m, s_red[w]);
-        tile_nproc[tile] = m;
-        __threadfence();
-        s_last = atomicAdd(&hdr_rw->blend_done, 1u) == (uint32_t)num_tiles - 1u;
-    }
-    __syncthreads();
-    if (!s_last) return;
-    __threadfence();
-    const uint32_t *np = tile_nproc;
-    order_tiles_descending(num_tiles, [np](int t) { return __ldcg(np + t); }, order_bwd, s_bins);
+__device__ __forceinline__ WarpBlock warp_block(int tid, int tile_x, int tile_y) {
+    return warp_block(tid >> 5, tid & 31, tile_x, tile_y);
 }
 
 // Three Gaussians at once: 3 x 10 partials (+2 zeros) per lane, summed over the 32 lanes, land on 32 DIFFERENT lanes
@@ -259,181 +97,30 @@ __device__ __forceinline__ float butterfly32(float (&w)[32], uint32_t lane) {
     return keep + __shfl_xor_sync(0xffffffffu, send, 1);
 }
 
-template <bool INVDEPTH>
-__global__ void __launch_bounds__(TILE_PIX) blend_backward_kernel(
-    const RasterHeader *__restrict__ hdr, const uint2 *__restrict__ ranges, const uint32_t *__restrict__ vals0,
-    const uint32_t *__restrict__ vals1, int W, int H, const float *__restrict__ bg, const float2 *__restrict__ xy,
-    const float4 *__restrict__ conic_opacity, const float *__restrict__ colors, const float *__restrict__ depths,
-    const float *__restrict__ final_T, const uint32_t *__restrict__ n_contrib, const float *__restrict__ dL_dpix,
-    const float *__restrict__ dL_dinvdepth_pix, float *__restrict__ grad_acc, int grid_x,
-    const uint32_t *__restrict__ order_bwd) {
-    // double-buffered staging: batch i+1 is gathered into registers while batch i is processed, then parked in the
-    // other buffer -- one CTA barrier per batch
-    __shared__ float2 s_xy[2][BATCH];
-    __shared__ float4 s_co[2][BATCH];
-    __shared__ float4 s_feat[2][BATCH];
-    __shared__ float4 s_box[2][BATCH];
-    __shared__ uint32_t s_id[2][BATCH];
-    __shared__ uint8_t s_list[TILE_PIX / 32][BATCH];
-    __shared__ uint32_t s_max[TILE_PIX / 32];
-
-    const uint32_t tile = order_bwd[blockIdx.x];   // deepest contributor first
-    const int tid = threadIdx.x;
-    const uint32_t lane = tid & 31, warp = tid >> 5;
-    const WarpBlock wb = warp_block(tid, (int)(tile % (uint32_t)grid_x), (int)(tile / (uint32_t)grid_x));
-    const int px = wb.px, py = wb.py;
-    const bool inside = px < W && py < H;
-    const float pxf = (float)px, pyf = (float)py;
-    uint2 range = make_uint2(0, 0);
-    if (!hdr->overflow) range = ranges[tile];
-    if (range.y <= range.x) return;
-    const uint32_t *point_list = hdr->final_sel ? vals1 : vals0;
-    const size_t pid = (size_t)py * W + px, plane = (size_t)H * W;
-
-    const float T_final = inside ? final_T[pid] : 0.f;
-    float T = T_final;
-    const uint32_t last_contributor = inside ? n_contrib[pid] : 0u;
-    // Only the first n_proc Gaussians of the tile's list reached any pixel in the forward: nothing behind them is
-    // staged at all (the forward stops a pixel at T < 1e-4, typically after a small fraction of a deep list).
-    const uint32_t warp_last = __reduce_max_sync(0xffffffffu, last_contributor);
-    if (lane == 0) s_max[warp] = warp_last;
-    __syncthreads();
-    uint32_t n_proc = 0;
-#pragma unroll
-    for (int w = 0; w < TILE_PIX / 32; w++) n_proc = max(n_proc, s_max[w]);
-    if (n_proc == 0) return;
-    const int rounds = (int)((n_proc + BATCH - 1) / BATCH);
-
-    float acc0 = 0.f, acc1 = 0.f, acc2 = 0.f, acci = 0.f;
-    float lc0 = 0.f, lc1 = 0.f, lc2 = 0.f, lci = 0.f, last_alpha = 0.f;
-    float g0 = 0.f, g1 = 0.f, g2 = 0.f, gi = 0.f;
-    if (inside) {
-        g0 = dL_dpix[pid]; g1 = dL_dpix[plane + pid]; g2 = dL_dpix[2 * plane + pid];
-        if (INVDEPTH) gi = dL_dinvdepth_pix[pid];
-    }
-    const float bg_dot = bg[0] * g0 + bg[1] * g1 + bg[2] * g2;
-    const float ddelx_dx = 0.5f * (float)W, ddely_dy = 0.5f * (float)H;
-    const uint32_t slot = lane % 10u, group = lane / 10u;   // lane l (< 30) ends up with sum `slot` of Gaussian `group`
-
-    uint32_t p_id = 0;
-    float2 p_xy = make_float2(0.f, 0.f);
-    float4 p_co = make_float4(0.f, 0.f, 0.f, 0.f), p_feat = make_float4(0.f, 0.f, 0.f, 0.f);
-    // staged slot t of batch i holds the Gaussian at forward position q = n_proc - 1 - (i * BATCH + t): back to front
-    auto gather = [&](uint32_t progress) {
-        p_id = point_list[range.x + (n_proc - 1u - progress)];
-        p_xy = xy[p_id];
-        p_co = conic_opacity[p_id];
-        p_feat = make_float4(colors[3 * (size_t)p_id], colors[3 * (size_t)p_id + 1], colors[3 * (size_t)p_id + 2],
-                             INVDEPTH ? __fdividef(1.f, depths[p_id]) : 0.f);
-    };
-    auto park = [&](int buf) {
-        s_id[buf][tid] = p_id;
-        s_xy[buf][tid] = p_xy;
-        s_co[buf][tid] = p_co;
-        s_box[buf][tid] = footprint_box(p_xy, p_co);
-        s_feat[buf][tid] = p_feat;
-    };
-    if ((uint32_t)tid < n_proc) { gather(tid); park(0); }
-    __syncthreads();
-
-    for (int i = 0; i < rounds; i++) {
-        const int buf = i & 1;
-        const uint32_t next = (uint32_t)(i + 1) * BATCH + tid;
-        if (next < n_proc) gather(next);   // in flight while this batch is processed
-        const int n = (int)min((uint32_t)BATCH, n_proc - (uint32_t)i * BATCH);
-        const uint32_t q_first = n_proc - 1u - (uint32_t)i * BATCH;   // forward position of staged slot 0
-        int cnt = 0;
-#pragma unroll
-        for (int r = 0; r < BATCH / 32; r++) {
-            const int g = r * 32 + (int)lane;
-            const float4 b = s_box[buf][g];
-            const bool hit = g < n && (q_first - (uint32_t)g) < warp_last && b.y >= wb.x0 && b.x <= wb.x1 &&
-                             b.w >= wb.y0 && b.z <= wb.y1;
-            const uint32_t m = __ballot_sync(0xffffffffu, hit);
-            if (hit) s_list[warp][cnt + __popc(m & lanemask_lt())] = (uint8_t)g;
-            cnt += __popc(m);
-        }
-        __syncwarp();
-        // three list entries at a time: independent alpha evaluation, sequential transmittance recurrence, then ONE
-        // 32-value butterfly for the 3 x 10 partial derivatives and one RED instruction (30 lanes, <= 3 rows)
-        for (int k = 0; k < cnt; k += 3) {
-            int jj[3];
-            float G_[3], al[3], dx_[3], dy_[3];
-            bool ok[3];
-#pragma unroll
-            for (int u = 0; u < 3; u++) {
-                const bool valid = k + u < cnt;
-                const int j = valid ? (int)s_list[warp][k + u] : 0;
-                const float2 c = s_xy[buf][j];
-                const float dx = c.x - pxf, dy = c.y - pyf;
-                const float4 co = s_co[buf][j];
-                const float power = -0.5f * (co.x * dx * dx + co.z * dy * dy) - co.y * dx * dy;
-                const float G = __expf(power);
-                const float alpha = fminf(0.99f, co.w * G);
-                ok[u] = valid && (q_first - (uint32_t)j) < last_contributor && !(power > 0.f) && alpha >= 1.f / 255.f;
-                jj[u] = j; G_[u] = G; al[u] = alpha; dx_[u] = dx; dy_[u] = dy;
-            }
-            if (!__any_sync(0xffffffffu, ok[0] || ok[1] || ok[2])) continue;
-            float w[32];
-#pragma unroll
-            for (int e = 0; e < 32; e++) w[e] = 0.f;
-#pragma unroll
-            for (int u = 0; u < 3; u++) {
-                if (!ok[u]) continue;
-                const float alpha = al[u], G = G_[u], dx = dx_[u], dy = dy_[u];
-                const float4 co = s_co[buf][jj[u]];
-                const float4 f = s_feat[buf][jj[u]];
-                const float inv_1ma = __fdividef(1.f, 1.f - alpha);
-                T = T * inv_1ma;
-                const float dchannel_dcolor = alpha * T;
-                acc0 = last_alpha * lc0 + (1.f - last_alpha) * acc0; lc0 = f.x;
-                acc1 = last_alpha * lc1 + (1.f - last_alpha) * acc1; lc1 = f.y;
-                acc2 = last_alpha * lc2 + (1.f - last_alpha) * acc2; lc2 = f.z;
-                float dL_dalpha = (f.x - acc0) * g0 + (f.y - acc1) * g1 + (f.z - acc2) * g2;
-                w[10 * u + 6] = dchannel_dcolor * g0;
-                w[10 * u + 7] = dchannel_dcolor * g1;
-                w[10 * u + 8] = dchannel_dcolor * g2;
-                if (INVDEPTH) {
-                    acci = last_alpha * lci + (1.f - last_alpha) * acci; lci = f.w;
-                    dL_dalpha += (f.w - acci) * gi;
-                    w[10 * u + 9] = dchannel_dcolor * gi;
-                }
-                dL_dalpha *= T;
-                last_alpha = alpha;
-                dL_dalpha += (-T_final * inv_1ma) * bg_dot;
-                const float dL_dG = co.w * dL_dalpha;
-                const float gdx = G * dx, gdy = G * dy;
-                w[10 * u + 0] = dL_dG * (-gdx * co.x - gdy * co.y) * ddelx_dx;
-                w[10 * u + 1] = dL_dG * (-gdy * co.z - gdx * co.y) * ddely_dy;
-                w[10 * u + 2] = -0.5f * gdx * dx * dL_dG;
-                w[10 * u + 3] = -0.5f * gdx * dy * dL_dG;
-                w[10 * u + 4] = -0.5f * gdy * dy * dL_dG;
-                w[10 * u + 5] = G * dL_dalpha;
-            }
-            const float sum = butterfly32(w, lane);
-            if (lane < 30u && sum != 0.f) {
-                const int j = group == 0u ? jj[0] : (group == 1u ? jj[1] : jj[2]);
-                atomicAdd(grad_acc + (size_t)s_id[buf][j] * GRAD_ACC_FLOATS + slot, sum);
-            }
-        }
-        if (next < n_proc) park(buf ^ 1);
-        __syncthreads();
-    }
-}
-
-
-// ---- warp-autonomous variants ------------------------------------------------------------------------------------------
-// Same arithmetic as the kernels above, different staging: the CTA still owns a tile, but each warp walks the tile's
-// list ON ITS OWN -- 32 Gaussians per step, one per lane, gathered a step ahead in registers, tested against the warp's
-// 8x4 pixel block, and only the survivors are parked (compacted, in list order) in a per-warp ring in shared memory from
-// which the blend loop takes them in groups.  There is no CTA barrier in the loop: in the CTA-staged kernels a third of
-// all warp-stall samples sit on that barrier (profiles/r1_ncu_full_final.csv), because per-warp culling gives the eight
-// warps of a tile very different amounts of work.  A warp whose pixels are all finished simply stops.  The price is that
-// the eight warps each read the tile's list (L1 hits for seven of them) and each evaluate the footprint test.
 constexpr int RING = 64;                     // per-warp ring of staged survivors (>= group - 1 + 32)
+constexpr int FWD_WARPS = TILE_PIX / 32;    // (splitting a tile over 2 or 4 smaller CTAs was measured: no gain)
+#define FWD_MIN_CTAS 4
+#define BWD_MIN_CTAS 1
+#ifdef D3GA_BLEND_STATS
+// development counters: [0..3] forward (warp-steps, survivors, groups, passing pixel-Gaussian pairs), [4..7] backward
+__device__ unsigned long long g_blend_stats[8];
+__device__ unsigned long long *g_blend_trace = nullptr;   // [tiles * 8][4]: start ns, end ns, (smid << 32 | steps), survivors
+__device__ __forceinline__ unsigned long long global_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+#ifdef D3GA_BLEND_TRACE_ONLY   // the counters cost a global atomic per step; the trace alone does not perturb the timing
+#define STAT_ADD(i, v) do { } while (0)
+#else
+#define STAT_ADD(i, v) do { const unsigned long long _t = (unsigned long long)(v); if (_t) atomicAdd(&g_blend_stats[i], _t); } while (0)
+#endif
+#else
+#define STAT_ADD(i, v) do { } while (0)
+#endif
 
 // Exact version of the footprint test for one warp's pixel block: does the ellipse d^T C d <= 2 tau (outside of which
-// alpha < 1/255, see footprint_box) reach any pixel centre of the block?  The quadratic is convex with its minimum at
+// alpha < 1/255: power >= -tau with tau = ln(255 o) bounds d^T C d <= 2 tau) reach any pixel centre of the block?  The quadratic is convex with its minimum at
 // the Gaussian centre, so when the centre lies outside the block its minimum over the block sits on the edge(s) facing
 // the centre; on an edge it is a 1-D quadratic, minimised in closed form and clamped.  A relative and an absolute
 // margin keep the test conservative against rounding (a false "hit" only costs time, the per-pixel test decides);
@@ -462,7 +149,7 @@ __device__ __forceinline__ bool footprint_hit(float2 c, float4 co, const WarpBlo
 }
 
 template <bool INVDEPTH>
-__global__ void __launch_bounds__(TILE_PIX, 4) blend_forward_warp_kernel(
+__global__ void __launch_bounds__(FWD_WARPS * 32, FWD_MIN_CTAS) blend_forward_kernel(
     const RasterHeader *__restrict__ hdr, const uint2 *__restrict__ ranges, const uint32_t *__restrict__ vals0,
     const uint32_t *__restrict__ vals1, int W, int H, const float2 *__restrict__ xy,
     const float4 *__restrict__ conic_opacity, const float *__restrict__ colors, const float *__restrict__ depths,
@@ -470,17 +157,18 @@ __global__ void __launch_bounds__(TILE_PIX, 4) blend_forward_warp_kernel(
     float *__restrict__ out_color, float *__restrict__ out_invdepth, RasterHeader *__restrict__ hdr_rw, int grid_x,
     int num_tiles, const uint32_t *__restrict__ order_fwd, uint32_t *__restrict__ tile_nproc,
     uint32_t *__restrict__ order_bwd) {
-    __shared__ float4 s_a[TILE_PIX / 32][RING];      // x, y, list position + 1 (bits), unused
-    __shared__ float4 s_co[TILE_PIX / 32][RING];     // pre-scaled conic, opacity
-    __shared__ float4 s_feat[TILE_PIX / 32][RING];   // r, g, b, 1/depth
+    __shared__ float4 s_a[FWD_WARPS][RING];      // x, y, list position + 1 (bits), unused
+    __shared__ float4 s_co[FWD_WARPS][RING];     // pre-scaled conic, opacity
+    __shared__ float4 s_feat[FWD_WARPS][RING];   // r, g, b, 1/depth
     __shared__ uint32_t s_bins[257];
-    __shared__ uint32_t s_red[TILE_PIX / 32];
     __shared__ uint32_t s_last;
 
-    const uint32_t tile = order_fwd[blockIdx.x];   // longest Gaussian list first
+    constexpr uint32_t SPLIT = 8 / FWD_WARPS;          // CTAs per tile
+    const uint32_t tile = order_fwd[blockIdx.x / SPLIT];   // longest Gaussian list first
     const int tid = threadIdx.x;
     const uint32_t lane = tid & 31, warp = tid >> 5;
-    const WarpBlock wb = warp_block(tid, (int)(tile % (uint32_t)grid_x), (int)(tile / (uint32_t)grid_x));
+    const WarpBlock wb = warp_block((int)((blockIdx.x % SPLIT) * FWD_WARPS + warp), (int)lane,
+                                    (int)(tile % (uint32_t)grid_x), (int)(tile / (uint32_t)grid_x));
     const int px = wb.px, py = wb.py;
     const bool inside = px < W && py < H;
     const float pxf = (float)px, pyf = (float)py;
@@ -494,6 +182,10 @@ __global__ void __launch_bounds__(TILE_PIX, 4) blend_forward_warp_kernel(
     float T = 1.f, C0 = 0.f, C1 = 0.f, C2 = 0.f, invd = 0.f;
     uint32_t last = 0;
     float4(*ra)[RING] = s_a, (*rco)[RING] = s_co, (*rfeat)[RING] = s_feat;
+#ifdef D3GA_BLEND_STATS
+    const unsigned long long tr_t0 = global_ns();
+    unsigned tr_steps = 0, tr_surv = 0;
+#endif
 
     float2 p_xy = make_float2(0.f, 0.f);
     float4 p_co = make_float4(0.f, 0.f, 0.f, 0.f), p_feat = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -521,37 +213,47 @@ __global__ void __launch_bounds__(TILE_PIX, 4) blend_forward_warp_kernel(
             rfeat[warp][slot] = p_feat;
         }
         tail += __popc(m);
+        if (lane == 0) { STAT_ADD(0, 1); STAT_ADD(1, __popc(m)); }
+#ifdef D3GA_BLEND_STATS
+        tr_steps++; tr_surv += __popc(m);
+#endif
         if (pos + 32u < count) gather(id_next);                      // in flight while the ring is blended
         if (pos + 64u < count) id_next = point_list[pos + 64u];
         __syncwarp();
         const bool flush = c + 1u == nchunks;
         bool all_done = false;
+        // four ring entries at a time (head stays a multiple of four, so a group never wraps): their alphas are
+        // independent; the transmittance recurrence that follows is branch-free
         while (tail - head >= 4u || (flush && tail != head)) {
             const uint32_t avail = min(4u, tail - head);
+            const uint32_t base = head & (RING - 1);
+            const float4 *ga = &ra[warp][base], *gco = &rco[warp][base], *gf = &rfeat[warp][base];
             float a[4];
-            uint32_t ss[4];
+            uint32_t posv[4];
 #pragma unroll
             for (int u = 0; u < 4; u++) {
-                const uint32_t s = (head + (uint32_t)u) & (RING - 1);
-                const float4 e = ra[warp][s];
+                const float4 e = ga[u];
                 const float dx = e.x - pxf, dy = e.y - pyf;
-                const float4 co = rco[warp][s];   // pre-scaled: log2 domain
+                const float4 co = gco[u];   // pre-scaled: log2 domain
                 const float power = dx * (co.x * dx + co.y * dy) + co.z * dy * dy;
                 const float alpha = fminf(0.99f, co.w * fast_exp2(power));
                 a[u] = ((uint32_t)u < avail && !(power > 0.f) && alpha >= 1.f / 255.f) ? alpha : 0.f;
-                ss[u] = s;
+                posv[u] = __float_as_uint(e.z);
             }
+            if (lane == 0) STAT_ADD(2, 1);
 #pragma unroll
             for (int u = 0; u < 4; u++) {
-                if (done || a[u] == 0.f) continue;
+                const float4 f = gf[u];
                 const float test_T = T * (1.f - a[u]);
-                if (test_T < 0.0001f) { done = true; continue; }
-                const float4 f = rfeat[warp][ss[u]];
-                const float w = a[u] * T;
+                const bool live = !done && a[u] != 0.f;
+                const bool stop = live && test_T < 0.0001f;
+                const bool upd = live && !stop;
+                done = done || stop;
+                const float w = upd ? a[u] * T : 0.f;
                 C0 += f.x * w; C1 += f.y * w; C2 += f.z * w;
                 if (INVDEPTH) invd += f.w * w;
-                T = test_T;
-                last = __float_as_uint(ra[warp][ss[u]].z);
+                T = upd ? test_T : T;
+                last = upd ? posv[u] : last;
             }
             head += avail;
             if (__all_sync(0xffffffffu, done)) { all_done = true; break; }
@@ -567,17 +269,20 @@ __global__ void __launch_bounds__(TILE_PIX, 4) blend_forward_warp_kernel(
         out_color[2 * plane + pid] = C2 + T * bg[2];
         if (INVDEPTH) out_invdepth[pid] = invd;
     }
+#ifdef D3GA_BLEND_STATS
+    if (g_blend_trace && lane == 0) {
+        unsigned sm;
+        asm("mov.u32 %0, %%smid;" : "=r"(sm));
+        unsigned long long *o = g_blend_trace + 4 * ((size_t)blockIdx.x * FWD_WARPS + warp);
+        o[0] = tr_t0; o[1] = global_ns(); o[2] = ((unsigned long long)sm << 32) | tr_steps; o[3] = ((unsigned long long)count << 32) | tr_surv;
+    }
+#endif
     // deepest contributor of the tile = how far the backward has to go; the last CTA orders the backward's tiles
     const uint32_t wmax = __reduce_max_sync(0xffffffffu, inside ? last : 0u);
-    if (lane == 0) s_red[warp] = wmax;
+    if (lane == 0 && wmax) atomicMax(tile_nproc + tile, wmax);   // zeroed by the launcher
+    __threadfence();
     __syncthreads();
-    if (tid == 0) {
-        uint32_t mx = 0;
-        for (int w = 0; w < TILE_PIX / 32; w++) mx = max(mx, s_red[w]);
-        tile_nproc[tile] = mx;
-        __threadfence();
-        s_last = atomicAdd(&hdr_rw->blend_done, 1u) == (uint32_t)num_tiles - 1u;
-    }
+    if (tid == 0) s_last = atomicAdd(&hdr_rw->blend_done, 1u) == gridDim.x - 1u;
     __syncthreads();
     if (!s_last) return;
     __threadfence();
@@ -586,7 +291,7 @@ __global__ void __launch_bounds__(TILE_PIX, 4) blend_forward_warp_kernel(
 }
 
 template <bool INVDEPTH>
-__global__ void __launch_bounds__(TILE_PIX) blend_backward_warp_kernel(
+__global__ void __launch_bounds__(TILE_PIX, BWD_MIN_CTAS) blend_backward_kernel(
     const RasterHeader *__restrict__ hdr, const uint2 *__restrict__ ranges, const uint32_t *__restrict__ vals0,
     const uint32_t *__restrict__ vals1, int W, int H, const float *__restrict__ bg, const float2 *__restrict__ xy,
     const float4 *__restrict__ conic_opacity, const float *__restrict__ colors, const float *__restrict__ depths,
@@ -653,6 +358,7 @@ __global__ void __launch_bounds__(TILE_PIX) blend_backward_warp_kernel(
             s_feat[warp][s] = p_feat;
         }
         tail += __popc(m);
+        if (lane == 0) { STAT_ADD(4, 1); STAT_ADD(5, __popc(m)); }
         if (back + 32u < n_proc) gather(id_next);
         if (back + 64u < n_proc) id_next = point_list[n_proc - 65u - back];
         __syncwarp();
@@ -678,6 +384,9 @@ __global__ void __launch_bounds__(TILE_PIX) blend_backward_warp_kernel(
                 ss[u] = s; G_[u] = G; al[u] = alpha; dx_[u] = dx; dy_[u] = dy;
             }
             head += avail;
+            if (lane == 0) STAT_ADD(6, 1);
+            STAT_ADD(7, __popc(__ballot_sync(0xffffffffu, ok[0])) + __popc(__ballot_sync(0xffffffffu, ok[1])) +
+                            __popc(__ballot_sync(0xffffffffu, ok[2])));
             if (!__any_sync(0xffffffffu, ok[0] || ok[1] || ok[2])) continue;
             float w[32];
 #pragma unroll
@@ -725,10 +434,18 @@ __global__ void __launch_bounds__(TILE_PIX) blend_backward_warp_kernel(
 
 }  // namespace
 
-#ifdef D3GA_DEBUG_TIMING
-extern "C" int d3ga_debug_set_buffer(void *p) {
+#ifdef D3GA_BLEND_STATS
+extern "C" int d3ga_debug_blend_trace(void *p) {
     unsigned long long *v = (unsigned long long *)p;
-    return cudaMemcpyToSymbol(g_dbg_buf, &v, sizeof(v)) == cudaSuccess ? 0 : -2;
+    return cudaMemcpyToSymbol(g_blend_trace, &v, sizeof(v)) == cudaSuccess ? 0 : -2;
+}
+extern "C" int d3ga_debug_blend_stats(unsigned long long *out, int reset) {
+    if (cudaMemcpyFromSymbol(out, g_blend_stats, sizeof(g_blend_stats)) != cudaSuccess) return -2;
+    if (reset) {
+        unsigned long long z[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        if (cudaMemcpyToSymbol(g_blend_stats, z, sizeof(z)) != cudaSuccess) return -2;
+    }
+    return 0;
 }
 #endif
 
@@ -750,23 +467,17 @@ int launch_blend_forward(int W, int H, const float *background, const float *col
     uint32_t *order_bwd = reinterpret_cast<uint32_t *>(image + IL.order_bwd);
     uint32_t *tile_nproc = reinterpret_cast<uint32_t *>(image + IL.tile_nproc);
     ProfScope prof(K_BLEND_FWD, stream);
-    if (blend_mode() == BLEND_WARP) {
+    {
+        D3GA_CUDA(cudaMemsetAsync(tile_nproc, 0, sizeof(uint32_t) * (size_t)num_tiles, stream));
         if (out_invdepth)
-            blend_forward_warp_kernel<true><<<num_tiles, TILE_PIX, 0, stream>>>(
+            blend_forward_kernel<true><<<num_tiles * (8 / FWD_WARPS), FWD_WARPS * 32, 0, stream>>>(
                 hdr, ranges, v0, v1, W, H, xy, co, colors, depth, background, final_T, n_contrib, out_color, out_invdepth,
                 hdr_rw, gx, num_tiles, order_fwd, tile_nproc, order_bwd);
         else
-            blend_forward_warp_kernel<false><<<num_tiles, TILE_PIX, 0, stream>>>(
+            blend_forward_kernel<false><<<num_tiles * (8 / FWD_WARPS), FWD_WARPS * 32, 0, stream>>>(
                 hdr, ranges, v0, v1, W, H, xy, co, colors, depth, background, final_T, n_contrib, out_color, nullptr,
                 hdr_rw, gx, num_tiles, order_fwd, tile_nproc, order_bwd);
-    } else if (out_invdepth)
-        blend_forward_kernel<true><<<num_tiles, TILE_PIX, 0, stream>>>(
-            hdr, ranges, v0, v1, W, H, xy, co, colors, depth, background, final_T, n_contrib, out_color, out_invdepth,
-            hdr_rw, gx, num_tiles, order_fwd, tile_nproc, order_bwd);
-    else
-        blend_forward_kernel<false><<<num_tiles, TILE_PIX, 0, stream>>>(
-            hdr, ranges, v0, v1, W, H, xy, co, colors, depth, background, final_T, n_contrib, out_color, nullptr,
-            hdr_rw, gx, num_tiles, order_fwd, tile_nproc, order_bwd);
+    }
     D3GA_LAUNCH_CHECK();
     return D3GA_OK;
 }
@@ -787,23 +498,16 @@ int launch_blend_backward(int W, int H, const float *background, const float *co
     const uint32_t *n_contrib = reinterpret_cast<const uint32_t *>(image + IL.n_contrib);
     const uint32_t *order_bwd = reinterpret_cast<const uint32_t *>(image + IL.order_bwd);
     ProfScope prof(K_BLEND_BWD, stream);
-    if (blend_mode() == BLEND_WARP) {
+    {
         if (dL_dinvdepth_pix)
-            blend_backward_warp_kernel<true><<<num_tiles, TILE_PIX, 0, stream>>>(
+            blend_backward_kernel<true><<<num_tiles, TILE_PIX, 0, stream>>>(
                 hdr, ranges, v0, v1, W, H, background, xy, co, colors, depth, final_T, n_contrib, dL_dpix,
                 dL_dinvdepth_pix, grad_acc, gx, order_bwd);
         else
-            blend_backward_warp_kernel<false><<<num_tiles, TILE_PIX, 0, stream>>>(
+            blend_backward_kernel<false><<<num_tiles, TILE_PIX, 0, stream>>>(
                 hdr, ranges, v0, v1, W, H, background, xy, co, colors, depth, final_T, n_contrib, dL_dpix, nullptr,
                 grad_acc, gx, order_bwd);
-    } else if (dL_dinvdepth_pix)
-        blend_backward_kernel<true><<<num_tiles, TILE_PIX, 0, stream>>>(
-            hdr, ranges, v0, v1, W, H, background, xy, co, colors, depth, final_T, n_contrib, dL_dpix, dL_dinvdepth_pix,
-            grad_acc, gx, order_bwd);
-    else
-        blend_backward_kernel<false><<<num_tiles, TILE_PIX, 0, stream>>>(
-            hdr, ranges, v0, v1, W, H, background, xy, co, colors, depth, final_T, n_contrib, dL_dpix, nullptr, grad_acc,
-            gx, order_bwd);
+    }
     D3GA_LAUNCH_CHECK();
     return D3GA_OK;
 }

@@ -103,6 +103,54 @@ def _same_tensors(cached, now):
     return True
 
 
+# ---- deferred overflow check (CUDA-graph capture) -----------------------------------------------------------------------
+# The eager forward waits for stage 1 and reads (num_rendered, overflow) back before it returns, growing the binning
+# workspace and running again when the guess was too small.  Inside a CUDA graph nothing may wait: under
+# `deferred_overflow_check()` the forward trusts the capacity hint, folds the header's (num_rendered, overflow) into a
+# small device tensor with one elementwise maximum, and the caller asks `collect_deferred(device)` after the replay --
+# (largest num_rendered, any overflow) -- and must redo the work with a larger capacity (`set_capacity_hint`) if it
+# overflowed.
+_defer_depth = 0
+_deferred_stats = {}
+_deferred_key = {}
+
+
+class deferred_overflow_check:
+    def __enter__(self):
+        global _defer_depth
+        _defer_depth += 1
+        return self
+
+    def __exit__(self, *exc):
+        global _defer_depth
+        _defer_depth -= 1
+        return False
+
+
+def _deferred_stats_tensor(device):
+    t = _deferred_stats.get(device)
+    if t is None:
+        t = torch.zeros(2, dtype=torch.int32, device=device)
+        _deferred_stats[device] = t
+    return t
+
+
+def collect_deferred(device):
+    """(largest num_rendered, overflowed?) of the forwards run under deferred_overflow_check() since the last call.
+    Synchronises the current stream.  On overflow the capacity hint of that problem size is raised, so the next
+    capture / eager call sizes its workspace for the largest view seen."""
+    t = _deferred_stats_tensor(device)
+    d, ovf = (int(x) for x in t.cpu())
+    t.zero_()
+    d &= 0xFFFFFFFF
+    key = _deferred_key.get(device)
+    if key is not None and d:
+        need = min((1 << 31) - 1, int(d * CAPACITY_SLACK) + 4096)
+        if ovf or need > _capacity_hint.get(key, 0):
+            _capacity_hint[key] = need
+    return d, bool(ovf)
+
+
 def _pinned_counter(device):
     slot = _pinned_slots.get(device)
     if slot is None:
@@ -194,7 +242,8 @@ def rasterize_forward(means3D, sh, colors_precomp, opacities, scales, rotations,
         st.image = torch.empty(ib, dtype=torch.uint8, device=dev)
         host = _pinned_counter(dev)
         host_np = host.numpy()
-        ev = torch.cuda.Event()
+        defer = _defer_depth > 0
+        ev = None if defer else torch.cuda.Event()
         while True:
             _, bb, _ = _workspace_bytes(P, W, H, cap)
             st.binning = torch.empty(bb, dtype=torch.uint8, device=dev)
@@ -206,10 +255,19 @@ def rasterize_forward(means3D, sh, colors_precomp, opacities, scales, rotations,
                 float(rs.tanfovx), float(rs.tanfovy), int(bool(rs.prefiltered)), int(bool(rs.antialiasing)),
                 st.geom.data_ptr(), st.binning.data_ptr(), cap, _lib.ptr(radii), host.data_ptr(), stream),
                 "raster_forward_geometry")
-            ev.record()
+            if not defer:
+                ev.record()
             _lib.check(lib.d3ga_raster_forward_render(
                 P, W, H, bg.data_ptr(), _lib.ptr(colors_precomp), st.geom.data_ptr(), st.binning.data_ptr(), cap,
                 st.image.data_ptr(), color.data_ptr(), _lib.ptr(invdepth), stream), "raster_forward_render")
+            if defer:
+                # (num_rendered, overflow) are the first two words of the geometry workspace's header
+                stats = _deferred_stats_tensor(dev)
+                torch.maximum(stats, st.geom[:8].view(torch.int32), out=stats)
+                _deferred_key[dev] = key
+                st.num_rendered = -1
+                D = None
+                break
             ev.synchronize()   # waits for stage 1 only; stage 2 keeps running
             D, overflow = int(host_np[0]) & 0xFFFFFFFF, int(host_np[1])
             D, overflow = int(D), int(overflow)
@@ -219,10 +277,12 @@ def rasterize_forward(means3D, sh, colors_precomp, opacities, scales, rotations,
             if D >= (1 << 31) - 1:
                 raise _lib.D3GAError(f"{D} (tile, Gaussian) duplicates exceed the 2^31-1 limit")
             cap = min((1 << 31) - 1, int(D * CAPACITY_SLACK) + 4096)
-        _capacity_hint[key] = min((1 << 31) - 1, int(D * CAPACITY_SLACK) + 4096)
+        if D is not None:
+            _capacity_hint[key] = min((1 << 31) - 1, int(D * CAPACITY_SLACK) + 4096)
     global _last_state
     _last_state = st
-    last_stats.update(num_rendered=D, capacity=st.capacity)
+    if D is not None:
+        last_stats.update(num_rendered=D, capacity=st.capacity)
     if gkey is not None:
         cam = (rs.viewmatrix.detach(), rs.projmatrix.detach(), rs.campos.detach())
         _geom_cache[dev] = {"key": gkey, "cam": cam, "state": st, "radii": radii,

@@ -24,12 +24,16 @@ class CameraBank:
         self.slot = torch.empty(35, dtype=torch.float32, device=device)   # e2e: per-view upload target
 
     def settings(self, i, W, H, bg, from_host=False):
-        c = self.cams[i]
         if from_host:
             self.slot.copy_(self.host[i], non_blocking=True)
             row = self.slot
         else:
             row = self.dev[i]
+        return self.settings_from_row(i, row, W, H, bg)
+
+    def settings_from_row(self, i, row, W, H, bg):
+        """Settings of camera i whose 35 floats (view | proj | campos) are in the device tensor `row`."""
+        c = self.cams[i]
         return GaussianRasterizationSettings(
             image_height=H, image_width=W, tanfovx=c.tanfovx, tanfovy=c.tanfovy, bg=bg, scale_modifier=1.0,
             viewmatrix=row[0:16].view(4, 4), projmatrix=row[16:32].view(4, 4), sh_degree=0, campos=row[32:35],
@@ -76,27 +80,35 @@ def view_step(avatar, rs, weights):
 
 
 class HostFeed:
-    """Per-view inputs that arrive from pinned host memory (the e2e arm of bench.py): the target / weight image is
-    copied on a side stream one view ahead into a double buffer, so the 3*H*W*4-byte upload overlaps the previous
-    view's kernels -- what a data loader with a prefetch queue does (train.py:426-434 uses pinned DataLoader memory)."""
+    """Per-view inputs that arrive from pinned host memory (the e2e arm of bench.py): the target / weight image, the
+    camera (35 floats) and the cage vertices are copied on a side stream ONE VIEW AHEAD into a double buffer, so the
+    uploads (12.6 MB at 1024^2) overlap the previous view's kernels and no host-to-device DMA sits on the compute stream
+    -- what a data loader with a prefetch queue does (train.py:426-434 uses pinned DataLoader memory)."""
 
-    def __init__(self, weights_host, device):
+    def __init__(self, weights_host, device, cam_host=None, tetpoints_host=None):
         self.host = weights_host
+        self.cam_host, self.tet_host = cam_host, tetpoints_host
         self.stream = torch.cuda.Stream(device=device)
         self.bufs = [torch.empty_like(weights_host, device=device) for _ in range(2)]
+        self.cams = [torch.empty(35, dtype=torch.float32, device=device) for _ in range(2)]
+        self.tets = [None if tetpoints_host is None else torch.empty_like(tetpoints_host, device=device) for _ in range(2)]
         self.ready = [torch.cuda.Event() for _ in range(2)]
         self.free = [torch.cuda.Event() for _ in range(2)]
         for e in self.free:
             e.record()
         self.k = 0
 
-    def prefetch(self):
-        """Enqueue the upload of the next view's image; returns the slot it will land in."""
+    def prefetch(self, cam_id=None):
+        """Enqueue the upload of the next view's inputs; returns the slot they will land in."""
         slot = self.k % 2
         self.k += 1
         with torch.cuda.stream(self.stream):
             self.stream.wait_event(self.free[slot])      # the view that used this buffer has finished with it
             self.bufs[slot].copy_(self.host, non_blocking=True)
+            if cam_id is not None and self.cam_host is not None:
+                self.cams[slot].copy_(self.cam_host[cam_id], non_blocking=True)
+            if self.tet_host is not None:
+                self.tets[slot].copy_(self.tet_host, non_blocking=True)
             self.ready[slot].record(self.stream)
         return slot
 
@@ -113,14 +125,20 @@ def multi_view_step(avatar, bank, cam_ids, weights, bg, from_host=False, feed=No
     camera, cage vertices and target image come from pinned host memory and the step's loss is read back at the end."""
     avatar.grads.zero_()
     total = None
-    slot = feed.prefetch() if from_host else None
+    slot = feed.prefetch(cam_ids[0]) if from_host else None
     for n, i in enumerate(cam_ids):
         if from_host:
-            with torch.no_grad():
-                avatar.tetpoints.copy_(avatar.tetpoints_host, non_blocking=True)
             weights = feed.acquire(slot)
-            nxt = feed.prefetch() if n + 1 < len(cam_ids) else None
-        rs = bank.settings(i, avatar.W, avatar.H, bg, from_host=from_host)
+            with torch.no_grad():
+                if feed.tet_host is not None:
+                    avatar.tetpoints.copy_(feed.tets[slot], non_blocking=True)
+                else:
+                    avatar.tetpoints.copy_(avatar.tetpoints_host, non_blocking=True)
+            nxt = feed.prefetch(cam_ids[n + 1]) if n + 1 < len(cam_ids) else None
+        if from_host and feed.cam_host is not None:
+            rs = bank.settings_from_row(i, feed.cams[slot], avatar.W, avatar.H, bg)
+        else:
+            rs = bank.settings(i, avatar.W, avatar.H, bg, from_host=from_host)
         loss = view_step(avatar, rs, weights)
         if from_host:
             feed.release(slot)
@@ -131,6 +149,110 @@ def multi_view_step(avatar, bank, cam_ids, weights, bg, from_host=False, feed=No
         loss_host.copy_(total, non_blocking=True)     # the step's result goes back to the host
         torch.cuda.current_stream().synchronize()
     return total
+
+
+class GraphedViewStep:
+    """`view_step` captured once into a CUDA graph and replayed per camera.
+
+    The eager per-view path costs about a millisecond of Python, autograd and launch overhead -- as much as the kernels
+    themselves at 1 M Gaussians and more than them below that -- and waits for the binning count in the middle of every
+    view.  The captured graph holds the same launches (deformation, the rasterizer's two stages, the loss, the whole
+    backward) with static inputs: the camera is a 35-float device buffer (view | proj | campos) the rasterization
+    settings alias, the target / weight image a fixed [3,H,W] buffer, the parameters and their flat gradient buffer the
+    avatar's own tensors.  Intrinsics (tanfov) and the background are baked in at capture.
+
+    The binning workspace is sized from the capacity hint at capture time; every replay folds its (num_rendered,
+    overflow) into a device counter and `finish()` reads it back: if a view overflowed, the hint has been raised, the
+    graph must be captured again (`capture()`) and the step redone -- `multi_view_step(..., graphed=...)` does that."""
+
+    def __init__(self, avatar, cam, bg, weights=None):
+        from d3ga_b200 import diff_gaussian_rasterization as dgr
+        self.dgr = dgr
+        self.avatar = avatar
+        dev = avatar.device
+        self.cam = torch.zeros(35, dtype=torch.float32, device=dev)
+        self.weights = torch.empty((3, avatar.H, avatar.W), dtype=torch.float32, device=dev) if weights is None else weights
+        self.total = torch.zeros((), dtype=torch.float32, device=dev)     # sum of the losses since reset()
+        self.rs = GaussianRasterizationSettings(
+            image_height=avatar.H, image_width=avatar.W, tanfovx=cam.tanfovx, tanfovy=cam.tanfovy, bg=bg,
+            scale_modifier=1.0, viewmatrix=self.cam[0:16].view(4, 4), projmatrix=self.cam[16:32].view(4, 4), sh_degree=0,
+            campos=self.cam[32:35], prefiltered=False, debug=False, antialiasing=False)
+        self.graph = None
+        self.launches_per_replay = 0
+        self.replays = 0
+        self.captures = 0
+
+    def capture(self, cam_row):
+        """Warm up eagerly on a side stream (sizes the capacity hint, fills the allocator), then capture one view."""
+        from d3ga_b200 import _lib
+        self.cam.copy_(cam_row, non_blocking=True)
+        keep = self.avatar.grads.flat.clone()            # the warm-up views must not leak into the caller's gradients
+        side = torch.cuda.Stream(device=self.avatar.device)
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for _ in range(2):
+                view_step(self.avatar, self.rs, self.weights)
+        torch.cuda.current_stream().wait_stream(side)
+        self.avatar.grads.flat.copy_(keep)
+        torch.cuda.synchronize()
+        self.graph = torch.cuda.CUDAGraph()
+        l0 = _lib.launch_count()
+        with self.dgr.deferred_overflow_check(), torch.cuda.graph(self.graph):
+            loss = view_step(self.avatar, self.rs, self.weights)
+            self.total += loss.detach()
+        self.launches_per_replay = _lib.launch_count() - l0
+        self.captures += 1
+        self.dgr.collect_deferred(self.avatar.device)   # the capture itself launched nothing; clear the counter
+
+    def run(self, cam_row, weights=None):
+        """One view: cam_row [35] (device or pinned host), weights None = already in self.weights."""
+        from d3ga_b200 import _lib
+        if self.graph is None:
+            self.capture(cam_row)
+        self.cam.copy_(cam_row, non_blocking=True)
+        if weights is not None and weights.data_ptr() != self.weights.data_ptr():
+            self.weights.copy_(weights, non_blocking=True)
+        self.graph.replay()
+        self.replays += 1
+        _lib.note_graph_launches(self.launches_per_replay)
+
+    def reset(self):
+        self.total.zero_()
+
+    def finish(self):
+        """Waits for the replays issued so far; returns (largest num_rendered, overflowed)."""
+        return self.dgr.collect_deferred(self.avatar.device)
+
+
+def multi_view_step_graphed(avatar, bank, cam_ids, gv, weights=None, from_host=False, feed=None, loss_host=None):
+    """multi_view_step through a GraphedViewStep: same work per view, one host synchronisation per step (the overflow
+    check; with from_host also the loss read-back).  Redoes the step after re-capturing if a view overflowed."""
+    while True:
+        avatar.grads.zero_()
+        gv.reset()
+        slot = feed.prefetch(cam_ids[0]) if from_host else None
+        for n, i in enumerate(cam_ids):
+            w, row = weights, bank.dev[i]
+            if from_host:
+                w = feed.acquire(slot)
+                with torch.no_grad():
+                    if feed.tet_host is not None:
+                        avatar.tetpoints.copy_(feed.tets[slot], non_blocking=True)
+                    else:
+                        avatar.tetpoints.copy_(avatar.tetpoints_host, non_blocking=True)
+                row = feed.cams[slot] if feed.cam_host is not None else bank.host[i]
+                nxt = feed.prefetch(cam_ids[n + 1]) if n + 1 < len(cam_ids) else None
+            gv.run(row, w)
+            if from_host:
+                feed.release(slot)
+                slot = nxt
+        avatar.grads.all_reduce()
+        if from_host:
+            loss_host.copy_(gv.total, non_blocking=True)
+        _, overflowed = gv.finish()
+        if not overflowed:
+            return gv.total
+        gv.capture(bank.dev[cam_ids[0]])     # the capacity hint now covers the largest view seen
 
 
 def frame_step(avatar, bank, cam_id, weights, bg):

@@ -1,0 +1,82 @@
+"""-m gpu tests of training.GraphedViewStep: one view captured into a CUDA graph must give the eager path's loss and
+gradients, for device-resident and host-fed inputs, and must notice (and recover from) a binning overflow that the
+eager path would have handled in the middle of the view."""
+import numpy as np
+import pytest
+import torch
+
+from d3ga_b200 import diff_gaussian_rasterization as dgr
+from d3ga_b200 import synth, training
+
+pytestmark = pytest.mark.gpu
+
+
+def setup(name="tiny"):
+    dev = torch.device("cuda", 0)
+    scene = synth.make_workload(name)
+    cams = synth.camera_ring(scene.W, scene.H, 8)
+    avatar = training.Avatar(scene, dev)
+    bank = training.CameraBank(cams, dev)
+    bg = torch.ones(3, device=dev)
+    wh = torch.from_numpy(np.random.default_rng(0).uniform(-1, 1, (3, scene.H, scene.W)).astype(np.float32)).pin_memory()
+    return dev, scene, cams, avatar, bank, bg, wh
+
+
+def rel(a, b):
+    return float((a - b).norm() / b.norm())
+
+
+def test_graphed_step_matches_eager(cuda_lib):
+    dev, scene, cams, avatar, bank, bg, wh = setup()
+    w = wh.to(dev)
+    ids = [0, 3, 5, 6]
+    tot_e = training.multi_view_step(avatar, bank, ids, w, bg).clone()
+    g_e = avatar.grads.flat.clone()
+    gv = training.GraphedViewStep(avatar, cams[0], bg)
+    tot_g = training.multi_view_step_graphed(avatar, bank, ids, gv, weights=w).clone()
+    assert gv.captures == 1 and gv.replays == len(ids) and gv.launches_per_replay >= 10
+    assert abs(float(tot_g) - float(tot_e)) <= 1e-5 * abs(float(tot_e))
+    assert rel(avatar.grads.flat, g_e) < 1e-5          # float atomics reorder, nothing else differs
+    # a second step re-uses the graph; host-fed inputs (camera, cage vertices and image uploaded a view ahead)
+    feed = training.HostFeed(wh, dev, cam_host=bank.host, tetpoints_host=avatar.tetpoints_host)
+    loss_h = torch.zeros((), dtype=torch.float32).pin_memory()
+    training.multi_view_step_graphed(avatar, bank, ids, gv, from_host=True, feed=feed, loss_host=loss_h)
+    torch.cuda.synchronize()
+    assert gv.captures == 1
+    assert abs(float(loss_h) - float(tot_e)) <= 1e-5 * abs(float(tot_e))
+    assert rel(avatar.grads.flat, g_e) < 1e-5
+    loss_e = torch.zeros((), dtype=torch.float32).pin_memory()
+    training.multi_view_step(avatar, bank, ids, w, bg, from_host=True, feed=feed, loss_host=loss_e)
+    assert abs(float(loss_e) - float(tot_e)) <= 1e-5 * abs(float(tot_e))
+    assert rel(avatar.grads.flat, g_e) < 1e-5
+
+
+def test_graphed_step_recovers_from_overflow(cuda_lib):
+    """Capture with a binning workspace that is too small for the other cameras: the replay must report the overflow,
+    the step must be redone on a re-captured graph and still equal the eager result."""
+    dev, scene, cams, avatar, bank, bg, wh = setup()
+    w = wh.to(dev)
+    ids = [0, 1, 2, 3]
+    tot_e = training.multi_view_step(avatar, bank, ids, w, bg).clone()
+    g_e = avatar.grads.flat.clone()
+    gv = training.GraphedViewStep(avatar, cams[0], bg)
+    gv.capture(bank.dev[0])
+    key = (dev, scene.N, scene.W, scene.H)
+    assert key in dgr._capacity_hint
+    # shrink the hint and capture again without the eager warm-up correcting it
+    small = 64
+    dgr._capacity_hint[key] = small
+    gv.graph = torch.cuda.CUDAGraph()
+    from d3ga_b200 import _lib
+    l0 = _lib.launch_count()
+    with dgr.deferred_overflow_check(), torch.cuda.graph(gv.graph):
+        loss = training.view_step(avatar, gv.rs, gv.weights)
+        gv.total += loss.detach()
+    gv.launches_per_replay = _lib.launch_count() - l0
+    dgr.collect_deferred(dev)
+    before = gv.captures
+    tot_g = training.multi_view_step_graphed(avatar, bank, ids, gv, weights=w).clone()
+    assert gv.captures == before + 1, "the overflow must force a re-capture"
+    assert dgr._capacity_hint[key] > small
+    assert abs(float(tot_g) - float(tot_e)) <= 1e-5 * abs(float(tot_e))
+    assert rel(avatar.grads.flat, g_e) < 1e-5
