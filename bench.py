@@ -51,6 +51,7 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-graph", action="store_true", help="eager per-view launches instead of the captured CUDA graph")
+    ap.add_argument("--lanes", type=int, default=4, help="views in flight on separate streams (graph replay only)")
     return ap.parse_args()
 
 
@@ -71,12 +72,12 @@ class ClockSampler:
          "clocks_event_reasons.sw_power_cap")
 
     def __init__(self, gpu_index):
-        self.idx, self.rows, self.proc = gpu_index, [], None
+        self.idx, self.rows, self.proc, self.t_mark = gpu_index, [], None, 0.0
 
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.idx}", f"--query-gpu={self.Q}",
-                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE,
+                                          "--format=csv,noheader,nounits", "-lms", "20"], stdout=subprocess.PIPE,
                                          stderr=subprocess.DEVNULL, text=True)
             threading.Thread(target=self._read, daemon=True).start()
         except Exception:
@@ -84,17 +85,23 @@ class ClockSampler:
 
     def _read(self):
         for line in self.proc.stdout:
-            self.rows.append([x.strip() for x in line.split(",")])
+            self.rows.append([x.strip() for x in line.split(",")] + [time.perf_counter()])
+
+    def mark(self):
+        """The timed region starts now.  (The sampler is started before the >= 1 s pre-warm of the same work, so that
+        nvidia-smi is already up; only samples from here on -- plus the one just before, taken under the same load --
+        are reported.)"""
+        self.t_mark = time.perf_counter() - 0.03
 
     def stop(self):
         if self.proc is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        time.sleep(0.15)
         self.proc.terminate()
-        sm = [float(r[1]) for r in self.rows if len(r) >= 9 and r[1].replace(".", "").isdigit()]
-        mx = [float(r[2]) for r in self.rows if len(r) >= 9 and r[2].replace(".", "").isdigit()]
+        rows = [r for r in self.rows if r[-1] >= self.t_mark]
+        sm = [float(r[1]) for r in rows if len(r) >= 9 and r[1].replace(".", "").isdigit()]
+        mx = [float(r[2]) for r in rows if len(r) >= 9 and r[2].replace(".", "").isdigit()]
         reasons = set()
-        for r in self.rows:
+        for r in rows:
             if len(r) >= 9:
                 for name, v in zip(["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"], r[5:9]):
                     if v.lower().startswith("active"):
@@ -173,7 +180,7 @@ def workload_config(scene, args, views):
     return {"workload": f"{scene.name}: {scene.N} Gaussians in {scene.tets.shape[0]} tets over {len(scene.meta['garments'])} "
                         f"cage(s), {scene.W}x{scene.H}, cov3D_precomp + colors_precomp path",
             "views_per_rank_per_step": views, "cameras": args.cameras, "parallelism": f"camera-sharded dp{args.gpus}",
-            "launch": "eager" if args.no_graph else "one CUDA-graph replay per view",
+            "launch": "eager" if args.no_graph else f"one CUDA-graph replay per view, {max(1, args.lanes)} view(s) in flight on separate streams",
             "l2": "working set (>= 150 MB of Gaussian state + binning buffers per view) exceeds the 126 MB L2; no flush"}
 
 
@@ -205,7 +212,12 @@ def run_ours(args):
         return [mine[(step * V + v) % len(mine)] for v in range(V)]
 
     # one view = one replay of the captured graph (training.GraphedViewStep); --no-graph launches every view eagerly
-    gv = None if args.no_graph else training.GraphedViewStep(avatar, cams[0], bg)
+    gv = pv = None
+    if not args.no_graph:
+        if args.lanes > 1:
+            pv = training.PipelinedViews(avatar, cams[0], bg, lanes=args.lanes)
+        else:
+            gv = training.GraphedViewStep(avatar, cams[0], bg)
 
     def region(n_steps, first_step, eager=False, **kw):
         ddist.barrier()
@@ -213,8 +225,11 @@ def run_ours(args):
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         a.record()
         for s in range(n_steps):
-            if gv is not None and not eager:
-                kw2 = {k: v for k, v in kw.items() if k != "from_host"}
+            kw2 = {k: v for k, v in kw.items() if k != "from_host"}
+            if pv is not None and not eager:
+                training.multi_view_step_pipelined(avatar, bank, cam_ids(first_step + s), pv, weights=weights,
+                                                   from_host=kw.get("from_host", False), **kw2)
+            elif gv is not None and not eager:
                 training.multi_view_step_graphed(avatar, bank, cam_ids(first_step + s), gv, weights=weights,
                                                  from_host=kw.get("from_host", False), **kw2)
             else:
@@ -228,14 +243,16 @@ def run_ours(args):
     # same work running until the GPU has been busy for about a second so clocks and power state have ramped
     ms_w = region(args.warmup, 0)                     # max over ranks: the same number on every rank
     extra = min(200, int(1000.0 / max(1e-3, ms_w / max(1, args.warmup))) + 1)
-    region(extra, 0)
     clocks = ClockSampler(local) if rank == 0 else None
     if clocks:
         clocks.start()
+    region(extra, 0)
+    if clocks:
+        clocks.mark()
     l0 = _lib.launch_count()
     ms = region(args.steps, args.warmup)
-    launches = _lib.launch_count() - l0
     clk = clocks.stop() if clocks else None
+    launches = _lib.launch_count() - l0
     views_total = world * V * args.steps
     value = views_total / (ms * 1e-3)
 
@@ -292,14 +309,15 @@ def run_ours(args):
     # e2e: the same steps through the public API with this step's inputs in pinned HOST memory
     e2e = None
     if not args.no_e2e:
-        feed = training.HostFeed(weights_h, dev, cam_host=bank.host, tetpoints_host=avatar.tetpoints_host)
+        feed = training.HostFeed(weights_h, dev, cam_host=bank.host, tetpoints_host=avatar.tetpoints_host,
+                                 slots=2 * max(1, args.lanes))
         region(1, 0, from_host=True, feed=feed, loss_host=loss_h)
         ms_e = region(args.steps, args.warmup, from_host=True, feed=feed, loss_host=loss_h)
         h2d = 35 * 4 + avatar.tetpoints.numel() * 4 + weights.numel() * 4
         e2e = {"value": views_total / (ms_e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d * V,
                "d2h_bytes_per_step": 4,
                "inputs_from_host": "per view: camera (35 floats), cage vertices tetpoints [V,3], target/weight image [3,H,W] "
-                                   "(all uploaded one view ahead on a side stream); the step's loss is read back once per step; "
+                                   "(all uploaded ahead of the view on a side stream); the step's loss is read back once per step; "
                                    "Gaussian parameters stay resident like nn.Parameters"}
 
     # a D3GA training FRAME renders the same Gaussians twice (RGB + silhouette); frames/s with and

@@ -163,6 +163,10 @@ __global__ void __launch_bounds__(FWD_WARPS * 32, FWD_MIN_CTAS) blend_forward_ke
     __shared__ uint32_t s_bins[257];
     __shared__ uint32_t s_last;
 
+    // The blend loop below is branch-free: entries of a partly filled last group are multiplied by a weight of zero
+    // rather than skipped, so a ring slot that was never written must not hold a NaN or Inf bit pattern.
+    for (int i = threadIdx.x; i < FWD_WARPS * RING; i += FWD_WARPS * 32) (&s_feat[0][0])[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    __syncthreads();
     constexpr uint32_t SPLIT = 8 / FWD_WARPS;          // CTAs per tile
     const uint32_t tile = order_fwd[blockIdx.x / SPLIT];   // longest Gaussian list first
     const int tid = threadIdx.x;

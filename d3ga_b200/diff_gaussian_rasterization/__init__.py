@@ -128,20 +128,28 @@ class deferred_overflow_check:
 
 
 def _deferred_stats_tensor(device):
-    t = _deferred_stats.get(device)
+    """One counter per (device, stream the forward is enqueued / captured on): graphs replayed concurrently on several
+    streams must not share a read-modify-write target."""
+    key = (device, torch.cuda.current_stream(device).cuda_stream)
+    t = _deferred_stats.get(key)
     if t is None:
         t = torch.zeros(2, dtype=torch.int32, device=device)
-        _deferred_stats[device] = t
+        _deferred_stats[key] = t
     return t
 
 
 def collect_deferred(device):
-    """(largest num_rendered, overflowed?) of the forwards run under deferred_overflow_check() since the last call.
-    Synchronises the current stream.  On overflow the capacity hint of that problem size is raised, so the next
-    capture / eager call sizes its workspace for the largest view seen."""
-    t = _deferred_stats_tensor(device)
-    d, ovf = (int(x) for x in t.cpu())
-    t.zero_()
+    """(largest num_rendered, overflowed?) of the forwards run under deferred_overflow_check() since the last call, over
+    all streams of the device.  The caller must have made the current stream wait for those streams; this synchronises
+    it.  On overflow the capacity hint of that problem size is raised, so the next capture / eager call sizes its
+    workspace for the largest view seen."""
+    ts = [t for (dev, _), t in _deferred_stats.items() if dev == device]
+    if not ts:
+        return 0, False
+    allt = torch.stack(ts).amax(0).cpu()
+    for t in ts:
+        t.zero_()
+    d, ovf = int(allt[0]), int(allt[1])
     d &= 0xFFFFFFFF
     key = _deferred_key.get(device)
     if key is not None and d:

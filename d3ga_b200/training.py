@@ -61,6 +61,18 @@ class Avatar:
         if device.type == "cuda":
             self.tetpoints_host = self.tetpoints_host.pin_memory()
 
+    def shadow(self):
+        """A second handle on the same parameters with its OWN gradient buffer and its own copy of the per-view input
+        `tetpoints`: what a view needs to run on another stream concurrently with a view of `self`."""
+        import copy
+        o = copy.copy(self)
+        o.tetpoints = self.tetpoints.detach().clone().requires_grad_(True)
+        o.barys, o.scales, o.rotation, o.opacity, o.colors = (
+            p.detach().requires_grad_(True) for p in (self.barys, self.scales, self.rotation, self.opacity, self.colors))
+        o.params = [o.tetpoints, o.barys, o.scales, o.rotation, o.opacity, o.colors]
+        o.grads = ddist.FlatGrads(o.params)
+        return o
+
     def render(self, rs):
         """What GarmentNet.forward + render() do on the hot path (cage_net.py:218-230, renderer.py:122-141)."""
         means3D, cov6 = deform_gaussians(self.tetpoints, self.tets, self.tetra_id, self.barys, self.cg, self.scales,
@@ -85,22 +97,24 @@ class HostFeed:
     uploads (12.6 MB at 1024^2) overlap the previous view's kernels and no host-to-device DMA sits on the compute stream
     -- what a data loader with a prefetch queue does (train.py:426-434 uses pinned DataLoader memory)."""
 
-    def __init__(self, weights_host, device, cam_host=None, tetpoints_host=None):
+    def __init__(self, weights_host, device, cam_host=None, tetpoints_host=None, slots=2):
         self.host = weights_host
         self.cam_host, self.tet_host = cam_host, tetpoints_host
         self.stream = torch.cuda.Stream(device=device)
-        self.bufs = [torch.empty_like(weights_host, device=device) for _ in range(2)]
-        self.cams = [torch.empty(35, dtype=torch.float32, device=device) for _ in range(2)]
-        self.tets = [None if tetpoints_host is None else torch.empty_like(tetpoints_host, device=device) for _ in range(2)]
-        self.ready = [torch.cuda.Event() for _ in range(2)]
-        self.free = [torch.cuda.Event() for _ in range(2)]
+        self.slots = slots       # views in flight + views being uploaded (2 lanes of PipelinedViews want 4)
+        self.bufs = [torch.empty_like(weights_host, device=device) for _ in range(slots)]
+        self.cams = [torch.empty(35, dtype=torch.float32, device=device) for _ in range(slots)]
+        self.tets = [None if tetpoints_host is None else torch.empty_like(tetpoints_host, device=device)
+                     for _ in range(slots)]
+        self.ready = [torch.cuda.Event() for _ in range(slots)]
+        self.free = [torch.cuda.Event() for _ in range(slots)]
         for e in self.free:
             e.record()
         self.k = 0
 
     def prefetch(self, cam_id=None):
         """Enqueue the upload of the next view's inputs; returns the slot they will land in."""
-        slot = self.k % 2
+        slot = self.k % self.slots
         self.k += 1
         with torch.cuda.stream(self.stream):
             self.stream.wait_event(self.free[slot])      # the view that used this buffer has finished with it
@@ -178,7 +192,8 @@ class GraphedViewStep:
             scale_modifier=1.0, viewmatrix=self.cam[0:16].view(4, 4), projmatrix=self.cam[16:32].view(4, 4), sh_degree=0,
             campos=self.cam[32:35], prefiltered=False, debug=False, antialiasing=False)
         self.graph = None
-        self.launches_per_replay = 0
+        self.capture_stream = torch.cuda.Stream(device=dev)   # not torch's shared default: the deferred overflow
+        self.launches_per_replay = 0                          # counter is kept per capture stream
         self.replays = 0
         self.captures = 0
 
@@ -197,7 +212,7 @@ class GraphedViewStep:
         torch.cuda.synchronize()
         self.graph = torch.cuda.CUDAGraph()
         l0 = _lib.launch_count()
-        with self.dgr.deferred_overflow_check(), torch.cuda.graph(self.graph):
+        with self.dgr.deferred_overflow_check(), torch.cuda.graph(self.graph, stream=self.capture_stream):
             loss = view_step(self.avatar, self.rs, self.weights)
             self.total += loss.detach()
         self.launches_per_replay = _lib.launch_count() - l0
@@ -222,6 +237,97 @@ class GraphedViewStep:
     def finish(self):
         """Waits for the replays issued so far; returns (largest num_rendered, overflowed)."""
         return self.dgr.collect_deferred(self.avatar.device)
+
+
+class PipelinedViews:
+    """`lanes` GraphedViewSteps on as many streams, used round-robin: consecutive views of a step are independent given
+    the parameters, so view n+1's preprocess / sort / emission fill the SMs that view n's blend kernels leave idle in
+    their tails (the heaviest tiles' serial chains) and the latency-bound binning kernels overlap each other.  Each lane
+    works on a shadow of the avatar (same parameter storage, own gradient buffer and own cage-vertex input); `finish()`
+    adds the lanes' gradients into the avatar's flat buffer."""
+
+    def __init__(self, avatar, cam, bg, lanes=2):
+        self.avatar = avatar
+        self.shadows = [avatar.shadow() for _ in range(lanes)]
+        self.streams = [torch.cuda.Stream(device=avatar.device) for _ in range(lanes)]
+        self.gvs = [GraphedViewStep(sh, cam, bg) for sh in self.shadows]
+
+    @property
+    def captures(self):
+        return sum(g.captures for g in self.gvs)
+
+    def capture(self, cam_row):
+        for g, st in zip(self.gvs, self.streams):
+            st.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(st):
+                g.capture(cam_row)
+            torch.cuda.current_stream().wait_stream(st)
+
+    def begin(self, cam_row):
+        if self.gvs[0].graph is None:
+            self.capture(cam_row)
+        main = torch.cuda.current_stream()
+        for g, sh, st in zip(self.gvs, self.shadows, self.streams):
+            st.wait_stream(main)
+            with torch.cuda.stream(st):
+                sh.grads.zero_()
+                g.reset()
+
+    def lane(self, n):
+        k = n % len(self.gvs)
+        return self.gvs[k], self.shadows[k], self.streams[k]
+
+    def finish(self):
+        """Joins the lanes; returns (sum of losses, overflowed)."""
+        main = torch.cuda.current_stream()
+        for st in self.streams:
+            main.wait_stream(st)
+        flat = self.avatar.grads.flat
+        torch.add(self.shadows[0].grads.flat, self.shadows[1].grads.flat, out=flat)
+        for sh in self.shadows[2:]:
+            flat.add_(sh.grads.flat)
+        total = self.gvs[0].total + self.gvs[1].total
+        for g in self.gvs[2:]:
+            total = total + g.total
+        _, overflowed = self.gvs[0].finish()
+        return total, overflowed
+
+
+def multi_view_step_pipelined(avatar, bank, cam_ids, pv, weights=None, from_host=False, feed=None, loss_host=None):
+    """multi_view_step over a PipelinedViews: view n runs on lane n % lanes.  Same result as the eager step up to the
+    order of the floating-point gradient sums.  With from_host the feed needs 2 * lanes slots: `lanes` views in flight
+    plus `lanes` being uploaded."""
+    lanes = len(pv.gvs)
+    while True:
+        pv.begin(bank.dev[cam_ids[0]])
+        queue = []
+        if from_host:
+            assert feed.slots >= 2 * lanes, "HostFeed(slots=2*lanes) for pipelined views"
+            queue = [feed.prefetch(i) for i in cam_ids[:lanes]]
+        for n, i in enumerate(cam_ids):
+            gv, sh, st = pv.lane(n)
+            with torch.cuda.stream(st):
+                w, row = weights, bank.dev[i]
+                if from_host:
+                    slot = queue.pop(0)
+                    w = feed.acquire(slot)
+                    with torch.no_grad():
+                        sh.tetpoints.copy_(feed.tets[slot] if feed.tet_host is not None else avatar.tetpoints_host,
+                                           non_blocking=True)
+                    row = feed.cams[slot] if feed.cam_host is not None else bank.host[i]
+                    if n + lanes < len(cam_ids):
+                        queue.append(feed.prefetch(cam_ids[n + lanes]))
+                gv.run(row, w)
+                if from_host:
+                    feed.release(slot)
+        total, overflowed = pv.finish()
+        avatar.grads.all_reduce()
+        if from_host:
+            loss_host.copy_(total, non_blocking=True)
+            torch.cuda.current_stream().synchronize()
+        if not overflowed:
+            return total
+        pv.capture(bank.dev[cam_ids[0]])     # the capacity hint now covers the largest view seen
 
 
 def multi_view_step_graphed(avatar, bank, cam_ids, gv, weights=None, from_host=False, feed=None, loss_host=None):

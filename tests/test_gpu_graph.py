@@ -51,6 +51,28 @@ def test_graphed_step_matches_eager(cuda_lib):
     assert rel(avatar.grads.flat, g_e) < 1e-5
 
 
+def test_pipelined_views_match_eager(cuda_lib):
+    """Two graph-replayed views in flight on two streams (shadow avatars, own gradient buffers) give the eager step's
+    loss and gradients, device-resident and host-fed (an odd number of views: the lanes end unevenly)."""
+    dev, scene, cams, avatar, bank, bg, wh = setup()
+    w = wh.to(dev)
+    ids = [0, 3, 5, 6, 2]
+    tot_e = training.multi_view_step(avatar, bank, ids, w, bg).clone()
+    g_e = avatar.grads.flat.clone()
+    pv = training.PipelinedViews(avatar, cams[0], bg, lanes=2)
+    tot_p = training.multi_view_step_pipelined(avatar, bank, ids, pv, weights=w).clone()
+    assert pv.captures == 2
+    assert abs(float(tot_p) - float(tot_e)) <= 1e-5 * abs(float(tot_e))
+    assert rel(avatar.grads.flat, g_e) < 1e-5
+    feed = training.HostFeed(wh, dev, cam_host=bank.host, tetpoints_host=avatar.tetpoints_host, slots=4)
+    loss_h = torch.zeros((), dtype=torch.float32).pin_memory()
+    for _ in range(2):
+        training.multi_view_step_pipelined(avatar, bank, ids, pv, from_host=True, feed=feed, loss_host=loss_h)
+        assert abs(float(loss_h) - float(tot_e)) <= 1e-5 * abs(float(tot_e))
+        assert rel(avatar.grads.flat, g_e) < 1e-5
+    assert pv.captures == 2
+
+
 def test_graphed_step_recovers_from_overflow(cuda_lib):
     """Capture with a binning workspace that is too small for the other cameras: the replay must report the overflow,
     the step must be redone on a re-captured graph and still equal the eager result."""

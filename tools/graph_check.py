@@ -51,3 +51,20 @@ for _ in range(10):
 b.record()
 torch.cuda.synchronize()
 print(f"H2D: {wh.numel() * 4 * 10 / (a.elapsed_time(b) * 1e-3) / 1e9:.1f} GB/s for {wh.numel() * 4 / 1e6:.1f} MB images")
+# two lanes
+LANES = int(os.environ.get("LANES", "2"))
+pv = training.PipelinedViews(avatar, cams[0], bg, lanes=LANES)
+feed4 = training.HostFeed(wh, dev, cam_host=bank.host, tetpoints_host=avatar.tetpoints_host, slots=2 * LANES)
+tot_p = training.multi_view_step_pipelined(avatar, bank, ids, pv, weights=w).clone()
+torch.cuda.synchronize()
+print(f"pipelined: loss {float(tot_p):.6e}, grad rel-L2 diff vs eager {float((g_e - avatar.grads.flat).norm() / g_e.norm()):.2e}, captures {pv.captures}")
+for name, fn in (("pipelined", lambda: training.multi_view_step_pipelined(avatar, bank, ids, pv, weights=w)),
+                 ("pipelined e2e", lambda: training.multi_view_step_pipelined(avatar, bank, ids, pv, from_host=True, feed=feed4, loss_host=loss_h))):
+    for _ in range(2):
+        fn()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(4):
+        fn()
+    torch.cuda.synchronize()
+    print(f"{name}: {(time.perf_counter() - t0) / 64 * 1e6:.0f} us/view (captures so far {pv.captures})")
