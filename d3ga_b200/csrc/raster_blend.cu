@@ -68,39 +68,10 @@ __device__ __forceinline__ WarpBlock warp_block(int tid, int tile_x, int tile_y)
     return warp_block(tid >> 5, tid & 31, tile_x, tile_y);
 }
 
-// Three Gaussians at once: 3 x 10 partials (+2 zeros) per lane, summed over the 32 lanes, land on 32 DIFFERENT lanes
-// (lane l ends up holding the total of value l) after 16+8+4+2+1 = 31 shuffles -- 10.3 per Gaussian, and the shuffles
-// of a stage are independent, so their latency overlaps instead of adding up per Gaussian.
-__device__ __forceinline__ float butterfly32(float (&w)[32], uint32_t lane) {
-    const bool b4 = lane & 16u, b3 = lane & 8u, b2 = lane & 4u, b1 = lane & 2u, b0 = lane & 1u;
-#pragma unroll
-    for (int k = 0; k < 16; k++) {
-        const float send = b4 ? w[k] : w[k + 16], keep = b4 ? w[k + 16] : w[k];
-        w[k] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
-    }
-#pragma unroll
-    for (int k = 0; k < 8; k++) {
-        const float send = b3 ? w[k] : w[k + 8], keep = b3 ? w[k + 8] : w[k];
-        w[k] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
-    }
-#pragma unroll
-    for (int k = 0; k < 4; k++) {
-        const float send = b2 ? w[k] : w[k + 4], keep = b2 ? w[k + 4] : w[k];
-        w[k] = keep + __shfl_xor_sync(0xffffffffu, send, 4);
-    }
-#pragma unroll
-    for (int k = 0; k < 2; k++) {
-        const float send = b1 ? w[k] : w[k + 2], keep = b1 ? w[k + 2] : w[k];
-        w[k] = keep + __shfl_xor_sync(0xffffffffu, send, 2);
-    }
-    const float send = b0 ? w[0] : w[1], keep = b0 ? w[1] : w[0];
-    return keep + __shfl_xor_sync(0xffffffffu, send, 1);
-}
-
 constexpr int RING = 64;                     // per-warp ring of staged survivors (>= group - 1 + 32)
 constexpr int FWD_WARPS = TILE_PIX / 32;    // (splitting a tile over 2 or 4 smaller CTAs was measured: no gain)
 #define FWD_MIN_CTAS 4
-#define BWD_MIN_CTAS 1
+#define BWD_MIN_CTAS 3
 #ifdef D3GA_BLEND_STATS
 // development counters: [0..3] forward (warp-steps, survivors, groups, passing pixel-Gaussian pairs), [4..7] backward
 __device__ unsigned long long g_blend_stats[8];
@@ -294,6 +265,66 @@ __global__ void __launch_bounds__(FWD_WARPS * 32, FWD_MIN_CTAS) blend_forward_ke
     order_tiles_descending(num_tiles, [np](int t) { return __ldcg(np + t); }, order_bwd, s_bins);
 }
 
+// ---- backward -----------------------------------------------------------------------------------------------------------
+// All nine (ten) sums a (warp, Gaussian) pair owes the accumulator are LINEAR in two per-pixel scalars: the six raw moments
+// are sums over the block's pixels of p = G dL/dalpha times (1, dx, dy, dx^2, dx dy, dy^2) -- weights that depend on the
+// pixel position only -- and the colour / inverse-depth derivatives are sums of aT = alpha T times dL/dpixel, which does
+// not depend on the Gaussian at all.  So the pixel loop (phase 1) only produces p and aT and parks them in shared memory,
+// [Gaussian][pixel]; every NB Gaussians the warp turns around (phase 2): lane (h, g) takes Gaussian g and the 16 pixels of
+// half h, forms the ten weighted sums in registers, the two halves meet with one shuffle per sum, and 16 lanes issue
+// vector reductions (RED.ADD.v4.F32) into 16 different accumulator rows.  Shared memory is the transposer: ~18 warp
+// instructions per Gaussian instead of the ~41 of a register butterfly (31 shuffles + 62 selects + 31 adds per three
+// Gaussians) that the kernel used before.
+constexpr int NB = 16;             // Gaussians per turn-around
+constexpr int NB_PITCH = 33;       // floats per Gaussian row: lanes of both halves hit 32 different banks
+struct BwdWarpSmem {
+    float4 ring_a[RING];           // x, y, Gaussian id (bits), forward list position (bits)
+    float4 ring_co[RING];          // pre-scaled conic, opacity
+    float4 ring_feat[RING];        // r, g, b, 1/depth
+    float4 meta[NB];               // x, y, Gaussian id (bits) of the parked Gaussians
+    float4 dpix[32];               // dL/dpixel (r, g, b, inverse depth) of the block's pixels
+    float p[NB * NB_PITCH];
+    float aT[NB * NB_PITCH];
+};
+
+template <bool INVDEPTH>
+__device__ __forceinline__ void backward_turn_around(BwdWarpSmem &sm, int n, uint32_t lane, const WarpBlock &wb,
+                                                     float *__restrict__ grad_acc) {
+    const int g = (int)(lane & 15u), h = (int)(lane >> 4);
+    float S0 = 0.f, Sx = 0.f, Sy = 0.f, Sxx = 0.f, Sxy = 0.f, Syy = 0.f, c0 = 0.f, c1 = 0.f, c2 = 0.f, c3 = 0.f;
+    const float4 m = sm.meta[g];
+    if (g < n) {
+        // pixel q = 16 h + l of the block sits at (x0 + l % 8, y0 + 2 h + l / 8);  d = centre - pixel
+        const float X0 = m.x - wb.x0, Y0 = m.y - (wb.y0 + (float)(2 * h));
+        const float *pp = sm.p + g * NB_PITCH + 16 * h, *pa = sm.aT + g * NB_PITCH + 16 * h;
+        const float4 *pw = sm.dpix + 16 * h;
+#pragma unroll
+        for (int l = 0; l < 16; l++) {
+            const float pv = pp[l], av = pa[l];
+            const float4 w = pw[l];
+            const float dx = X0 - (float)(l & 7), dy = Y0 - (float)(l >> 3);
+            const float pdx = pv * dx, pdy = pv * dy;
+            S0 += pv; Sx += pdx; Sy += pdy;
+            Sxx += pdx * dx; Sxy += pdx * dy; Syy += pdy * dy;
+            c0 += av * w.x; c1 += av * w.y; c2 += av * w.z;
+            if (INVDEPTH) c3 += av * w.w;
+        }
+    }
+    S0 += __shfl_xor_sync(0xffffffffu, S0, 16); Sx += __shfl_xor_sync(0xffffffffu, Sx, 16);
+    Sy += __shfl_xor_sync(0xffffffffu, Sy, 16); Sxx += __shfl_xor_sync(0xffffffffu, Sxx, 16);
+    Sxy += __shfl_xor_sync(0xffffffffu, Sxy, 16); Syy += __shfl_xor_sync(0xffffffffu, Syy, 16);
+    c0 += __shfl_xor_sync(0xffffffffu, c0, 16); c1 += __shfl_xor_sync(0xffffffffu, c1, 16);
+    c2 += __shfl_xor_sync(0xffffffffu, c2, 16);
+    if (INVDEPTH) c3 += __shfl_xor_sync(0xffffffffu, c3, 16);
+    if (h == 0 && g < n) {
+        float *row = grad_acc + (size_t)__float_as_uint(m.z) * GRAD_ACC_FLOATS;
+        red_add_v4(row, Sx, Sy, Sxx, Sxy);
+        red_add_v4(row + 4, Syy, S0, c0, c1);
+        if (INVDEPTH) red_add_v2(row + 8, c2, c3);
+        else atomicAdd(row + 8, c2);
+    }
+}
+
 template <bool INVDEPTH>
 __global__ void __launch_bounds__(TILE_PIX, BWD_MIN_CTAS) blend_backward_kernel(
     const RasterHeader *__restrict__ hdr, const uint2 *__restrict__ ranges, const uint32_t *__restrict__ vals0,
@@ -302,13 +333,12 @@ __global__ void __launch_bounds__(TILE_PIX, BWD_MIN_CTAS) blend_backward_kernel(
     const float *__restrict__ final_T, const uint32_t *__restrict__ n_contrib, const float *__restrict__ dL_dpix,
     const float *__restrict__ dL_dinvdepth_pix, float *__restrict__ grad_acc, int grid_x,
     const uint32_t *__restrict__ order_bwd) {
-    __shared__ float4 s_a[TILE_PIX / 32][RING];      // x, y, Gaussian id (bits), forward list position (bits)
-    __shared__ float4 s_co[TILE_PIX / 32][RING];
-    __shared__ float4 s_feat[TILE_PIX / 32][RING];
-
-    const uint32_t tile = order_bwd[blockIdx.x];   // deepest contributor first
+    extern __shared__ __align__(16) unsigned char s_raw[];
     const int tid = threadIdx.x;
     const uint32_t lane = tid & 31, warp = tid >> 5;
+    BwdWarpSmem &sm = reinterpret_cast<BwdWarpSmem *>(s_raw)[warp];
+
+    const uint32_t tile = order_bwd[blockIdx.x];   // deepest contributor first
     const WarpBlock wb = warp_block(tid, (int)(tile % (uint32_t)grid_x), (int)(tile / (uint32_t)grid_x));
     const int px = wb.px, py = wb.py;
     const bool inside = px < W && py < H;
@@ -333,8 +363,8 @@ __global__ void __launch_bounds__(TILE_PIX, BWD_MIN_CTAS) blend_backward_kernel(
         g0 = dL_dpix[pid]; g1 = dL_dpix[plane + pid]; g2 = dL_dpix[2 * plane + pid];
         if (INVDEPTH) gi = dL_dinvdepth_pix[pid];
     }
-    const float bg_dot = bg[0] * g0 + bg[1] * g1 + bg[2] * g2;
-    const uint32_t slot10 = lane % 10u, group = lane / 10u;   // lane l (< 30) ends up with sum `slot10` of Gaussian `group`
+    sm.dpix[lane] = make_float4(g0, g1, g2, gi);
+    const float bg_term = T_final * (bg[0] * g0 + bg[1] * g1 + bg[2] * g2);
 
     uint32_t p_id = 0, id_next = 0;
     float2 p_xy = make_float2(0.f, 0.f);
@@ -350,6 +380,7 @@ __global__ void __launch_bounds__(TILE_PIX, BWD_MIN_CTAS) blend_backward_kernel(
     if (lane < n_proc) gather(point_list[n_proc - 1u - lane]);
     if (32u + lane < n_proc) id_next = point_list[n_proc - 33u - lane];
     uint32_t head = 0, tail = 0;
+    int nb = 0;                     // Gaussians parked for the next turn-around
     for (uint32_t c = 0; c < nchunks; c++) {
         const uint32_t back = c * 32u + lane;
         bool hit = false;
@@ -357,9 +388,9 @@ __global__ void __launch_bounds__(TILE_PIX, BWD_MIN_CTAS) blend_backward_kernel(
         const uint32_t m = __ballot_sync(0xffffffffu, hit);
         if (hit) {
             const uint32_t s = (tail + __popc(m & lanemask_lt())) & (RING - 1);
-            s_a[warp][s] = make_float4(p_xy.x, p_xy.y, __uint_as_float(p_id), __uint_as_float(n_proc - 1u - back));
-            s_co[warp][s] = prescale_conic(p_co);
-            s_feat[warp][s] = p_feat;
+            sm.ring_a[s] = make_float4(p_xy.x, p_xy.y, __uint_as_float(p_id), __uint_as_float(n_proc - 1u - back));
+            sm.ring_co[s] = prescale_conic(p_co);
+            sm.ring_feat[s] = p_feat;
         }
         tail += __popc(m);
         if (lane == 0) { STAT_ADD(4, 1); STAT_ADD(5, __popc(m)); }
@@ -367,72 +398,57 @@ __global__ void __launch_bounds__(TILE_PIX, BWD_MIN_CTAS) blend_backward_kernel(
         if (back + 64u < n_proc) id_next = point_list[n_proc - 65u - back];
         __syncwarp();
         const bool flush = c + 1u == nchunks;
-        // three ring entries at a time: independent alpha evaluation, sequential transmittance recurrence, then ONE
-        // 32-value butterfly for the 3 x 10 partial derivatives and one RED instruction (30 lanes, <= 3 rows)
-        while (tail - head >= 3u || (flush && tail != head)) {
-            const uint32_t avail = min(3u, tail - head);
-            uint32_t ss[3];
-            float G_[3], al[3], dx_[3], dy_[3];
-            bool ok[3];
+        // phase 1, four ring entries at a time (head stays a multiple of four: a group never wraps): the forward's
+        // alphas, evaluated independently, then the transmittance recurrence entry by entry
+        while (tail - head >= 4u || (flush && tail != head)) {
+            const uint32_t avail = min(4u, tail - head);
+            const uint32_t base = head & (RING - 1);
+            float G_[4], al[4];
+            bool ok[4];
 #pragma unroll
-            for (int u = 0; u < 3; u++) {
-                const uint32_t s = (head + (uint32_t)u) & (RING - 1);
-                const float4 e = s_a[warp][s];
+            for (int u = 0; u < 4; u++) {
+                const float4 e = sm.ring_a[base + u];
                 const float dx = e.x - pxf, dy = e.y - pyf;
-                const float4 co = s_co[warp][s];   // pre-scaled (log2 domain): exactly the forward's alpha
+                const float4 co = sm.ring_co[base + u];   // pre-scaled (log2 domain): exactly the forward's alpha
                 const float power = dx * (co.x * dx + co.y * dy) + co.z * dy * dy;
                 const float G = fast_exp2(power);
                 const float alpha = fminf(0.99f, co.w * G);
                 ok[u] = (uint32_t)u < avail && __float_as_uint(e.w) < last_contributor && !(power > 0.f) &&
                         alpha >= 1.f / 255.f;
-                ss[u] = s; G_[u] = G; al[u] = alpha; dx_[u] = dx; dy_[u] = dy;
+                G_[u] = G; al[u] = alpha;
             }
             head += avail;
             if (lane == 0) STAT_ADD(6, 1);
-            STAT_ADD(7, __popc(__ballot_sync(0xffffffffu, ok[0])) + __popc(__ballot_sync(0xffffffffu, ok[1])) +
-                            __popc(__ballot_sync(0xffffffffu, ok[2])));
-            if (!__any_sync(0xffffffffu, ok[0] || ok[1] || ok[2])) continue;
-            float w[32];
 #pragma unroll
-            for (int e = 0; e < 32; e++) w[e] = 0.f;
-#pragma unroll
-            for (int u = 0; u < 3; u++) {
-                if (!ok[u]) continue;
-                const float alpha = al[u], dx = dx_[u], dy = dy_[u];
-                const float4 f = s_feat[warp][ss[u]];
+            for (int u = 0; u < 4; u++) {
+                if (!__any_sync(0xffffffffu, ok[u])) continue;   // warp-uniform: no pixel of the block is touched
+                const float4 f = sm.ring_feat[base + u];
+                const float alpha = al[u];
                 const float ra = __fdividef(1.f, 1.f - alpha);
-                T = T * ra;                                   // transmittance in front of this Gaussian
-                const float aT = alpha * T;
-                float cg = f.x * g0 + f.y * g1 + f.z * g2;    // (colour . dL/dpixel)
-                w[10 * u + 6] = aT * g0;
-                w[10 * u + 7] = aT * g1;
-                w[10 * u + 8] = aT * g2;
-                if (INVDEPTH) {
-                    cg += f.w * gi;
-                    w[10 * u + 9] = aT * gi;
-                }
+                T = ok[u] ? T * ra : T;                            // transmittance in front of this Gaussian
+                const float aT = ok[u] ? alpha * T : 0.f;
+                float cg = f.x * g0 + f.y * g1 + f.z * g2;        // (colour . dL/dpixel)
+                if (INVDEPTH) cg += f.w * gi;
                 // dL/dalpha = (c - accum_rec) . g T - T_final/(1-alpha) (bg . g) with accum_rec T = behind / (1 - alpha),
                 // behind = sum over the contributors behind this one of (c . g) alpha T  (the upstream recurrence,
                 // contracted with g before instead of after)
-                const float dL_dalpha = cg * T - (behind + T_final * bg_dot) * ra;
+                const float dL_dalpha = cg * T - (behind + bg_term) * ra;
                 behind += cg * aT;
-                // raw moments of p = G dL/dalpha about the Gaussian centre; the preprocess backward turns them into
-                // dL/dmean2D, dL/dconic and dL/dopacity with the per-Gaussian conic (raster_backward.cu)
-                const float pw = G_[u] * dL_dalpha;
-                const float pdx = pw * dx, pdy = pw * dy;
-                w[10 * u + 0] = pdx;
-                w[10 * u + 1] = pdy;
-                w[10 * u + 2] = pdx * dx;
-                w[10 * u + 3] = pdx * dy;
-                w[10 * u + 4] = pdy * dy;
-                w[10 * u + 5] = pw;
-            }
-            const float sum = butterfly32(w, lane);
-            if (lane < 30u && sum != 0.f) {
-                const uint32_t s = group == 0u ? ss[0] : (group == 1u ? ss[1] : ss[2]);
-                atomicAdd(grad_acc + (size_t)__float_as_uint(s_a[warp][s].z) * GRAD_ACC_FLOATS + slot10, sum);
+                sm.p[nb * NB_PITCH + (int)lane] = ok[u] ? G_[u] * dL_dalpha : 0.f;
+                sm.aT[nb * NB_PITCH + (int)lane] = aT;
+                if (lane == 0) sm.meta[nb] = sm.ring_a[base + u];
+                if (++nb == NB) {
+                    __syncwarp();
+                    backward_turn_around<INVDEPTH>(sm, NB, lane, wb, grad_acc);
+                    __syncwarp();
+                    nb = 0;
+                }
             }
         }
+    }
+    if (nb) {
+        __syncwarp();
+        backward_turn_around<INVDEPTH>(sm, nb, lane, wb, grad_acc);
     }
 }
 
@@ -501,14 +517,22 @@ int launch_blend_backward(int W, int H, const float *background, const float *co
     const float *final_T = reinterpret_cast<const float *>(image + IL.final_T);
     const uint32_t *n_contrib = reinterpret_cast<const uint32_t *>(image + IL.n_contrib);
     const uint32_t *order_bwd = reinterpret_cast<const uint32_t *>(image + IL.order_bwd);
+    const size_t smem = sizeof(BwdWarpSmem) * (TILE_PIX / 32);
+    static const int attr_set = [] {
+        const int bytes = (int)(sizeof(BwdWarpSmem) * (TILE_PIX / 32));
+        cudaFuncSetAttribute(blend_backward_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+        cudaFuncSetAttribute(blend_backward_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+        return 1;
+    }();
+    (void)attr_set;
     ProfScope prof(K_BLEND_BWD, stream);
     {
         if (dL_dinvdepth_pix)
-            blend_backward_kernel<true><<<num_tiles, TILE_PIX, 0, stream>>>(
+            blend_backward_kernel<true><<<num_tiles, TILE_PIX, smem, stream>>>(
                 hdr, ranges, v0, v1, W, H, background, xy, co, colors, depth, final_T, n_contrib, dL_dpix,
                 dL_dinvdepth_pix, grad_acc, gx, order_bwd);
         else
-            blend_backward_kernel<false><<<num_tiles, TILE_PIX, 0, stream>>>(
+            blend_backward_kernel<false><<<num_tiles, TILE_PIX, smem, stream>>>(
                 hdr, ranges, v0, v1, W, H, background, xy, co, colors, depth, final_T, n_contrib, dL_dpix, nullptr,
                 grad_acc, gx, order_bwd);
     }
