@@ -15,18 +15,12 @@
 // Forward semantics (same order of tests as upstream): skip power > 0, alpha = min(.99, o * exp(power)), skip
 // alpha < 1/255, stop the pixel when T * (1 - alpha) < 1e-4, out = C + T * bg.
 //
-// Backward: every (pixel, Gaussian) pair produces nine or ten partial sums: the six raw moments of p = G dL/dalpha about
-// the Gaussian's 2-D centre (sum p dx, p dy, p dx^2, p dx dy, p dy^2, p -- the preprocess backward turns them into
-// dL/dmean2D, dL/dconic, dL/dopacity with the per-Gaussian conic, so the pixel loop never touches the conic again), the
-// three colour derivatives and the inverse-depth one.  Instead of ten global atomics per pair (upstream) they are reduced
-// in two levels:
-//   warp   : butterfly transpose-reduction over three Gaussians at a time -- 31 shuffles bring the 30 32-lane sums
-//            to 30 different lanes (a plain reduction would need 150), skipped entirely for Gaussians no lane of
-//            the warp touches;
-//   global : the 30 sums sit on 30 lanes, so ONE reduction instruction (RED.ADD.F32, <= 3 rows of 48 bytes, i.e. a
-//            handful of L2 sectors) adds them into the packed per-Gaussian accumulator that the preprocess backward
-//            (R8) then reads once -- one RED instruction per (warp, 3 Gaussians) instead of ten atomics per
-//            (pixel, Gaussian).
+// Backward: every (pixel, Gaussian) pair owes the per-Gaussian accumulator nine or ten partial sums: the six raw moments
+// of p = G dL/dalpha about the Gaussian's 2-D centre (sum p dx, p dy, p dx^2, p dx dy, p dy^2, p -- the preprocess backward
+// turns them into dL/dmean2D, dL/dconic, dL/dopacity with the per-Gaussian conic, so the pixel loop never touches the
+// conic again), the three colour derivatives and the inverse-depth one.  Instead of ten global atomics per pair (upstream)
+// the pixel loop parks two scalars per pair in shared memory and a per-warp "turn-around" every 16 Gaussians forms the
+// sums and issues vector reductions -- see the comment above backward_turn_around.
 // dL/dalpha uses upstream's recurrence contracted with dL/dpixel BEFORE the loop instead of after (one scalar "behind"
 // = sum over the contributors behind of (c . g) alpha T instead of a running colour per channel).
 // Algorithmic bytes: forward 40 B per duplicate + 20 B per pixel; backward 40 B read + 40 B gradient RMW per
