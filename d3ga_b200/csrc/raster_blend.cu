@@ -162,7 +162,7 @@ __global__ void __launch_bounds__(FWD_WARPS * 32, FWD_MIN_CTAS) blend_forward_ke
         p_xy = xy[id];
         p_co = conic_opacity[id];
         p_feat = make_float4(colors[3 * (size_t)id], colors[3 * (size_t)id + 1], colors[3 * (size_t)id + 2],
-                             INVDEPTH ? __fdividef(1.f, depths[id]) : 0.f);
+                             INVDEPTH ? depths[id] : 1.f   /* raw depth: dividing here would wait for the load */);
     };
     // ids run two steps ahead of the blend, the Gaussians themselves one step
     uint32_t id_next = 0;
@@ -179,7 +179,7 @@ __global__ void __launch_bounds__(FWD_WARPS * 32, FWD_MIN_CTAS) blend_forward_ke
             const uint32_t slot = (tail + __popc(m & lanemask_lt())) & (RING - 1);
             ra[warp][slot] = make_float4(p_xy.x, p_xy.y, __uint_as_float(pos + 1u), 0.f);
             rco[warp][slot] = prescale_conic(p_co);
-            rfeat[warp][slot] = p_feat;
+            rfeat[warp][slot] = make_float4(p_feat.x, p_feat.y, p_feat.z, INVDEPTH ? __fdividef(1.f, p_feat.w) : 0.f);
         }
         tail += __popc(m);
         if (lane == 0) { STAT_ADD(0, 1); STAT_ADD(1, __popc(m)); }
@@ -368,7 +368,7 @@ __global__ void __launch_bounds__(TILE_PIX, BWD_MIN_CTAS) blend_backward_kernel(
         p_xy = xy[id];
         p_co = conic_opacity[id];
         p_feat = make_float4(colors[3 * (size_t)id], colors[3 * (size_t)id + 1], colors[3 * (size_t)id + 2],
-                             INVDEPTH ? __fdividef(1.f, depths[id]) : 0.f);
+                             INVDEPTH ? depths[id] : 1.f   /* raw depth: dividing here would wait for the load */);
     };
     // lane l of step c looks at forward position q = n_proc - 1 - (32 c + l)
     if (lane < n_proc) gather(point_list[n_proc - 1u - lane]);
@@ -384,7 +384,7 @@ __global__ void __launch_bounds__(TILE_PIX, BWD_MIN_CTAS) blend_backward_kernel(
             const uint32_t s = (tail + __popc(m & lanemask_lt())) & (RING - 1);
             sm.ring_a[s] = make_float4(p_xy.x, p_xy.y, __uint_as_float(p_id), __uint_as_float(n_proc - 1u - back));
             sm.ring_co[s] = prescale_conic(p_co);
-            sm.ring_feat[s] = p_feat;
+            sm.ring_feat[s] = make_float4(p_feat.x, p_feat.y, p_feat.z, INVDEPTH ? __fdividef(1.f, p_feat.w) : 0.f);
         }
         tail += __popc(m);
         if (lane == 0) { STAT_ADD(4, 1); STAT_ADD(5, __popc(m)); }
@@ -397,11 +397,12 @@ __global__ void __launch_bounds__(TILE_PIX, BWD_MIN_CTAS) blend_backward_kernel(
         while (tail - head >= 4u || (flush && tail != head)) {
             const uint32_t avail = min(4u, tail - head);
             const uint32_t base = head & (RING - 1);
-            float G_[4], al[4];
+            float G_[4], al[4], ex[4], ey[4], eid[4];
             bool ok[4];
 #pragma unroll
             for (int u = 0; u < 4; u++) {
                 const float4 e = sm.ring_a[base + u];
+                ex[u] = e.x; ey[u] = e.y; eid[u] = e.z;
                 const float dx = e.x - pxf, dy = e.y - pyf;
                 const float4 co = sm.ring_co[base + u];   // pre-scaled (log2 domain): exactly the forward's alpha
                 const float power = dx * (co.x * dx + co.y * dy) + co.z * dy * dy;
@@ -430,7 +431,7 @@ __global__ void __launch_bounds__(TILE_PIX, BWD_MIN_CTAS) blend_backward_kernel(
                 behind += cg * aT;
                 sm.p[nb * NB_PITCH + (int)lane] = ok[u] ? G_[u] * dL_dalpha : 0.f;
                 sm.aT[nb * NB_PITCH + (int)lane] = aT;
-                if (lane == 0) sm.meta[nb] = sm.ring_a[base + u];
+                if (lane == 0) sm.meta[nb] = make_float4(ex[u], ey[u], eid[u], 0.f);
                 if (++nb == NB) {
                     __syncwarp();
                     backward_turn_around<INVDEPTH>(sm, NB, lane, wb, grad_acc);

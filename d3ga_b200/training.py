@@ -57,6 +57,7 @@ class Avatar:
         self.silhouette = torch.ones_like(self.colors)   # models/cage_net.py:249 silhouette_rgb
         self.params = [self.tetpoints, self.barys, self.scales, self.rotation, self.opacity, self.colors]
         self.grads = ddist.FlatGrads(self.params)
+        self._means2D = None
         self.tetpoints_host = torch.from_numpy(scene.tetpoints.copy())
         if device.type == "cuda":
             self.tetpoints_host = self.tetpoints_host.pin_memory()
@@ -77,16 +78,35 @@ class Avatar:
         """What GarmentNet.forward + render() do on the hot path (cage_net.py:218-230, renderer.py:122-141)."""
         means3D, cov6 = deform_gaussians(self.tetpoints, self.tets, self.tetra_id, self.barys, self.cg, self.scales,
                                          self.rotation)
-        means2D = torch.zeros_like(means3D, requires_grad=True) + 0
+        # renderer.py:122-126 allocates zeroed screen-space points per call only to receive a gradient nobody reads on
+        # this path; a resident zero buffer serves the API without two extra kernels per view
+        if self._means2D is None or self._means2D.shape != means3D.shape:
+            self._means2D = torch.zeros_like(means3D)
+        means2D = self._means2D
         return GaussianRasterizer(raster_settings=rs)(
             means3D=means3D, means2D=means2D, shs=None, colors_precomp=self.colors, opacities=self.opacity,
             scales=None, rotations=None, cov3D_precomp=cov6)[0]
 
 
+class _WeightedSum(torch.autograd.Function):
+    """sum(image * weights) as one dot product forward and one multiply backward (torch's own kernels; three launches and
+    an [3,H,W] temporary less per view than the composed expression)."""
+
+    @staticmethod
+    def forward(ctx, img, weights):
+        ctx.save_for_backward(weights)
+        return torch.dot(img.reshape(-1), weights.reshape(-1))
+
+    @staticmethod
+    def backward(ctx, g):
+        (weights,) = ctx.saved_tensors
+        return weights * g, None
+
+
 def view_step(avatar, rs, weights):
     """One view forward + backward; loss = sum(image * weights)."""
     img = avatar.render(rs)
-    loss = (img * weights).sum()
+    loss = _WeightedSum.apply(img, weights)
     loss.backward()
     return loss
 
