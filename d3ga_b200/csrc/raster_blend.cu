@@ -64,8 +64,12 @@ __device__ __forceinline__ WarpBlock warp_block(int tid, int tile_x, int tile_y)
 
 constexpr int RING = 64;                     // per-warp ring of staged survivors (>= group - 1 + 32)
 constexpr int FWD_WARPS = TILE_PIX / 32;    // (splitting a tile over 2 or 4 smaller CTAs was measured: no gain)
-#define FWD_MIN_CTAS 4
+#ifndef FWD_MIN_CTAS
+#define FWD_MIN_CTAS 3                       // 80 registers, no spills: 165 us; 4 CTAs/SM (64 registers, spills): 181 us
+#endif
+#ifndef BWD_MIN_CTAS
 #define BWD_MIN_CTAS 3
+#endif
 #ifdef D3GA_BLEND_STATS
 // development counters: [0..3] forward (warp-steps, survivors, groups, passing pixel-Gaussian pairs), [4..7] backward
 __device__ unsigned long long g_blend_stats[8];
