@@ -213,11 +213,15 @@ def run_ours(args):
 
     # one view = one replay of the captured graph (training.GraphedViewStep); --no-graph launches every view eagerly
     gv = pv = None
+    lanes = 1
     if not args.no_graph:
-        if args.lanes > 1:
-            pv = training.PipelinedViews(avatar, cams[0], bg, lanes=args.lanes)
+        training.multi_view_step(avatar, bank, [mine[0]], weights, bg)     # one eager view: settles the capacity hint
+        lanes = training.PipelinedViews.lanes_that_fit(avatar, args.lanes)
+        if lanes > 1:
+            pv = training.PipelinedViews(avatar, cams[0], bg, lanes=lanes)
         else:
             gv = training.GraphedViewStep(avatar, cams[0], bg)
+    args.lanes = lanes
 
     def region(n_steps, first_step, eager=False, **kw):
         ddist.barrier()

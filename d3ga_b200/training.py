@@ -266,6 +266,19 @@ class PipelinedViews:
     works on a shadow of the avatar (same parameter storage, own gradient buffer and own cage-vertex input); `finish()`
     adds the lanes' gradients into the avatar's flat buffer."""
 
+    @staticmethod
+    def lanes_that_fit(avatar, wanted, fraction=0.5):
+        """Lanes whose workspaces fit in `fraction` of the free device memory.  A lane keeps a geometry + binning + image
+        workspace, the deformation outputs and the backward temporaries alive in its graph pool, and the eager warm-up
+        of a capture needs the same again: about 2.5 x the workspace bytes at the current capacity hint (an eager view
+        must have run, so that the hint reflects the workload: the 4 M-Gaussian 4K stress needs ~40 GB per lane)."""
+        from d3ga_b200 import _lib
+        from d3ga_b200 import diff_gaussian_rasterization as dgr
+        cap = dgr._capacity_hint.get((avatar.device, avatar.N, avatar.W, avatar.H), 6 * avatar.N)
+        per_lane = 2.5 * sum(_lib.workspace_bytes(avatar.N, avatar.W, avatar.H, cap)) + 400 * avatar.N
+        free, _ = torch.cuda.mem_get_info(avatar.device)
+        return int(max(1, min(wanted, fraction * free // per_lane)))
+
     def __init__(self, avatar, cam, bg, lanes=2):
         self.avatar = avatar
         self.shadows = [avatar.shadow() for _ in range(lanes)]
