@@ -12,10 +12,14 @@ name, src, flags = sys.argv[1], sys.argv[2], sys.argv[3:]
 B.build_library()
 root = os.path.dirname(B.HERE)
 os.makedirs(os.path.join(root, "variants"), exist_ok=True)
-obj = os.path.join(root, "variants", f"{name}_{src.replace('.cu', '.o')}")
-extra = dict(B.SOURCES)[src]
-subprocess.check_call([B.NVCC] + B.COMMON + extra + flags + ["-c", os.path.join(B.CSRC, src), "-o", obj])
-objs = [obj if n == src else os.path.join(B.OBJ, n.replace(".cu", ".o")) for n, _ in B.SOURCES]
+objs = []
+for n, extra in B.SOURCES:                      # <file.cu> = ALL rebuilds every source with the flags
+    if src in (n, "ALL"):
+        obj = os.path.join(root, "variants", f"{name}_{n.replace('.cu', '.o')}")
+        subprocess.check_call([B.NVCC] + B.COMMON + extra + flags + ["-c", os.path.join(B.CSRC, n), "-o", obj])
+    else:
+        obj = os.path.join(B.OBJ, n.replace(".cu", ".o"))
+    objs.append(obj)
 out = os.path.join(root, "variants", f"libd3ga_{name}.so")
 subprocess.check_call([B.NVCC, "-shared", "-cudart", "static", "-gencode", "arch=compute_100a,code=sm_100a", "-o", out] + objs)
 print(out)
