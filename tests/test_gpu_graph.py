@@ -95,6 +95,7 @@ def test_graphed_step_recovers_from_overflow(cuda_lib):
         loss = training.view_step(avatar, gv.rs, gv.weights)
         gv.total += loss.detach()
     gv.launches_per_replay = _lib.launch_count() - l0
+    del loss          # a live loss keeps this capture's autograd nodes (bound to its capture stream) alive
     dgr.collect_deferred(dev)
     before = gv.captures
     tot_g = training.multi_view_step_graphed(avatar, bank, ids, gv, weights=w).clone()
