@@ -221,7 +221,20 @@ def run_ours(args):
             pv = training.PipelinedViews(avatar, cams[0], bg, lanes=lanes)
         else:
             gv = training.GraphedViewStep(avatar, cams[0], bg)
+    if pv is not None or gv is not None:
+        # capture now, so that a failure (memory, an unsupported driver) degrades to eager launches instead of
+        # costing the whole run; said in config.launch
+        try:
+            (pv.capture if pv is not None else gv.capture)(bank.dev[mine[0]])
+            torch.cuda.synchronize()
+        except Exception as e:   # noqa: BLE001
+            print(f"bench.py: CUDA-graph capture failed ({type(e).__name__}: {e}); falling back to eager launches",
+                  file=sys.stderr, flush=True)
+            gv = pv = None
+            lanes = 0
+            torch.cuda.synchronize()
     args.lanes = lanes
+    args.no_graph = args.no_graph or lanes == 0
 
     def region(n_steps, first_step, eager=False, **kw):
         ddist.barrier()

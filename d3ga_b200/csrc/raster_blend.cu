@@ -253,9 +253,11 @@ __global__ void __launch_bounds__(FWD_WARPS * 32, FWD_MIN_CTAS) blend_forward_ke
     // deepest contributor of the tile = how far the backward has to go; the last CTA orders the backward's tiles
     const uint32_t wmax = __reduce_max_sync(0xffffffffu, inside ? last : 0u);
     if (lane == 0 && wmax) atomicMax(tile_nproc + tile, wmax);   // zeroed by the launcher
-    __threadfence();
     __syncthreads();
-    if (tid == 0) s_last = atomicAdd(&hdr_rw->blend_done, 1u) == gridDim.x - 1u;
+    if (tid == 0) {
+        __threadfence();   // one fence, after the barrier: cumulative over the eight warps' reductions above
+        s_last = atomicAdd(&hdr_rw->blend_done, 1u) == gridDim.x - 1u;
+    }
     __syncthreads();
     if (!s_last) return;
     __threadfence();
