@@ -294,7 +294,7 @@ def run_ours(args):
         "depth_sort_pass_kernel": 16 * N,
         "sort_pass_kernel": 24 * D, "segment_sort_kernel": 12 * D, "tile_ranges_kernel": 8 * D + 8 * Tl, "blend_forward_kernel": 40 * D + 20 * P,
         "blend_backward_kernel": 80 * D + 20 * P, "preprocess_backward_kernel": 104 * N,
-        "deform_backward_kernel": 212 * N}
+        "deform_backward_kernel": 212 * N, "rect_grid_kernel": 12 * N, "tile_plan_kernel": 12 * Tl}
     peak, peak_kind = measured_peak()
     kern = {}
     for name, (tms, cnt) in prof.items():

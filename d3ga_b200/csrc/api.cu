@@ -31,7 +31,8 @@ static const char *const g_kernel_names[K_COUNT] = {
     "compute_bary_kernel", "segment_sort_kernel", "preprocess_kernel", "emit_sorted_kernel", "depth_histogram_kernel",
     "depth_sort_pass_kernel", "fem_energy_forward_kernel", "fem_energy_backward_kernel",
     "ssim_forward_kernel", "ssim_backward_kernel", "lbs_skeleton_kernel", "lbs_skin_forward_kernel",
-    "lbs_skin_backward_kernel", "lbs_unskin_kernel", "lbs_skin_dense_forward_kernel", "lbs_skin_dense_backward_kernel"};
+    "lbs_skin_backward_kernel", "lbs_unskin_kernel", "lbs_skin_dense_forward_kernel", "lbs_skin_dense_backward_kernel",
+    "rect_grid_kernel", "tile_plan_kernel"};
 
 bool profiling_enabled() { return g_prof_on.load(std::memory_order_relaxed) != 0; }
 
@@ -179,8 +180,8 @@ int d3ga_raster_forward_render(int P, int W, int H, const float *background, con
     const ImgLayout IL = img_layout(W, H);
     const int num_tiles = ((W + TILE - 1) / TILE) * ((H + TILE - 1) / TILE);
     const int sort_bits = 32 + higher_msb((uint32_t)num_tiles);
-    int rc = launch_sort_and_ranges((uint8_t *)geom, (uint8_t *)binning, BL, capacity, sort_bits, (uint8_t *)image, IL,
-                                    num_tiles, stream);
+    int rc = launch_sort_and_ranges((uint8_t *)geom, GL, (W + TILE - 1) / TILE, (H + TILE - 1) / TILE, (uint8_t *)binning,
+                                    BL, capacity, sort_bits, (uint8_t *)image, IL, num_tiles, stream);
     if (rc) return rc;
     const float *colors = colors_precomp ? colors_precomp : reinterpret_cast<const float *>((uint8_t *)geom + GL.rgb);
     return launch_blend_forward(W, H, background, colors, (const uint8_t *)geom, GL, (const uint8_t *)binning, BL,

@@ -14,7 +14,10 @@ constexpr int SORT_THREADS = 512;
 constexpr int SORT_ITEMS = 8;      // keys per thread per onesweep tile
 constexpr int SORT_TILE = SORT_THREADS * SORT_ITEMS;  // 4096 pairs = 48 KB of payload per CTA
 constexpr int SORT_MAX_PASSES = 8;
-constexpr uint32_t MAX_DUPLICATES = (1u << 31) - 1;  // an inclusive look-back word keeps 1 flag bit
+constexpr uint32_t MAX_DUPLICATES = (1u << 31) - 1;
+// (gx+1)(gy+1) up to which the per-tile counts come from the rect difference grid (48 KB of shared memory)
+constexpr int TILE_GRID_CELLS_MAX = 12288;
+inline bool tile_plan_from_grid(int gx, int gy) { return (gx + 1) * (gy + 1) <= TILE_GRID_CELLS_MAX; }  // an inclusive look-back word keeps 1 flag bit
 
 // ---- workspace layouts ------------------------------------------------------------------------------------------
 struct RasterHeader {          // first 256 bytes of the geom workspace; zeroed at the start of every forward
@@ -43,7 +46,7 @@ static_assert(sizeof(RasterHeader) == 256, "header is 256 bytes");
 
 struct GeomLayout {
     uint64_t header, depth, xy, conic_opacity, rgb, cov3D, tiles, offsets, clamped, scan_state;
-    uint64_t rect_pack, dkeys, dvals, dep_hist, dep_bins, dep_state, total;   // depth-first binning
+    uint64_t rect_pack, dkeys, dvals, dep_hist, dep_bins, dep_state, tile_diff, total;   // depth-first binning
     uint64_t p_pad;
 };
 struct BinLayout {
@@ -76,6 +79,7 @@ inline GeomLayout geom_layout(int P) {
     L.dep_hist = o;      o = align256(o + 4 * 256 * 4);
     L.dep_bins = o;      o = align256(o + 4 * 256 * 4);
     L.dep_state = o;     o = align256(o + 4ull * 256 * 4 * ((p + SORT_TILE - 1) / SORT_TILE + 1));
+    L.tile_diff = o;     o = align256(o + 4ull * TILE_GRID_CELLS_MAX);   // 2-D difference grid of the tile rects
     L.total = o;
     return L;
 }
@@ -118,7 +122,7 @@ constexpr int GRAD_ACC_FLOATS = 12;
 enum KernelId {
     K_GEOMETRY = 0, K_SORT_HIST, K_SORT_PASS, K_RANGES, K_BLEND_FWD, K_BLEND_BWD, K_PRE_BWD, K_DEFORM_FWD, K_DEFORM_BWD,
     K_BARY, K_SEG_SORT, K_PREPROCESS, K_EMIT, K_DEPTH_HIST, K_DEPTH_PASS, K_FEM_FWD, K_FEM_BWD, K_SSIM_FWD, K_SSIM_BWD,
-    K_LBS_SKELETON, K_LBS_SKIN_FWD, K_LBS_SKIN_BWD, K_LBS_UNSKIN, K_LBS_DENSE_FWD, K_LBS_DENSE_BWD, K_COUNT
+    K_LBS_SKELETON, K_LBS_SKIN_FWD, K_LBS_SKIN_BWD, K_LBS_UNSKIN, K_LBS_DENSE_FWD, K_LBS_DENSE_BWD, K_RECT_GRID, K_TILE_PLAN, K_COUNT
 };
 // Optional per-kernel CUDA-event timing (d3ga_profile_* in the C-ABI; bench.py's roofline figures come from it).
 // A no-op unless profiling is enabled.
@@ -150,7 +154,7 @@ int launch_geometry(int P, int sh_degree, int sh_coeffs, const float *means3D, c
                     const float *projmatrix, const float *campos, int W, int H, float tanfovx, float tanfovy,
                     int antialiasing, uint8_t *geom, const GeomLayout &GL, uint8_t *binning, const BinLayout &BL,
                     uint64_t capacity, int32_t *radii, cudaStream_t stream);
-int launch_sort_and_ranges(uint8_t *geom, uint8_t *binning, const BinLayout &BL, uint64_t capacity, int sort_bits,
+int launch_sort_and_ranges(uint8_t *geom, const GeomLayout &GL, int gx, int gy, uint8_t *binning, const BinLayout &BL, uint64_t capacity, int sort_bits,
                            uint8_t *image, const ImgLayout &IL, int num_tiles, cudaStream_t stream);
 int launch_depth_sort(int P, uint8_t *geom, const GeomLayout &GL, cudaStream_t stream);
 enum SortMode { SORT_DEPTH_FIRST = 0, SORT_GLOBAL = 1, SORT_SEGMENTED = 2 };

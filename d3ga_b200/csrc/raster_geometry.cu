@@ -70,6 +70,7 @@ struct GeoParams {
     uint2 *rect_pack;      // [P] (x0 | y0 << 16, width) of the tile rect
     uint32_t *dkeys, *dvals;   // [2][P_pad] ping-pong of the 32-bit depth sort
     uint32_t P_pad;
+    int32_t *tile_diff;    // [(gy+1)][(gx+1)] +1/-1 at the rect corners (null: grid too large, counts come from the keys)
 };
 
 constexpr uint64_t FLAG_AGG = 1ull << 62, FLAG_INC = 2ull << 62, FLAG_MASK = 3ull << 62;
@@ -355,6 +356,35 @@ __global__ void __launch_bounds__(GEO_THREADS) preprocess_kernel(const GeoParams
     p.dvals[idx] = (uint32_t)idx;
 }
 
+// Per-tile duplicate counts without touching the duplicates: +1 over a Gaussian's tile rect = four corner updates of a
+// 2-D difference grid whose prefix sum (tile_plan_kernel, raster_sort.cu) is the count of every tile.  The avatar covers
+// a third of the image, so a few thousand cells would each take thousands of global atomics (measured: +140 us when the
+// emission kernel issued them directly); a small persistent grid of CTAs therefore accumulates in shared memory and
+// flushes its non-zero cells once.
+__global__ void __launch_bounds__(512) rect_grid_kernel(int P, const uint2 *__restrict__ rect_pack,
+                                                        const uint32_t *__restrict__ tiles, int gx, int gy,
+                                                        int32_t *__restrict__ diff) {
+    extern __shared__ int32_t s_grid[];
+    const int pitch = gx + 1, cells = pitch * (gy + 1);
+    for (int i = threadIdx.x; i < cells; i += blockDim.x) s_grid[i] = 0;
+    __syncthreads();
+    for (int g = blockIdx.x * blockDim.x + threadIdx.x; g < P; g += gridDim.x * blockDim.x) {
+        const uint32_t count = __ldcs(tiles + g);
+        if (!count) continue;
+        const uint2 rw = __ldcs(rect_pack + g);
+        const int x0 = (int)(rw.x & 0xffffu), y0 = (int)(rw.x >> 16), x1 = x0 + (int)rw.y, y1 = y0 + (int)(count / rw.y);
+        atomicAdd(&s_grid[y0 * pitch + x0], 1);
+        atomicAdd(&s_grid[y0 * pitch + x1], -1);
+        atomicAdd(&s_grid[y1 * pitch + x0], -1);
+        atomicAdd(&s_grid[y1 * pitch + x1], 1);
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < cells; i += blockDim.x) {
+        const int v = s_grid[i];
+        if (v) atomicAdd(diff + i, v);
+    }
+}
+
 // Depth-first binning, step 3: R2 + R3 over the Gaussians in depth order (`order` = values of the depth sort).  The
 // duplicate list comes out ordered by (depth, Gaussian), so the global sort only has to run on the tile digits.
 __global__ void __launch_bounds__(GEO_THREADS) emit_sorted_kernel(const GeoParams p) {
@@ -419,6 +449,11 @@ int launch_geometry(int P, int sh_degree, int sh_coeffs, const float *means3D, c
     p.dkeys = reinterpret_cast<uint32_t *>(geom + GL.dkeys);
     p.dvals = reinterpret_cast<uint32_t *>(geom + GL.dvals);
     p.P_pad = (uint32_t)GL.p_pad;
+    p.tile_diff = nullptr;
+    if (sort_mode() == SORT_DEPTH_FIRST && tile_plan_from_grid(p.gx, p.gy)) {
+        p.tile_diff = reinterpret_cast<int32_t *>(geom + GL.tile_diff);
+        D3GA_CUDA(cudaMemsetAsync(p.tile_diff, 0, 4ull * (p.gx + 1) * (p.gy + 1), stream));
+    }
     if (p.num_ctas == 0) return D3GA_OK;
     if (sort_mode() != SORT_DEPTH_FIRST) {
         ProfScope prof(K_GEOMETRY, stream);
@@ -432,6 +467,11 @@ int launch_geometry(int P, int sh_degree, int sh_coeffs, const float *means3D, c
         preprocess_kernel<<<p.num_ctas, GEO_THREADS, 0, stream>>>(p);
     }
     D3GA_LAUNCH_CHECK();
+    if (p.tile_diff) {
+        ProfScope prof(K_RECT_GRID, stream);
+        rect_grid_kernel<<<296, 512, 4 * (p.gx + 1) * (p.gy + 1), stream>>>(P, p.rect_pack, p.tiles, p.gx, p.gy, p.tile_diff);
+        D3GA_LAUNCH_CHECK();
+    }
     int rc = launch_depth_sort(P, geom, GL, stream);
     if (rc) return rc;
     {

@@ -338,6 +338,81 @@ __global__ void __launch_bounds__(HIST_THREADS) depth_histogram_kernel(RasterHea
     if (tid == 0) hdr->dep_final_sel = src;
 }
 
+// Depth-first binning: ranges, tile-digit histograms, pass plan and the forward's tile order from the rects' 2-D difference
+// grid (rect_grid_kernel) instead of two passes over the D keys (sort_histogram_kernel before the sort, tile_ranges_kernel
+// after it).  One CTA, the grid in shared memory:
+//   1. prefix sums along x, then along y: cell (ty, tx) = number of duplicates of tile ty * gx + tx;
+//   2. exclusive scan over the tiles in id order = where each tile's run starts in the sorted list -> ranges (a tile
+//      without duplicates keeps (0, 0), like upstream's zero-initialised ranges);
+//   3. digit counts of the tile passes -> bin offsets and the plan (a pass whose digit is constant is skipped);
+//   4. counting sort of the tiles by list length (launch order of the blend forward).
+__global__ void __launch_bounds__(256) tile_plan_kernel(RasterHeader *hdr, const int32_t *diff, int gx, int gy,
+                                                        uint2 *ranges, uint32_t *bins, uint32_t *order_fwd, int sort_bits,
+                                                        int num_passes, int first_pass) {
+    extern __shared__ int32_t s_grid[];            // the difference grid, then the counts
+    __shared__ uint32_t s_hist[SORT_MAX_PASSES][256];
+    __shared__ uint32_t s_tmp[8];
+    __shared__ uint32_t s_bins[257];
+    const int tid = threadIdx.x, pitch = gx + 1, num_tiles = gx * gy, cells = pitch * (gy + 1);
+    for (int i = tid; i < cells; i += 256) s_grid[i] = __ldcg(diff + i);
+    for (int p = 0; p < num_passes; p++) s_hist[p][tid] = 0;
+    __syncthreads();
+    for (int y = tid; y <= gy; y += 256) {
+        int run = 0;
+        for (int x = 0; x <= gx; x++) { run += s_grid[y * pitch + x]; s_grid[y * pitch + x] = run; }
+    }
+    __syncthreads();
+    for (int x = tid; x <= gx; x += 256) {
+        int run = 0;
+        for (int y = 0; y <= gy; y++) { run += s_grid[y * pitch + x]; s_grid[y * pitch + x] = run; }
+    }
+    __syncthreads();
+    auto count_of = [&](int t) { return (uint32_t)s_grid[(t / gx) * pitch + (t % gx)]; };
+    // exclusive scan over the tiles: every thread owns a contiguous chunk
+    const int per = (num_tiles + 255) / 256, t0 = min(num_tiles, tid * per), t1 = min(num_tiles, t0 + per);
+    uint32_t local = 0;
+    for (int t = t0; t < t1; t++) local += count_of(t);
+    uint32_t total = 0;
+    uint32_t start = block_excl_scan_256(local, s_tmp, &total);
+    for (int t = t0; t < t1; t++) {
+        const uint32_t c = count_of(t);
+        ranges[t] = c ? make_uint2(start, start + c) : make_uint2(0u, 0u);
+        start += c;
+        if (c) {
+            for (int p = first_pass; p < num_passes; p++) {
+                const int shift = 8 * p - 32;
+                const uint32_t nb = min(8, sort_bits - 8 * p);
+                atomicAdd(&s_hist[p][((uint32_t)t >> shift) & ((1u << nb) - 1u)], c);
+            }
+        }
+    }
+    __syncthreads();
+    const uint32_t D = total;
+    uint32_t src = 0;
+    if (tid < first_pass) {   // the depth digits are already in order: those passes are skipped
+        hdr->pass_skip[tid] = 1u;
+        hdr->pass_src[tid] = 0u;
+    }
+    for (int p = first_pass; p < num_passes; p++) {
+        const uint32_t c = s_hist[p][tid];
+        const int all_in_one = __syncthreads_or(D == 0 || c == D);
+        const uint32_t ex = block_excl_scan_256(c, s_tmp, nullptr);
+        bins[p * 256 + tid] = ex;
+        if (tid == 0) {
+            hdr->pass_skip[p] = all_in_one ? 1u : 0u;
+            hdr->pass_src[p] = src;
+        }
+        if (!all_in_one) src ^= 1u;
+    }
+    if (tid == 0) {
+        hdr->final_sel = src;
+        hdr->sort_bits = (uint32_t)sort_bits;
+        hdr->num_passes = (uint32_t)num_passes;
+    }
+    __syncthreads();
+    order_tiles_descending(num_tiles, count_of, order_fwd, s_bins);
+}
+
 __global__ void __launch_bounds__(256) tile_ranges_kernel(RasterHeader *hdr, const uint64_t *keys0,
                                                           const uint64_t *keys1, uint2 *ranges, int num_tiles,
                                                           uint32_t *order_fwd) {
@@ -375,7 +450,7 @@ __global__ void __launch_bounds__(256) tile_ranges_kernel(RasterHeader *hdr, con
 
 static int g_sort_attr_set = 0;
 
-int launch_sort_and_ranges(uint8_t *geom, uint8_t *binning, const BinLayout &BL, uint64_t capacity, int sort_bits,
+int launch_sort_and_ranges(uint8_t *geom, const GeomLayout &GL, int gx, int gy, uint8_t *binning, const BinLayout &BL, uint64_t capacity, int sort_bits,
                            uint8_t *image, const ImgLayout &IL, int num_tiles, cudaStream_t stream) {
     RasterHeader *hdr = reinterpret_cast<RasterHeader *>(geom);
     uint64_t *keys0 = reinterpret_cast<uint64_t *>(binning + BL.keys0);
@@ -407,11 +482,24 @@ int launch_sort_and_ranges(uint8_t *geom, uint8_t *binning, const BinLayout &BL,
     D3GA_CUDA(cudaMemsetAsync(tile_state, 0, 4ull * 256 * tiles_cap * num_passes, stream));
     D3GA_CUDA(cudaMemsetAsync(ranges, 0, 8ull * num_tiles, stream));
 
-    const uint64_t per_cta = (uint64_t)HIST_THREADS * HIST_ITEMS;
-    int hist_grid = (int)((capacity + per_cta - 1) / per_cta);
-    if (hist_grid > 148 * 8) hist_grid = 148 * 8;
-    if (hist_grid < 1) hist_grid = 1;
-    {
+    // depth-first with a tile grid small enough for the rect difference grid: the plan comes from the per-tile counts, no
+    // histogram pass over the keys before and no ranges pass after the sort
+    const bool from_grid = mode == SORT_DEPTH_FIRST && tile_plan_from_grid(gx, gy);
+    if (from_grid) {
+        static const int attr_set = [] {
+            cudaFuncSetAttribute(tile_plan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 4 * TILE_GRID_CELLS_MAX);
+            return 1;
+        }();
+        (void)attr_set;
+        ProfScope prof(K_TILE_PLAN, stream);
+        tile_plan_kernel<<<1, 256, 4 * (gx + 1) * (gy + 1), stream>>>(
+            hdr, reinterpret_cast<const int32_t *>(geom + GL.tile_diff), gx, gy, ranges, bins,
+            reinterpret_cast<uint32_t *>(image + IL.order_fwd), sort_bits, num_passes, first_pass);
+    } else {
+        const uint64_t per_cta = (uint64_t)HIST_THREADS * HIST_ITEMS;
+        int hist_grid = (int)((capacity + per_cta - 1) / per_cta);
+        if (hist_grid > 148 * 8) hist_grid = 148 * 8;
+        if (hist_grid < 1) hist_grid = 1;
         ProfScope prof(K_SORT_HIST, stream);
         sort_histogram_kernel<<<hist_grid, HIST_THREADS, 0, stream>>>(hdr, keys0, ghist, bins, sort_bits, num_passes,
                                                                       first_pass);
@@ -427,6 +515,7 @@ int launch_sort_and_ranges(uint8_t *geom, uint8_t *binning, const BinLayout &BL,
         }
         D3GA_LAUNCH_CHECK();
     }
+    if (from_grid) return D3GA_OK;
     int rg = (int)((capacity + 255) / 256);
     if (rg > 148 * 16) rg = 148 * 16;
     if (rg < 1) rg = 1;
