@@ -349,12 +349,18 @@ __global__ void __launch_bounds__(HIST_THREADS) depth_histogram_kernel(RasterHea
 __global__ void __launch_bounds__(256) tile_plan_kernel(RasterHeader *hdr, const int32_t *diff, int gx, int gy,
                                                         uint2 *ranges, uint32_t *bins, uint32_t *order_fwd, int sort_bits,
                                                         int num_passes, int first_pass) {
-    extern __shared__ int32_t s_grid[];            // the difference grid, then the counts
+    extern __shared__ int32_t s_grid[];            // the difference grid [(gy+1)(gx+1)], then the counts [gy gx]
     __shared__ uint32_t s_hist[SORT_MAX_PASSES][256];
     __shared__ uint32_t s_tmp[8];
     __shared__ uint32_t s_bins[257];
     const int tid = threadIdx.x, pitch = gx + 1, num_tiles = gx * gy, cells = pitch * (gy + 1);
-    for (int i = tid; i < cells; i += 256) s_grid[i] = __ldcg(diff + i);
+    for (int i0 = 0; i0 < cells; i0 += 256 * 8) {   // batched: a single CTA is latency-bound on these loads
+        int32_t v[8];
+#pragma unroll
+        for (int u = 0; u < 8; u++) { const int i = i0 + u * 256 + tid; v[u] = i < cells ? __ldcg(diff + i) : 0; }
+#pragma unroll
+        for (int u = 0; u < 8; u++) { const int i = i0 + u * 256 + tid; if (i < cells) s_grid[i] = v[u]; }
+    }
     for (int p = 0; p < num_passes; p++) s_hist[p][tid] = 0;
     __syncthreads();
     for (int y = tid; y <= gy; y += 256) {
@@ -362,12 +368,13 @@ __global__ void __launch_bounds__(256) tile_plan_kernel(RasterHeader *hdr, const
         for (int x = 0; x <= gx; x++) { run += s_grid[y * pitch + x]; s_grid[y * pitch + x] = run; }
     }
     __syncthreads();
-    for (int x = tid; x <= gx; x += 256) {
+    int32_t *s_cnt = s_grid + cells;               // [num_tiles] the counts in tile-id order (no div / mod later)
+    for (int x = tid; x < gx; x += 256) {
         int run = 0;
-        for (int y = 0; y <= gy; y++) { run += s_grid[y * pitch + x]; s_grid[y * pitch + x] = run; }
+        for (int y = 0; y < gy; y++) { run += s_grid[y * pitch + x]; s_cnt[y * gx + x] = run; }
     }
     __syncthreads();
-    auto count_of = [&](int t) { return (uint32_t)s_grid[(t / gx) * pitch + (t % gx)]; };
+    auto count_of = [&](int t) { return (uint32_t)s_cnt[t]; };
     // exclusive scan over the tiles: every thread owns a contiguous chunk
     const int per = (num_tiles + 255) / 256, t0 = min(num_tiles, tid * per), t1 = min(num_tiles, t0 + per);
     uint32_t local = 0;
@@ -487,12 +494,12 @@ int launch_sort_and_ranges(uint8_t *geom, const GeomLayout &GL, int gx, int gy, 
     const bool from_grid = mode == SORT_DEPTH_FIRST && tile_plan_from_grid(gx, gy);
     if (from_grid) {
         static const int attr_set = [] {
-            cudaFuncSetAttribute(tile_plan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 4 * TILE_GRID_CELLS_MAX);
+            cudaFuncSetAttribute(tile_plan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 8 * TILE_GRID_CELLS_MAX);
             return 1;
         }();
         (void)attr_set;
         ProfScope prof(K_TILE_PLAN, stream);
-        tile_plan_kernel<<<1, 256, 4 * (gx + 1) * (gy + 1), stream>>>(
+        tile_plan_kernel<<<1, 256, 4 * ((gx + 1) * (gy + 1) + gx * gy), stream>>>(
             hdr, reinterpret_cast<const int32_t *>(geom + GL.tile_diff), gx, gy, ranges, bins,
             reinterpret_cast<uint32_t *>(image + IL.order_fwd), sort_bits, num_passes, first_pass);
     } else {
