@@ -185,6 +185,21 @@ def make_scene(name: str, N: int, n_tets: int, W: int, H: int, seed=0, scale_mul
 
 _GARMENTS = (0.26, 0.37, 0.37)  # body / upper / lower = 35k / 50k / 50k of 135k (configs/actorshq_actor02.yml:123-142)
 
+def sort_scene_by_tet(scene: "Scene") -> "Scene":
+    """The same avatar with its Gaussians stored in tet order (a stable argsort of tetra_id applied to every per-Gaussian
+    array).  The order of the Gaussians means nothing to the model; stored like this, Gaussians that share a tet -- and
+    are therefore close in space -- are neighbours in memory, which the deformation kernels (coalesced instead of
+    gathered accesses, in-warp vertex sums) and the blend kernels' gathers reward.  What a user does once after
+    `compute_bary` in CageBase.load_tetra (lib/cage.py:308-337)."""
+    import dataclasses
+    o = np.argsort(scene.tetra_id, kind="stable")
+    take = lambda a: None if a is None else np.ascontiguousarray(a[o])  # noqa: E731
+    return dataclasses.replace(scene, tetra_id=take(scene.tetra_id), barys=take(scene.barys),
+                               canonical_gradient=take(scene.canonical_gradient), scales=take(scene.scales),
+                               rotation=take(scene.rotation), opacity=take(scene.opacity), colors=take(scene.colors),
+                               shs=take(scene.shs), meta=dict(scene.meta, tet_sorted=True))
+
+
 WORKLOADS = {
     # name: (N, n_tets, W, H, scale_mul, garments)
     "c1": (100_000, 10_368, 512, 512, 1.0, (1.0,)),

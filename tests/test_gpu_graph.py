@@ -103,3 +103,20 @@ def test_graphed_step_recovers_from_overflow(cuda_lib):
     assert dgr._capacity_hint[key] > small
     assert abs(float(tot_g) - float(tot_e)) <= 1e-5 * abs(float(tot_e))
     assert rel(avatar.grads.flat, g_e) < 1e-5
+
+
+def test_tet_sorted_storage_is_the_same_avatar(cuda_lib):
+    """synth.sort_scene_by_tet only permutes the Gaussians: same loss, gradients permuted the same way."""
+    dev, scene, cams, avatar, bank, bg, wh = setup()
+    w = wh.to(dev)
+    ids = [0, 5]
+    tot = training.multi_view_step(avatar, bank, ids, w, bg).clone()
+    order = torch.from_numpy(np.argsort(scene.tetra_id, kind="stable")).to(dev)
+    sorted_scene = synth.sort_scene_by_tet(scene)
+    assert (np.diff(sorted_scene.tetra_id) >= 0).all() and sorted_scene.N == scene.N
+    av2 = training.Avatar(sorted_scene, dev)
+    tot2 = training.multi_view_step(av2, bank, ids, w, bg).clone()
+    assert abs(float(tot2) - float(tot)) <= 2e-5 * abs(float(tot))
+    assert rel(av2.tetpoints.grad, avatar.tetpoints.grad) < 1e-4
+    for name in ("barys", "scales", "rotation", "opacity", "colors"):
+        assert rel(getattr(av2, name).grad, getattr(avatar, name).grad[order]) < 1e-4, name
