@@ -294,7 +294,10 @@ def run_ours(args):
         "depth_sort_pass_kernel": 16 * N,
         "sort_pass_kernel": 24 * D, "segment_sort_kernel": 12 * D, "tile_ranges_kernel": 8 * D + 8 * Tl, "blend_forward_kernel": 40 * D + 20 * P,
         "blend_backward_kernel": 80 * D + 20 * P, "preprocess_backward_kernel": 104 * N,
-        "deform_backward_kernel": 212 * N, "rect_grid_kernel": 12 * N, "tile_plan_kernel": 12 * Tl}
+        "deform_backward_kernel": 212 * N, "rect_grid_kernel": 12 * N, "tile_plan_kernel": 12 * Tl,
+        # direct tile scatter (raster_direct.cu): gathers + records; ids written once, straight into their final slots
+        # (the count rows and their prefix, 2-6 B x rows x tiles, are scratch traffic and not counted)
+        "direct_count_kernel": 36 * N, "direct_plan_kernel": 12 * Tl, "direct_scatter_kernel": 16 * N + 4 * D}
     peak, peak_kind = measured_peak()
     kern = {}
     for name, (tms, cnt) in prof.items():
@@ -304,6 +307,10 @@ def run_ours(args):
                           "GBps": bytes_per_launch.get(name, 0) / (avg * 1e-3) / 1e9 if avg > 0 else None}
     dominant = max(kern, key=lambda k: kern[k]["total_ms"]) if kern else None
     view_bytes = 540 * N + (148 + 24 * passes) * D + 40 * P + 8 * Tl
+    if prof.get("direct_scatter_kernel", (0, 0))[1]:
+        # no duplicate list is emitted, sorted or scanned for ranges (12 + 8 + 8 B per duplicate): the ids are written once
+        passes = 0
+        view_bytes = 540 * N + (120 + 4) * D + 40 * P + 8 * Tl
     roof = None
     traffic = None
     try:   # DRAM bytes per launch of the dominant kernel from the committed `ncu --set full` capture (profiles/)

@@ -21,6 +21,7 @@ SOURCES = [
     ("api.cu", []),
     ("raster_geometry.cu", ["-fmad=false"]),
     ("raster_sort.cu", []),
+    ("raster_direct.cu", []),
     ("raster_segsort.cu", []),
     ("raster_blend.cu", []),
     ("raster_backward.cu", []),

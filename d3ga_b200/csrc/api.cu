@@ -32,7 +32,8 @@ static const char *const g_kernel_names[K_COUNT] = {
     "depth_sort_pass_kernel", "fem_energy_forward_kernel", "fem_energy_backward_kernel",
     "ssim_forward_kernel", "ssim_backward_kernel", "lbs_skeleton_kernel", "lbs_skin_forward_kernel",
     "lbs_skin_backward_kernel", "lbs_unskin_kernel", "lbs_skin_dense_forward_kernel", "lbs_skin_dense_backward_kernel",
-    "rect_grid_kernel", "tile_plan_kernel"};
+    "rect_grid_kernel", "tile_plan_kernel", "direct_count_kernel", "direct_segsum_kernel", "direct_plan_kernel",
+    "direct_base_kernel", "direct_scatter_kernel"};
 
 bool profiling_enabled() { return g_prof_on.load(std::memory_order_relaxed) != 0; }
 
@@ -58,7 +59,8 @@ int sort_mode() {
         const char *v = getenv("D3GA_SORT_MODE");
         if (v && strcmp(v, "global") == 0) return (int)SORT_GLOBAL;
         if (v && strcmp(v, "segmented") == 0) return (int)SORT_SEGMENTED;
-        return (int)SORT_DEPTH_FIRST;
+        if (v && strcmp(v, "depthfirst") == 0) return (int)SORT_DEPTH_FIRST;
+        return (int)SORT_DIRECT;
     }();
     return mode;
 }
@@ -129,6 +131,27 @@ int d3ga_raster_workspace_bytes(int P, int W, int H, uint64_t capacity, uint64_t
     return D3GA_OK;
 }
 
+int d3ga_raster_binning_path(int P, int W, int H, uint64_t capacity) {
+    if (P < 0 || W <= 0 || H <= 0) return D3GA_EINVAL;
+    return direct_plan(P, (W + TILE - 1) / TILE, (H + TILE - 1) / TILE, capacity).ok ? 1 : 0;
+}
+
+int d3ga_raster_sorted_keys(int P, int W, int H, const void *geom, const void *binning, uint64_t capacity, const void *image,
+                            uint64_t *keys_out, d3ga_stream_t stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    if (P < 0 || W <= 0 || H <= 0 || !geom || !binning || !image || !keys_out) return D3GA_EINVAL;
+    if (capacity > MAX_DUPLICATES) return D3GA_ETOOBIG;
+    const GeomLayout GL = geom_layout(P);
+    const BinLayout BL = bin_layout(capacity);
+    const ImgLayout IL = img_layout(W, H);
+    const int gx = (W + TILE - 1) / TILE, gy = (H + TILE - 1) / TILE;
+    if (direct_plan(P, gx, gy, capacity).ok)
+        return launch_sorted_keys(gx * gy, (const uint8_t *)geom, GL, (const uint8_t *)binning, BL, (const uint8_t *)image, IL,
+                                  keys_out, stream);
+    // radix paths: the list is in one of the two key buffers; the header says which (device-side selection, no host sync)
+    return launch_copy_sorted_keys((const uint8_t *)geom, GL, (const uint8_t *)binning, BL, capacity, keys_out, stream);
+}
+
 int d3ga_raster_layout(int P, int W, int H, uint64_t capacity, uint64_t *out) {
     if (P < 0 || W <= 0 || H <= 0 || !out) return D3GA_EINVAL;
     const GeomLayout G = geom_layout(P);
@@ -180,7 +203,7 @@ int d3ga_raster_forward_render(int P, int W, int H, const float *background, con
     const ImgLayout IL = img_layout(W, H);
     const int num_tiles = ((W + TILE - 1) / TILE) * ((H + TILE - 1) / TILE);
     const int sort_bits = 32 + higher_msb((uint32_t)num_tiles);
-    int rc = launch_sort_and_ranges((uint8_t *)geom, GL, (W + TILE - 1) / TILE, (H + TILE - 1) / TILE, (uint8_t *)binning,
+    int rc = launch_sort_and_ranges(P, (uint8_t *)geom, GL, (W + TILE - 1) / TILE, (H + TILE - 1) / TILE, (uint8_t *)binning,
                                     BL, capacity, sort_bits, (uint8_t *)image, IL, num_tiles, stream);
     if (rc) return rc;
     const float *colors = colors_precomp ? colors_precomp : reinterpret_cast<const float *>((uint8_t *)geom + GL.rgb);

@@ -1,6 +1,7 @@
 // common.cuh -- shared declarations of libd3ga_b200 (sm_100a).  Host + device.
 #pragma once
 #include <cuda_runtime.h>
+#include <stddef.h>
 #include <stdint.h>
 
 #include "../../include/d3ga_b200.h"
@@ -40,13 +41,19 @@ struct RasterHeader {          // first 256 bytes of the geom workspace; zeroed 
     uint32_t dep_skip[4];
     uint32_t dep_src[4];
     uint32_t dep_ticket[4];
-    uint32_t pad1[64 - 9 - 3 * SORT_MAX_PASSES - 3 - 12];
+    // direct tile scatter (raster_direct.cu)
+    uint64_t direct_total;     // duplicates counted so far by the count rows
+    uint32_t direct_done;      // rows of direct_count_kernel that have finished (the last one publishes num_rendered)
+    uint32_t pad1[64 - 9 - 3 * SORT_MAX_PASSES - 3 - 12 - 3];
 };
+static_assert(offsetof(RasterHeader, direct_total) % 8 == 0, "64-bit counter must be aligned");
 static_assert(sizeof(RasterHeader) == 256, "header is 256 bytes");
 
 struct GeomLayout {
     uint64_t header, depth, xy, conic_opacity, rgb, cov3D, tiles, offsets, clamped, scan_state;
     uint64_t rect_pack, dkeys, dvals, dep_hist, dep_bins, dep_state, tile_diff, total;   // depth-first binning
+    uint64_t ordered;    // direct tile scatter: the Gaussians' packed records in depth order (16 B each)
+    uint64_t grec;       // ... and in Gaussian order, as the preprocess wrote them
     uint64_t p_pad;
 };
 struct BinLayout {
@@ -80,6 +87,8 @@ inline GeomLayout geom_layout(int P) {
     L.dep_bins = o;      o = align256(o + 4 * 256 * 4);
     L.dep_state = o;     o = align256(o + 4ull * 256 * 4 * ((p + SORT_TILE - 1) / SORT_TILE + 1));
     L.tile_diff = o;     o = align256(o + 4ull * TILE_GRID_CELLS_MAX);   // 2-D difference grid of the tile rects
+    L.ordered = o;       o = align256(o + 16 * L.p_pad);
+    L.grec = o;          o = align256(o + 16 * L.p_pad);
     L.total = o;
     return L;
 }
@@ -122,7 +131,8 @@ constexpr int GRAD_ACC_FLOATS = 12;
 enum KernelId {
     K_GEOMETRY = 0, K_SORT_HIST, K_SORT_PASS, K_RANGES, K_BLEND_FWD, K_BLEND_BWD, K_PRE_BWD, K_DEFORM_FWD, K_DEFORM_BWD,
     K_BARY, K_SEG_SORT, K_PREPROCESS, K_EMIT, K_DEPTH_HIST, K_DEPTH_PASS, K_FEM_FWD, K_FEM_BWD, K_SSIM_FWD, K_SSIM_BWD,
-    K_LBS_SKELETON, K_LBS_SKIN_FWD, K_LBS_SKIN_BWD, K_LBS_UNSKIN, K_LBS_DENSE_FWD, K_LBS_DENSE_BWD, K_RECT_GRID, K_TILE_PLAN, K_COUNT
+    K_LBS_SKELETON, K_LBS_SKIN_FWD, K_LBS_SKIN_BWD, K_LBS_UNSKIN, K_LBS_DENSE_FWD, K_LBS_DENSE_BWD, K_RECT_GRID, K_TILE_PLAN,
+    K_DIRECT_COUNT, K_DIRECT_SEGSUM, K_DIRECT_PLAN, K_DIRECT_BASE, K_DIRECT_SCATTER, K_COUNT
 };
 // Optional per-kernel CUDA-event timing (d3ga_profile_* in the C-ABI; bench.py's roofline figures come from it).
 // A no-op unless profiling is enabled.
@@ -154,11 +164,31 @@ int launch_geometry(int P, int sh_degree, int sh_coeffs, const float *means3D, c
                     const float *projmatrix, const float *campos, int W, int H, float tanfovx, float tanfovy,
                     int antialiasing, uint8_t *geom, const GeomLayout &GL, uint8_t *binning, const BinLayout &BL,
                     uint64_t capacity, int32_t *radii, cudaStream_t stream);
-int launch_sort_and_ranges(uint8_t *geom, const GeomLayout &GL, int gx, int gy, uint8_t *binning, const BinLayout &BL, uint64_t capacity, int sort_bits,
+int launch_sort_and_ranges(int P, uint8_t *geom, const GeomLayout &GL, int gx, int gy, uint8_t *binning, const BinLayout &BL, uint64_t capacity, int sort_bits,
                            uint8_t *image, const ImgLayout &IL, int num_tiles, cudaStream_t stream);
 int launch_depth_sort(int P, uint8_t *geom, const GeomLayout &GL, cudaStream_t stream);
-enum SortMode { SORT_DEPTH_FIRST = 0, SORT_GLOBAL = 1, SORT_SEGMENTED = 2 };
-int sort_mode();   // D3GA_SORT_MODE = depthfirst (default) | global | segmented
+enum SortMode { SORT_DEPTH_FIRST = 0, SORT_GLOBAL = 1, SORT_SEGMENTED = 2, SORT_DIRECT = 3 };
+int sort_mode();   // D3GA_SORT_MODE = direct (default) | depthfirst | global | segmented
+// the two modes that sort the Gaussians by depth first; `direct` falls back to `depthfirst` where its plan does not apply
+inline bool depth_first_mode(int mode) { return mode == SORT_DEPTH_FIRST || mode == SORT_DIRECT; }
+// Direct tile scatter (raster_direct.cu): rows of `chunk` depth-ordered Gaussians, one private tile histogram per row.
+constexpr int DIRECT_MAX_TILES = 6144;    // 8 B x tiles of shared memory per row in the scatter: at least four rows per SM
+constexpr int DIRECT_MAX_CHUNK = 8192;    // a (row, tile) count must fit 16 bits
+struct DirectPlan {
+    int ok;                    // 0: not applicable (mode, tile grid too large, capacity too small for the scratch)
+    uint32_t chunk, rows, tl_pad, nseg, rows_per_seg, colblocks;
+    uint64_t seg_off, tot_off, start_off, ticket_off, before_off;   // byte offsets inside the unused key buffer
+};
+DirectPlan direct_plan(int P, int gx, int gy, uint64_t capacity);
+int launch_direct_count(int P, int gx, int gy, uint8_t *geom, const GeomLayout &GL, uint8_t *binning, const BinLayout &BL,
+                        uint64_t capacity, const DirectPlan &pl, cudaStream_t stream);
+int launch_sorted_keys(int num_tiles, const uint8_t *geom, const GeomLayout &GL, const uint8_t *binning, const BinLayout &BL,
+                       const uint8_t *image, const ImgLayout &IL, uint64_t *keys_out, cudaStream_t stream);
+int launch_copy_sorted_keys(const uint8_t *geom, const GeomLayout &GL, const uint8_t *binning, const BinLayout &BL,
+                            uint64_t capacity, uint64_t *keys_out, cudaStream_t stream);
+int launch_direct_scatter(int P, int gx, int gy, uint8_t *geom, const GeomLayout &GL, uint8_t *binning, const BinLayout &BL,
+                          uint64_t capacity, int sort_bits, uint8_t *image, const ImgLayout &IL, const DirectPlan &pl,
+                          cudaStream_t stream);
 int launch_segment_sort(uint8_t *geom, uint8_t *binning, const BinLayout &BL, uint8_t *image, const ImgLayout &IL,
                         int num_tiles, cudaStream_t stream);
 int launch_blend_forward(int W, int H, const float *background, const float *colors, const uint8_t *geom,

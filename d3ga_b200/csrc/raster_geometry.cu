@@ -71,6 +71,7 @@ struct GeoParams {
     uint32_t *dkeys, *dvals;   // [2][P_pad] ping-pong of the 32-bit depth sort
     uint32_t P_pad;
     int32_t *tile_diff;    // [(gy+1)][(gx+1)] +1/-1 at the rect corners (null: grid too large, counts come from the keys)
+    uint4 *grec;           // direct tile scatter: [P] x0 | y0 << 16, width | height << 16, Gaussian id, depth bits (else null)
 };
 
 constexpr uint64_t FLAG_AGG = 1ull << 62, FLAG_INC = 2ull << 62, FLAG_MASK = 3ull << 62;
@@ -352,6 +353,7 @@ __global__ void __launch_bounds__(GEO_THREADS) preprocess_kernel(const GeoParams
     uint32_t count, rect, width, dbits;
     preprocess_one(p, idx, s_view, s_proj, s_cam, count, rect, width, dbits);
     p.rect_pack[idx] = make_uint2(rect, width);
+    if (p.grec) p.grec[idx] = make_uint4(rect, count ? (width | ((count / width) << 16)) : 0u, (uint32_t)idx, dbits);
     p.dkeys[idx] = count ? dbits : 0xffffffffu;
     p.dvals[idx] = (uint32_t)idx;
 }
@@ -450,12 +452,14 @@ int launch_geometry(int P, int sh_degree, int sh_coeffs, const float *means3D, c
     p.dvals = reinterpret_cast<uint32_t *>(geom + GL.dvals);
     p.P_pad = (uint32_t)GL.p_pad;
     p.tile_diff = nullptr;
-    if (sort_mode() == SORT_DEPTH_FIRST && tile_plan_from_grid(p.gx, p.gy)) {
+    const DirectPlan direct = direct_plan(P, p.gx, p.gy, capacity);
+    p.grec = direct.ok ? reinterpret_cast<uint4 *>(geom + GL.grec) : nullptr;
+    if (depth_first_mode(sort_mode()) && !direct.ok && tile_plan_from_grid(p.gx, p.gy)) {
         p.tile_diff = reinterpret_cast<int32_t *>(geom + GL.tile_diff);
         D3GA_CUDA(cudaMemsetAsync(p.tile_diff, 0, 4ull * (p.gx + 1) * (p.gy + 1), stream));
     }
     if (p.num_ctas == 0) return D3GA_OK;
-    if (sort_mode() != SORT_DEPTH_FIRST) {
+    if (!depth_first_mode(sort_mode())) {
         ProfScope prof(K_GEOMETRY, stream);
         geometry_kernel<<<p.num_ctas, GEO_THREADS, 0, stream>>>(p);
         D3GA_LAUNCH_CHECK();
@@ -474,6 +478,8 @@ int launch_geometry(int P, int sh_degree, int sh_coeffs, const float *means3D, c
     }
     int rc = launch_depth_sort(P, geom, GL, stream);
     if (rc) return rc;
+    // direct tile scatter: count rows instead of an emission; the duplicates are written once, in stage 2
+    if (direct.ok) return launch_direct_count(P, p.gx, p.gy, geom, GL, binning, BL, capacity, direct, stream);
     {
         ProfScope prof(K_EMIT, stream);
         emit_sorted_kernel<<<p.num_ctas, GEO_THREADS, 0, stream>>>(p);

@@ -457,7 +457,7 @@ __global__ void __launch_bounds__(256) tile_ranges_kernel(RasterHeader *hdr, con
 
 static int g_sort_attr_set = 0;
 
-int launch_sort_and_ranges(uint8_t *geom, const GeomLayout &GL, int gx, int gy, uint8_t *binning, const BinLayout &BL, uint64_t capacity, int sort_bits,
+int launch_sort_and_ranges(int P, uint8_t *geom, const GeomLayout &GL, int gx, int gy, uint8_t *binning, const BinLayout &BL, uint64_t capacity, int sort_bits,
                            uint8_t *image, const ImgLayout &IL, int num_tiles, cudaStream_t stream) {
     RasterHeader *hdr = reinterpret_cast<RasterHeader *>(geom);
     uint64_t *keys0 = reinterpret_cast<uint64_t *>(binning + BL.keys0);
@@ -477,6 +477,10 @@ int launch_sort_and_ranges(uint8_t *geom, const GeomLayout &GL, int gx, int gy, 
     const int mode = sort_mode();
     const bool segmented = mode == SORT_SEGMENTED;
     const int first_pass = mode == SORT_GLOBAL ? 0 : 4;
+    // direct (default): no sort of the duplicates at all -- a stable counting scatter by tile (raster_direct.cu)
+    const DirectPlan direct = direct_plan(P, gx, gy, capacity);
+    if (direct.ok)
+        return launch_direct_scatter(P, gx, gy, geom, GL, binning, BL, capacity, sort_bits, image, IL, direct, stream);
 
     if (!g_sort_attr_set) {
         D3GA_CUDA(cudaFuncSetAttribute(sort_pass_kernel<uint64_t, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -491,7 +495,7 @@ int launch_sort_and_ranges(uint8_t *geom, const GeomLayout &GL, int gx, int gy, 
 
     // depth-first with a tile grid small enough for the rect difference grid: the plan comes from the per-tile counts, no
     // histogram pass over the keys before and no ranges pass after the sort
-    const bool from_grid = mode == SORT_DEPTH_FIRST && tile_plan_from_grid(gx, gy);
+    const bool from_grid = depth_first_mode(mode) && tile_plan_from_grid(gx, gy);
     if (from_grid) {
         static const int attr_set = [] {
             cudaFuncSetAttribute(tile_plan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 8 * TILE_GRID_CELLS_MAX);

@@ -70,6 +70,23 @@ int d3ga_profile_collect(double *ms, uint64_t *launches);
 int d3ga_raster_workspace_bytes(int P, int W, int H, uint64_t capacity,
                                 uint64_t *geom_bytes, uint64_t *binning_bytes, uint64_t *image_bytes);
 
+/* Which binning strategy the two forward stages will use for these sizes (measurement and tests; no counterpart in the
+ * reference): 1 = direct tile scatter (the default where it applies: the N Gaussians are sorted by depth, stage 1 only
+ * COUNTS the duplicates per tile, stage 2 stores every duplicate once, straight into its final slot of the sorted list --
+ * no unsorted duplicate list exists after stage 1); 0 = a radix sort of the duplicate list that stage 1 emitted
+ * (D3GA_SORT_MODE=depthfirst|global|segmented, tile grids beyond 6144 tiles, or a capacity too small to hold the
+ * scatter's count rows).  Either way the sorted list, the ranges and num_rendered are bit-identical. */
+int d3ga_raster_binning_path(int P, int W, int H, uint64_t capacity);
+
+/* The sorted (tile << 32 | depth bits) key list of the last forward -- upstream's binningBuffer keys after
+ * cub::DeviceRadixSort::SortPairs -- written to keys_out [num_rendered] (device memory, caller-owned).  Call after
+ * d3ga_raster_forward_render.  The radix paths copy the list they sorted; the direct tile scatter never stores keys (the
+ * blend reads Gaussian ids and ranges only, and 8 scattered bytes per duplicate cost more than the rest of the scatter),
+ * so there the list is rebuilt from what defines it: slot i of tile t's range holds (t << 32) | bits(depth[id[i]]).
+ * Used by the parity tests (bit-exact against the oracle's sorted keys) and for inspection. */
+int d3ga_raster_sorted_keys(int P, int W, int H, const void *geom, const void *binning, uint64_t capacity,
+                            const void *image, uint64_t *keys_out, d3ga_stream_t stream);
+
 /* Stage 1 = preprocess (R1) + scan (R2) + key duplication (R3), one fused kernel.
  * Exactly one of {cov3D_precomp} / {scales, rotations} and one of {colors_precomp} / {shs} is non-null.
  * radii [P] int32 is an output (the second element of the tuple GaussianRasterizer returns).

@@ -44,6 +44,8 @@ def forward_stages(g, cam, W, H, bg, path="precomp", aa=False, capacity=None, in
     lay = _lib.raster_layout(P, W, H, cap)
     D, overflow = int(host[0]) & 0xFFFFFFFF, int(host[1])
     out = dict(P=P, num_rendered=D, overflow=overflow, capacity=cap, radii=radii[:P].cpu().numpy(), layout=lay)
+    # 1 = direct tile scatter: stage 1 only counts, there is no unsorted duplicate list and no per-Gaussian offsets
+    out["direct"] = int(lib.d3ga_raster_binning_path(P, W, H, cap)) == 1
     out["depths"] = section(geom, lay["geom_depth"], P, np.float32)
     out["xy"] = section(geom, lay["geom_xy"], 2 * P, np.float32).reshape(P, 2)
     out["conic_opacity"] = section(geom, lay["geom_conic_opacity"], 4 * P, np.float32).reshape(P, 4)
@@ -69,7 +71,11 @@ def forward_stages(g, cam, W, H, bg, path="precomp", aa=False, capacity=None, in
     hdr = section(geom, lay["geom_header"], 64, np.uint32)
     out["header"] = hdr
     sel = int(hdr[3])
-    out["keys"] = section(binning, lay["bin_keys1" if sel else "bin_keys0"], D, np.uint64)
+    keys = torch.zeros(max(D, 1), dtype=torch.int64, device="cuda")
+    _lib.check(lib.d3ga_raster_sorted_keys(P, W, H, geom.data_ptr(), binning.data_ptr(), cap, image.data_ptr(),
+                                           keys.data_ptr(), stream), "sorted_keys")
+    torch.cuda.synchronize()
+    out["keys"] = keys[:D].cpu().numpy().view(np.uint64).copy()
     out["point_list"] = section(binning, lay["bin_vals1" if sel else "bin_vals0"], D, np.uint32)
     tiles = ((W + 15) // 16) * ((H + 15) // 16)
     out["ranges"] = section(image, lay["img_ranges"], 2 * tiles, np.uint32).reshape(tiles, 2)
