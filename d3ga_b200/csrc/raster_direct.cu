@@ -171,9 +171,6 @@ __device__ DIRECT_INLINE void scatter_batch(const DirectParams &p, ScatterWarp &
         t0[r] = v & 0xffffu; sn[r] = (v >> 16) & 0x7ffu; src[r] = v >> 27;
         wm[r] = (uint32_t)r * 32 < total ? __reduce_max_sync(0xffffffffu, sn[r]) : 0u;
     }
-#ifdef DIRECT_DEBUG_NOWALK
-    if (total != 0xfffffff0u) return;
-#endif
 #pragma unroll
     for (int r = 0; r < STRIP_ROUNDS; r++)
         for (uint32_t k = 0; k < wm[r]; k++)
@@ -188,9 +185,6 @@ __device__ DIRECT_INLINE void scatter_batch(const DirectParams &p, ScatterWarp &
             if (k < sn[r]) {
                 const uint2 v = pm[t0[r] + k];
                 const uint32_t dst = v.x + (uint32_t)__popc(v.y & lower);
-#ifdef DIRECT_DEBUG_NOSTORE
-                if (dst == 0xfffffff0u)
-#endif
                 p.vals[dst] = id;
             }
         }
@@ -233,16 +227,8 @@ __global__ void __launch_bounds__(SC_WARPS * 32) direct_scatter_kernel(const Dir
         const uint32_t s = slot0 + b * 32 + lane;
         return (b < nb && s < (uint32_t)p.P) ? p.rec[s] : make_uint4(0, 0, 0, 0);
     };
-#ifdef DIRECT_DEBUG_NOLOOP
-    if (row != 0xfffffff0u) return;
-#endif
     uint32_t qh = 0, qn = 0;   // the FIFO's head and fill (warp-uniform)
-    // records: two batches ahead in registers, the lines of six batches ahead on their way into L1
-    auto prefetch = [&](uint32_t b) {
-        const uint32_t s = slot0 + b * 32 + lane;
-        if (b < nb && s < (uint32_t)p.P) asm volatile("prefetch.global.L1 [%0];" ::"l"(p.rec + s));
-    };
-    for (uint32_t b = 2; b < 6; b++) prefetch(b);
+    // records: two batches ahead in registers (an L1 prefetch further ahead was measured: no gain)
     uint4 rec_a = load(0), rec_b = load(1), rec = make_uint4(0, 0, 0, 0);
     uint32_t b = 0, first = 0, c = 0;
     uint32_t rest = 0, i0 = 0;   // lanes of the current batch that still have entries to queue (the rare tall rects)
@@ -271,7 +257,6 @@ __global__ void __launch_bounds__(SC_WARPS * 32) direct_scatter_kernel(const Dir
             rec = rec_a;
             rec_a = rec_b;
             rec_b = load(b + 2);
-            prefetch(b + 6);
             b++;
             // the blocks of tile rows this lane's rect spans, and those of them that are this warp's
             const uint32_t w = rec.y & 0xffffu, h = rec.y >> 16, y0 = rec.x >> 16, y1 = y0 + h;

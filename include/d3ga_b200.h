@@ -87,7 +87,8 @@ int d3ga_raster_binning_path(int P, int W, int H, uint64_t capacity);
 int d3ga_raster_sorted_keys(int P, int W, int H, const void *geom, const void *binning, uint64_t capacity,
                             const void *image, uint64_t *keys_out, d3ga_stream_t stream);
 
-/* Stage 1 = preprocess (R1) + scan (R2) + key duplication (R3), one fused kernel.
+/* Stage 1 = preprocess (R1) + scan (R2) + key duplication (R3); with the direct tile scatter: preprocess, depth sort of
+ * the Gaussians and the per-tile counts (which give num_rendered).
  * Exactly one of {cov3D_precomp} / {scales, rotations} and one of {colors_precomp} / {shs} is non-null.
  * radii [P] int32 is an output (the second element of the tuple GaussianRasterizer returns).
  * num_rendered_host: pinned HOST memory, 2 x uint32, may be null. */
@@ -100,7 +101,8 @@ int d3ga_raster_forward_geometry(int P, int sh_degree, int sh_coeffs,
                                  void *geom, void *binning, uint64_t capacity,
                                  int32_t *radii, uint32_t *num_rendered_host, d3ga_stream_t stream);
 
-/* Stage 2 = radix sort (R4) + tile ranges (R5) + alpha blending (R6).  out_invdepth may be null. */
+/* Stage 2 = sort (R4) + tile ranges (R5) + alpha blending (R6); with the direct tile scatter R2-R5 are the offsets from
+ * stage 1's per-tile counts and one store of every duplicate into its final slot.  out_invdepth may be null. */
 int d3ga_raster_forward_render(int P, int W, int H, const float *background, const float *colors_precomp,
                                void *geom, void *binning, uint64_t capacity, void *image,
                                float *out_color, float *out_invdepth, d3ga_stream_t stream);
@@ -172,12 +174,15 @@ enum {
     D3GA_L_GEOM_RGB,        /* float  [P,3] (SH path; the colors_precomp path reads the caller's tensor)   */
     D3GA_L_GEOM_COV3D,      /* float  [P,6] (scales/rotations path)                                        */
     D3GA_L_GEOM_TILES,      /* uint32 [P] tiles touched                                                    */
-    D3GA_L_GEOM_OFFSETS,    /* uint32 [P] inclusive prefix sum of tiles touched, in emission order         */
+    D3GA_L_GEOM_OFFSETS,    /* uint32 [P] inclusive prefix sum of tiles touched, in emission order (radix paths)*/
     D3GA_L_GEOM_CLAMPED,    /* uint8  [P,3]                                                                */
-    D3GA_L_BIN_KEYS0,       /* uint64 [capacity]  unsorted keys after stage 1 (emission order: by depth in the
-                             * default depth-first binning, by Gaussian index with D3GA_SORT_MODE=global)   */
+    D3GA_L_BIN_KEYS0,       /* uint64 [capacity]  radix paths (d3ga_raster_binning_path() == 0): unsorted keys after
+                             * stage 1 (emission order: by depth with D3GA_SORT_MODE=depthfirst, by Gaussian index
+                             * with =global); the header's final_sel word says which buffer holds the sorted list.
+                             * Direct tile scatter: not written -- use d3ga_raster_sorted_keys()              */
     D3GA_L_BIN_KEYS1,       /* uint64 [capacity]                                                           */
-    D3GA_L_BIN_VALS0,       /* uint32 [capacity]  unsorted Gaussian indices after stage 1                  */
+    D3GA_L_BIN_VALS0,       /* uint32 [capacity]  radix paths: unsorted Gaussian indices after stage 1; direct tile
+                             * scatter: the sorted indices after stage 2                                     */
     D3GA_L_BIN_VALS1,       /* uint32 [capacity]                                                           */
     D3GA_L_IMG_RANGES,      /* uint2  [tiles]                                                              */
     D3GA_L_IMG_FINAL_T,     /* float  [H*W]                                                                */
