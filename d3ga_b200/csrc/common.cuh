@@ -172,11 +172,13 @@ int sort_mode();   // D3GA_SORT_MODE = direct (default) | depthfirst | global | 
 // the two modes that sort the Gaussians by depth first; `direct` falls back to `depthfirst` where its plan does not apply
 inline bool depth_first_mode(int mode) { return mode == SORT_DEPTH_FIRST || mode == SORT_DIRECT; }
 // Direct tile scatter (raster_direct.cu): rows of `chunk` depth-ordered Gaussians, one private tile histogram per row.
-constexpr int DIRECT_MAX_TILES = 6144;    // 8 B x tiles of shared memory per row in the scatter: at least four rows per SM
+constexpr int DIRECT_MAX_TILES = 49152;   // the plan CTA keeps 4 B per tile in shared memory
+constexpr int DIRECT_MAX_CELLS = 53248;   // (gx+1)(gy+1): the count CTA's difference grid, 4 B per cell (208 KB)
 constexpr int DIRECT_MAX_CHUNK = 8192;    // a (row, tile) count must fit 16 bits
 struct DirectPlan {
     int ok;                    // 0: not applicable (mode, tile grid too large, capacity too small for the scratch)
     uint32_t chunk, rows, tl_pad, nseg, rows_per_seg, colblocks;
+    uint32_t bands, band_rows, band_tiles_pad;   // the scatter's split of the image into bands of tile rows
     uint64_t seg_off, tot_off, start_off, ticket_off, before_off;   // byte offsets inside the unused key buffer
 };
 DirectPlan direct_plan(int P, int gx, int gy, uint64_t capacity);

@@ -28,8 +28,9 @@
 // (each 12 B load + MATCH-based ranking + 12 B store) before; a row is independent of every other row and nothing looks
 // back at a predecessor.  Algorithmic bytes: 36 N (gathers + records) + 2 R Tl (count rows) in (1), 16 N + 6 R Tl + 12 D in (5).
 // Scratch (M, segment sums) lives in the second halves of the binning workspace's key / value ping-pong, which this path
-// does not use.  The row length is chosen so that the rows fill the GPU once (8 B x tiles of shared memory per row); the
-// path is not taken (the radix sort runs instead) for tile grids beyond DIRECT_MAX_TILES or when the scratch does not fit.
+// does not use.  The row length is chosen so that the rows fill the GPU once (8 B x tiles of shared memory per row; larger
+// images are cut into bands of tile rows); the path is not taken (the radix sort runs instead) for tile grids beyond
+// DIRECT_MAX_TILES or when the scratch does not fit.
 #include <cstdlib>
 
 #include "common.cuh"
@@ -40,6 +41,7 @@ namespace {
 
 constexpr int COL_THREADS = 256;       // tile pairs per CTA in the column kernels
 constexpr int DIRECT_MAX_SEGS = 32;
+constexpr uint64_t SCATTER_SMEM_BUDGET = 36 * 1024;
 
 struct DirectParams {
     RasterHeader *hdr;
@@ -202,16 +204,22 @@ __device__ DIRECT_INLINE void scatter_batch(const DirectParams &p, ScatterWarp &
     __syncwarp();
 }
 
-__global__ void __launch_bounds__(SC_WARPS * 32) direct_scatter_kernel(const DirectParams p, int gy) {
+__global__ void __launch_bounds__(SC_WARPS * 32) direct_scatter_kernel(const DirectParams p, int gy, int band_rows) {
     extern __shared__ __align__(16) uint8_t smem[];
     __shared__ ScatterWarp s_warp[SC_WARPS];
     const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, row = blockIdx.x;
     if (p.hdr->overflow) return;
-    uint2 *pm = reinterpret_cast<uint2 *>(smem);   // [tl_pad] x: next free slot of the tile's run, y: owners of the batch on it
+    // this CTA's band of tile rows [yb0, yb1) (the whole image when it fits the shared memory budget); tiles, tile rows
+    // and blocks below are relative to the band
+    const uint32_t gx = (uint32_t)p.gx, yb0 = blockIdx.y * (uint32_t)band_rows, yb1 = min((uint32_t)gy, yb0 + (uint32_t)band_rows);
+    const uint32_t tbase = yb0 * gx, ntiles = (yb1 - yb0) * gx;
+    uint2 *pm = reinterpret_cast<uint2 *>(smem);   // [tiles of the band] x: next free slot of the tile's run, y: owners of the batch on it
     {
-        const uint4 *srow = reinterpret_cast<const uint4 *>(p.seg + (size_t)(row / p.rows_per_seg) * p.tl_pad);
-        const uint2 *mrow = reinterpret_cast<const uint2 *>(p.before + (size_t)row * p.tl_pad);
-        for (uint32_t i = tid; i < p.tl_pad / 4; i += SC_WARPS * 32) {
+        // (tbase is a multiple of 4: bands start on a multiple of 16 tile rows; reads past the band's last tile stay
+        // inside the rows' tl_pad)
+        const uint4 *srow = reinterpret_cast<const uint4 *>(p.seg + (size_t)(row / p.rows_per_seg) * p.tl_pad + tbase);
+        const uint2 *mrow = reinterpret_cast<const uint2 *>(p.before + (size_t)row * p.tl_pad + tbase);
+        for (uint32_t i = tid; i < (ntiles + 3) / 4; i += SC_WARPS * 32) {
             const uint4 v = __ldg(srow + i);
             const uint2 m = __ldg(mrow + i);
             uint4 *o = reinterpret_cast<uint4 *>(pm + 4 * i);
@@ -220,7 +228,7 @@ __global__ void __launch_bounds__(SC_WARPS * 32) direct_scatter_kernel(const Dir
         }
     }
     __syncthreads();
-    if (warp << BLK_SHIFT >= (uint32_t)gy) return;   // fewer blocks of tile rows than warps
+    if (warp << BLK_SHIFT >= yb1 - yb0) return;   // fewer blocks of tile rows than warps
     ScatterWarp &sw = s_warp[warp];
     const uint32_t slot0 = row * p.chunk, nb = p.chunk / 32, below = (1u << lane) - 1u;
     auto load = [&](uint32_t b) {
@@ -230,27 +238,27 @@ __global__ void __launch_bounds__(SC_WARPS * 32) direct_scatter_kernel(const Dir
     uint32_t qh = 0, qn = 0;   // the FIFO's head and fill (warp-uniform)
     // records: two batches ahead in registers (an L1 prefetch further ahead was measured: no gain)
     uint4 rec_a = load(0), rec_b = load(1), rec = make_uint4(0, 0, 0, 0);
-    uint32_t b = 0, first = 0, c = 0;
-    uint32_t rest = 0, i0 = 0;   // lanes of the current batch that still have entries to queue (the rare tall rects)
+    uint32_t b = 0;
+    uint32_t ya = 0, yb = 0, first = 0, last = 0, c = 0;   // this lane's rect inside the band: tile rows, this warp's blocks
+    uint32_t kcur = 1, kend = 0;   // blocks of the current batch still to be queued (tall rects only)
+    auto enqueue = [&](uint32_t mask, bool mine, uint32_t blk) {   // one entry per lane of `mask`, in lane order
+        if (mine) {
+            const uint32_t y0e = max(ya, blk << BLK_SHIFT), y1e = min(yb, (blk + 1) << BLK_SHIFT);
+            sw.queue[(qh + qn + (uint32_t)__popc(mask & below)) & (QUEUE - 1)] =
+                make_uint4((rec.x & 0xffffu) | (y0e << 16), (rec.y & 0xffffu) | ((y1e - y0e) << 16), rec.z, rec.w);
+        }
+        qn += (uint32_t)__popc(mask);
+        __syncwarp();
+    };
     for (;;) {
         while (qn < 32) {
-            if (rest) {
-                // a rect that spans several of this warp's blocks: lane by lane (depth order), 32 entries at a time
-                const int L = __ffs(rest) - 1;
-                const uint32_t cL = __shfl_sync(0xffffffffu, c, L), fL = __shfl_sync(0xffffffffu, first, L);
-                const uint32_t rx = __shfl_sync(0xffffffffu, rec.x, L), ry = __shfl_sync(0xffffffffu, rec.y, L);
-                const uint32_t rz = __shfl_sync(0xffffffffu, rec.z, L), rw = __shfl_sync(0xffffffffu, rec.w, L);
-                const uint32_t Y0 = rx >> 16, Y1 = Y0 + (ry >> 16), i = i0 + lane;
-                if (i < cL) {
-                    const uint32_t blk = fL + i * SC_WARPS;
-                    const uint32_t ya = max(Y0, blk << BLK_SHIFT), yb = min(Y1, (blk + 1) << BLK_SHIFT);
-                    sw.queue[(qh + qn + lane) & (QUEUE - 1)] =
-                        make_uint4((rx & 0xffffu) | (ya << 16), (ry & 0xffffu) | ((yb - ya) << 16), rz, rw);
-                }
-                qn += min(32u, cL - i0);
-                i0 += 32;
-                if (i0 >= cL) { rest &= rest - 1; i0 = 0; }
-                __syncwarp();
+            if (kcur <= kend) {
+                // rects that span several of this warp's blocks: block by block.  Entries that can share a tile lie in
+                // the same block, so inside every block they are queued in lane order = depth order.
+                const bool mine = c && first <= kcur && kcur <= last;
+                const uint32_t m = __ballot_sync(0xffffffffu, mine);
+                if (m) enqueue(m, mine, kcur);
+                kcur += SC_WARPS;
                 continue;
             }
             if (b >= nb) break;
@@ -258,25 +266,25 @@ __global__ void __launch_bounds__(SC_WARPS * 32) direct_scatter_kernel(const Dir
             rec_a = rec_b;
             rec_b = load(b + 2);
             b++;
-            // the blocks of tile rows this lane's rect spans, and those of them that are this warp's
-            const uint32_t w = rec.y & 0xffffu, h = rec.y >> 16, y0 = rec.x >> 16, y1 = y0 + h;
-            first = 0; c = 0;
-            if (w && h) {
-                const uint32_t blk0 = y0 >> BLK_SHIFT, blk1 = (y1 - 1) >> BLK_SHIFT;
+            // the lane's rect clipped to the band, the blocks of tile rows it spans, and those of them that are this warp's
+            const uint32_t w = rec.y & 0xffffu, y0 = rec.x >> 16, y1 = y0 + (rec.y >> 16);
+            ya = max(y0, yb0); yb = min(y1, yb1);
+            c = 0;
+            if (w && yb > ya) {
+                ya -= yb0; yb -= yb0;
+                const uint32_t blk0 = ya >> BLK_SHIFT, blk1 = (yb - 1) >> BLK_SHIFT;
                 first = blk0 + ((warp - blk0) & (SC_WARPS - 1));
-                c = first <= blk1 ? (blk1 - first) / SC_WARPS + 1 : 0u;
+                if (first <= blk1) { c = (blk1 - first) / SC_WARPS + 1; last = first + (c - 1) * SC_WARPS; }
             }
             const uint32_t any = __ballot_sync(0xffffffffu, c > 0);
             if (!any) continue;
-            if (__ballot_sync(0xffffffffu, c > 1)) { rest = any; i0 = 0; continue; }
-            // at most one entry per lane (rects under 13 tile rows: practically always): queue them in lane order
-            if (c) {
-                const uint32_t ya = max(y0, first << BLK_SHIFT), yb = min(y1, (first + 1) << BLK_SHIFT);
-                sw.queue[(qh + qn + (uint32_t)__popc(any & below)) & (QUEUE - 1)] =
-                    make_uint4((rec.x & 0xffffu) | (ya << 16), w | ((yb - ya) << 16), rec.z, rec.w);
+            if (__ballot_sync(0xffffffffu, c > 1)) {
+                kcur = __reduce_min_sync(0xffffffffu, c ? first : 0xffffffffu);
+                kend = __reduce_max_sync(0xffffffffu, c ? last : 0u);
+                continue;
             }
-            qn += (uint32_t)__popc(any);
-            __syncwarp();
+            // at most one entry per lane (rects under 13 tile rows: practically always at 1024^2)
+            enqueue(any, c != 0, first);
         }
         if (qn == 0) break;
         const uint32_t n = min(qn, 32u);
@@ -431,7 +439,7 @@ DirectParams make_params(int P, int gx, uint8_t *geom, const GeomLayout &GL, uin
 int set_smem_attrs() {
     static int done = 0;
     if (done) return D3GA_OK;
-    const int scatter = 8 * DIRECT_MAX_TILES, plan = 4 * DIRECT_MAX_TILES, count = 4 * 2 * (DIRECT_MAX_TILES + 2);
+    const int scatter = 200 * 1024, plan = 4 * DIRECT_MAX_TILES, count = 4 * DIRECT_MAX_CELLS;
     D3GA_CUDA(cudaFuncSetAttribute(direct_count_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, count));
     D3GA_CUDA(cudaFuncSetAttribute(direct_scatter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, scatter));
     D3GA_CUDA(cudaFuncSetAttribute(direct_plan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, plan));
@@ -444,19 +452,36 @@ int set_smem_attrs() {
 DirectPlan direct_plan(int P, int gx, int gy, uint64_t capacity) {
     DirectPlan pl = {};
     const uint64_t tl = (uint64_t)gx * gy, cap = capacity < 1 ? 1 : capacity;
-    if (sort_mode() != SORT_DIRECT || P < 1 || tl < 1 || tl > DIRECT_MAX_TILES || gx > 2047) return pl;
+    if (sort_mode() != SORT_DIRECT || P < 1 || tl < 1 || tl > DIRECT_MAX_TILES || gx > 2047 ||
+        (uint64_t)(gx + 1) * (gy + 1) > DIRECT_MAX_CELLS)
+        return pl;
     pl.tl_pad = (uint32_t)((tl + 7) & ~7ull);
     pl.colblocks = (pl.tl_pad / 2 + COL_THREADS - 1) / COL_THREADS;
-    // rows that are resident at once: 8 B x tiles of shared memory each (+1 KB the hardware reserves per CTA), 228 KB and
-    // at most 16 of these one-warp CTAs per SM; the row length is what fills them once
-    uint64_t per_sm = (228ull * 1024) / (8ull * pl.tl_pad + 1024 + sizeof(ScatterWarp) * SC_WARPS);
+    // The scatter keeps 8 B per tile in shared memory.  Images whose tiles do not fit a ~36 KB budget (six CTAs per SM)
+    // are cut into bands of tile rows (a multiple of 16: four blocks per warp-round), one CTA per (row, band).
+    pl.band_rows = (uint32_t)gy;
+    pl.bands = 1;
+    if (8ull * pl.tl_pad > SCATTER_SMEM_BUDGET) {
+        uint64_t br = SCATTER_SMEM_BUDGET / (8ull * gx) / 16 * 16;
+        if (br < 16) br = 16;
+        if (8ull * br * gx + 64 > 200 * 1024) return pl;   // a single band of 16 tile rows does not fit: not this path
+        pl.band_rows = (uint32_t)br;
+        pl.bands = (uint32_t)((gy + br - 1) / br);
+    }
+    pl.band_tiles_pad = (uint32_t)((((uint64_t)(pl.bands > 1 ? pl.band_rows : gy) * gx) + 7) & ~7ull);
+    // CTAs that are resident at once (+1 KB the hardware reserves per CTA, 228 KB and at most 16 of these CTAs per SM);
+    // the row length is what fills them once
+    uint64_t per_sm = (228ull * 1024) / (8ull * pl.band_tiles_pad + 1024 + sizeof(ScatterWarp) * SC_WARPS);
     if (per_sm > 16) per_sm = 16;
     if (per_sm < 1) return pl;
     uint64_t chunk = chunk_override();
     if (!chunk) {
-        chunk = ((uint64_t)P + 148 * per_sm - 1) / (148 * per_sm);
+        uint64_t rows_target = 148 * per_sm / pl.bands;
+        if (rows_target < 148) rows_target = 148;
+        chunk = ((uint64_t)P + rows_target - 1) / rows_target;
         chunk = (chunk + 31) / 32 * 32;
         if (chunk < 256) chunk = 256;
+        if (chunk > DIRECT_MAX_CHUNK) chunk = DIRECT_MAX_CHUNK;
     }
     // scratch: M (2 B x rows x tiles) in the unused value buffer (4 B x capacity); segment offsets, totals, starts and
     // the column-block tickets in the unused key buffer (8 B x capacity).  Longer rows when M would not fit.
@@ -577,7 +602,7 @@ int launch_direct_scatter(int P, int gx, int gy, uint8_t *geom, const GeomLayout
     D3GA_LAUNCH_CHECK();
     {
         ProfScope prof(K_DIRECT_SCATTER, stream);
-        direct_scatter_kernel<<<pl.rows, 32 * SC_WARPS, 8 * (size_t)pl.tl_pad, stream>>>(p, gy);
+        direct_scatter_kernel<<<dim3(pl.rows, pl.bands), 32 * SC_WARPS, 8 * (size_t)pl.band_tiles_pad, stream>>>(p, gy, (int)pl.band_rows);
     }
     D3GA_LAUNCH_CHECK();
     return D3GA_OK;

@@ -74,7 +74,7 @@ int d3ga_raster_workspace_bytes(int P, int W, int H, uint64_t capacity,
  * reference): 1 = direct tile scatter (the default where it applies: the N Gaussians are sorted by depth, stage 1 only
  * COUNTS the duplicates per tile, stage 2 stores every duplicate once, straight into its final slot of the sorted list --
  * no unsorted duplicate list exists after stage 1); 0 = a radix sort of the duplicate list that stage 1 emitted
- * (D3GA_SORT_MODE=depthfirst|global|segmented, tile grids beyond 6144 tiles, or a capacity too small to hold the
+ * (D3GA_SORT_MODE=depthfirst|global|segmented, tile grids beyond 49152 tiles, or a capacity too small to hold the
  * scatter's count rows).  Either way the sorted list, the ranges and num_rendered are bit-identical. */
 int d3ga_raster_binning_path(int P, int W, int H, uint64_t capacity);
 

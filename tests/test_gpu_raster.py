@@ -183,7 +183,7 @@ def test_python_dropin_autograd(cuda_lib, oracle_libs, path):
     assert util.rel_l2(means2D.grad.cpu().numpy(), rg["mean2D"]) < GRAD_TOL
 
 
-@pytest.mark.parametrize("workload", ["c1", "c2"])
+@pytest.mark.parametrize("workload", ["c1", "c2", "c3"])
 def test_full_size_properties(cuda_lib, oracle_libs, workload):
     """BASELINE.json sizes: oracle comparison where it finishes in seconds plus size-independent properties."""
     sc = synth.make_workload(workload)
@@ -270,8 +270,11 @@ def test_c4_stress_billion_duplicates(cuda_lib):
     hdr = st.geom[:256].cpu().numpy().view(np.uint32)
     assert int(hdr[0]) == D and int(hdr[1]) == 0
     sel = int(hdr[3])
-    koff, voff = lay["bin_keys1" if sel else "bin_keys0"], lay["bin_vals1" if sel else "bin_vals0"]
-    keys = st.binning[koff:koff + 8 * D].view(torch.int64)
+    voff = lay["bin_vals1" if sel else "bin_vals0"]
+    keys = torch.zeros(D, dtype=torch.int64, device="cuda")
+    dgr._lib.check(dgr._lib.load().d3ga_raster_sorted_keys(
+        sc.N, sc.W, sc.H, st.geom.data_ptr(), st.binning.data_ptr(), st.capacity, st.image.data_ptr(), keys.data_ptr(),
+        torch.cuda.current_stream().cuda_stream), "sorted_keys")
     tiles_of_key = keys >> 32
     assert bool((tiles_of_key[1:] >= tiles_of_key[:-1]).all())
     depth_of_key = keys & 0xFFFFFFFF
