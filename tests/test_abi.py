@@ -41,6 +41,23 @@ def test_size_queries_need_no_gpu():
         _lib.workspace_bytes(10, 64, 48, 1 << 32)
 
 
+def test_binning_path_choice_needs_no_gpu():
+    """The direct tile scatter is the default wherever its scratch fits the binning workspace; the choice is a pure
+    function of the sizes (both forward stages must agree on it)."""
+    lib = _lib.load()
+    if os.environ.get("D3GA_SORT_MODE", "direct") != "direct":
+        pytest.skip("a radix mode is forced")
+    assert lib.d3ga_raster_binning_path(1_000_000, 1024, 1024, 8_000_000) == 1     # the metric workload
+    assert lib.d3ga_raster_binning_path(1_000_000, 2048, 1334, 16_000_000) == 1    # c3: bands of tile rows
+    assert lib.d3ga_raster_binning_path(4_000_000, 3840, 2160, 1_600_000_000) == 1   # c4
+    assert lib.d3ga_raster_binning_path(1000, 64, 48, 5000) == 1
+    assert lib.d3ga_raster_binning_path(0, 64, 48, 5000) == 0                      # nothing to bin
+    assert lib.d3ga_raster_binning_path(1_000_000, 1024, 1024, 100) == 0           # count rows would not fit: radix path
+    assert lib.d3ga_raster_binning_path(1000, 16 * 4096, 16, 1 << 20) == 0         # 4096 tiles in one row: strip width limit
+    assert lib.d3ga_raster_binning_path(1000, 8192, 8192, 1 << 24) == 0            # 262144 tiles: beyond the plan's shared memory
+    assert lib.d3ga_raster_binning_path(-1, 64, 48, 5000) < 0
+
+
 def test_settings_and_rasterizer_interface():
     from d3ga_b200.diff_gaussian_rasterization import GaussianRasterizationSettings, GaussianRasterizer
 
