@@ -436,14 +436,16 @@ DirectParams make_params(int P, int gx, uint8_t *geom, const GeomLayout &GL, uin
     return p;
 }
 
-int set_smem_attrs() {
-    static int done = 0;
-    if (done) return D3GA_OK;
+int set_smem_attrs() {   // per device: a function attribute belongs to the device that was current when it was set
+    static bool done[64] = {};
+    int dev = 0;
+    D3GA_CUDA(cudaGetDevice(&dev));
+    if (dev >= 0 && dev < 64 && done[dev]) return D3GA_OK;
     const int scatter = 200 * 1024, plan = 4 * DIRECT_MAX_TILES, count = 4 * DIRECT_MAX_CELLS;
     D3GA_CUDA(cudaFuncSetAttribute(direct_count_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, count));
     D3GA_CUDA(cudaFuncSetAttribute(direct_scatter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, scatter));
     D3GA_CUDA(cudaFuncSetAttribute(direct_plan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, plan));
-    done = 1;
+    if (dev >= 0 && dev < 64) done[dev] = true;
     return D3GA_OK;
 }
 
