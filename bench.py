@@ -181,7 +181,9 @@ def workload_config(scene, args, views):
                         f"cage(s), {scene.W}x{scene.H}, cov3D_precomp + colors_precomp path",
             "views_per_rank_per_step": views, "cameras": args.cameras, "parallelism": f"camera-sharded dp{args.gpus}",
             "launch": "eager" if args.no_graph else f"one CUDA-graph replay per view, {max(1, args.lanes)} view(s) in flight on separate streams",
-            "l2": "working set (>= 150 MB of Gaussian state + binning buffers per view) exceeds the 126 MB L2; no flush"}
+            "l2": "working set (>= 150 MB of Gaussian state + binning buffers per view) exceeds the 126 MB L2; no flush",
+            "binning": "direct tile scatter; inside the replayed graphs its rows are sized for the views in flight "
+                       "(one view's scatter takes ~1/n of the GPU for n times as long)"}
 
 
 # ---- the GPU arm -------------------------------------------------------------------------------------------------------------
@@ -328,7 +330,8 @@ def run_ours(args):
                 "whole_view": {"bytes": view_bytes, "GBps": view_bytes * (V * args.steps) / (ms * 1e-3) / 1e9,
                                "frac": view_bytes * (V * args.steps) / (ms * 1e-3) / 1e9 / peak,
                                "frac_of_nominal_8000": view_bytes * (V * args.steps) / (ms * 1e-3) / 1e9 / 8000.0},
-                "kernels": kern, "num_rendered": D, "sort_passes_executed": passes}
+                "kernels": kern, "num_rendered": D, "sort_passes_executed": passes,
+                "kernel_times_from": "an identical region of eager launches with per-kernel CUDA events (single-view sizing)"}
 
     # e2e: the same steps through the public API with this step's inputs in pinned HOST memory
     e2e = None

@@ -131,6 +131,8 @@ int d3ga_raster_workspace_bytes(int P, int W, int H, uint64_t capacity, uint64_t
     return D3GA_OK;
 }
 
+void d3ga_set_views_in_flight(int n) { set_views_in_flight(n); }
+
 int d3ga_raster_binning_path(int P, int W, int H, uint64_t capacity) {
     if (P < 0 || W <= 0 || H <= 0) return D3GA_EINVAL;
     return direct_plan(P, (W + TILE - 1) / TILE, (H + TILE - 1) / TILE, capacity).ok ? 1 : 0;

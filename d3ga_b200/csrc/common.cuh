@@ -182,6 +182,7 @@ struct DirectPlan {
     uint64_t seg_off, tot_off, start_off, ticket_off, before_off;   // byte offsets inside the unused key buffer
 };
 DirectPlan direct_plan(int P, int gx, int gy, uint64_t capacity);
+void set_views_in_flight(int n);
 int launch_direct_count(int P, int gx, int gy, uint8_t *geom, const GeomLayout &GL, uint8_t *binning, const BinLayout &BL,
                         uint64_t capacity, const DirectPlan &pl, cudaStream_t stream);
 int launch_sorted_keys(int num_tiles, const uint8_t *geom, const GeomLayout &GL, const uint8_t *binning, const BinLayout &BL,

@@ -31,6 +31,7 @@
 // does not use.  The row length is chosen so that the rows fill the GPU once (8 B x tiles of shared memory per row; larger
 // images are cut into bands of tile rows); the path is not taken (the radix sort runs instead) for tile grids beyond
 // DIRECT_MAX_TILES or when the scratch does not fit.
+#include <atomic>
 #include <cstdlib>
 
 #include "common.cuh"
@@ -409,6 +410,8 @@ __global__ void __launch_bounds__(COL_THREADS) direct_base_kernel(const uint32_t
     }
 }
 
+std::atomic<int> g_views_in_flight{1};
+
 uint32_t chunk_override() {
     static const uint32_t v = [] {
         const char *e = getenv("D3GA_DIRECT_CHUNK");
@@ -478,7 +481,12 @@ DirectPlan direct_plan(int P, int gx, int gy, uint64_t capacity) {
     if (per_sm < 1) return pl;
     uint64_t chunk = chunk_override();
     if (!chunk) {
-        uint64_t rows_target = 148 * per_sm / pl.bands;
+        // ... once for a single view; a caller that keeps n views in flight on separate streams (d3ga_set_views_in_flight)
+        // gets rows n times as long: each view's scatter then holds about 1/n of the shared memory and warp slots for n
+        // times as long instead of all of them, which leaves the other views' kernels room beside it
+        int vif = g_views_in_flight.load(std::memory_order_relaxed);
+        if (vif < 1) vif = 1;
+        uint64_t rows_target = 148 * per_sm / pl.bands / (uint64_t)vif;
         if (rows_target < 148) rows_target = 148;
         chunk = ((uint64_t)P + rows_target - 1) / rows_target;
         chunk = (chunk + 31) / 32 * 32;
@@ -552,6 +560,8 @@ int launch_copy_sorted_keys(const uint8_t *geom, const GeomLayout &GL, const uin
     D3GA_LAUNCH_CHECK();
     return D3GA_OK;
 }
+
+void set_views_in_flight(int n) { g_views_in_flight.store(n < 1 ? 1 : (n > 64 ? 64 : n), std::memory_order_relaxed); }
 
 // Stage 1 tail: the count rows, the depth-ordered records and the duplicate total.
 int launch_direct_count(int P, int gx, int gy, uint8_t *geom, const GeomLayout &GL, uint8_t *binning, const BinLayout &BL,

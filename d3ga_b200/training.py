@@ -199,10 +199,11 @@ class GraphedViewStep:
     overflow) into a device counter and `finish()` reads it back: if a view overflowed, the hint has been raised, the
     graph must be captured again (`capture()`) and the step redone -- `multi_view_step(..., graphed=...)` does that."""
 
-    def __init__(self, avatar, cam, bg, weights=None):
+    def __init__(self, avatar, cam, bg, weights=None, views_in_flight=1):
         from d3ga_b200 import diff_gaussian_rasterization as dgr
         self.dgr = dgr
         self.avatar = avatar
+        self.views_in_flight = int(views_in_flight)   # how many such graphs the caller replays concurrently
         dev = avatar.device
         self.cam = torch.zeros(35, dtype=torch.float32, device=dev)
         self.weights = torch.empty((3, avatar.H, avatar.W), dtype=torch.float32, device=dev) if weights is None else weights
@@ -232,9 +233,16 @@ class GraphedViewStep:
         torch.cuda.synchronize()
         self.graph = torch.cuda.CUDAGraph()
         l0 = _lib.launch_count()
-        with self.dgr.deferred_overflow_check(), torch.cuda.graph(self.graph, stream=self.capture_stream):
-            loss = view_step(self.avatar, self.rs, self.weights)
-            self.total += loss.detach()
+        # the launch configurations baked into the graph are sized for `views_in_flight` concurrent replays (the direct
+        # tile scatter then takes about 1/n of the GPU for n times as long); eager calls keep the single-view sizing
+        lib = _lib.load()
+        lib.d3ga_set_views_in_flight(self.views_in_flight)
+        try:
+            with self.dgr.deferred_overflow_check(), torch.cuda.graph(self.graph, stream=self.capture_stream):
+                loss = view_step(self.avatar, self.rs, self.weights)
+                self.total += loss.detach()
+        finally:
+            lib.d3ga_set_views_in_flight(1)
         self.launches_per_replay = _lib.launch_count() - l0
         self.captures += 1
         self.dgr.collect_deferred(self.avatar.device)   # the capture itself launched nothing; clear the counter
@@ -283,7 +291,7 @@ class PipelinedViews:
         self.avatar = avatar
         self.shadows = [avatar.shadow() for _ in range(lanes)]
         self.streams = [torch.cuda.Stream(device=avatar.device) for _ in range(lanes)]
-        self.gvs = [GraphedViewStep(sh, cam, bg) for sh in self.shadows]
+        self.gvs = [GraphedViewStep(sh, cam, bg, views_in_flight=lanes) for sh in self.shadows]
 
     @property
     def captures(self):

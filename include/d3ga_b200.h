@@ -70,6 +70,14 @@ int d3ga_profile_collect(double *ms, uint64_t *launches);
 int d3ga_raster_workspace_bytes(int P, int W, int H, uint64_t capacity,
                                 uint64_t *geom_bytes, uint64_t *binning_bytes, uint64_t *image_bytes);
 
+/* Sizing hint (no counterpart in the reference): how many independent views the caller keeps in flight on separate
+ * streams (d3ga_b200.training.PipelinedViews does; default 1).  The direct tile scatter sizes its rows so that one view's
+ * scatter occupies about 1/n of the GPU for n times as long -- alone that is slower, with n views in flight it leaves the
+ * other views' kernels room beside it (measured at n = 4: +6 % views/s).  Results do not depend on it.  Process-wide; both
+ * stages of a view must see the same value.  d3ga_b200.training sets it only while it captures a view's CUDA graph (the
+ * launch configurations are baked into the graph) and restores 1, so eager calls keep the single-view sizing. */
+void d3ga_set_views_in_flight(int n);
+
 /* Which binning strategy the two forward stages will use for these sizes (measurement and tests; no counterpart in the
  * reference): 1 = direct tile scatter (the default where it applies: the N Gaussians are sorted by depth, stage 1 only
  * COUNTS the duplicates per tile, stage 2 stores every duplicate once, straight into its final slot of the sorted list --
