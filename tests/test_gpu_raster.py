@@ -225,6 +225,30 @@ def test_full_size_properties(cuda_lib, oracle_libs, workload):
         assert util.rel_l2(g1[k], rg[k]) < GRAD_TOL, (k, util.rel_l2(g1[k], rg[k]))
 
 
+def test_views_in_flight_hint_changes_nothing_but_the_row_length(cuda_lib, oracle_libs):
+    """d3ga_set_views_in_flight(n) only re-sizes the direct tile scatter's rows (a view then takes ~1/n of the GPU): lists,
+    ranges and image must stay bit-identical.  Checked on the 300 k-Gaussian 1024^2 scene, where n = 1, 4 and 64 give rows of
+    a few hundred, a thousand and 8192 Gaussians (several, one and almost no rows per SM)."""
+    sc = synth.make_workload("c2")
+    means, cov6 = util.scene_geometry(sc)
+    g = dict(means=means, cov6=cov6, opacity=sc.opacity, colors=sc.colors)
+    cam = synth.make_camera(sc.W, sc.H, 20, 10)
+    lib = cuda_lib
+    outs = []
+    try:
+        for n in (1, 4, 64):
+            lib.d3ga_set_views_in_flight(n)
+            outs.append(gpu_util.forward_stages(g, cam, sc.W, sc.H, [1, 1, 1]))
+    finally:
+        lib.d3ga_set_views_in_flight(1)
+    a = outs[0]
+    assert a["direct"]
+    for b in outs[1:]:
+        assert np.array_equal(a["point_list"], b["point_list"]) and np.array_equal(a["keys"], b["keys"])
+        assert np.array_equal(a["ranges"], b["ranges"]) and np.array_equal(a["color"], b["color"])
+        assert a["num_rendered"] == b["num_rendered"]
+
+
 def test_segmented_sort_mode_is_bit_exact_too(cuda_lib, oracle_libs):
     """The alternative binning strategies (D3GA_SORT_MODE=depthfirst: depth sort of the Gaussians, emission in depth order,
     radix passes on the tile digits; =global: one 64-bit LSD sort of the duplicates in Gaussian
