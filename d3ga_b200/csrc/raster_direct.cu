@@ -8,29 +8,32 @@
 // Once the N Gaussians are in depth order (raster_sort.cu: launch_depth_sort), the sorted duplicate list is fully
 // determined by COUNTS: the slot of duplicate (Gaussian g, tile t) is
 //     start[t]  +  #duplicates of t among the Gaussians before g in depth order.
-// The depth-ordered list is cut into rows of `chunk` Gaussians, one warp per row, one Gaussian per lane, 32 at a time;
-// a lane walks the tiles of its own rect (row-major, no division, no search):
-//   1. direct_count_kernel   : per-tile counts of the row in a private 16-bit histogram in shared memory -> M[row][tile];
-//                              also leaves the row's Gaussians as packed records (rect, extent, id, depth bits) so the
-//                              scatter reads them coalesced, and adds the row's total to D (num_rendered, overflow).
+// The depth-ordered list is cut into rows of `chunk` Gaussians, one CTA per row:
+//   1. direct_count_kernel   : per-tile counts of the row (a 2-D difference grid in shared memory: four corner updates per
+//                              rect, then prefix sums) -> M[row][tile] (u16); also leaves the row's Gaussians as packed
+//                              records (rect, extent, id, depth bits) in depth order so the scatter reads them coalesced,
+//                              and adds the row's total to D (num_rendered, overflow).
 //   2. direct_segsum_kernel  : column sums of M over segments of rows; the last CTA of a column block turns them into
 //                              exclusive segment offsets and the per-tile totals.
 //   3. direct_plan_kernel    : one CTA: exclusive scan of the totals in tile order = ranges (a tile without duplicates
 //                              keeps (0, 0), like upstream's zero-initialised ranges) and the blend's tile launch order.
 //   4. direct_base_kernel    : segment offsets += start[tile]; before[row][tile] = exclusive prefix of M inside the segment.
 //   5. direct_scatter_kernel : the row keeps pos[tile] (next free slot) and mask[tile] in shared memory.  Per batch of 32
-//                              Gaussians three walks: (A) every lane ORs its bit into mask[t] of its tiles; (B) the slot of
-//                              (lane, t) is pos[t] + popc(mask[t] below the lane) -- the lanes that share a tile are ordered
-//                              by lane = by depth, whatever order the walks reach the tile in -- and the value and the
-//                              (tile | depth) key are stored straight into their final slots; (C) the highest lane of
-//                              mask[t] advances pos[t] by popc(mask[t]) and clears the mask.
-// Per duplicate that is four cheap visits and one 12-byte store, against an emission (12 B store) plus two radix passes
+//                              rect pieces three walks: (A) every owner ORs its bit into mask[t] of its tiles; (B) the
+//                              slot of (owner, t) is pos[t] + popc(mask[t] below the owner) -- owners that share a tile
+//                              are ordered by position in the batch = by depth, whatever order the walks reach the tile
+//                              in -- and the Gaussian id is stored straight into its final slot; (C) the highest owner of
+//                              mask[t] advances pos[t] by popc(mask[t]) and clears the mask.  (Details above the kernel.)
+// Per duplicate that is three cheap visits and one 4-byte store, against an emission (12 B store) plus two radix passes
 // (each 12 B load + MATCH-based ranking + 12 B store) before; a row is independent of every other row and nothing looks
-// back at a predecessor.  Algorithmic bytes: 36 N (gathers + records) + 2 R Tl (count rows) in (1), 16 N + 6 R Tl + 12 D in (5).
-// Scratch (M, segment sums) lives in the second halves of the binning workspace's key / value ping-pong, which this path
-// does not use.  The row length is chosen so that the rows fill the GPU once (8 B x tiles of shared memory per row; larger
-// images are cut into bands of tile rows); the path is not taken (the radix sort runs instead) for tile grids beyond
-// DIRECT_MAX_TILES or when the scratch does not fit.
+// back at a predecessor.  The sorted keys are not stored (the blend does not read them; sorted_keys_kernel rebuilds them
+// on request).  Algorithmic bytes: 36 N (gathers + records) in (1), 16 N + 4 D in (5); the count rows and their prefixes
+// (6 B x rows x tiles) are scratch traffic.
+// Scratch (M, segment sums, prefixes) lives in the second halves of the binning workspace's key / value ping-pong, which
+// this path does not use.  The row length is chosen so that the rows fill the GPU once -- or 1/n of it when the caller
+// keeps n views in flight (d3ga_set_views_in_flight) -- at 8 B x tiles of shared memory per row; larger images are cut into
+// bands of tile rows.  The path is not taken (the radix sort runs instead) for tile grids beyond DIRECT_MAX_TILES or when
+// the scratch does not fit.
 #include <atomic>
 #include <cstdlib>
 
