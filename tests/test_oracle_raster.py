@@ -140,3 +140,57 @@ def test_backward_matches_finite_differences(oracle_libs, path, aa):
             fd = (f(run(**{key: hi})[1]) - f(run(**{key: lo})[1])) / (2 * eps)
             an = grads[gname].reshape(base.shape)[idx]
             assert abs(fd - an) <= 1e-4 * (abs(fd) + abs(an)) + 1e-9, (gname, idx, fd, an)
+
+
+@pytest.mark.parametrize("chunk,rows_per_seg", [(32, 3), (96, 1), (4096, 4)])
+def test_counting_identity_of_the_direct_tile_scatter(oracle_libs, chunk, rows_per_seg):
+    """The arithmetic csrc/raster_direct.cu rests on, replayed in numpy on the oracle's own duplicate list: with the
+    Gaussians in (depth bits, index) order and cut into rows of `chunk`, the slot of duplicate (g, tile) in the sorted list
+    is  start[tile] + (duplicates of the tile in earlier segments) + (in earlier rows of g's segment) + (before g in
+    its row)  -- counts only, no sort of the duplicates.  Must reproduce the oracle's sorted ids, keys and ranges."""
+    rng = np.random.default_rng(chunk)
+    g = util.random_gaussians(700, rng, sigma=0.1, with_behind=True)
+    cam, W, H = synth.make_camera(112, 80, 15, 5), 112, 80
+    _, st = util.oracle_forward(g, cam, W, H, [0, 0, 0])
+    tiles = (st["keys_unsorted"] >> np.uint64(32)).astype(np.int64)          # one entry per duplicate, Gaussian order
+    gid = st["vals_unsorted"].astype(np.int64)
+    D, Tl = len(gid), ((W + 15) // 16) * ((H + 15) // 16)
+    assert D == st["num_rendered"] and D > 2000
+    # depth order of the Gaussians: culled ones carry the key 0xffffffff and sort to the end (preprocess_kernel)
+    key = np.where(st["tiles_touched"] > 0, st["depths"].view(np.uint32), np.uint32(0xFFFFFFFF))
+    order = np.argsort(key, kind="stable")
+    slot_of = np.empty_like(order)
+    slot_of[order] = np.arange(len(order))
+    slot = slot_of[gid]                                                      # the duplicate's Gaussian in depth order
+    row, seg = slot // chunk, slot // chunk // rows_per_seg
+    nrows, nseg = int(row.max()) + 1, int(seg.max()) + 1
+    M = np.zeros((nrows, Tl), np.int64)                                      # direct_count_kernel
+    np.add.at(M, (row, tiles), 1)
+    assert M.max() <= min(chunk, 65535)
+    segsum = np.add.reduceat(M, np.arange(0, nrows, rows_per_seg), axis=0)   # direct_segsum_kernel
+    assert segsum.shape[0] == nseg
+    tot = segsum.sum(0)
+    segx = np.cumsum(segsum, 0) - segsum
+    start = np.cumsum(tot) - tot                                             # direct_plan_kernel
+    ranges = np.where(tot[:, None] > 0, np.stack([start, start + tot], 1), 0)
+    before = np.zeros_like(M)                                                # direct_base_kernel
+    for s in range(nseg):
+        blk = M[s * rows_per_seg:(s + 1) * rows_per_seg]
+        before[s * rows_per_seg:(s + 1) * rows_per_seg] = np.cumsum(blk, 0) - blk
+    assert before.max() <= 65535
+    # direct_scatter_kernel: rank inside the row = earlier Gaussians of the row on the same tile
+    in_row = np.zeros(D, np.int64)
+    o = np.lexsort((slot, tiles, row))
+    r_s, t_s = row[o], tiles[o]
+    new_group = np.r_[True, (r_s[1:] != r_s[:-1]) | (t_s[1:] != t_s[:-1])]
+    idx = np.arange(D)
+    in_row[o] = idx - np.maximum.accumulate(np.where(new_group, idx, 0))
+    dst = start[tiles] + segx[seg, tiles] + before[row, tiles] + in_row
+    assert len(np.unique(dst)) == D and dst.max() == D - 1
+    point_list = np.empty(D, np.uint32)
+    point_list[dst] = gid
+    keys = np.empty(D, np.uint64)
+    keys[dst] = (tiles.astype(np.uint64) << np.uint64(32)) | st["depths"].view(np.uint32)[gid].astype(np.uint64)
+    assert np.array_equal(point_list, st["point_list"])
+    assert np.array_equal(keys, st["keys"])
+    assert np.array_equal(ranges.astype(np.uint32), st["ranges"])
