@@ -16,7 +16,7 @@ EXPORTS = [
     "d3ga_version", "d3ga_error_string", "d3ga_last_cuda_error", "d3ga_launch_count",
     "d3ga_profile_enable", "d3ga_profile_kernel_count", "d3ga_profile_kernel_name", "d3ga_profile_collect",
     "d3ga_raster_workspace_bytes", "d3ga_raster_forward_geometry", "d3ga_raster_forward_render",
-    "d3ga_raster_forward_blend", "d3ga_raster_binning_path", "d3ga_set_views_in_flight", "d3ga_raster_sorted_keys",
+    "d3ga_raster_forward_blend", "d3ga_raster_binning_path", "d3ga_set_views_in_flight", "d3ga_mark_visible", "d3ga_raster_sorted_keys",
     "d3ga_raster_backward_scratch_bytes", "d3ga_raster_backward", "d3ga_raster_backward_noalloc", "d3ga_raster_layout",
     "d3ga_deform_forward", "d3ga_deform_backward", "d3ga_deform_backward_ordered", "d3ga_compute_bary",
     "d3ga_fem_energy_forward", "d3ga_fem_energy_backward", "d3ga_ssim_l1_forward", "d3ga_ssim_l1_backward",
@@ -62,6 +62,7 @@ def load() -> C.CDLL:
     lib.d3ga_raster_layout.argtypes = [i32, i32, i32, u64, C.POINTER(u64)]
     lib.d3ga_raster_binning_path.argtypes = [i32, i32, i32, u64]
     lib.d3ga_set_views_in_flight.argtypes = [i32]
+    lib.d3ga_mark_visible.argtypes = [i32, vp, vp, vp, vp, vp]
     lib.d3ga_set_views_in_flight.restype = None
     lib.d3ga_raster_sorted_keys.argtypes = [i32, i32, i32, vp, vp, u64, vp, vp, vp]
     lib.d3ga_raster_forward_geometry.argtypes = (

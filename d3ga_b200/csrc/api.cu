@@ -133,6 +133,13 @@ int d3ga_raster_workspace_bytes(int P, int W, int H, uint64_t capacity, uint64_t
 
 void d3ga_set_views_in_flight(int n) { set_views_in_flight(n); }
 
+int d3ga_mark_visible(int P, const float *means3D, const float *viewmatrix, const float *projmatrix, uint8_t *present,
+                      d3ga_stream_t stream) {
+    (void)projmatrix;   // upstream passes it to in_frustum, which only uses it for a value it never tests
+    if (P < 0 || !viewmatrix || (P > 0 && (!means3D || !present))) return D3GA_EINVAL;
+    return launch_mark_visible(P, means3D, viewmatrix, present, (cudaStream_t)stream);
+}
+
 int d3ga_raster_binning_path(int P, int W, int H, uint64_t capacity) {
     if (P < 0 || W <= 0 || H <= 0) return D3GA_EINVAL;
     return direct_plan(P, (W + TILE - 1) / TILE, (H + TILE - 1) / TILE, capacity).ok ? 1 : 0;

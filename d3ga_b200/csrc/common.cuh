@@ -164,6 +164,7 @@ int launch_geometry(int P, int sh_degree, int sh_coeffs, const float *means3D, c
                     const float *projmatrix, const float *campos, int W, int H, float tanfovx, float tanfovy,
                     int antialiasing, uint8_t *geom, const GeomLayout &GL, uint8_t *binning, const BinLayout &BL,
                     uint64_t capacity, int32_t *radii, cudaStream_t stream);
+int launch_mark_visible(int P, const float *means3D, const float *viewmatrix, uint8_t *present, cudaStream_t stream);
 int launch_sort_and_ranges(int P, uint8_t *geom, const GeomLayout &GL, int gx, int gy, uint8_t *binning, const BinLayout &BL, uint64_t capacity, int sort_bits,
                            uint8_t *image, const ImgLayout &IL, int num_tiles, cudaStream_t stream);
 int launch_depth_sort(int P, uint8_t *geom, const GeomLayout &GL, cudaStream_t stream);

@@ -411,7 +411,26 @@ __global__ void __launch_bounds__(GEO_THREADS) emit_sorted_kernel(const GeoParam
                   &s_base);
 }
 
+// Upstream's markVisible (checkFrustum): a point is "present" when it lies in front of the near plane, z_view > 0.2 -- the
+// same test, on the same arithmetic, that the preprocess culls with.
+__global__ void __launch_bounds__(GEO_THREADS) mark_visible_kernel(int P, const float *__restrict__ means3D,
+                                                                   const float *__restrict__ view, uint8_t *present) {
+    __shared__ float s_view[16];
+    if (threadIdx.x < 16) s_view[threadIdx.x] = view[threadIdx.x];
+    __syncthreads();
+    const int idx = blockIdx.x * GEO_THREADS + threadIdx.x;
+    if (idx >= P) return;
+    present[idx] = tp(s_view, 2, means3D[3 * (size_t)idx], means3D[3 * (size_t)idx + 1], means3D[3 * (size_t)idx + 2]) > 0.2f;
+}
+
 }  // namespace
+
+int launch_mark_visible(int P, const float *means3D, const float *viewmatrix, uint8_t *present, cudaStream_t stream) {
+    if (P == 0) return D3GA_OK;
+    mark_visible_kernel<<<(P + GEO_THREADS - 1) / GEO_THREADS, GEO_THREADS, 0, stream>>>(P, means3D, viewmatrix, present);
+    D3GA_LAUNCH_CHECK();
+    return D3GA_OK;
+}
 
 int launch_geometry(int P, int sh_degree, int sh_coeffs, const float *means3D, const float *scales,
                     float scale_modifier, const float *rotations, const float *opacities, const float *shs,

@@ -376,11 +376,18 @@ class GaussianRasterizer(nn.Module):
         self.raster_settings = raster_settings
 
     def markVisible(self, positions):
-        """Boolean mask of the points in front of the near plane (z_view > 0.2), like upstream's mark_visible."""
-        with torch.no_grad():
-            v = self.raster_settings.viewmatrix
-            z = positions[:, 0] * v[0, 2] + positions[:, 1] * v[1, 2] + positions[:, 2] * v[2, 2] + v[3, 2]
-            return z > 0.2
+        """Boolean mask of the points in front of the near plane (z_view > 0.2), like upstream's mark_visible
+        (d3ga_mark_visible: the preprocess's own cull test)."""
+        positions = _f32c(positions.detach(), "positions")
+        rs = self.raster_settings
+        view, proj = _f32c(rs.viewmatrix, "viewmatrix"), _f32c(rs.projmatrix, "projmatrix")
+        P = positions.shape[0]
+        present = torch.zeros((P,), dtype=torch.bool, device=positions.device)
+        with torch.cuda.device(positions.device):
+            _lib.check(_lib.load().d3ga_mark_visible(P, _lib.ptr(positions), view.data_ptr(), proj.data_ptr(),
+                                                     _lib.ptr(present), torch.cuda.current_stream().cuda_stream),
+                       "mark_visible")
+        return present
 
     def forward(self, means3D, means2D, opacities, shs=None, colors_precomp=None, scales=None, rotations=None,
                 cov3D_precomp=None):

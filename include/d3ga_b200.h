@@ -70,6 +70,13 @@ int d3ga_profile_collect(double *ms, uint64_t *launches);
 int d3ga_raster_workspace_bytes(int P, int W, int H, uint64_t capacity,
                                 uint64_t *geom_bytes, uint64_t *binning_bytes, uint64_t *image_bytes);
 
+/* Replaces diff_gaussian_rasterization._C.mark_visible (GaussianRasterizer.markVisible upstream; D3GA's renderer.py never
+ * calls it, it is part of the module's surface): present[i] = 1 when means3D[i] lies in front of the near plane
+ * (z_view > 0.2), with the arithmetic the preprocess culls with.  present: uint8 [P] (a torch.bool tensor's storage).
+ * projmatrix is accepted for signature parity and not read. */
+int d3ga_mark_visible(int P, const float *means3D, const float *viewmatrix, const float *projmatrix, uint8_t *present,
+                      d3ga_stream_t stream);
+
 /* Sizing hint (no counterpart in the reference): how many independent views the caller keeps in flight on separate
  * streams (d3ga_b200.training.PipelinedViews does; default 1).  The direct tile scatter sizes its rows so that one view's
  * scatter occupies about 1/n of the GPU for n times as long -- alone that is slower, with n views in flight it leaves the

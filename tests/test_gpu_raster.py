@@ -225,6 +225,27 @@ def test_full_size_properties(cuda_lib, oracle_libs, workload):
         assert util.rel_l2(g1[k], rg[k]) < GRAD_TOL, (k, util.rel_l2(g1[k], rg[k]))
 
 
+def test_mark_visible(cuda_lib, oracle_libs):
+    """GaussianRasterizer.markVisible: z_view > 0.2 with the preprocess's arithmetic -- every Gaussian the forward gives
+    a radius is marked, and the mask equals the float64 test away from the threshold."""
+    from d3ga_b200 import diff_gaussian_rasterization as dgr
+
+    g, cam, W, H = CASES["random"]
+    _, ref = util.oracle_forward(g, cam, W, H, BG)
+    t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).cuda()  # noqa: E731
+    rs = dgr.GaussianRasterizationSettings(
+        image_height=H, image_width=W, tanfovx=cam.tanfovx, tanfovy=cam.tanfovy, bg=torch.zeros(3, device="cuda"),
+        scale_modifier=1.0, viewmatrix=t(cam.viewmatrix), projmatrix=t(cam.projmatrix), sh_degree=0, campos=t(cam.campos),
+        prefiltered=False, debug=False, antialiasing=False)
+    got = dgr.GaussianRasterizer(raster_settings=rs).markVisible(t(g["means"])).cpu().numpy()
+    assert got.dtype == np.bool_ and got.shape == (g["means"].shape[0],)
+    z = g["means"].astype(np.float64) @ cam.viewmatrix.astype(np.float64)[:3, 2] + float(cam.viewmatrix[3, 2])
+    clear = np.abs(z - 0.2) > 1e-5
+    assert np.array_equal(got[clear], (z > 0.2)[clear]) and 0 < got.sum() < got.size
+    assert got[ref["radii"] > 0].all()
+    assert dgr.GaussianRasterizer(raster_settings=rs).markVisible(torch.zeros((0, 3), device="cuda")).numel() == 0
+
+
 def test_views_in_flight_hint_changes_nothing_but_the_row_length(cuda_lib, oracle_libs):
     """d3ga_set_views_in_flight(n) only re-sizes the direct tile scatter's rows (a view then takes ~1/n of the GPU): lists,
     ranges and image must stay bit-identical.  Checked on the 300 k-Gaussian 1024^2 scene, where n = 1, 4 and 64 give rows of
