@@ -112,3 +112,35 @@ def test_skin_tables_match_reference():
     for r in range(dense.shape[0]):
         rebuilt[r, pt.csr_col_idx.numpy()[rp[r]:rp[r + 1]]] = pt.csr_vals.numpy()[rp[r]:rp[r + 1]]
     assert np.array_equal(rebuilt, dense)
+
+
+def test_tetra_sampler_import_surface_of_smplman():
+    """lib/smplman.py:9,16 imports tetra_sampler.lbs.batch_rodrigues and tetra_sampler.body_model.SMPLlayer: both resolve
+    when this package stands in for tetra_sampler, and batch_rodrigues reproduces the reference's own outputs."""
+    import importlib
+    import sys
+
+    import torch
+
+    import d3ga_b200.tetra_sampler as ts
+    saved = {k: sys.modules.get(k) for k in ("tetra_sampler", "tetra_sampler.lbs", "tetra_sampler.body_model")}
+    try:
+        sys.modules["tetra_sampler"] = ts
+        sys.modules.pop("tetra_sampler.lbs", None)
+        sys.modules.pop("tetra_sampler.body_model", None)
+        lbs = importlib.import_module("tetra_sampler.lbs")
+        bm = importlib.import_module("tetra_sampler.body_model")
+    finally:
+        for k, v in saved.items():
+            if v is None:
+                sys.modules.pop(k, None)
+            else:
+                sys.modules[k] = v
+    G = np.load(os.path.join(os.path.dirname(__file__), "golden", "lbs_golden.npz"))
+    R = lbs.batch_rodrigues(torch.from_numpy(G["smpl_Rh"]))
+    assert R.dtype == torch.float32 and np.abs(R.numpy() - G["rodrigues"]).max() < 1e-6
+    assert np.allclose(lbs.batch_rodrigues(torch.zeros(2, 3)).numpy(), np.eye(3)[None].repeat(2, 0), atol=1e-6)
+    assert hasattr(bm, "SMPLlayer")
+    if not os.environ.get("D3GA_REFERENCE_TETRA_SAMPLER"):
+        with pytest.raises(ImportError, match="D3GA_REFERENCE_TETRA_SAMPLER"):
+            bm.SMPLlayer("models")
