@@ -287,14 +287,12 @@ def run_ours(args):
     stats.update(dgr.sort_plan_of_last_forward())
     D = int(stats.get("num_rendered", 0))
     passes = int(stats.get("passes_executed", 6))
-    if prof.get("segment_sort_kernel", (0, 0))[1]:
-        passes += 1     # the per-tile shared-memory depth sort reads and writes every pair once
     N, P, Tl = scene.N, scene.W * scene.H, ((scene.W + 15) // 16) * ((scene.H + 15) // 16)
     bytes_per_launch = {
         "deform_forward_kernel": 120 * N, "geometry_kernel": 84 * N + 12 * D, "sort_histogram_kernel": 8 * D,
         "preprocess_kernel": 96 * N, "emit_sorted_kernel": 20 * N + 12 * D, "depth_histogram_kernel": 4 * N,
         "depth_sort_pass_kernel": 16 * N,
-        "sort_pass_kernel": 24 * D, "segment_sort_kernel": 12 * D, "tile_ranges_kernel": 8 * D + 8 * Tl, "blend_forward_kernel": 40 * D + 20 * P,
+        "sort_pass_kernel": 24 * D, "tile_ranges_kernel": 8 * D + 8 * Tl, "blend_forward_kernel": 40 * D + 20 * P,
         "blend_backward_kernel": 80 * D + 20 * P, "preprocess_backward_kernel": 104 * N,
         "deform_backward_kernel": 212 * N, "rect_grid_kernel": 12 * N, "tile_plan_kernel": 12 * Tl,
         # direct tile scatter (raster_direct.cu): gathers + records; ids written once, straight into their final slots

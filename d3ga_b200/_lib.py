@@ -86,7 +86,7 @@ def load() -> C.CDLL:
     lib.d3ga_fem_energy_forward.argtypes = [i32, i32, vp, vp, vp, vp, vp]
     lib.d3ga_fem_energy_backward.argtypes = [i32, i32, vp, vp, vp, vp, vp, vp]
     lib.d3ga_ssim_l1_forward.argtypes = [i32, i32, i32, vp, vp, vp, vp, vp, vp, vp]
-    lib.d3ga_ssim_l1_backward.argtypes = [i32, i32, i32, vp, vp, vp, vp, vp, f32, f32, vp, vp]
+    lib.d3ga_ssim_l1_backward.argtypes = [i32, i32, i32, vp, vp, vp, vp, vp, f32, f32, vp, vp, vp]
     lib.d3ga_compute_bary.argtypes = [i32, i32, i32, vp, vp, vp, vp, vp, vp, vp, vp, vp]
     i64 = C.c_int64
     lib.d3ga_lbs_skeleton_forward.argtypes = [i32, i32, i32, i32, vp, vp, i64, i32] + [vp] * 11

@@ -22,7 +22,6 @@ SOURCES = [
     ("raster_geometry.cu", ["-fmad=false"]),
     ("raster_sort.cu", []),
     ("raster_direct.cu", []),
-    ("raster_segsort.cu", []),
     ("raster_blend.cu", []),
     ("raster_backward.cu", []),
     ("raster_backward_noalloc.cu", []),

@@ -28,7 +28,7 @@ static std::vector<ProfRec> g_prof_recs;
 static const char *const g_kernel_names[K_COUNT] = {
     "geometry_kernel", "sort_histogram_kernel", "sort_pass_kernel", "tile_ranges_kernel", "blend_forward_kernel",
     "blend_backward_kernel", "preprocess_backward_kernel", "deform_forward_kernel", "deform_backward_kernel",
-    "compute_bary_kernel", "segment_sort_kernel", "preprocess_kernel", "emit_sorted_kernel", "depth_histogram_kernel",
+    "compute_bary_kernel", "preprocess_kernel", "emit_sorted_kernel", "depth_histogram_kernel",
     "depth_sort_pass_kernel", "fem_energy_forward_kernel", "fem_energy_backward_kernel",
     "ssim_forward_kernel", "ssim_backward_kernel", "lbs_skeleton_kernel", "lbs_skin_forward_kernel",
     "lbs_skin_backward_kernel", "lbs_unskin_kernel", "lbs_skin_dense_forward_kernel", "lbs_skin_dense_backward_kernel",
@@ -54,11 +54,21 @@ ProfScope::~ProfScope() {
     delete r;
 }
 
+int device_sm_count() {
+    static std::atomic<int> cached[64];
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return 148;
+    if (dev >= 0 && dev < 64 && cached[dev].load(std::memory_order_relaxed) > 0) return cached[dev].load(std::memory_order_relaxed);
+    int n = 0;
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n < 1) n = 148;
+    if (dev >= 0 && dev < 64) cached[dev].store(n, std::memory_order_relaxed);
+    return n;
+}
+
 int sort_mode() {
     static const int mode = [] {
         const char *v = getenv("D3GA_SORT_MODE");
         if (v && strcmp(v, "global") == 0) return (int)SORT_GLOBAL;
-        if (v && strcmp(v, "segmented") == 0) return (int)SORT_SEGMENTED;
         if (v && strcmp(v, "depthfirst") == 0) return (int)SORT_DEPTH_FIRST;
         return (int)SORT_DIRECT;
     }();
@@ -154,7 +164,9 @@ int d3ga_raster_sorted_keys(int P, int W, int H, const void *geom, const void *b
     const BinLayout BL = bin_layout(capacity);
     const ImgLayout IL = img_layout(W, H);
     const int gx = (W + TILE - 1) / TILE, gy = (H + TILE - 1) / TILE;
-    if (direct_plan(P, gx, gy, capacity).ok)
+    DirectPlan direct;
+    if (!recall_direct_plan(geom, P, gx, gy, capacity, &direct)) return D3GA_ENOTREADY;
+    if (direct.ok)
         return launch_sorted_keys(gx * gy, (const uint8_t *)geom, GL, (const uint8_t *)binning, BL, (const uint8_t *)image, IL,
                                   keys_out, stream);
     // radix paths: the list is in one of the two key buffers; the header says which (device-side selection, no host sync)

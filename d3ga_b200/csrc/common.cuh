@@ -1,6 +1,7 @@
 // common.cuh -- shared declarations of libd3ga_b200 (sm_100a).  Host + device.
 #pragma once
 #include <cuda_runtime.h>
+#include <atomic>
 #include <stddef.h>
 #include <stdint.h>
 
@@ -130,7 +131,7 @@ constexpr int GRAD_ACC_FLOATS = 12;
 // ---- host-side helpers -----------------------------------------------------------------------------------------
 enum KernelId {
     K_GEOMETRY = 0, K_SORT_HIST, K_SORT_PASS, K_RANGES, K_BLEND_FWD, K_BLEND_BWD, K_PRE_BWD, K_DEFORM_FWD, K_DEFORM_BWD,
-    K_BARY, K_SEG_SORT, K_PREPROCESS, K_EMIT, K_DEPTH_HIST, K_DEPTH_PASS, K_FEM_FWD, K_FEM_BWD, K_SSIM_FWD, K_SSIM_BWD,
+    K_BARY, K_PREPROCESS, K_EMIT, K_DEPTH_HIST, K_DEPTH_PASS, K_FEM_FWD, K_FEM_BWD, K_SSIM_FWD, K_SSIM_BWD,
     K_LBS_SKELETON, K_LBS_SKIN_FWD, K_LBS_SKIN_BWD, K_LBS_UNSKIN, K_LBS_DENSE_FWD, K_LBS_DENSE_BWD, K_RECT_GRID, K_TILE_PLAN,
     K_DIRECT_COUNT, K_DIRECT_SEGSUM, K_DIRECT_PLAN, K_DIRECT_BASE, K_DIRECT_SCATTER, K_COUNT
 };
@@ -157,6 +158,21 @@ int set_cuda_error(cudaError_t e);
         if (_e != cudaSuccess) return d3ga::set_cuda_error(_e); \
     } while (0)
 
+// Function attributes (the opt-in to more than 48 KB of dynamic shared memory) belong to the device that is current when
+// they are set, so a launcher applies them the first time it runs on EACH device: `mask` has one bit per device
+// ordinal (ordinals >= 64 simply set them on every call).  f() returns a D3GA_* code.
+template <typename F>
+inline int once_per_device(std::atomic<uint64_t> &mask, F &&f) {
+    int dev = 0;
+    D3GA_CUDA(cudaGetDevice(&dev));
+    const uint64_t bit = dev >= 0 && dev < 64 ? (1ull << dev) : 0ull;
+    if (bit && (mask.load(std::memory_order_acquire) & bit)) return D3GA_OK;
+    const int rc = f();
+    if (rc == D3GA_OK && bit) mask.fetch_or(bit, std::memory_order_release);
+    return rc;
+}
+int device_sm_count();   // multiprocessors of the current device (cached per device)
+
 // stage launchers (defined in the per-stage .cu files)
 int launch_geometry(int P, int sh_degree, int sh_coeffs, const float *means3D, const float *scales,
                     float scale_modifier, const float *rotations, const float *opacities, const float *shs,
@@ -168,8 +184,8 @@ int launch_mark_visible(int P, const float *means3D, const float *viewmatrix, ui
 int launch_sort_and_ranges(int P, uint8_t *geom, const GeomLayout &GL, int gx, int gy, uint8_t *binning, const BinLayout &BL, uint64_t capacity, int sort_bits,
                            uint8_t *image, const ImgLayout &IL, int num_tiles, cudaStream_t stream);
 int launch_depth_sort(int P, uint8_t *geom, const GeomLayout &GL, cudaStream_t stream);
-enum SortMode { SORT_DEPTH_FIRST = 0, SORT_GLOBAL = 1, SORT_SEGMENTED = 2, SORT_DIRECT = 3 };
-int sort_mode();   // D3GA_SORT_MODE = direct (default) | depthfirst | global | segmented
+enum SortMode { SORT_DEPTH_FIRST = 0, SORT_GLOBAL = 1, SORT_DIRECT = 3 };
+int sort_mode();   // D3GA_SORT_MODE = direct (default) | depthfirst (its fallback) | global (upstream's order: cross-check)
 // the two modes that sort the Gaussians by depth first; `direct` falls back to `depthfirst` where its plan does not apply
 inline bool depth_first_mode(int mode) { return mode == SORT_DEPTH_FIRST || mode == SORT_DIRECT; }
 // Direct tile scatter (raster_direct.cu): rows of `chunk` depth-ordered Gaussians, one private tile histogram per row.
@@ -182,7 +198,10 @@ struct DirectPlan {
     uint32_t bands, band_rows, band_tiles_pad;   // the scatter's split of the image into bands of tile rows
     uint64_t seg_off, tot_off, start_off, ticket_off, before_off;   // byte offsets inside the unused key buffer
 };
-DirectPlan direct_plan(int P, int gx, int gy, uint64_t capacity);
+DirectPlan direct_plan(int P, int gx, int gy, uint64_t capacity);   // stage 1 only: reads the views-in-flight hint
+// the plan stage 1 used on this geometry workspace (false: no stage 1 has run on it with these sizes)
+void remember_direct_plan(const void *geom, int P, int gx, int gy, uint64_t capacity, const DirectPlan &pl);
+bool recall_direct_plan(const void *geom, int P, int gx, int gy, uint64_t capacity, DirectPlan *pl);
 void set_views_in_flight(int n);
 int launch_direct_count(int P, int gx, int gy, uint8_t *geom, const GeomLayout &GL, uint8_t *binning, const BinLayout &BL,
                         uint64_t capacity, const DirectPlan &pl, cudaStream_t stream);
@@ -193,8 +212,6 @@ int launch_copy_sorted_keys(const uint8_t *geom, const GeomLayout &GL, const uin
 int launch_direct_scatter(int P, int gx, int gy, uint8_t *geom, const GeomLayout &GL, uint8_t *binning, const BinLayout &BL,
                           uint64_t capacity, int sort_bits, uint8_t *image, const ImgLayout &IL, const DirectPlan &pl,
                           cudaStream_t stream);
-int launch_segment_sort(uint8_t *geom, uint8_t *binning, const BinLayout &BL, uint8_t *image, const ImgLayout &IL,
-                        int num_tiles, cudaStream_t stream);
 int launch_blend_forward(int W, int H, const float *background, const float *colors, const uint8_t *geom,
                          const GeomLayout &GL, const uint8_t *binning, const BinLayout &BL, uint8_t *image,
                          const ImgLayout &IL, float *out_color, float *out_invdepth, cudaStream_t stream);

@@ -519,13 +519,13 @@ int launch_blend_backward(int W, int H, const float *background, const float *co
     const uint32_t *n_contrib = reinterpret_cast<const uint32_t *>(image + IL.n_contrib);
     const uint32_t *order_bwd = reinterpret_cast<const uint32_t *>(image + IL.order_bwd);
     const size_t smem = sizeof(BwdWarpSmem) * (TILE_PIX / 32);
-    static const int attr_set = [] {
-        const int bytes = (int)(sizeof(BwdWarpSmem) * (TILE_PIX / 32));
-        cudaFuncSetAttribute(blend_backward_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
-        cudaFuncSetAttribute(blend_backward_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
-        return 1;
-    }();
-    (void)attr_set;
+    static std::atomic<uint64_t> attr_devices{0};
+    const int arc = once_per_device(attr_devices, [&]() -> int {
+        D3GA_CUDA(cudaFuncSetAttribute(blend_backward_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        D3GA_CUDA(cudaFuncSetAttribute(blend_backward_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        return D3GA_OK;
+    });
+    if (arc) return arc;
     ProfScope prof(K_BLEND_BWD, stream);
     {
         if (dL_dinvdepth_pix)

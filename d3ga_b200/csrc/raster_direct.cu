@@ -36,6 +36,7 @@
 // the scratch does not fit.
 #include <atomic>
 #include <cstdlib>
+#include <mutex>
 
 #include "common.cuh"
 
@@ -442,18 +443,31 @@ DirectParams make_params(int P, int gx, uint8_t *geom, const GeomLayout &GL, uin
     return p;
 }
 
-int set_smem_attrs() {   // per device: a function attribute belongs to the device that was current when it was set
-    static bool done[64] = {};
-    int dev = 0;
-    D3GA_CUDA(cudaGetDevice(&dev));
-    if (dev >= 0 && dev < 64 && done[dev]) return D3GA_OK;
-    const int scatter = 200 * 1024, plan = 4 * DIRECT_MAX_TILES, count = 4 * DIRECT_MAX_CELLS;
-    D3GA_CUDA(cudaFuncSetAttribute(direct_count_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, count));
-    D3GA_CUDA(cudaFuncSetAttribute(direct_scatter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, scatter));
-    D3GA_CUDA(cudaFuncSetAttribute(direct_plan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, plan));
-    if (dev >= 0 && dev < 64) done[dev] = true;
-    return D3GA_OK;
+int set_smem_attrs() {
+    static std::atomic<uint64_t> devices{0};
+    return once_per_device(devices, []() -> int {
+        const int scatter = 200 * 1024, plan = 4 * DIRECT_MAX_TILES, count = 4 * DIRECT_MAX_CELLS;
+        D3GA_CUDA(cudaFuncSetAttribute(direct_count_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, count));
+        D3GA_CUDA(cudaFuncSetAttribute(direct_scatter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, scatter));
+        D3GA_CUDA(cudaFuncSetAttribute(direct_plan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, plan));
+        return D3GA_OK;
+    });
 }
+
+// Stage 1 decides the plan -- it depends on the views-in-flight hint, a process-wide setting another thread may change at
+// any moment -- and files it under the geometry workspace it ran on; stage 2 (and d3ga_raster_sorted_keys) take the plan
+// from there instead of deciding again, so the two stages of a view can never disagree about rows, segments or offsets.
+struct PlanRecord {
+    int dev;
+    const void *geom;
+    int P, gx, gy;
+    uint64_t capacity;
+    DirectPlan plan;
+};
+constexpr int PLAN_RECORDS = 512;   // workspaces between their stage 1 and their last use of the plan
+std::mutex g_plan_mu;
+PlanRecord g_plans[PLAN_RECORDS];
+unsigned g_plan_next = 0;
 
 }  // namespace
 
@@ -489,8 +503,9 @@ DirectPlan direct_plan(int P, int gx, int gy, uint64_t capacity) {
         // times as long instead of all of them, which leaves the other views' kernels room beside it
         int vif = g_views_in_flight.load(std::memory_order_relaxed);
         if (vif < 1) vif = 1;
-        uint64_t rows_target = 148 * per_sm / pl.bands / (uint64_t)vif;
-        if (rows_target < 148) rows_target = 148;
+        const uint64_t sms = (uint64_t)device_sm_count();
+        uint64_t rows_target = sms * per_sm / pl.bands / (uint64_t)vif;
+        if (rows_target < sms) rows_target = sms;
         chunk = ((uint64_t)P + rows_target - 1) / rows_target;
         chunk = (chunk + 31) / 32 * 32;
         if (chunk < 256) chunk = 256;
@@ -562,6 +577,32 @@ int launch_copy_sorted_keys(const uint8_t *geom, const GeomLayout &GL, const uin
         reinterpret_cast<const uint64_t *>(binning + BL.keys1), keys_out);
     D3GA_LAUNCH_CHECK();
     return D3GA_OK;
+}
+
+void remember_direct_plan(const void *geom, int P, int gx, int gy, uint64_t capacity, const DirectPlan &pl) {
+    int dev = 0;
+    (void)cudaGetDevice(&dev);
+    std::lock_guard<std::mutex> lk(g_plan_mu);
+    for (int i = 0; i < PLAN_RECORDS; i++)
+        if (g_plans[i].geom == geom && g_plans[i].dev == dev) {
+            g_plans[i] = PlanRecord{dev, geom, P, gx, gy, capacity, pl};
+            return;
+        }
+    g_plans[g_plan_next++ % PLAN_RECORDS] = PlanRecord{dev, geom, P, gx, gy, capacity, pl};
+}
+bool recall_direct_plan(const void *geom, int P, int gx, int gy, uint64_t capacity, DirectPlan *pl) {
+    int dev = 0;
+    (void)cudaGetDevice(&dev);
+    std::lock_guard<std::mutex> lk(g_plan_mu);
+    for (int i = 0; i < PLAN_RECORDS; i++) {
+        const PlanRecord &r = g_plans[i];
+        if (r.geom == geom && r.dev == dev) {
+            if (r.P != P || r.gx != gx || r.gy != gy || r.capacity != capacity) return false;
+            *pl = r.plan;
+            return true;
+        }
+    }
+    return false;
 }
 
 void set_views_in_flight(int n) { g_views_in_flight.store(n < 1 ? 1 : (n > 64 ? 64 : n), std::memory_order_relaxed); }

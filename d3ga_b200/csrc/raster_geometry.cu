@@ -472,6 +472,7 @@ int launch_geometry(int P, int sh_degree, int sh_coeffs, const float *means3D, c
     p.P_pad = (uint32_t)GL.p_pad;
     p.tile_diff = nullptr;
     const DirectPlan direct = direct_plan(P, p.gx, p.gy, capacity);
+    remember_direct_plan(geom, P, p.gx, p.gy, capacity, direct);
     p.grec = direct.ok ? reinterpret_cast<uint4 *>(geom + GL.grec) : nullptr;
     if (depth_first_mode(sort_mode()) && !direct.ok && tile_plan_from_grid(p.gx, p.gy)) {
         p.tile_diff = reinterpret_cast<int32_t *>(geom + GL.tile_diff);

@@ -455,7 +455,17 @@ __global__ void __launch_bounds__(256) tile_ranges_kernel(RasterHeader *hdr, con
 
 }  // namespace
 
-static int g_sort_attr_set = 0;
+static int set_sort_attrs() {
+    static std::atomic<uint64_t> devices{0};
+    return once_per_device(devices, []() -> int {
+        D3GA_CUDA(cudaFuncSetAttribute(sort_pass_kernel<uint64_t, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       sort_smem_bytes<uint64_t>()));
+        D3GA_CUDA(cudaFuncSetAttribute(sort_pass_kernel<uint32_t, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       sort_smem_bytes<uint32_t>()));
+        D3GA_CUDA(cudaFuncSetAttribute(tile_plan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 8 * TILE_GRID_CELLS_MAX));
+        return D3GA_OK;
+    });
+}
 
 int launch_sort_and_ranges(int P, uint8_t *geom, const GeomLayout &GL, int gx, int gy, uint8_t *binning, const BinLayout &BL, uint64_t capacity, int sort_bits,
                            uint8_t *image, const ImgLayout &IL, int num_tiles, cudaStream_t stream) {
@@ -473,21 +483,17 @@ int launch_sort_and_ranges(int P, uint8_t *geom, const GeomLayout &GL, int gx, i
     const uint32_t tiles_cap = (uint32_t)sort_tiles(capacity);
     // depth-first (default): the duplicate list was emitted in depth order, only the tile digits are left to sort.
     // global   : the full 64-bit LSD sort (depth digits first, constant digits skipped).
-    // segmented: tile digits globally, then each tile's depths in shared memory (raster_segsort.cu).
     const int mode = sort_mode();
-    const bool segmented = mode == SORT_SEGMENTED;
     const int first_pass = mode == SORT_GLOBAL ? 0 : 4;
     // direct (default): no sort of the duplicates at all -- a stable counting scatter by tile (raster_direct.cu)
-    const DirectPlan direct = direct_plan(P, gx, gy, capacity);
+    DirectPlan direct;
+    if (!recall_direct_plan(geom, P, gx, gy, capacity, &direct)) return D3GA_ENOTREADY;   // stage 1 has not run on this workspace
     if (direct.ok)
         return launch_direct_scatter(P, gx, gy, geom, GL, binning, BL, capacity, sort_bits, image, IL, direct, stream);
 
-    if (!g_sort_attr_set) {
-        D3GA_CUDA(cudaFuncSetAttribute(sort_pass_kernel<uint64_t, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       sort_smem_bytes<uint64_t>()));
-        D3GA_CUDA(cudaFuncSetAttribute(sort_pass_kernel<uint32_t, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       sort_smem_bytes<uint32_t>()));
-        g_sort_attr_set = 1;
+    {
+        const int arc = set_sort_attrs();
+        if (arc) return arc;
     }
     D3GA_CUDA(cudaMemsetAsync(ghist, 0, 4 * 256 * SORT_MAX_PASSES, stream));
     D3GA_CUDA(cudaMemsetAsync(tile_state, 0, 4ull * 256 * tiles_cap * num_passes, stream));
@@ -497,11 +503,6 @@ int launch_sort_and_ranges(int P, uint8_t *geom, const GeomLayout &GL, int gx, i
     // histogram pass over the keys before and no ranges pass after the sort
     const bool from_grid = depth_first_mode(mode) && tile_plan_from_grid(gx, gy);
     if (from_grid) {
-        static const int attr_set = [] {
-            cudaFuncSetAttribute(tile_plan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 8 * TILE_GRID_CELLS_MAX);
-            return 1;
-        }();
-        (void)attr_set;
         ProfScope prof(K_TILE_PLAN, stream);
         tile_plan_kernel<<<1, 256, 4 * ((gx + 1) * (gy + 1) + gx * gy), stream>>>(
             hdr, reinterpret_cast<const int32_t *>(geom + GL.tile_diff), gx, gy, ranges, bins,
@@ -536,7 +537,6 @@ int launch_sort_and_ranges(int P, uint8_t *geom, const GeomLayout &GL, int gx, i
                                                    reinterpret_cast<uint32_t *>(image + IL.order_fwd));
     }
     D3GA_LAUNCH_CHECK();
-    if (segmented) return launch_segment_sort(geom, binning, BL, image, IL, num_tiles, stream);
     return D3GA_OK;
 }
 
@@ -549,12 +549,9 @@ int launch_depth_sort(int P, uint8_t *geom, const GeomLayout &GL, cudaStream_t s
     uint32_t *bins = reinterpret_cast<uint32_t *>(geom + GL.dep_bins);
     uint32_t *state = reinterpret_cast<uint32_t *>(geom + GL.dep_state);
     const uint32_t tiles = (uint32_t)((P + SORT_TILE - 1) / SORT_TILE);
-    if (!g_sort_attr_set) {
-        D3GA_CUDA(cudaFuncSetAttribute(sort_pass_kernel<uint64_t, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       sort_smem_bytes<uint64_t>()));
-        D3GA_CUDA(cudaFuncSetAttribute(sort_pass_kernel<uint32_t, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       sort_smem_bytes<uint32_t>()));
-        g_sort_attr_set = 1;
+    {
+        const int arc = set_sort_attrs();
+        if (arc) return arc;
     }
     D3GA_CUDA(cudaMemsetAsync(ghist, 0, 4 * 256 * 4, stream));
     D3GA_CUDA(cudaMemsetAsync(state, 0, 4ull * 256 * 4 * (tiles + 1), stream));

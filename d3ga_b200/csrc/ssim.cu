@@ -93,7 +93,8 @@ __global__ void __launch_bounds__(SS_T * SS_T) ssim_backward_kernel(int H, int W
                                                                    const float *__restrict__ dm_dmu1,
                                                                    const float *__restrict__ dm_dE11,
                                                                    const float *__restrict__ dm_dE12, float g_ssim,
-                                                                   float g_l1, float *__restrict__ dL_dimg1) {
+                                                                   float g_l1, const float *__restrict__ upstream,
+                                                                   float *__restrict__ dL_dimg1) {
     __shared__ float s[3][SS_W][SS_W + 1];
     __shared__ float h[3][SS_W][SS_T + 1];
     const int tx = threadIdx.x % SS_T, ty = threadIdx.x / SS_T, tid = threadIdx.x;
@@ -131,7 +132,8 @@ __global__ void __launch_bounds__(SS_T * SS_T) ssim_backward_kernel(int H, int W
     const float p = img1[o], q = img2[o];
     const float diff = p - q;
     const float sgn = diff > 0.f ? 1.f : (diff < 0.f ? -1.f : 0.f);
-    dL_dimg1[o] = g_ssim * (a + 2.f * p * b + q * d) + g_l1 * sgn;
+    const float up = upstream ? __ldg(upstream) : 1.f;   // dL/dloss, a device scalar: no host read-back in autograd
+    dL_dimg1[o] = up * (g_ssim * (a + 2.f * p * b + q * d) + g_l1 * sgn);
 }
 
 }  // namespace
@@ -163,13 +165,13 @@ extern "C" int d3ga_ssim_l1_forward(int C, int H, int W, const float *img1, cons
 
 extern "C" int d3ga_ssim_l1_backward(int C, int H, int W, const float *img1, const float *img2, const float *dm_dmu1,
                                      const float *dm_dE11, const float *dm_dE12, float g_ssim, float g_l1,
-                                     float *dL_dimg1, d3ga_stream_t stream_) {
+                                     const float *upstream, float *dL_dimg1, d3ga_stream_t stream_) {
     cudaStream_t stream = (cudaStream_t)stream_;
     if (C <= 0 || H <= 0 || W <= 0 || !img1 || !img2 || !dm_dmu1 || !dm_dE11 || !dm_dE12 || !dL_dimg1) return D3GA_EINVAL;
     const dim3 grid((W + SS_T - 1) / SS_T, (H + SS_T - 1) / SS_T, C);
     ProfScope prof(K_SSIM_BWD, stream);
     ssim_backward_kernel<<<grid, SS_T * SS_T, 0, stream>>>(H, W, img1, img2, make_window(), dm_dmu1, dm_dE11, dm_dE12,
-                                                           g_ssim, g_l1, dL_dimg1);
+                                                           g_ssim, g_l1, upstream, dL_dimg1);
     D3GA_LAUNCH_CHECK();
     return D3GA_OK;
 }

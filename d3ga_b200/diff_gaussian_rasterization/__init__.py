@@ -127,14 +127,32 @@ class deferred_overflow_check:
         return False
 
 
+def prepare_deferred(device, stream=None):
+    """Creates and zeroes -- eagerly -- the overflow counter of the forwards that will be enqueued or captured on `stream`
+    (default: the current stream) under deferred_overflow_check().  Must be called BEFORE a capture on that stream
+    begins: a counter first created inside `torch.cuda.graph(...)` would come from the graph's private pool and its
+    zero fill would be a node of the graph, i.e. every replay would wipe what the replays before it had recorded."""
+    s = torch.cuda.current_stream(device) if stream is None else stream
+    key = (device, s.cuda_stream)
+    t = _deferred_stats.get(key)
+    if t is None:
+        if torch.cuda.is_current_stream_capturing():
+            raise _lib.D3GAError("prepare_deferred() must run before the capture starts")
+        t = torch.zeros(1, dtype=torch.int64, device=device)
+        _deferred_stats[key] = t
+    return t
+
+
 def _deferred_stats_tensor(device):
     """One counter per (device, stream the forward is enqueued / captured on): graphs replayed concurrently on several
-    streams must not share a read-modify-write target."""
+    streams must not share a read-modify-write target.  The counter is one 64-bit word, overflow << 32 | num_rendered
+    -- the header's first two words read as they lie -- so a single signed maximum keeps the largest duplicate count of
+    the views that overflowed if any did (they are the ones above the capacity), else the largest count; a saturated
+    0xffffffff count does not turn negative."""
     key = (device, torch.cuda.current_stream(device).cuda_stream)
     t = _deferred_stats.get(key)
     if t is None:
-        t = torch.zeros(2, dtype=torch.int32, device=device)
-        _deferred_stats[key] = t
+        t = prepare_deferred(device)
     return t
 
 
@@ -146,11 +164,12 @@ def collect_deferred(device):
     ts = [t for (dev, _), t in _deferred_stats.items() if dev == device]
     if not ts:
         return 0, False
-    allt = torch.stack(ts).amax(0).cpu()
+    word = int(torch.stack(ts).amax(0).cpu()[0])
     for t in ts:
         t.zero_()
-    d, ovf = int(allt[0]), int(allt[1])
-    d &= 0xFFFFFFFF
+    d, ovf = word & 0xFFFFFFFF, word >> 32
+    if ovf and d >= (1 << 31) - 1:   # the eager path raises here too; growing the workspace cannot help
+        raise _lib.D3GAError(f"{d} (tile, Gaussian) duplicates exceed the 2^31-1 limit")
     key = _deferred_key.get(device)
     if key is not None and d:
         need = min((1 << 31) - 1, int(d * CAPACITY_SLACK) + 4096)
@@ -186,18 +205,34 @@ class RasterState:
 
 
 def _shared_forward(lib, dev, P, W, H, rs, colors_precomp, want_invdepth, gkey, cam):
-    """Second render of the same geometry: blend only.  Returns None on a cache miss."""
+    """Second render of the same geometry: blend only.  Returns None on a cache miss.
+
+    The camera must be the same.  When the caller passes the very tensors of the first render (same storage, same
+    version) that is known without looking at them -- no synchronisation, and the call can sit inside a graph capture.
+    Otherwise (renderer.py builds a fresh Camera, i.e. fresh uploads, per render) the values are compared on the device;
+    the blend is enqueued BEHIND the comparison before the host waits for its verdict, so the GPU has work while the
+    host reads the flag (the eager forward waits for the duplicate count at the same place), and on a mismatch -- the
+    same Gaussians from another camera, which D3GA never does within a frame -- the speculative blend is discarded and
+    the full forward runs."""
     ent = _geom_cache.get(dev)
     if ent is None:
         return None
-    same = None
-    for a, b in zip(ent["cam"], cam):   # equal camera? compared on the device, one read-back
-        if a.shape != b.shape:
-            return None
-        e = (a == b).all()
-        same = e if same is None else (same & e)
-    if not bool(same.item()):
-        return None
+    identical = all(a.shape == b.shape and a.data_ptr() == b.data_ptr() and v == b._version
+                    for (a, v), b in zip(ent["cam"], cam))
+    verdict = ev = None
+    if not identical:
+        if _defer_depth > 0 or torch.cuda.is_current_stream_capturing():
+            return None          # nothing may wait here
+        same = None
+        for (a, _), b in zip(ent["cam"], cam):
+            if a.shape != b.shape:
+                return None
+            e = (a == b).all()
+            same = e if same is None else (same & e)
+        verdict = _pinned_counter(dev)
+        verdict[:1].copy_(same.to(torch.int32).reshape(1), non_blocking=True)
+        ev = torch.cuda.Event()
+        ev.record()
     src = ent["state"]
     with _lib.device_guard(dev):
         stream = _lib.raw_stream(dev)
@@ -211,8 +246,16 @@ def _shared_forward(lib, dev, P, W, H, rs, colors_precomp, want_invdepth, gkey, 
             P, W, H, _f32c(rs.bg, "bg").data_ptr(), _lib.ptr(colors_precomp), st.geom.data_ptr(), st.binning.data_ptr(),
             st.capacity, src.image.data_ptr(), st.image.data_ptr(), color.data_ptr(), _lib.ptr(invdepth), stream),
             "raster_forward_blend")
+    if ev is not None:
+        ev.synchronize()
+        if not int(verdict[0]):
+            return None
     share_stats["hits"] += 1
-    return color, ent["radii"].clone(), invdepth, st
+    radii = ent["radii"].clone()
+    # a training frame renders twice (models/trainer.py:102-110): the pair is complete, stop pinning the first render's
+    # workspaces (its autograd node still owns them until its backward has run)
+    _geom_cache.pop(dev, None)
+    return color, radii, invdepth, st
 
 
 def rasterize_forward(means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp, rs,
@@ -271,7 +314,7 @@ def rasterize_forward(means3D, sh, colors_precomp, opacities, scales, rotations,
             if defer:
                 # (num_rendered, overflow) are the first two words of the geometry workspace's header
                 stats = _deferred_stats_tensor(dev)
-                torch.maximum(stats, st.geom[:8].view(torch.int32), out=stats)
+                torch.maximum(stats, st.geom[:8].view(torch.int64), out=stats)
                 _deferred_key[dev] = key
                 st.num_rendered = -1
                 D = None
@@ -292,7 +335,7 @@ def rasterize_forward(means3D, sh, colors_precomp, opacities, scales, rotations,
     if D is not None:
         last_stats.update(num_rendered=D, capacity=st.capacity)
     if gkey is not None:
-        cam = (rs.viewmatrix.detach(), rs.projmatrix.detach(), rs.campos.detach())
+        cam = tuple((t.detach(), t._version) for t in (rs.viewmatrix, rs.projmatrix, rs.campos))
         _geom_cache[dev] = {"key": gkey, "cam": cam, "state": st, "radii": radii,
                             "tensors": tuple(None if t is None else (t.detach(), t._version) for t in geo_now)}
         share_stats["misses"] += 1

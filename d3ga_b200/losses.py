@@ -42,12 +42,12 @@ class _SsimL1(torch.autograd.Function):
         H, W = int(p.shape[-2]), int(p.shape[-1])
         C = p.numel() // (H * W)
         dev = p.device
-        go = float(grad_out)   # scalar upstream gradient (one read-back; the loss is the end of the graph in train.py)
+        go = grad_out.to(torch.float32).reshape(1).contiguous()   # dL/dloss stays on the device: no host sync in backward
         with _lib.device_guard(dev):
             out = torch.empty_like(p)
             _lib.check(lib.d3ga_ssim_l1_backward(
                 C, H, W, p.data_ptr(), g.data_ptr(), maps[0].data_ptr(), maps[1].data_ptr(), maps[2].data_ptr(),
-                go * w_ssim / n, go * w_l1 / n, out.data_ptr(), _lib.raw_stream(dev)), "ssim_l1_backward")
+                w_ssim / n, w_l1 / n, go.data_ptr(), out.data_ptr(), _lib.raw_stream(dev)), "ssim_l1_backward")
         return out, None, None, None
 
 

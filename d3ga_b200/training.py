@@ -218,19 +218,29 @@ class GraphedViewStep:
         self.replays = 0
         self.captures = 0
 
-    def capture(self, cam_row):
-        """Warm up eagerly on a side stream (sizes the capacity hint, fills the allocator), then capture one view."""
+    def capture(self, cam_row, warm=True):
+        """Warm up eagerly on a side stream (sizes the capacity hint, fills the allocator), then capture one view.
+        warm=False captures against the capacity hint as it stands (tests use it to provoke an overflow)."""
         from d3ga_b200 import _lib
         self.cam.copy_(cam_row, non_blocking=True)
-        keep = self.avatar.grads.flat.clone()            # the warm-up views must not leak into the caller's gradients
-        side = torch.cuda.Stream(device=self.avatar.device)
-        side.wait_stream(torch.cuda.current_stream())
-        with torch.cuda.stream(side):
-            for _ in range(2):
-                view_step(self.avatar, self.rs, self.weights)
-        torch.cuda.current_stream().wait_stream(side)
-        self.avatar.grads.flat.copy_(keep)
+        if warm:
+            # an eager view sets the capacity hint from ITS duplicate count; the graph must be sized for the largest view
+            # seen so far (collect_deferred raised the hint after an overflow), so the warm-up may only raise it
+            hkey = (self.avatar.device, self.avatar.N, self.avatar.W, self.avatar.H)
+            hint = self.dgr._capacity_hint.get(hkey, 0)
+            keep = self.avatar.grads.flat.clone()        # the warm-up views must not leak into the caller's gradients
+            side = torch.cuda.Stream(device=self.avatar.device)
+            side.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(side):
+                for _ in range(2):
+                    view_step(self.avatar, self.rs, self.weights)
+            torch.cuda.current_stream().wait_stream(side)
+            self.avatar.grads.flat.copy_(keep)
+            self.dgr._capacity_hint[hkey] = max(hint, self.dgr._capacity_hint.get(hkey, 0))
         torch.cuda.synchronize()
+        # the overflow counter of this lane must exist (and be zero) before the capture: created inside it, its zero fill
+        # would be replayed with every view and only the last view of a step would ever be seen
+        self.dgr.prepare_deferred(self.avatar.device, self.capture_stream)
         self.graph = torch.cuda.CUDAGraph()
         l0 = _lib.launch_count()
         # the launch configurations baked into the graph are sized for `views_in_flight` concurrent replays (the direct
@@ -245,7 +255,6 @@ class GraphedViewStep:
             lib.d3ga_set_views_in_flight(1)
         self.launches_per_replay = _lib.launch_count() - l0
         self.captures += 1
-        self.dgr.collect_deferred(self.avatar.device)   # the capture itself launched nothing; clear the counter
 
     def run(self, cam_row, weights=None):
         """One view: cam_row [35] (device or pinned host), weights None = already in self.weights."""
@@ -324,11 +333,14 @@ class PipelinedViews:
         for st in self.streams:
             main.wait_stream(st)
         flat = self.avatar.grads.flat
-        torch.add(self.shadows[0].grads.flat, self.shadows[1].grads.flat, out=flat)
-        for sh in self.shadows[2:]:
-            flat.add_(sh.grads.flat)
-        total = self.gvs[0].total + self.gvs[1].total
-        for g in self.gvs[2:]:
+        if len(self.shadows) == 1:
+            flat.copy_(self.shadows[0].grads.flat)
+        else:
+            torch.add(self.shadows[0].grads.flat, self.shadows[1].grads.flat, out=flat)
+            for sh in self.shadows[2:]:
+                flat.add_(sh.grads.flat)
+        total = self.gvs[0].total.clone()
+        for g in self.gvs[1:]:
             total = total + g.total
         _, overflowed = self.gvs[0].finish()
         return total, overflowed

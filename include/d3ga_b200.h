@@ -80,16 +80,19 @@ int d3ga_mark_visible(int P, const float *means3D, const float *viewmatrix, cons
 /* Sizing hint (no counterpart in the reference): how many independent views the caller keeps in flight on separate
  * streams (d3ga_b200.training.PipelinedViews does; default 1).  The direct tile scatter sizes its rows so that one view's
  * scatter occupies about 1/n of the GPU for n times as long -- alone that is slower, with n views in flight it leaves the
- * other views' kernels room beside it (measured at n = 4: +6 % views/s).  Results do not depend on it.  Process-wide; both
- * stages of a view must see the same value.  d3ga_b200.training sets it only while it captures a view's CUDA graph (the
- * launch configurations are baked into the graph) and restores 1, so eager calls keep the single-view sizing. */
+ * other views' kernels room beside it (measured at n = 4: +6 % views/s).  Results do not depend on it.  Process-wide, and
+ * read by stage 1 (d3ga_raster_forward_geometry) ONLY: stage 1 files the row plan it chose under the geometry workspace
+ * it ran on, and stage 2 / d3ga_raster_sorted_keys take the plan from there (D3GA_ENOTREADY when no stage 1 has run on
+ * that workspace with the same sizes), so changing the hint between the two stages of a view -- from another thread,
+ * say -- cannot make them disagree.  d3ga_b200.training sets it only while it captures a view's CUDA graph (the launch
+ * configurations are baked into the graph) and restores 1, so eager calls keep the single-view sizing. */
 void d3ga_set_views_in_flight(int n);
 
 /* Which binning strategy the two forward stages will use for these sizes (measurement and tests; no counterpart in the
  * reference): 1 = direct tile scatter (the default where it applies: the N Gaussians are sorted by depth, stage 1 only
  * COUNTS the duplicates per tile, stage 2 stores every duplicate once, straight into its final slot of the sorted list --
  * no unsorted duplicate list exists after stage 1); 0 = a radix sort of the duplicate list that stage 1 emitted
- * (D3GA_SORT_MODE=depthfirst|global|segmented, tile grids beyond 49152 tiles, or a capacity too small to hold the
+ * (D3GA_SORT_MODE=depthfirst|global, tile grids beyond 49152 tiles, or a capacity too small to hold the
  * scatter's count rows).  Either way the sorted list, the ranges and num_rendered are bit-identical. */
 int d3ga_raster_binning_path(int P, int W, int H, uint64_t capacity);
 
@@ -248,12 +251,14 @@ int d3ga_fem_energy_backward(int T, int V, const float *tetpoints, const int64_t
  * autograd backward, as combined at train.py:190-193.  img1 (prediction), img2 (target): [C,H,W] f32.
  * Forward: sums[0] = sum of the SSIM map, sums[1] = sum of |img1 - img2| (device, 2 floats, overwritten); the three
  * derivative maps [C,H,W] are optional (all or none) and only needed for the backward.
- * Backward: dL_dimg1 = g_ssim * dSSIMsum/dimg1 + g_l1 * sign(img1 - img2)  (written). */
+ * Backward: dL_dimg1 = u * (g_ssim * dSSIMsum/dimg1 + g_l1 * sign(img1 - img2))  (written); u = *upstream, the scalar
+ * dL/dloss in DEVICE memory (autograd's grad_output: no host read-back, so the loss can sit inside a captured graph),
+ * or 1 when upstream is null. */
 int d3ga_ssim_l1_forward(int C, int H, int W, const float *img1, const float *img2, float *sums, float *dm_dmu1,
                          float *dm_dE11, float *dm_dE12, d3ga_stream_t stream);
 int d3ga_ssim_l1_backward(int C, int H, int W, const float *img1, const float *img2, const float *dm_dmu1,
-                          const float *dm_dE11, const float *dm_dE12, float g_ssim, float g_l1, float *dL_dimg1,
-                          d3ga_stream_t stream);
+                          const float *dm_dE11, const float *dm_dE12, float g_ssim, float g_l1, const float *upstream,
+                          float *dL_dimg1, d3ga_stream_t stream);
 
 /* ---- cage-vertex linear blend skinning -------------------------------------------
  * The step that produces `tetpoints` right before the deformation.  Quaternions are (x, y, z, w); joint matrices

@@ -14,7 +14,8 @@ def section(buf, off, count, dtype):
     return buf[off:off + nbytes].cpu().numpy().view(dtype).copy()
 
 
-def forward_stages(g, cam, W, H, bg, path="precomp", aa=False, capacity=None, invdepth=True, stop_after=None):
+def forward_stages(g, cam, W, H, bg, path="precomp", aa=False, capacity=None, invdepth=True, stop_after=None,
+                   between_stages=None):
     """Runs d3ga_raster_forward_geometry (+ d3ga_raster_forward_render) and returns every intermediate as numpy."""
     lib = _lib.load()
     P = g["means"].shape[0]
@@ -62,6 +63,8 @@ def forward_stages(g, cam, W, H, bg, path="precomp", aa=False, capacity=None, in
                           campos=campos, bg=bgt, geom=geom, binning=binning, image=image, radii=radii, M=M)
     if stop_after == "geometry" or overflow:
         return out
+    if between_stages is not None:
+        between_stages()
     color = torch.zeros((3, H, W), dtype=torch.float32, device="cuda")
     inv = torch.zeros((1, H, W), dtype=torch.float32, device="cuda") if invdepth else None
     _lib.check(lib.d3ga_raster_forward_render(P, W, H, bgt.data_ptr(), _lib.ptr(col), geom.data_ptr(),

@@ -11,10 +11,10 @@ from d3ga_b200 import synth, training
 pytestmark = pytest.mark.gpu
 
 
-def setup(name="tiny"):
+def setup(name="tiny", n_cams=8):
     dev = torch.device("cuda", 0)
     scene = synth.make_workload(name)
-    cams = synth.camera_ring(scene.W, scene.H, 8)
+    cams = synth.camera_ring(scene.W, scene.H, n_cams)
     avatar = training.Avatar(scene, dev)
     bank = training.CameraBank(cams, dev)
     bg = torch.ones(3, device=dev)
@@ -88,21 +88,44 @@ def test_graphed_step_recovers_from_overflow(cuda_lib):
     # shrink the hint and capture again without the eager warm-up correcting it
     small = 64
     dgr._capacity_hint[key] = small
-    gv.graph = torch.cuda.CUDAGraph()
-    from d3ga_b200 import _lib
-    l0 = _lib.launch_count()
-    with dgr.deferred_overflow_check(), torch.cuda.graph(gv.graph):
-        loss = training.view_step(avatar, gv.rs, gv.weights)
-        gv.total += loss.detach()
-    gv.launches_per_replay = _lib.launch_count() - l0
-    del loss          # a live loss keeps this capture's autograd nodes (bound to its capture stream) alive
-    dgr.collect_deferred(dev)
+    gv.capture(bank.dev[0], warm=False)
     before = gv.captures
     tot_g = training.multi_view_step_graphed(avatar, bank, ids, gv, weights=w).clone()
     assert gv.captures == before + 1, "the overflow must force a re-capture"
     assert dgr._capacity_hint[key] > small
     assert abs(float(tot_g) - float(tot_e)) <= 1e-5 * abs(float(tot_e))
     assert rel(avatar.grads.flat, g_e) < 1e-5
+
+
+def test_overflow_of_a_middle_view_is_seen(cuda_lib):
+    """Only the MIDDLE view of a lane overflows its binning workspace (the views around it fit): the step must still
+    notice, re-capture and equal the eager result.  The counter of a lane is created before its capture; when it was
+    first touched inside the capture every replay wiped it and only a step's last view was ever checked -- an
+    overflowed view in the middle rendered background only, silently."""
+    dev, scene, cams, avatar, bank, bg, wh = setup(n_cams=16)
+    w = wh.to(dev)
+    Ds = []
+    for i in range(len(cams)):
+        training.multi_view_step(avatar, bank, [i], w, bg)
+        Ds.append(int(dgr.last_stats["num_rendered"]))
+    small, big = int(np.argmin(Ds)), int(np.argmax(Ds))
+    assert Ds[big] > Ds[small] + 8
+    for lanes in (1, 2):
+        ids = [small, big, small] if lanes == 1 else [small, small, big, big, small, small]
+        tot_e = training.multi_view_step(avatar, bank, ids, w, bg).clone()
+        g_e = avatar.grads.flat.clone()
+        key = (dev, scene.N, scene.W, scene.H)
+        pv = training.PipelinedViews(avatar, cams[small], bg, lanes=lanes)
+        pv.capture(bank.dev[small])
+        dgr._capacity_hint[key] = Ds[big] - 4          # fits every view but the big one
+        for g in pv.gvs:
+            g.capture(bank.dev[small], warm=False)
+        before = pv.captures
+        tot = training.multi_view_step_pipelined(avatar, bank, ids, pv, weights=w).clone()
+        assert pv.captures == before + lanes, "the overflow of the middle view must force a re-capture"
+        assert dgr._capacity_hint[key] >= Ds[big]
+        assert abs(float(tot) - float(tot_e)) <= 1e-5 * abs(float(tot_e))
+        assert rel(avatar.grads.flat, g_e) < 1e-5
 
 
 def test_tet_sorted_storage_is_the_same_avatar(cuda_lib):

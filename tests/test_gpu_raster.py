@@ -146,10 +146,10 @@ def test_capacity_overflow_is_reported_and_retried(cuda_lib, oracle_libs):
     assert_image_close(img.detach().cpu().numpy(), ref["color"])
 
 
-def render_api(g, cam, W, H, path="precomp", grads=False):
+def render_api(g, cam, W, H, path="precomp", grads=False, device="cuda"):
     from d3ga_b200.diff_gaussian_rasterization import GaussianRasterizationSettings, GaussianRasterizer
 
-    d = gpu_util.dev
+    d = lambda a: gpu_util.dev(a).to(device)  # noqa: E731
     rs = GaussianRasterizationSettings(
         image_height=H, image_width=W, tanfovx=cam.tanfovx, tanfovy=cam.tanfovy, bg=d(np.asarray(BG, np.float32)),
         scale_modifier=1.0, viewmatrix=d(cam.viewmatrix), projmatrix=d(cam.projmatrix), sh_degree=3,
@@ -270,17 +270,64 @@ def test_views_in_flight_hint_changes_nothing_but_the_row_length(cuda_lib, oracl
         assert a["num_rendered"] == b["num_rendered"]
 
 
-def test_segmented_sort_mode_is_bit_exact_too(cuda_lib, oracle_libs):
-    """The alternative binning strategies (D3GA_SORT_MODE=depthfirst: depth sort of the Gaussians, emission in depth order,
-    radix passes on the tile digits; =global: one 64-bit LSD sort of the duplicates in Gaussian
-    order, like upstream; =segmented: tile digits globally + per-tile depth sort in shared memory) are chosen when the
-    library first sorts, so each is exercised in a fresh process; all must give the same lists as the default."""
+def test_hint_flipped_between_the_stages_changes_nothing(cuda_lib, oracle_libs):
+    """Stage 1 files the row plan it chose with the workspace and stage 2 takes it from there: a views-in-flight hint that
+    changes BETWEEN the two stages of a view (another thread, a capture in progress) must not touch the lists.  Before,
+    both stages derived the plan from the process-wide hint and a flip silently corrupted the sorted list."""
+    sc = synth.make_workload("c1")
+    means, cov6 = util.scene_geometry(sc)
+    g = dict(means=means, cov6=cov6, opacity=sc.opacity, colors=sc.colors)
+    cam = synth.make_camera(sc.W, sc.H, 20, 10)
+    lib = cuda_lib
+    ref = gpu_util.forward_stages(g, cam, sc.W, sc.H, [1, 1, 1])
+    assert ref["direct"]
+    try:
+        for first, second in ((1, 16), (16, 1), (4, 64)):
+            lib.d3ga_set_views_in_flight(first)
+            got = gpu_util.forward_stages(g, cam, sc.W, sc.H, [1, 1, 1], between_stages=lambda: lib.d3ga_set_views_in_flight(second))
+            assert np.array_equal(ref["point_list"], got["point_list"]) and np.array_equal(ref["keys"], got["keys"])
+            assert np.array_equal(ref["ranges"], got["ranges"]) and np.array_equal(ref["color"], got["color"])
+    finally:
+        lib.d3ga_set_views_in_flight(1)
+    # stage 2 on a workspace no stage 1 has run on is refused, not guessed
+    t = ref["tensors"]
+    geom2 = t["geom"].clone()
+    out = torch.zeros((3, sc.H, sc.W), device="cuda")
+    rc = lib.d3ga_raster_forward_render(ref["P"], sc.W, sc.H, t["bg"].data_ptr(), t["col"].data_ptr(), geom2.data_ptr(),
+                                        t["binning"].data_ptr(), ref["capacity"], t["image"].data_ptr(), out.data_ptr(), None,
+                                        torch.cuda.current_stream().cuda_stream)
+    assert rc == -4   # D3GA_ENOTREADY
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs in one process")
+def test_second_device_in_one_process(cuda_lib, oracle_libs):
+    """Function attributes (the dynamic shared-memory opt-ins of the blend backward, the sorts and the scatter) are
+    per device: a view on cuda:1 after one on cuda:0 in the same process must launch and match the oracle."""
+    g, cam, W, H = CASES["tiny_avatar"]
+    orc, ref = util.oracle_forward(g, cam, W, H, BG)
+    w = np.random.default_rng(4).uniform(-1, 1, (3, H, W)).astype(np.float32)
+    rg = orc.backward(ref, w)
+    for d in (0, 1, 0):
+        with torch.cuda.device(d):
+            img, out, t, _ = render_api(g, cam, W, H, grads=True, device=f"cuda:{d}")
+            (img * torch.from_numpy(w).to(img.device)).sum().backward()
+            torch.cuda.synchronize()
+            assert_image_close(img.detach().cpu().numpy(), ref["color"])
+            for a, b in (("means", "means3D"), ("opacity", "opacity"), ("colors", "colors"), ("cov6", "cov3D")):
+                assert util.rel_l2(t[a].grad.cpu().numpy(), rg[b]) < GRAD_TOL, (d, a)
+
+
+def test_other_binning_modes_are_bit_exact_too(cuda_lib, oracle_libs):
+    """The two other binning strategies (D3GA_SORT_MODE=depthfirst: the fallback for tile grids the scatter cannot take --
+    depth sort of the Gaussians, emission in depth order, radix passes on the tile digits; =global: one 64-bit LSD sort of
+    the duplicates in Gaussian order, upstream's own sequence, kept as a cross-check) are chosen when the library first
+    sorts, so each is exercised in a fresh process; both must give the same lists as the default."""
     import os
     import subprocess
     import sys
 
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-    for mode in ("depthfirst", "global", "segmented"):
+    for mode in ("depthfirst", "global"):
         env = dict(os.environ, D3GA_SORT_MODE=mode)
         r = subprocess.run([sys.executable, "-m", "pytest", "-q", "-x", "-m", "gpu",
                             os.path.join(root, "tests", "test_gpu_raster.py"), "-k",
