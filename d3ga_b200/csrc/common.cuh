@@ -55,6 +55,7 @@ struct GeomLayout {
     uint64_t rect_pack, dkeys, dvals, dep_hist, dep_bins, dep_state, tile_diff, total;   // depth-first binning
     uint64_t ordered;    // direct tile scatter: the Gaussians' packed records in depth order (16 B each)
     uint64_t grec;       // ... and in Gaussian order, as the preprocess wrote them
+    uint64_t splat;      // what the blend kernels gather per list entry: 2 x float4 per Gaussian (SplatRecord below)
     uint64_t p_pad;
 };
 struct BinLayout {
@@ -62,8 +63,21 @@ struct BinLayout {
     uint64_t tile_state_bytes;
 };
 struct ImgLayout {
-    uint64_t ranges, final_T, n_contrib, order_fwd, order_bwd, tile_nproc, total;
+    uint64_t ranges, final_T, n_contrib, order_fwd, order_bwd, tile_nproc, ballots, total;
 };
+// The blend kernels' per-Gaussian gather: ONE 32-byte sector, two 16-byte loads (before: xy 8 B + conic/opacity 16 B +
+// depth 4 B from three arrays).  The conic is pre-scaled to the log2 domain (log2 G = A dx^2 + B dx dy + C dy^2) and the
+// footprint bound of the per-block cull comes with it, so no logarithm is evaluated per (warp, list entry).
+//   g0 = (x, y, lim2, opacity)      g1 = (A, B, C, 1 / depth)
+//   lim2: a pixel block can hold a pixel with alpha >= 1/255 only if max over the block of (A dx^2 + B dx dy + C dy^2)
+//         >= lim2;  +inf = never (opacity below 1/255), -inf = never culled (degenerate conic)
+struct SplatRecord {
+    float4 g0, g1;
+};
+static_assert(sizeof(SplatRecord) == 32, "one sector per Gaussian");
+// Survivor ballots of the forward blend, replayed by the backward: one word per (32-entry chunk of a tile's list, warp).
+// Tile t's chunks start at word row (range.x / 32 + t): consecutive tiles never overlap (ceil(n / 32) <= n / 32 + 1).
+__host__ __device__ inline uint64_t ballot_rows(uint64_t capacity, uint64_t tiles) { return capacity / 32 + tiles + 1; }
 
 __host__ __device__ inline uint64_t align256(uint64_t x) { return (x + 255) & ~uint64_t(255); }
 
@@ -90,6 +104,7 @@ inline GeomLayout geom_layout(int P) {
     L.tile_diff = o;     o = align256(o + 4ull * TILE_GRID_CELLS_MAX);   // 2-D difference grid of the tile rects
     L.ordered = o;       o = align256(o + 16 * L.p_pad);
     L.grec = o;          o = align256(o + 16 * L.p_pad);
+    L.splat = o;         o = align256(o + 32 * p);
     L.total = o;
     return L;
 }
@@ -109,7 +124,7 @@ inline BinLayout bin_layout(uint64_t capacity) {
     L.total = o;
     return L;
 }
-inline ImgLayout img_layout(int W, int H) {
+inline ImgLayout img_layout(int W, int H, uint64_t capacity) {
     ImgLayout L;
     uint64_t o = 0, tiles = (uint64_t)((W + TILE - 1) / TILE) * ((H + TILE - 1) / TILE), px = (uint64_t)W * H;
     L.ranges = o;    o = align256(o + 8 * tiles);
@@ -118,6 +133,7 @@ inline ImgLayout img_layout(int W, int H) {
     L.order_fwd = o;  o = align256(o + 4 * tiles);   // tiles, longest list first (blend forward launch order)
     L.order_bwd = o;  o = align256(o + 4 * tiles);   // tiles, deepest contributor first (blend backward)
     L.tile_nproc = o; o = align256(o + 4 * tiles);   // max over the tile's pixels of n_contrib
+    L.ballots = o;    o = align256(o + 4ull * 8 * ballot_rows(capacity, tiles));
     L.total = o;
     return L;
 }

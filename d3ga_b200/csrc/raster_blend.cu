@@ -4,16 +4,29 @@
 // and from autograd when models/trainer.py:186-192 calls loss.backward()).
 //
 // One CTA per 16x16 tile (longest list first), one thread per pixel, one warp per 8x4 pixel block.  Each warp walks the
-// tile's depth-sorted list ON ITS OWN -- 32 Gaussians per step, one per lane, gathered a step ahead in registers (ids two
-// steps ahead), tested exactly against the warp's pixel block (footprint_hit), and only the survivors are parked
-// (compacted, in list order) in a per-warp ring in shared memory from which the blend loop takes them in groups.  There
-// is no CTA barrier in the loop: with batches staged by the whole CTA a third of all warp-stall samples sat on that
-// barrier, because per-warp culling gives the eight warps of a tile very different amounts of work.  A warp whose pixels
-// are all finished simply stops.  The price is that the eight warps each read the tile's list (they run close enough
-// together that seven of them hit in L1) and each evaluate the footprint test.  Front to back in the forward, back to
-// front over the prefix its own pixels reached in the backward.
+// tile's depth-sorted list ON ITS OWN, 32 entries per step (one per lane), with no CTA barrier in the loop (with batches
+// staged by the whole CTA a third of all warp-stall samples sat on that barrier: per-warp culling gives the eight warps
+// of a tile very different amounts of work).  A warp whose pixels are all finished simply stops.
+//
+// What a list entry costs (round 2).  The per-Gaussian gather is ONE 32-byte sector: the SplatRecord the preprocess
+// writes (centre, opacity, conic pre-scaled to the log2 domain, 1/depth and the footprint bound lim2), two 16-byte loads,
+// fetched a step ahead in registers.  The footprint test of the warp's pixel block (footprint_hit) needs nothing else --
+// no logarithm, no determinant per (warp, entry).  Only the SURVIVORS (28 % on the 1 M-Gaussian avatar) are staged: their
+// record goes into a per-warp ring in shared memory and their colour is copied global -> shared by cp.async straight
+// from the caller's [N,3] tensor (three 4-byte copies; no register round trip, no wait: the ring is consumed one step
+// later).  The forward writes its survivor ballots -- one word per (chunk, warp), 1 B per duplicate -- and the BACKWARD
+// REPLAYS them: it never tests a footprint and never touches a Gaussian that did not survive; its survivors' records and
+// colours all arrive by cp.async.
+//   [TMA note: cp.async.bulk needs contiguous sources; a tile's survivors are an index gather of 32-byte records, so the
+//    per-thread cp.async (LDGSTS) is the asynchronous copy that fits.  A bulk copy would need the records re-packed in
+//    list order first: +64 B per duplicate of streaming writes and reads for lists of which 30 % (forward) and 14 %
+//    (backward) are ever visited.]
+//
 // Forward semantics (same order of tests as upstream): skip power > 0, alpha = min(.99, o * exp(power)), skip
-// alpha < 1/255, stop the pixel when T * (1 - alpha) < 1e-4, out = C + T * bg.
+// alpha < 1/255, stop the pixel when T * (1 - alpha) < 1e-4, out = C + T * bg.  alpha is evaluated with one ex2.approx on
+// the pre-scaled conic; when it lands within 2e-5 (relative) of the 1/255 cut the CUT -- not the value -- is decided again
+// in upstream's operation order with a correctly rounded exponential (exact_cut; taken ~1e-6 of the time), so that the
+// set of contributors is the reference's and not a function of this kernel's rounding.  The backward decides identically.
 //
 // Backward: every (pixel, Gaussian) pair owes the per-Gaussian accumulator nine or ten partial sums: the six raw moments
 // of p = G dL/dalpha about the Gaussian's 2-D centre (sum p dx, p dy, p dx^2, p dx dy, p dy^2, p -- the preprocess backward
@@ -27,23 +40,31 @@
 // duplicate + 20 B per pixel.  Both kernels are issue / latency bound rather than HBM bound.
 // Measured and dropped: persistent CTAs with a per-CTA tile queue or a per-CTA block dispenser (the warps of a tile drift
 // apart, the list no longer hits in L1: 273 -> 333-386 us backward), 2 or 4 warps per CTA, 4 CTAs/SM in the backward.
+#include <math_constants.h>
+
 #include "common.cuh"
 
 namespace d3ga {
 
 namespace {
 
-// Conic pre-scaled for the inner loop: log2(G) = A dx^2 + B dx dy + C dy^2 with A = -0.5 log2(e) conic.xx, B = -log2(e)
-// conic.xy, C = -0.5 log2(e) conic.yy, so G = exp2(.) costs one MUFU and no extra multiply.
-constexpr float LOG2E = 1.4426950408889634f;
-__device__ __forceinline__ float4 prescale_conic(float4 co) {
-    return make_float4(-0.5f * LOG2E * co.x, -LOG2E * co.y, -0.5f * LOG2E * co.z, co.w);
-}
 __device__ __forceinline__ float fast_exp2(float x) {
     float y;
     asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
     return y;
 }
+// Asynchronous global -> shared copies (LDGSTS): the data never passes through registers and the issuing lane does not
+// wait; cp_async_wait_all() + __syncwarp() make a warp's earlier copies visible to all its lanes.
+__device__ __forceinline__ void cp_async_16(void *smem_dst, const void *gmem_src) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(smem_dst)),
+                 "l"(gmem_src) : "memory");
+}
+__device__ __forceinline__ void cp_async_4(void *smem_dst, const void *gmem_src) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((uint32_t)__cvta_generic_to_shared(smem_dst)),
+                 "l"(gmem_src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 
 // Each warp owns an 8x4 pixel block of the 16x16 tile (compact blocks cull better than 16x2 strips).
 struct WarpBlock {
@@ -64,6 +85,8 @@ __device__ __forceinline__ WarpBlock warp_block(int tid, int tile_x, int tile_y)
 
 constexpr int RING = 64;                     // per-warp ring of staged survivors (>= group - 1 + 32)
 constexpr int FWD_WARPS = TILE_PIX / 32;    // (splitting a tile over 2 or 4 smaller CTAs was measured: no gain)
+constexpr float CUT = 1.f / 255.f;
+constexpr float CUT_BAND = 2e-5f;            // |255 alpha - 1| below which the cut is decided by exact_cut()
 #ifndef FWD_MIN_CTAS
 #define FWD_MIN_CTAS 3                       // 80 registers, no spills: 165 us; 4 CTAs/SM (64 registers, spills): 181 us
 #endif
@@ -71,77 +94,88 @@ constexpr int FWD_WARPS = TILE_PIX / 32;    // (splitting a tile over 2 or 4 sma
 #define BWD_MIN_CTAS 3
 #endif
 #ifdef D3GA_BLEND_STATS
-// development counters: [0..3] forward (warp-steps, survivors, groups, passing pixel-Gaussian pairs), [4..7] backward
+// development counters: [0..3] forward (warp-steps, survivors, groups, exact cuts), [4..7] backward
 __device__ unsigned long long g_blend_stats[8];
-__device__ unsigned long long *g_blend_trace = nullptr;   // [tiles * 8][4]: start ns, end ns, (smid << 32 | steps), survivors
-__device__ __forceinline__ unsigned long long global_ns() {
-    unsigned long long t;
-    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-    return t;
-}
-#ifdef D3GA_BLEND_TRACE_ONLY   // the counters cost a global atomic per step; the trace alone does not perturb the timing
-#define STAT_ADD(i, v) do { } while (0)
-#else
 #define STAT_ADD(i, v) do { const unsigned long long _t = (unsigned long long)(v); if (_t) atomicAdd(&g_blend_stats[i], _t); } while (0)
-#endif
 #else
 #define STAT_ADD(i, v) do { } while (0)
 #endif
 
-// Exact version of the footprint test for one warp's pixel block: does the ellipse d^T C d <= 2 tau (outside of which
-// alpha < 1/255: power >= -tau with tau = ln(255 o) bounds d^T C d <= 2 tau) reach any pixel centre of the block?  The quadratic is convex with its minimum at
-// the Gaussian centre, so when the centre lies outside the block its minimum over the block sits on the edge(s) facing
-// the centre; on an edge it is a 1-D quadratic, minimised in closed form and clamped.  A relative and an absolute
-// margin keep the test conservative against rounding (a false "hit" only costs time, the per-pixel test decides);
-// degenerate conics are never culled.  Rejects the diagonal, elongated splats the bounding box lets through.
-__device__ __forceinline__ bool footprint_hit(float2 c, float4 co, const WarpBlock &wb) {
-    if (co.w < 1.f / 255.f) return false;   // can never pass the cut
-    const float det = co.x * co.z - co.y * co.y;
-    const float tau = __logf(255.f * co.w);
-    if (!(det > 0.f) || !(tau >= 0.f) || !(co.x > 0.f) || !(co.z > 0.f)) return true;
-    const float lim = 2.f * tau * 1.002f + 0.01f;
-    const float xl = wb.x0 - c.x, xh = wb.x1 - c.x, yl = wb.y0 - c.y, yh = wb.y1 - c.y;
+// Can the Gaussian reach a pixel centre of the warp's block with alpha >= 1/255?  alpha = o 2^q2(d) with
+// q2 = A dx^2 + B dx dy + C dy^2 <= 0, so the question is whether max over the block of q2 >= log2(1 / (255 o)).  q2 is
+// concave with its maximum at the centre: when the centre lies outside the block the maximum over the block sits on the
+// edge(s) facing it, where q2 is a 1-D parabola, maximised in closed form and clamped to the edge.  lim2 (SplatRecord)
+// carries the bound with a relative and an absolute margin, so the test is conservative against rounding (a false hit
+// only costs time, the per-pixel test decides); +inf = opacity below the cut, -inf = degenerate conic, never culled.
+// Rejects the diagonal, elongated splats the bounding box lets through.
+__device__ __forceinline__ bool footprint_hit(const float4 g0, const float4 g1, const WarpBlock &wb) {
+    const float xl = wb.x0 - g0.x, xh = wb.x1 - g0.x, yl = wb.y0 - g0.y, yh = wb.y1 - g0.y;
     const bool in_x = xl <= 0.f && xh >= 0.f, in_y = yl <= 0.f && yh >= 0.f;
-    if (in_x && in_y) return true;
-    float qmin = INFINITY;
+    float qmax = -CUDART_INF_F;
     if (!in_x) {
         const float dx = xl > 0.f ? xl : xh;
-        const float dy = fminf(fmaxf(__fdividef(-co.y * dx, co.z), yl), yh);
-        qmin = co.x * dx * dx + 2.f * co.y * dx * dy + co.z * dy * dy;
+        const float dy = fminf(fmaxf(__fdividef(-0.5f * g1.y * dx, g1.z), yl), yh);
+        qmax = dx * (g1.x * dx + g1.y * dy) + g1.z * dy * dy;
     }
     if (!in_y) {
         const float dy = yl > 0.f ? yl : yh;
-        const float dx = fminf(fmaxf(__fdividef(-co.y * dy, co.x), xl), xh);
-        qmin = fminf(qmin, co.x * dx * dx + 2.f * co.y * dx * dy + co.z * dy * dy);
+        const float dx = fminf(fmaxf(__fdividef(-0.5f * g1.y * dy, g1.x), xl), xh);
+        qmax = fmaxf(qmax, dx * (g1.x * dx + g1.y * dy) + g1.z * dy * dy);
     }
-    return qmin <= lim;
+    return g0.z < CUDART_INF_F && ((in_x && in_y) || !(qmax < g0.z));
 }
+
+// The 1/255 cut of one (pixel, Gaussian) pair decided the way the oracle (and upstream) decide it: power in upstream's
+// operation order -- individually rounded, no contraction -- and a correctly rounded exponential (double exp rounded to
+// float; glibc's expf is correctly rounded in all but ~1e-9 of the cases).  Out of line: reached when the fast alpha is
+// within CUT_BAND of the cut, about once per million pairs.
+__device__ __noinline__ bool exact_cut(const float2 *__restrict__ xy, const float4 *__restrict__ conic_opacity, uint32_t id,
+                                       float pxf, float pyf) {
+    const float2 c = xy[id];
+    const float4 co = conic_opacity[id];
+    const float dx = __fsub_rn(c.x, pxf), dy = __fsub_rn(c.y, pyf);
+    const float t = __fadd_rn(__fmul_rn(__fmul_rn(co.x, dx), dx), __fmul_rn(__fmul_rn(co.z, dy), dy));
+    const float power = __fsub_rn(__fmul_rn(-0.5f, t), __fmul_rn(__fmul_rn(co.y, dx), dy));
+    if (power > 0.f) return false;
+    const float alpha = fminf(0.99f, __fmul_rn(co.w, (float)exp((double)power)));
+    return alpha >= CUT;
+}
+
+// The walk of a tile's list is a per-lane software pipeline in shared memory: lane l of a warp owns entry l of every
+// 32-entry chunk and keeps the copies of FWD_DEPTH chunks in flight (cp.async: 2 x 16 B of SplatRecord + 3 x 4 B of
+// colour per entry, into a slot only this lane reads and refills -- no cross-lane hazard, no barrier).  Entry ids run two
+// more chunks ahead in registers.  The critical path of a step holds no global load: a heavy tile's warp used to wait
+// for its one-step-ahead register prefetch on every chunk (ncu: long-scoreboard the top stall of the forward, the
+// busiest SM active for the whole kernel, the average SM for half of it).
+constexpr int FWD_DEPTH = 4;
+struct FwdWarpSmem {
+    float4 ring[RING][3];                 // staged survivors: [0] x, y, list position + 1 (bits), -   [1] conic, opacity
+                                          //                   [2] r, g, b, 1/depth
+    float4 stage[FWD_DEPTH][3][32];       // chunks in flight: [chunk][g0 | g1 | colour][lane]
+};
 
 template <bool INVDEPTH>
 __global__ void __launch_bounds__(FWD_WARPS * 32, FWD_MIN_CTAS) blend_forward_kernel(
     const RasterHeader *__restrict__ hdr, const uint2 *__restrict__ ranges, const uint32_t *__restrict__ vals0,
-    const uint32_t *__restrict__ vals1, int W, int H, const float2 *__restrict__ xy,
-    const float4 *__restrict__ conic_opacity, const float *__restrict__ colors, const float *__restrict__ depths,
+    const uint32_t *__restrict__ vals1, int W, int H, const SplatRecord *__restrict__ splat,
+    const float *__restrict__ colors, const float2 *__restrict__ xy, const float4 *__restrict__ conic_opacity,
     const float *__restrict__ bg, float *__restrict__ final_T, uint32_t *__restrict__ n_contrib,
     float *__restrict__ out_color, float *__restrict__ out_invdepth, RasterHeader *__restrict__ hdr_rw, int grid_x,
     int num_tiles, const uint32_t *__restrict__ order_fwd, uint32_t *__restrict__ tile_nproc,
-    uint32_t *__restrict__ order_bwd) {
-    __shared__ float4 s_a[FWD_WARPS][RING];      // x, y, list position + 1 (bits), unused
-    __shared__ float4 s_co[FWD_WARPS][RING];     // pre-scaled conic, opacity
-    __shared__ float4 s_feat[FWD_WARPS][RING];   // r, g, b, 1/depth
+    uint32_t *__restrict__ order_bwd, uint32_t *__restrict__ ballots) {
+    extern __shared__ __align__(16) unsigned char s_raw[];
     __shared__ uint32_t s_bins[257];
     __shared__ uint32_t s_last;
+    const int tid = threadIdx.x;
+    const uint32_t lane = tid & 31, warp = tid >> 5;
+    FwdWarpSmem &sm = reinterpret_cast<FwdWarpSmem *>(s_raw)[warp];
 
     // The blend loop below is branch-free: entries of a partly filled last group are multiplied by a weight of zero
     // rather than skipped, so a ring slot that was never written must not hold a NaN or Inf bit pattern.
-    for (int i = threadIdx.x; i < FWD_WARPS * RING; i += FWD_WARPS * 32) (&s_feat[0][0])[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-    __syncthreads();
-    constexpr uint32_t SPLIT = 8 / FWD_WARPS;          // CTAs per tile
-    const uint32_t tile = order_fwd[blockIdx.x / SPLIT];   // longest Gaussian list first
-    const int tid = threadIdx.x;
-    const uint32_t lane = tid & 31, warp = tid >> 5;
-    const WarpBlock wb = warp_block((int)((blockIdx.x % SPLIT) * FWD_WARPS + warp), (int)lane,
-                                    (int)(tile % (uint32_t)grid_x), (int)(tile / (uint32_t)grid_x));
+    for (int i = (int)lane; i < RING * 3; i += 32) (&sm.ring[0][0])[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    __syncwarp();
+    const uint32_t tile = order_fwd[blockIdx.x];   // longest Gaussian list first
+    const WarpBlock wb = warp_block((int)warp, (int)lane, (int)(tile % (uint32_t)grid_x), (int)(tile / (uint32_t)grid_x));
     const int px = wb.px, py = wb.py;
     const bool inside = px < W && py < H;
     const float pxf = (float)px, pyf = (float)py;
@@ -150,89 +184,124 @@ __global__ void __launch_bounds__(FWD_WARPS * 32, FWD_MIN_CTAS) blend_forward_ke
     const uint32_t *point_list = (hdr->final_sel ? vals1 : vals0) + range.x;
     const uint32_t count = range.y - range.x;
     const uint32_t nchunks = (count + 31u) / 32u;
+    uint32_t *ballot_w = ballots + ((size_t)(range.x >> 5) + tile) * 8 + warp;   // + 8 per chunk
 
     bool done = !inside;
     float T = 1.f, C0 = 0.f, C1 = 0.f, C2 = 0.f, invd = 0.f;
     uint32_t last = 0;
-    float4(*ra)[RING] = s_a, (*rco)[RING] = s_co, (*rfeat)[RING] = s_feat;
-#ifdef D3GA_BLEND_STATS
-    const unsigned long long tr_t0 = global_ns();
-    unsigned tr_steps = 0, tr_surv = 0;
-#endif
-
-    float2 p_xy = make_float2(0.f, 0.f);
-    float4 p_co = make_float4(0.f, 0.f, 0.f, 0.f), p_feat = make_float4(0.f, 0.f, 0.f, 0.f);
-    auto gather = [&](uint32_t id) {
-        p_xy = xy[id];
-        p_co = conic_opacity[id];
-        p_feat = make_float4(colors[3 * (size_t)id], colors[3 * (size_t)id + 1], colors[3 * (size_t)id + 2],
-                             INVDEPTH ? depths[id] : 1.f   /* raw depth: dividing here would wait for the load */);
-    };
-    // ids run two steps ahead of the blend, the Gaussians themselves one step
-    uint32_t id_next = 0;
-    if (lane < count) gather(point_list[lane]);
-    if (32u + lane < count) id_next = point_list[32u + lane];
     uint32_t head = 0, tail = 0;
-    const bool warp_active = !__all_sync(0xffffffffu, done);
-    for (uint32_t c = 0; c < nchunks && warp_active; c++) {
-        const uint32_t pos = c * 32u + lane;
-        bool hit = false;
-        if (pos < count) hit = footprint_hit(p_xy, p_co, wb);
-        const uint32_t m = __ballot_sync(0xffffffffu, hit);
-        if (hit) {
-            const uint32_t slot = (tail + __popc(m & lanemask_lt())) & (RING - 1);
-            ra[warp][slot] = make_float4(p_xy.x, p_xy.y, __uint_as_float(pos + 1u), 0.f);
-            rco[warp][slot] = prescale_conic(p_co);
-            rfeat[warp][slot] = make_float4(p_feat.x, p_feat.y, p_feat.z, INVDEPTH ? __fdividef(1.f, p_feat.w) : 0.f);
+    bool all_done = __all_sync(0xffffffffu, done);
+
+    // this lane's copies of one chunk entry: record + colour -> its private slot of stage `st`
+    auto fetch = [&](uint32_t st, uint32_t id) {
+        cp_async_16(&sm.stage[st][0][lane], &splat[id].g0);
+        cp_async_16(&sm.stage[st][1][lane], &splat[id].g1);
+        const float *csrc = colors + 3 * (size_t)id;
+        float *cdst = reinterpret_cast<float *>(&sm.stage[st][2][lane]);
+        cp_async_4(cdst, csrc);
+        cp_async_4(cdst + 1, csrc + 1);
+        cp_async_4(cdst + 2, csrc + 2);
+    };
+    // prologue: FWD_DEPTH chunks in flight (one commit group per chunk, empty ones included), ids of the next two
+    uint32_t id_a = 0, id_b = 0;   // ids of this lane's entries in chunks c + FWD_DEPTH and c + FWD_DEPTH + 1
+    if (!all_done) {
+#pragma unroll
+        for (uint32_t j = 0; j < (uint32_t)FWD_DEPTH; j++) {
+            if (j * 32u + lane < count) fetch(j, point_list[j * 32u + lane]);
+            cp_async_commit();
         }
-        tail += __popc(m);
-        if (lane == 0) { STAT_ADD(0, 1); STAT_ADD(1, __popc(m)); }
-#ifdef D3GA_BLEND_STATS
-        tr_steps++; tr_surv += __popc(m);
-#endif
-        if (pos + 32u < count) gather(id_next);                      // in flight while the ring is blended
-        if (pos + 64u < count) id_next = point_list[pos + 64u];
-        __syncwarp();
-        const bool flush = c + 1u == nchunks;
-        bool all_done = false;
-        // four ring entries at a time (head stays a multiple of four, so a group never wraps): their alphas are
-        // independent; the transmittance recurrence that follows is branch-free
+        if ((uint32_t)FWD_DEPTH * 32u + lane < count) id_a = point_list[(uint32_t)FWD_DEPTH * 32u + lane];
+        if ((uint32_t)(FWD_DEPTH + 1) * 32u + lane < count) id_b = point_list[(uint32_t)(FWD_DEPTH + 1) * 32u + lane];
+    }
+
+    // Blends the staged survivors, four ring entries at a time (head stays a multiple of four, so a group never wraps):
+    // their alphas are independent; the transmittance recurrence that follows is branch-free.
+    auto consume = [&](bool flush) {
         while (tail - head >= 4u || (flush && tail != head)) {
             const uint32_t avail = min(4u, tail - head);
-            const uint32_t base = head & (RING - 1);
-            const float4 *ga = &ra[warp][base], *gco = &rco[warp][base], *gf = &rfeat[warp][base];
+            const float4(*g)[3] = sm.ring + (head & (RING - 1));
             float a[4];
             uint32_t posv[4];
+            float nearest = 1.f;
 #pragma unroll
             for (int u = 0; u < 4; u++) {
-                const float4 e = ga[u];
+                const float4 e = g[u][0];
                 const float dx = e.x - pxf, dy = e.y - pyf;
-                const float4 co = gco[u];   // pre-scaled: log2 domain
+                const float4 co = g[u][1];   // pre-scaled: log2 domain
                 const float power = dx * (co.x * dx + co.y * dy) + co.z * dy * dy;
                 const float alpha = fminf(0.99f, co.w * fast_exp2(power));
-                a[u] = ((uint32_t)u < avail && !(power > 0.f) && alpha >= 1.f / 255.f) ? alpha : 0.f;
+                const bool keep = (uint32_t)u < avail && !(power > 0.f) && alpha >= CUT;
+                a[u] = keep ? alpha : 0.f;
+                nearest = fminf(nearest, fabsf(fmaf(alpha, 255.f, -1.f)));
                 posv[u] = __float_as_uint(e.z);
             }
-            if (lane == 0) STAT_ADD(2, 1);
+            if (nearest < CUT_BAND) {   // ~1e-6 of the pairs: the contributor set must not depend on this kernel's rounding
+#pragma unroll
+                for (int u = 0; u < 4; u++) {
+                    const float4 e = g[u][0];
+                    const float4 co = g[u][1];
+                    const float dx = e.x - pxf, dy = e.y - pyf;
+                    const float alpha = fminf(0.99f, co.w * fast_exp2(dx * (co.x * dx + co.y * dy) + co.z * dy * dy));
+                    if ((uint32_t)u < avail && fabsf(fmaf(alpha, 255.f, -1.f)) < CUT_BAND) {
+                        a[u] = exact_cut(xy, conic_opacity, point_list[posv[u] - 1u], pxf, pyf) ? alpha : 0.f;
+                        STAT_ADD(3, 1);
+                    }
+                }
+            }
+            // Transmittance recurrence, branch-free.  `done` is sticky; T never drops below 1e-4 (it is only updated when
+            // the product stays above), so an entry with alpha = 0 cannot trip the stop, and after the stop every weight
+            // is zero.  T (1 - alpha) is rounded like upstream's (subtract, then multiply): the stop decision is theirs.
 #pragma unroll
             for (int u = 0; u < 4; u++) {
-                const float4 f = gf[u];
+                const float4 f = g[u][2];
                 const float test_T = T * (1.f - a[u]);
-                const bool live = !done && a[u] != 0.f;
-                const bool stop = live && test_T < 0.0001f;
-                const bool upd = live && !stop;
-                done = done || stop;
-                const float w = upd ? a[u] * T : 0.f;
+                done = done | (test_T < 0.0001f);
+                const float w = done ? 0.f : a[u] * T;
+                T = done ? T : test_T;
                 C0 += f.x * w; C1 += f.y * w; C2 += f.z * w;
                 if (INVDEPTH) invd += f.w * w;
-                T = upd ? test_T : T;
-                last = upd ? posv[u] : last;
+                last = w != 0.f ? posv[u] : last;
             }
             head += avail;
             if (__all_sync(0xffffffffu, done)) { all_done = true; break; }
         }
-        if (all_done) break;
+    };
+
+    for (uint32_t c = 0; c < nchunks && !all_done; c++) {
+        // this lane's entry of chunk c has landed when at most FWD_DEPTH - 1 younger groups are still in flight
+        asm volatile("cp.async.wait_group %0;" ::"n"(FWD_DEPTH - 1) : "memory");
+        const uint32_t st = c % (uint32_t)FWD_DEPTH;
+        const uint32_t pos = c * 32u + lane;
+        float4 g0 = make_float4(0.f, 0.f, CUDART_INF_F, 0.f), g1 = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (pos < count) {
+            g0 = sm.stage[st][0][lane];
+            g1 = sm.stage[st][1][lane];
+        }
+        const bool hit = pos < count && footprint_hit(g0, g1, wb);
+        const uint32_t m = __ballot_sync(0xffffffffu, hit);
+        if (lane == 0) {
+            ballot_w[(size_t)c * 8] = m;     // replayed by the backward
+            STAT_ADD(0, 1); STAT_ADD(1, __popc(m));
+        }
+        if (hit) {
+            const float4 col = sm.stage[st][2][lane];
+            float4 *slot = sm.ring[(tail + __popc(m & lanemask_lt())) & (RING - 1)];
+            slot[0] = make_float4(g0.x, g0.y, __uint_as_float(pos + 1u), 0.f);
+            slot[1] = make_float4(g1.x, g1.y, g1.z, g0.w);
+            slot[2] = make_float4(col.x, col.y, col.z, g1.w);
+        }
+        tail += __popc(m);
+        // refill the slot with this lane's entry of chunk c + FWD_DEPTH; ids two further chunks ahead
+        const uint32_t ahead = pos + (uint32_t)FWD_DEPTH * 32u;
+        if (ahead < count) fetch(st, id_a);
+        cp_async_commit();
+        id_a = id_b;
+        if (ahead + 64u < count) id_b = point_list[ahead + 64u];
+        __syncwarp();
+        consume(false);
     }
+    if (!all_done) consume(true);
+    cp_async_wait_all();   // nothing may still be landing in shared memory when the CTA retires
     if (inside) {
         const size_t pid = (size_t)py * W + px, plane = (size_t)H * W;
         final_T[pid] = T;
@@ -242,14 +311,6 @@ __global__ void __launch_bounds__(FWD_WARPS * 32, FWD_MIN_CTAS) blend_forward_ke
         out_color[2 * plane + pid] = C2 + T * bg[2];
         if (INVDEPTH) out_invdepth[pid] = invd;
     }
-#ifdef D3GA_BLEND_STATS
-    if (g_blend_trace && lane == 0) {
-        unsigned sm;
-        asm("mov.u32 %0, %%smid;" : "=r"(sm));
-        unsigned long long *o = g_blend_trace + 4 * ((size_t)blockIdx.x * FWD_WARPS + warp);
-        o[0] = tr_t0; o[1] = global_ns(); o[2] = ((unsigned long long)sm << 32) | tr_steps; o[3] = ((unsigned long long)count << 32) | tr_surv;
-    }
-#endif
     // deepest contributor of the tile = how far the backward has to go; the last CTA orders the backward's tiles
     const uint32_t wmax = __reduce_max_sync(0xffffffffu, inside ? last : 0u);
     if (lane == 0 && wmax) atomicMax(tile_nproc + tile, wmax);   // zeroed by the launcher
@@ -278,24 +339,28 @@ __global__ void __launch_bounds__(FWD_WARPS * 32, FWD_MIN_CTAS) blend_forward_ke
 constexpr int NB = 16;             // Gaussians per turn-around
 constexpr int NB_PITCH = 33;       // floats per Gaussian row: lanes of both halves hit 32 different banks
 struct BwdWarpSmem {
-    float4 ring_a[RING];           // x, y, Gaussian id (bits), forward list position (bits)
-    float4 ring_co[RING];          // pre-scaled conic, opacity
-    float4 ring_feat[RING];        // r, g, b, 1/depth
+    // per staged survivor 48 contiguous bytes, all landing by cp.async:
+    //   [0] SplatRecord.g0 as it lies in global memory: x, y, (lim2), opacity   [1] SplatRecord.g1: pre-scaled conic, 1/depth
+    //   [2] r, g, b (from the colour tensor), unused
+    float4 ring[RING][3];
+    uint2 ring_m[RING];            // Gaussian id, forward list position
     float4 meta[NB];               // x, y, Gaussian id (bits) of the parked Gaussians
     float4 dpix[32];               // dL/dpixel (r, g, b, inverse depth) of the block's pixels
     float p[NB * NB_PITCH];
     float aT[NB * NB_PITCH];
 };
 
+// (Out of line: inlined at every place a group can fill the park, the kernel was ~95 KB of code and a tenth of its
+// issue slots were lost waiting for instructions.)
 template <bool INVDEPTH>
-__device__ __forceinline__ void backward_turn_around(BwdWarpSmem &sm, int n, uint32_t lane, const WarpBlock &wb,
-                                                     float *__restrict__ grad_acc) {
+__device__ __noinline__ void backward_turn_around(BwdWarpSmem &sm, int n, uint32_t lane, float bx0, float by0,
+                                                  float *__restrict__ grad_acc) {
     const int g = (int)(lane & 15u), h = (int)(lane >> 4);
     float S0 = 0.f, Sx = 0.f, Sy = 0.f, Sxx = 0.f, Sxy = 0.f, Syy = 0.f, c0 = 0.f, c1 = 0.f, c2 = 0.f, c3 = 0.f;
     const float4 m = sm.meta[g];
     if (g < n) {
         // pixel q = 16 h + l of the block sits at (x0 + l % 8, y0 + 2 h + l / 8);  d = centre - pixel
-        const float X0 = m.x - wb.x0, Y0 = m.y - (wb.y0 + (float)(2 * h));
+        const float X0 = m.x - bx0, Y0 = m.y - (by0 + (float)(2 * h));
         const float *pp = sm.p + g * NB_PITCH + 16 * h, *pa = sm.aT + g * NB_PITCH + 16 * h;
         const float4 *pw = sm.dpix + 16 * h;
 #pragma unroll
@@ -328,11 +393,11 @@ __device__ __forceinline__ void backward_turn_around(BwdWarpSmem &sm, int n, uin
 template <bool INVDEPTH>
 __global__ void __launch_bounds__(TILE_PIX, BWD_MIN_CTAS) blend_backward_kernel(
     const RasterHeader *__restrict__ hdr, const uint2 *__restrict__ ranges, const uint32_t *__restrict__ vals0,
-    const uint32_t *__restrict__ vals1, int W, int H, const float *__restrict__ bg, const float2 *__restrict__ xy,
-    const float4 *__restrict__ conic_opacity, const float *__restrict__ colors, const float *__restrict__ depths,
-    const float *__restrict__ final_T, const uint32_t *__restrict__ n_contrib, const float *__restrict__ dL_dpix,
-    const float *__restrict__ dL_dinvdepth_pix, float *__restrict__ grad_acc, int grid_x,
-    const uint32_t *__restrict__ order_bwd) {
+    const uint32_t *__restrict__ vals1, int W, int H, const float *__restrict__ bg,
+    const SplatRecord *__restrict__ splat, const float *__restrict__ colors, const float2 *__restrict__ xy,
+    const float4 *__restrict__ conic_opacity, const float *__restrict__ final_T, const uint32_t *__restrict__ n_contrib,
+    const float *__restrict__ dL_dpix, const float *__restrict__ dL_dinvdepth_pix, float *__restrict__ grad_acc,
+    int grid_x, const uint32_t *__restrict__ order_bwd, const uint32_t *__restrict__ ballots) {
     extern __shared__ __align__(16) unsigned char s_raw[];
     const int tid = threadIdx.x;
     const uint32_t lane = tid & 31, warp = tid >> 5;
@@ -347,6 +412,7 @@ __global__ void __launch_bounds__(TILE_PIX, BWD_MIN_CTAS) blend_backward_kernel(
     if (!hdr->overflow) range = ranges[tile];
     if (range.y <= range.x) return;
     const uint32_t *point_list = (hdr->final_sel ? vals1 : vals0) + range.x;
+    const uint32_t *ballot_w = ballots + ((size_t)(range.x >> 5) + tile) * 8 + warp;   // + 8 per forward chunk
     const size_t pid = (size_t)py * W + px, plane = (size_t)H * W;
 
     const float T_final = inside ? final_T[pid] : 0.f;
@@ -355,7 +421,6 @@ __global__ void __launch_bounds__(TILE_PIX, BWD_MIN_CTAS) blend_backward_kernel(
     // this warp only walks the prefix of the list that reached one of ITS pixels in the forward, back to front
     const uint32_t n_proc = __reduce_max_sync(0xffffffffu, last_contributor);
     if (n_proc == 0) return;
-    const uint32_t nchunks = (n_proc + 31u) / 32u;
 
     float behind = 0.f;
     float g0 = 0.f, g1 = 0.f, g2 = 0.f, gi = 0.f;
@@ -366,70 +431,65 @@ __global__ void __launch_bounds__(TILE_PIX, BWD_MIN_CTAS) blend_backward_kernel(
     sm.dpix[lane] = make_float4(g0, g1, g2, gi);
     const float bg_term = T_final * (bg[0] * g0 + bg[1] * g1 + bg[2] * g2);
 
-    uint32_t p_id = 0, id_next = 0;
-    float2 p_xy = make_float2(0.f, 0.f);
-    float4 p_co = make_float4(0.f, 0.f, 0.f, 0.f), p_feat = make_float4(0.f, 0.f, 0.f, 0.f);
-    auto gather = [&](uint32_t id) {
-        p_id = id;
-        p_xy = xy[id];
-        p_co = conic_opacity[id];
-        p_feat = make_float4(colors[3 * (size_t)id], colors[3 * (size_t)id + 1], colors[3 * (size_t)id + 2],
-                             INVDEPTH ? depths[id] : 1.f   /* raw depth: dividing here would wait for the load */);
-    };
-    // lane l of step c looks at forward position q = n_proc - 1 - (32 c + l)
-    if (lane < n_proc) gather(point_list[n_proc - 1u - lane]);
-    if (32u + lane < n_proc) id_next = point_list[n_proc - 33u - lane];
+    // The forward's chunks, last one first; lane l of a step looks at forward position q = 32 fc + 31 - l, so that the
+    // compaction (lower lanes first) keeps the back-to-front order.  The forward's ballot of (chunk, warp) says which of
+    // the 32 entries reached this warp's pixel block: nothing else is gathered, no footprint is tested again.
+    const int top = (int)((n_proc - 1u) >> 5);
+    const uint32_t top_mask = ((n_proc - 1u) & 31u) == 31u ? 0xffffffffu : ((2u << ((n_proc - 1u) & 31u)) - 1u);
+    // ballots and ids run two steps ahead in registers
+    uint32_t m_next = __ldg(ballot_w + (size_t)top * 8) & top_mask;
+    uint32_t id_next = point_list[min(32u * (uint32_t)top + 31u - lane, n_proc - 1u)];
+    uint32_t m_next2 = 0, id_next2 = 0;
+    if (top > 0) {
+        m_next2 = __ldg(ballot_w + (size_t)(top - 1) * 8);
+        id_next2 = point_list[32u * (uint32_t)(top - 1) + 31u - lane];
+    }
     uint32_t head = 0, tail = 0;
     int nb = 0;                     // Gaussians parked for the next turn-around
-    for (uint32_t c = 0; c < nchunks; c++) {
-        const uint32_t back = c * 32u + lane;
-        bool hit = false;
-        if (back < n_proc) hit = footprint_hit(p_xy, p_co, wb);
-        const uint32_t m = __ballot_sync(0xffffffffu, hit);
-        if (hit) {
-            const uint32_t s = (tail + __popc(m & lanemask_lt())) & (RING - 1);
-            sm.ring_a[s] = make_float4(p_xy.x, p_xy.y, __uint_as_float(p_id), __uint_as_float(n_proc - 1u - back));
-            sm.ring_co[s] = prescale_conic(p_co);
-            sm.ring_feat[s] = make_float4(p_feat.x, p_feat.y, p_feat.z, INVDEPTH ? __fdividef(1.f, p_feat.w) : 0.f);
-        }
-        tail += __popc(m);
-        if (lane == 0) { STAT_ADD(4, 1); STAT_ADD(5, __popc(m)); }
-        if (back + 32u < n_proc) gather(id_next);
-        if (back + 64u < n_proc) id_next = point_list[n_proc - 65u - back];
-        __syncwarp();
-        const bool flush = c + 1u == nchunks;
-        // phase 1, four ring entries at a time (head stays a multiple of four: a group never wraps): the forward's
-        // alphas, evaluated independently, then the transmittance recurrence entry by entry
+
+    // phase 1, four ring entries at a time (head stays a multiple of four: a group never wraps): the forward's
+    // alphas, evaluated independently, then the transmittance recurrence entry by entry
+    auto consume = [&](bool flush) {
         while (tail - head >= 4u || (flush && tail != head)) {
             const uint32_t avail = min(4u, tail - head);
             const uint32_t base = head & (RING - 1);
-            float G_[4], al[4], ex[4], ey[4], eid[4];
+            const float4(*g)[3] = sm.ring + base;
+            float G_[4], al[4], ex[4], ey[4];
+            uint32_t eid[4];
             bool ok[4];
+            uint32_t near = 0;
 #pragma unroll
             for (int u = 0; u < 4; u++) {
-                const float4 e = sm.ring_a[base + u];
-                ex[u] = e.x; ey[u] = e.y; eid[u] = e.z;
+                const float4 e = g[u][0];     // x, y, -, opacity
+                const float4 co = g[u][1];    // pre-scaled conic (log2 domain): exactly the forward's alpha
+                const uint2 mq = sm.ring_m[base + u];
+                ex[u] = e.x; ey[u] = e.y; eid[u] = mq.x;
                 const float dx = e.x - pxf, dy = e.y - pyf;
-                const float4 co = sm.ring_co[base + u];   // pre-scaled (log2 domain): exactly the forward's alpha
                 const float power = dx * (co.x * dx + co.y * dy) + co.z * dy * dy;
                 const float G = fast_exp2(power);
-                const float alpha = fminf(0.99f, co.w * G);
-                ok[u] = (uint32_t)u < avail && __float_as_uint(e.w) < last_contributor && !(power > 0.f) &&
-                        alpha >= 1.f / 255.f;
+                const float alpha = fminf(0.99f, e.w * G);
+                const bool mine = (uint32_t)u < avail && mq.y < last_contributor;
+                ok[u] = mine && !(power > 0.f) && alpha >= CUT;
+                near |= (mine && fabsf(fmaf(alpha, 255.f, -1.f)) < CUT_BAND) ? (1u << u) : 0u;
                 G_[u] = G; al[u] = alpha;
+            }
+            if (near) {   // the same decision as the forward's (see exact_cut)
+#pragma unroll
+                for (int u = 0; u < 4; u++)
+                    if ((near >> u) & 1u) ok[u] = exact_cut(xy, conic_opacity, eid[u], pxf, pyf);
             }
             head += avail;
             if (lane == 0) STAT_ADD(6, 1);
 #pragma unroll
             for (int u = 0; u < 4; u++) {
                 if (!__any_sync(0xffffffffu, ok[u])) continue;   // warp-uniform: no pixel of the block is touched
-                const float4 f = sm.ring_feat[base + u];
+                const float4 f = g[u][2];
                 const float alpha = al[u];
                 const float ra = __fdividef(1.f, 1.f - alpha);
                 T = ok[u] ? T * ra : T;                            // transmittance in front of this Gaussian
                 const float aT = ok[u] ? alpha * T : 0.f;
                 float cg = f.x * g0 + f.y * g1 + f.z * g2;        // (colour . dL/dpixel)
-                if (INVDEPTH) cg += f.w * gi;
+                if (INVDEPTH) cg += g[u][1].w * gi;
                 // dL/dalpha = (c - accum_rec) . g T - T_final/(1-alpha) (bg . g) with accum_rec T = behind / (1 - alpha),
                 // behind = sum over the contributors behind this one of (c . g) alpha T  (the upstream recurrence,
                 // contracted with g before instead of after)
@@ -437,29 +497,58 @@ __global__ void __launch_bounds__(TILE_PIX, BWD_MIN_CTAS) blend_backward_kernel(
                 behind += cg * aT;
                 sm.p[nb * NB_PITCH + (int)lane] = ok[u] ? G_[u] * dL_dalpha : 0.f;
                 sm.aT[nb * NB_PITCH + (int)lane] = aT;
-                if (lane == 0) sm.meta[nb] = make_float4(ex[u], ey[u], eid[u], 0.f);
-                if (++nb == NB) {
-                    __syncwarp();
-                    backward_turn_around<INVDEPTH>(sm, NB, lane, wb, grad_acc);
-                    __syncwarp();
-                    nb = 0;
-                }
+                if (lane == 0) sm.meta[nb] = make_float4(ex[u], ey[u], __uint_as_float(eid[u]), 0.f);
+                nb++;
+            }
+            if (nb > NB - 4) {   // the next group may not fit: one call site per group, not one per entry
+                __syncwarp();
+                backward_turn_around<INVDEPTH>(sm, nb, lane, wb.x0, wb.y0, grad_acc);
+                __syncwarp();
+                nb = 0;
             }
         }
+    };
+
+    for (int fc = top; fc >= 0; fc--) {
+        // the survivors staged by the previous steps (their records have had a whole step to land)
+        cp_async_wait_all();
+        __syncwarp();
+        consume(false);
+        const uint32_t mf = m_next, id = id_next;
+        m_next = m_next2;
+        id_next = id_next2;
+        if (fc > 1) {
+            m_next2 = __ldg(ballot_w + (size_t)(fc - 2) * 8);
+            id_next2 = point_list[32u * (uint32_t)(fc - 2) + 31u - lane];
+        }
+        const uint32_t m = __brev(mf);                       // bit l = lane l = forward position 32 fc + 31 - l
+        if ((m >> lane) & 1u) {
+            const uint32_t s = (tail + __popc(m & lanemask_lt())) & (RING - 1);
+            cp_async_16(&sm.ring[s][0], &splat[id].g0);
+            cp_async_16(&sm.ring[s][1], &splat[id].g1);
+            const float *csrc = colors + 3 * (size_t)id;
+            float *cdst = reinterpret_cast<float *>(&sm.ring[s][2]);
+            cp_async_4(cdst, csrc);
+            cp_async_4(cdst + 1, csrc + 1);
+            cp_async_4(cdst + 2, csrc + 2);
+            sm.ring_m[s] = make_uint2(id, 32u * (uint32_t)fc + 31u - lane);
+        }
+        cp_async_commit();
+        tail += __popc(m);
+        if (lane == 0) { STAT_ADD(4, 1); STAT_ADD(5, __popc(m)); }
     }
+    cp_async_wait_all();
+    __syncwarp();
+    consume(true);
     if (nb) {
         __syncwarp();
-        backward_turn_around<INVDEPTH>(sm, nb, lane, wb, grad_acc);
+        backward_turn_around<INVDEPTH>(sm, nb, lane, wb.x0, wb.y0, grad_acc);
     }
 }
 
 }  // namespace
 
 #ifdef D3GA_BLEND_STATS
-extern "C" int d3ga_debug_blend_trace(void *p) {
-    unsigned long long *v = (unsigned long long *)p;
-    return cudaMemcpyToSymbol(g_blend_trace, &v, sizeof(v)) == cudaSuccess ? 0 : -2;
-}
 extern "C" int d3ga_debug_blend_stats(unsigned long long *out, int reset) {
     if (cudaMemcpyFromSymbol(out, g_blend_stats, sizeof(g_blend_stats)) != cudaSuccess) return -2;
     if (reset) {
@@ -481,23 +570,32 @@ int launch_blend_forward(int W, int H, const float *background, const float *col
     const uint32_t *v1 = reinterpret_cast<const uint32_t *>(binning + BL.vals1);
     const float2 *xy = reinterpret_cast<const float2 *>(geom + GL.xy);
     const float4 *co = reinterpret_cast<const float4 *>(geom + GL.conic_opacity);
-    const float *depth = reinterpret_cast<const float *>(geom + GL.depth);
+    const SplatRecord *splat = reinterpret_cast<const SplatRecord *>(geom + GL.splat);
+    uint32_t *ballots = reinterpret_cast<uint32_t *>(image + IL.ballots);
     float *final_T = reinterpret_cast<float *>(image + IL.final_T);
     uint32_t *n_contrib = reinterpret_cast<uint32_t *>(image + IL.n_contrib);
     const uint32_t *order_fwd = reinterpret_cast<const uint32_t *>(image + IL.order_fwd);
     uint32_t *order_bwd = reinterpret_cast<uint32_t *>(image + IL.order_bwd);
     uint32_t *tile_nproc = reinterpret_cast<uint32_t *>(image + IL.tile_nproc);
+    const size_t smem = sizeof(FwdWarpSmem) * FWD_WARPS;
+    static std::atomic<uint64_t> attr_devices{0};
+    const int arc = once_per_device(attr_devices, [&]() -> int {
+        D3GA_CUDA(cudaFuncSetAttribute(blend_forward_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        D3GA_CUDA(cudaFuncSetAttribute(blend_forward_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        return D3GA_OK;
+    });
+    if (arc) return arc;
     ProfScope prof(K_BLEND_FWD, stream);
     {
         D3GA_CUDA(cudaMemsetAsync(tile_nproc, 0, sizeof(uint32_t) * (size_t)num_tiles, stream));
         if (out_invdepth)
-            blend_forward_kernel<true><<<num_tiles * (8 / FWD_WARPS), FWD_WARPS * 32, 0, stream>>>(
-                hdr, ranges, v0, v1, W, H, xy, co, colors, depth, background, final_T, n_contrib, out_color, out_invdepth,
-                hdr_rw, gx, num_tiles, order_fwd, tile_nproc, order_bwd);
+            blend_forward_kernel<true><<<num_tiles, FWD_WARPS * 32, smem, stream>>>(
+                hdr, ranges, v0, v1, W, H, splat, colors, xy, co, background, final_T, n_contrib, out_color, out_invdepth,
+                hdr_rw, gx, num_tiles, order_fwd, tile_nproc, order_bwd, ballots);
         else
-            blend_forward_kernel<false><<<num_tiles * (8 / FWD_WARPS), FWD_WARPS * 32, 0, stream>>>(
-                hdr, ranges, v0, v1, W, H, xy, co, colors, depth, background, final_T, n_contrib, out_color, nullptr,
-                hdr_rw, gx, num_tiles, order_fwd, tile_nproc, order_bwd);
+            blend_forward_kernel<false><<<num_tiles, FWD_WARPS * 32, smem, stream>>>(
+                hdr, ranges, v0, v1, W, H, splat, colors, xy, co, background, final_T, n_contrib, out_color, nullptr,
+                hdr_rw, gx, num_tiles, order_fwd, tile_nproc, order_bwd, ballots);
     }
     D3GA_LAUNCH_CHECK();
     return D3GA_OK;
@@ -514,7 +612,8 @@ int launch_blend_backward(int W, int H, const float *background, const float *co
     const uint32_t *v1 = reinterpret_cast<const uint32_t *>(binning + BL.vals1);
     const float2 *xy = reinterpret_cast<const float2 *>(geom + GL.xy);
     const float4 *co = reinterpret_cast<const float4 *>(geom + GL.conic_opacity);
-    const float *depth = reinterpret_cast<const float *>(geom + GL.depth);
+    const SplatRecord *splat = reinterpret_cast<const SplatRecord *>(geom + GL.splat);
+    const uint32_t *ballots = reinterpret_cast<const uint32_t *>(image + IL.ballots);
     const float *final_T = reinterpret_cast<const float *>(image + IL.final_T);
     const uint32_t *n_contrib = reinterpret_cast<const uint32_t *>(image + IL.n_contrib);
     const uint32_t *order_bwd = reinterpret_cast<const uint32_t *>(image + IL.order_bwd);
@@ -530,12 +629,12 @@ int launch_blend_backward(int W, int H, const float *background, const float *co
     {
         if (dL_dinvdepth_pix)
             blend_backward_kernel<true><<<num_tiles, TILE_PIX, smem, stream>>>(
-                hdr, ranges, v0, v1, W, H, background, xy, co, colors, depth, final_T, n_contrib, dL_dpix,
-                dL_dinvdepth_pix, grad_acc, gx, order_bwd);
+                hdr, ranges, v0, v1, W, H, background, splat, colors, xy, co, final_T, n_contrib, dL_dpix,
+                dL_dinvdepth_pix, grad_acc, gx, order_bwd, ballots);
         else
             blend_backward_kernel<false><<<num_tiles, TILE_PIX, smem, stream>>>(
-                hdr, ranges, v0, v1, W, H, background, xy, co, colors, depth, final_T, n_contrib, dL_dpix, nullptr,
-                grad_acc, gx, order_bwd);
+                hdr, ranges, v0, v1, W, H, background, splat, colors, xy, co, final_T, n_contrib, dL_dpix, nullptr,
+                grad_acc, gx, order_bwd, ballots);
     }
     D3GA_LAUNCH_CHECK();
     return D3GA_OK;

@@ -72,6 +72,7 @@ struct GeoParams {
     uint32_t P_pad;
     int32_t *tile_diff;    // [(gy+1)][(gx+1)] +1/-1 at the rect corners (null: grid too large, counts come from the keys)
     uint4 *grec;           // direct tile scatter: [P] x0 | y0 << 16, width | height << 16, Gaussian id, depth bits (else null)
+    SplatRecord *splat;    // [P] what the blend kernels gather per list entry (common.cuh)
 };
 
 constexpr uint64_t FLAG_AGG = 1ull << 62, FLAG_INC = 2ull << 62, FLAG_MASK = 3ull << 62;
@@ -211,6 +212,23 @@ __device__ __forceinline__ void preprocess_one(const GeoParams &p, int idx, cons
             }
         }
         if (!live) { pxi = 0.f; pyi = 0.f; }
+        if (live) {
+            // The blend kernels' record.  The conic goes to the log2 domain (one ex2 per alpha, no extra multiply) and the
+            // footprint bound with it: alpha >= 1/255 needs d^T C d <= 2 ln(255 o) =: 2 tau, i.e. q2 >= -0.5 log2(e) 2 tau,
+            // taken with a relative and an absolute margin (the per-pixel test decides; this only culls).
+            constexpr float LOG2E = 1.4426950408889634f;
+            float lim2 = -INFINITY;                                   // never culled (degenerate conic)
+            if (co.w < 1.f / 255.f) {
+                lim2 = INFINITY;                                      // can never pass the cut
+            } else {
+                const float det = co.x * co.z - co.y * co.y, tau = __logf(255.f * co.w);
+                if (det > 0.f && tau >= 0.f && co.x > 0.f && co.z > 0.f) lim2 = (-0.5f * LOG2E) * (2.f * tau * 1.002f + 0.01f);
+            }
+            SplatRecord r;
+            r.g0 = make_float4(pxi, pyi, lim2, co.w);
+            r.g1 = make_float4((-0.5f * LOG2E) * co.x, (-LOG2E) * co.y, (-0.5f * LOG2E) * co.z, DIV(1.f, depth));
+            p.splat[idx] = r;
+        }
         if (p.shs) {
             float rgb[3] = {0.f, 0.f, 0.f};
             uint8_t cl[3] = {0, 0, 0};
@@ -474,6 +492,7 @@ int launch_geometry(int P, int sh_degree, int sh_coeffs, const float *means3D, c
     const DirectPlan direct = direct_plan(P, p.gx, p.gy, capacity);
     remember_direct_plan(geom, P, p.gx, p.gy, capacity, direct);
     p.grec = direct.ok ? reinterpret_cast<uint4 *>(geom + GL.grec) : nullptr;
+    p.splat = reinterpret_cast<SplatRecord *>(geom + GL.splat);
     if (depth_first_mode(sort_mode()) && !direct.ok && tile_plan_from_grid(p.gx, p.gy)) {
         p.tile_diff = reinterpret_cast<int32_t *>(geom + GL.tile_diff);
         D3GA_CUDA(cudaMemsetAsync(p.tile_diff, 0, 4ull * (p.gx + 1) * (p.gy + 1), stream));

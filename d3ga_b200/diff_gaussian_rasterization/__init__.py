@@ -288,16 +288,16 @@ def rasterize_forward(means3D, sh, colors_precomp, opacities, scales, rotations,
         radii = torch.empty((P,), dtype=torch.int32, device=dev)
         st = RasterState()
         st.P, st.W, st.H = P, W, H
-        gb, _, ib = _workspace_bytes(P, W, H, 0)
+        gb, _, _ = _workspace_bytes(P, W, H, 0)
         st.geom = torch.empty(gb, dtype=torch.uint8, device=dev)
-        st.image = torch.empty(ib, dtype=torch.uint8, device=dev)
         host = _pinned_counter(dev)
         host_np = host.numpy()
         defer = _defer_depth > 0
         ev = None if defer else torch.cuda.Event()
         while True:
-            _, bb, _ = _workspace_bytes(P, W, H, cap)
+            _, bb, ib = _workspace_bytes(P, W, H, cap)    # the image workspace holds one survivor word per 32 duplicates
             st.binning = torch.empty(bb, dtype=torch.uint8, device=dev)
+            st.image = torch.empty(ib, dtype=torch.uint8, device=dev)
             st.capacity = cap
             _lib.check(lib.d3ga_raster_forward_geometry(
                 P, int(rs.sh_degree), M, _lib.ptr(means3D), _lib.ptr(scales), float(rs.scale_modifier),

@@ -62,7 +62,9 @@ class Camera:
     campos: np.ndarray  # [3] f32
 
 
-def make_camera(W: int, H: int, azim_deg=0.0, elev_deg=0.0, dist=3.0, center=(0.0, 0.0, 0.0), focal_mul=1.2) -> Camera:
+def camera_pose(W: int, H: int, azim_deg=0.0, elev_deg=0.0, dist=3.0, center=(0.0, 0.0, 0.0), focal_mul=1.2):
+    """What a dataset hands the reference's Camera (lib/cameras.py:29-44): R (camera-to-world rotation, columns = camera
+    axes, x right / y down / z forward), T (world-to-camera translation), FoVx, FoVy."""
     az, el = math.radians(azim_deg), math.radians(elev_deg)
     center = np.asarray(center, np.float64)
     eye = center + dist * np.array([math.sin(az) * math.cos(el), math.sin(el), math.cos(az) * math.cos(el)])
@@ -72,8 +74,16 @@ def make_camera(W: int, H: int, azim_deg=0.0, elev_deg=0.0, dist=3.0, center=(0.
     right = np.cross(f, up)
     right /= np.linalg.norm(right)
     down = np.cross(f, right)
-    R = np.stack([right, down, f], axis=1)  # camera-to-world rotation (columns = camera axes); x right, y down, z fwd
+    R = np.stack([right, down, f], axis=1)
     T = -R.T @ eye
+    focal = focal_mul * max(W, H)
+    return R, T, 2 * math.atan(W / (2 * focal)), 2 * math.atan(H / (2 * focal))
+
+
+def make_camera(W: int, H: int, azim_deg=0.0, elev_deg=0.0, dist=3.0, center=(0.0, 0.0, 0.0), focal_mul=1.2) -> Camera:
+    """The matrices lib/cameras.py:62-75 builds from camera_pose(...) (pinned to the reference's own Camera class by
+    tests/golden/camera_golden.npz)."""
+    R, T, _, _ = camera_pose(W, H, azim_deg, elev_deg, dist, center, focal_mul)
     # getWorld2View2 (utils/graphics_utils.py:41-52)
     Rt = np.zeros((4, 4))
     Rt[:3, :3] = R.T

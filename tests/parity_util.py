@@ -49,3 +49,31 @@ def rel_l2(a, b):
     a = np.asarray(a, np.float64).ravel()
     b = np.asarray(b, np.float64).ravel()
     return float(np.linalg.norm(a - b) / max(1e-30, np.linalg.norm(b)))
+
+
+def oracle_view(scene, cam, weights, bg=(1.0, 1.0, 1.0), raster_inputs=None):
+    """One whole view on the CPU -- deformation oracle -> rasterizer oracle -> loss = sum(image * weights) -> both
+    backward passes -- returning (loss, {parameter: gradient}) for the six hot-path parameters.
+
+    raster_inputs = (means3D, cov3D) evaluates the RASTERIZER oracle at those values instead of the deformation oracle's
+    own (the chain rule still runs through the deformation oracle).  The rasterizer is a discontinuous function of its
+    inputs -- depth order, the 1/255 cut, the transmittance stop -- so two float32 deformations that differ in the last
+    bit give images and gradients that differ by ~5e-4 relative L2 at 1 M Gaussians (the float32 and float64 oracles
+    differ from each other by that much); feeding the oracle the values the product path actually rasterized removes
+    that noise from the comparison, and the deformation itself is compared separately to ~1e-6."""
+    t = th.from_numpy
+    leaves = {k: t(np.ascontiguousarray(getattr(scene, k))).clone().requires_grad_(True)
+              for k in ("tetpoints", "barys", "scales", "rotation")}
+    means, cov6 = deform_oracle.deform_gaussians(leaves["tetpoints"], t(scene.tets), t(scene.tetra_id), leaves["barys"],
+                                                 t(scene.canonical_gradient), leaves["scales"], leaves["rotation"])
+    m_in, c_in = (means.detach().numpy(), cov6.detach().numpy()) if raster_inputs is None else raster_inputs
+    orc = RasterOracle(np.float32)
+    st = orc.forward(np.ascontiguousarray(m_in), scene.opacity, cam.viewmatrix, cam.projmatrix, cam.campos, scene.W, scene.H,
+                     cam.tanfovx, cam.tanfovy, list(bg), colors_precomp=scene.colors, cov3D_precomp=np.ascontiguousarray(c_in))
+    g = orc.backward(st, weights)
+    th.autograd.backward([means, cov6], [t(g["means3D"]), t(g["cov3D"])])
+    grads = {k: v.grad.numpy().astype(np.float64) for k, v in leaves.items()}
+    grads["opacity"] = np.asarray(g["opacity"], np.float64).reshape(scene.opacity.shape)
+    grads["colors"] = np.asarray(g["colors"], np.float64)
+    loss = float((st["color"].astype(np.float64) * weights.astype(np.float64)).sum())
+    return loss, grads

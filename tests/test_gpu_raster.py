@@ -183,7 +183,19 @@ def test_python_dropin_autograd(cuda_lib, oracle_libs, path):
     assert util.rel_l2(means2D.grad.cpu().numpy(), rg["mean2D"]) < GRAD_TOL
 
 
-@pytest.mark.parametrize("workload", ["c1", "c2", "c3"])
+def report_parity(record):
+    """Appends one JSON line per measured parity figure to $D3GA_PARITY_LOG (DESIGN.md's tables are made from it)."""
+    import json
+    import os
+
+    path = os.environ.get("D3GA_PARITY_LOG")
+    if path:
+        with open(path, "a") as f:
+            f.write(json.dumps(record) + "\n")
+    print("[parity]", json.dumps(record))
+
+
+@pytest.mark.parametrize("workload", ["c1", "c2", "c3", "metric"])
 def test_full_size_properties(cuda_lib, oracle_libs, workload):
     """BASELINE.json sizes: oracle comparison where it finishes in seconds plus size-independent properties."""
     sc = synth.make_workload(workload)
@@ -212,8 +224,21 @@ def test_full_size_properties(cuda_lib, oracle_libs, workload):
     orc, ref = util.oracle_forward(g, cam, W, H, [1, 1, 1])
     assert np.array_equal(keys, ref["keys"]) and np.array_equal(pl, ref["point_list"])
     assert np.array_equal(got["ranges"], ref["ranges"])
-    diff = np.abs(got["color"] - ref["color"])
-    assert np.mean(diff > IMG_TOL) <= 2e-5 and diff.max() < 2e-2, (np.mean(diff > IMG_TOL), diff.max())
+    # The image bar is 1e-4 max-abs.  A (pixel, Gaussian) pair whose alpha sits on the 1/255 cut is decided in upstream's
+    # own arithmetic (raster_blend.cu: exact_cut), so the contributor sets agree; what is left is the transmittance stop
+    # T (1 - alpha) < 1e-4, whose T carries the rounding of every alpha before it and cannot be decided "exactly" without
+    # making every alpha bit-identical.  Measured and asserted: the number of values beyond the bar and their maximum;
+    # every one of them must be a pixel whose contributor count differs from the oracle's (a flipped stop), nothing else.
+    diff = np.abs(got["color"].astype(np.float64) - ref["color"].astype(np.float64))
+    off = diff > IMG_TOL
+    n_off, mx = int(off.sum()), float(diff.max())
+    nc_diff = got["n_contrib"] != ref["n_contrib"]
+    px_off = off.any(axis=0).reshape(-1)
+    report_parity(dict(test="full_size_image", workload=workload, values=int(diff.size), beyond_1e_4=n_off, max_abs=mx,
+                       pixels_with_other_contributor_count=int(nc_diff.sum()),
+                       offenders_explained_by_contributor_count=int((px_off & nc_diff).sum()), offenders=int(px_off.sum())))
+    assert not (px_off & ~nc_diff).any(), "a pixel beyond 1e-4 with the oracle's own contributor set"
+    assert px_off.sum() <= 4 and mx <= 1e-2, (n_off, mx)
     # backward: linearity in dL/dimage and oracle agreement
     rng = np.random.default_rng(9)
     w = rng.uniform(-1, 1, size=(3, H, W)).astype(np.float32)
@@ -290,8 +315,11 @@ def test_hint_flipped_between_the_stages_changes_nothing(cuda_lib, oracle_libs):
     finally:
         lib.d3ga_set_views_in_flight(1)
     # stage 2 on a workspace no stage 1 has run on is refused, not guessed
+    # (a buffer at an address no geometry workspace can have had: inside a larger allocation, off its 512-byte grid)
     t = ref["tensors"]
-    geom2 = t["geom"].clone()
+    big = torch.zeros(t["geom"].numel() + 1024, dtype=torch.uint8, device="cuda")
+    geom2 = big[256:256 + t["geom"].numel()]
+    geom2.copy_(t["geom"])
     out = torch.zeros((3, sc.H, sc.W), device="cuda")
     rc = lib.d3ga_raster_forward_render(ref["P"], sc.W, sc.H, t["bg"].data_ptr(), t["col"].data_ptr(), geom2.data_ptr(),
                                         t["binning"].data_ptr(), ref["capacity"], t["image"].data_ptr(), out.data_ptr(), None,
