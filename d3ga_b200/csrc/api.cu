@@ -33,7 +33,7 @@ static const char *const g_kernel_names[K_COUNT] = {
     "ssim_forward_kernel", "ssim_backward_kernel", "lbs_skeleton_kernel", "lbs_skin_forward_kernel",
     "lbs_skin_backward_kernel", "lbs_unskin_kernel", "lbs_skin_dense_forward_kernel", "lbs_skin_dense_backward_kernel",
     "rect_grid_kernel", "tile_plan_kernel", "direct_count_kernel", "direct_segsum_kernel", "direct_plan_kernel",
-    "direct_base_kernel", "direct_scatter_kernel"};
+    "direct_base_kernel", "direct_scatter_kernel", "pack_features_kernel"};
 
 bool profiling_enabled() { return g_prof_on.load(std::memory_order_relaxed) != 0; }
 
@@ -137,7 +137,7 @@ int d3ga_raster_workspace_bytes(int P, int W, int H, uint64_t capacity, uint64_t
     if (capacity > MAX_DUPLICATES) return D3GA_ETOOBIG;
     if (geom_bytes) *geom_bytes = geom_layout(P).total;
     if (binning_bytes) *binning_bytes = bin_layout(capacity).total;
-    if (image_bytes) *image_bytes = img_layout(W, H, capacity).total;
+    if (image_bytes) *image_bytes = img_layout(P, W, H, capacity).total;
     return D3GA_OK;
 }
 
@@ -162,7 +162,7 @@ int d3ga_raster_sorted_keys(int P, int W, int H, const void *geom, const void *b
     if (capacity > MAX_DUPLICATES) return D3GA_ETOOBIG;
     const GeomLayout GL = geom_layout(P);
     const BinLayout BL = bin_layout(capacity);
-    const ImgLayout IL = img_layout(W, H, capacity);
+    const ImgLayout IL = img_layout(P, W, H, capacity);
     const int gx = (W + TILE - 1) / TILE, gy = (H + TILE - 1) / TILE;
     DirectPlan direct;
     if (!recall_direct_plan(geom, P, gx, gy, capacity, &direct)) return D3GA_ENOTREADY;
@@ -177,7 +177,7 @@ int d3ga_raster_layout(int P, int W, int H, uint64_t capacity, uint64_t *out) {
     if (P < 0 || W <= 0 || H <= 0 || !out) return D3GA_EINVAL;
     const GeomLayout G = geom_layout(P);
     const BinLayout B = bin_layout(capacity);
-    const ImgLayout I = img_layout(W, H, capacity);
+    const ImgLayout I = img_layout(P, W, H, capacity);
     out[D3GA_L_GEOM_HEADER] = G.header; out[D3GA_L_GEOM_DEPTH] = G.depth; out[D3GA_L_GEOM_XY] = G.xy;
     out[D3GA_L_GEOM_CONIC_OPACITY] = G.conic_opacity; out[D3GA_L_GEOM_RGB] = G.rgb; out[D3GA_L_GEOM_COV3D] = G.cov3D;
     out[D3GA_L_GEOM_TILES] = G.tiles; out[D3GA_L_GEOM_OFFSETS] = G.offsets; out[D3GA_L_GEOM_CLAMPED] = G.clamped;
@@ -221,14 +221,14 @@ int d3ga_raster_forward_render(int P, int W, int H, const float *background, con
     if (capacity > MAX_DUPLICATES) return D3GA_ETOOBIG;
     const GeomLayout GL = geom_layout(P);
     const BinLayout BL = bin_layout(capacity);
-    const ImgLayout IL = img_layout(W, H, capacity);
+    const ImgLayout IL = img_layout(P, W, H, capacity);
     const int num_tiles = ((W + TILE - 1) / TILE) * ((H + TILE - 1) / TILE);
     const int sort_bits = 32 + higher_msb((uint32_t)num_tiles);
     int rc = launch_sort_and_ranges(P, (uint8_t *)geom, GL, (W + TILE - 1) / TILE, (H + TILE - 1) / TILE, (uint8_t *)binning,
                                     BL, capacity, sort_bits, (uint8_t *)image, IL, num_tiles, stream);
     if (rc) return rc;
     const float *colors = colors_precomp ? colors_precomp : reinterpret_cast<const float *>((uint8_t *)geom + GL.rgb);
-    return launch_blend_forward(W, H, background, colors, (const uint8_t *)geom, GL, (const uint8_t *)binning, BL,
+    return launch_blend_forward(P, W, H, background, colors, (const uint8_t *)geom, GL, (const uint8_t *)binning, BL,
                                 (uint8_t *)image, IL, out_color, out_invdepth, stream);
 }
 
@@ -241,7 +241,7 @@ int d3ga_raster_forward_blend(int P, int W, int H, const float *background, cons
     if (capacity > MAX_DUPLICATES) return D3GA_ETOOBIG;
     const GeomLayout GL = geom_layout(P);
     const BinLayout BL = bin_layout(capacity);
-    const ImgLayout IL = img_layout(W, H, capacity);
+    const ImgLayout IL = img_layout(P, W, H, capacity);
     const uint64_t tiles = (uint64_t)((W + TILE - 1) / TILE) * ((H + TILE - 1) / TILE);
     // per-tile ranges and the forward launch order come from the render that did the binning
     D3GA_CUDA(cudaMemcpyAsync((uint8_t *)image + IL.ranges, (const uint8_t *)tile_src_image + IL.ranges, 8 * tiles,
@@ -251,7 +251,7 @@ int d3ga_raster_forward_blend(int P, int W, int H, const float *background, cons
     RasterHeader *hdr = reinterpret_cast<RasterHeader *>((uint8_t *)geom + GL.header);
     D3GA_CUDA(cudaMemsetAsync(&hdr->blend_done, 0, sizeof(uint32_t), stream));
     const float *colors = colors_precomp ? colors_precomp : reinterpret_cast<const float *>((uint8_t *)geom + GL.rgb);
-    return launch_blend_forward(W, H, background, colors, (const uint8_t *)geom, GL, (const uint8_t *)binning, BL,
+    return launch_blend_forward(P, W, H, background, colors, (const uint8_t *)geom, GL, (const uint8_t *)binning, BL,
                                 (uint8_t *)image, IL, out_color, out_invdepth, stream);
 }
 
@@ -280,7 +280,7 @@ int d3ga_raster_backward(int P, int sh_degree, int sh_coeffs, int W, int H, cons
     if (capacity > MAX_DUPLICATES) return D3GA_ETOOBIG;
     const GeomLayout GL = geom_layout(P);
     const BinLayout BL = bin_layout(capacity);
-    const ImgLayout IL = img_layout(W, H, capacity);
+    const ImgLayout IL = img_layout(P, W, H, capacity);
     float *acc = (float *)grad_scratch;
     D3GA_CUDA(cudaMemsetAsync(acc, 0, (size_t)P * GRAD_ACC_FLOATS * 4, stream));
     const float *colors = colors_precomp ? colors_precomp : reinterpret_cast<const float *>((const uint8_t *)geom + GL.rgb);

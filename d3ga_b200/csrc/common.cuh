@@ -56,6 +56,7 @@ struct GeomLayout {
     uint64_t ordered;    // direct tile scatter: the Gaussians' packed records in depth order (16 B each)
     uint64_t grec;       // ... and in Gaussian order, as the preprocess wrote them
     uint64_t splat;      // what the blend kernels gather per list entry: 2 x float4 per Gaussian (SplatRecord below)
+    uint64_t feat;       // ... and the colours stage 1 was given, packed (r, g, b, 0) -- see ImgLayout::feat
     uint64_t p_pad;
 };
 struct BinLayout {
@@ -63,7 +64,7 @@ struct BinLayout {
     uint64_t tile_state_bytes;
 };
 struct ImgLayout {
-    uint64_t ranges, final_T, n_contrib, order_fwd, order_bwd, tile_nproc, ballots, total;
+    uint64_t ranges, final_T, n_contrib, order_fwd, order_bwd, tile_nproc, ballots, feat, total;
 };
 // The blend kernels' per-Gaussian gather: ONE 32-byte sector, two 16-byte loads (before: xy 8 B + conic/opacity 16 B +
 // depth 4 B from three arrays).  The conic is pre-scaled to the log2 domain (log2 G = A dx^2 + B dx dy + C dy^2) and the
@@ -105,6 +106,7 @@ inline GeomLayout geom_layout(int P) {
     L.ordered = o;       o = align256(o + 16 * L.p_pad);
     L.grec = o;          o = align256(o + 16 * L.p_pad);
     L.splat = o;         o = align256(o + 32 * p);
+    L.feat = o;          o = align256(o + 16 * p);
     L.total = o;
     return L;
 }
@@ -124,7 +126,7 @@ inline BinLayout bin_layout(uint64_t capacity) {
     L.total = o;
     return L;
 }
-inline ImgLayout img_layout(int W, int H, uint64_t capacity) {
+inline ImgLayout img_layout(int P, int W, int H, uint64_t capacity) {
     ImgLayout L;
     uint64_t o = 0, tiles = (uint64_t)((W + TILE - 1) / TILE) * ((H + TILE - 1) / TILE), px = (uint64_t)W * H;
     L.ranges = o;    o = align256(o + 8 * tiles);
@@ -134,6 +136,10 @@ inline ImgLayout img_layout(int W, int H, uint64_t capacity) {
     L.order_bwd = o;  o = align256(o + 4 * tiles);   // tiles, deepest contributor first (blend backward)
     L.tile_nproc = o; o = align256(o + 4 * tiles);   // max over the tile's pixels of n_contrib
     L.ballots = o;    o = align256(o + 4ull * 8 * ballot_rows(capacity, tiles));
+    // this render's colours as one aligned 16-byte vector per Gaussian (r, g, b, 0), when they are not the colours stage 1
+    // packed into the geometry workspace: the second render of a training frame shares that workspace but blends
+    // other colours (the blend launchers pick by the colour pointer: recall_packed_colors)
+    L.feat = o;       o = align256(o + 16ull * (uint64_t)(P < 1 ? 1 : P));
     L.total = o;
     return L;
 }
@@ -149,7 +155,7 @@ enum KernelId {
     K_GEOMETRY = 0, K_SORT_HIST, K_SORT_PASS, K_RANGES, K_BLEND_FWD, K_BLEND_BWD, K_PRE_BWD, K_DEFORM_FWD, K_DEFORM_BWD,
     K_BARY, K_PREPROCESS, K_EMIT, K_DEPTH_HIST, K_DEPTH_PASS, K_FEM_FWD, K_FEM_BWD, K_SSIM_FWD, K_SSIM_BWD,
     K_LBS_SKELETON, K_LBS_SKIN_FWD, K_LBS_SKIN_BWD, K_LBS_UNSKIN, K_LBS_DENSE_FWD, K_LBS_DENSE_BWD, K_RECT_GRID, K_TILE_PLAN,
-    K_DIRECT_COUNT, K_DIRECT_SEGSUM, K_DIRECT_PLAN, K_DIRECT_BASE, K_DIRECT_SCATTER, K_COUNT
+    K_DIRECT_COUNT, K_DIRECT_SEGSUM, K_DIRECT_PLAN, K_DIRECT_BASE, K_DIRECT_SCATTER, K_PACK_FEAT, K_COUNT
 };
 // Optional per-kernel CUDA-event timing (d3ga_profile_* in the C-ABI; bench.py's roofline figures come from it).
 // A no-op unless profiling is enabled.
@@ -216,8 +222,11 @@ struct DirectPlan {
 };
 DirectPlan direct_plan(int P, int gx, int gy, uint64_t capacity);   // stage 1 only: reads the views-in-flight hint
 // the plan stage 1 used on this geometry workspace (false: no stage 1 has run on it with these sizes)
-void remember_direct_plan(const void *geom, int P, int gx, int gy, uint64_t capacity, const DirectPlan &pl);
+void remember_direct_plan(const void *geom, int P, int gx, int gy, uint64_t capacity, const DirectPlan &pl,
+                          const void *packed_colors);
 bool recall_direct_plan(const void *geom, int P, int gx, int gy, uint64_t capacity, DirectPlan *pl);
+// the colour array stage 1 packed into the geometry workspace's `feat` section (null: none / unknown workspace)
+const void *recall_packed_colors(const void *geom);
 void set_views_in_flight(int n);
 int launch_direct_count(int P, int gx, int gy, uint8_t *geom, const GeomLayout &GL, uint8_t *binning, const BinLayout &BL,
                         uint64_t capacity, const DirectPlan &pl, cudaStream_t stream);
@@ -228,7 +237,7 @@ int launch_copy_sorted_keys(const uint8_t *geom, const GeomLayout &GL, const uin
 int launch_direct_scatter(int P, int gx, int gy, uint8_t *geom, const GeomLayout &GL, uint8_t *binning, const BinLayout &BL,
                           uint64_t capacity, int sort_bits, uint8_t *image, const ImgLayout &IL, const DirectPlan &pl,
                           cudaStream_t stream);
-int launch_blend_forward(int W, int H, const float *background, const float *colors, const uint8_t *geom,
+int launch_blend_forward(int P, int W, int H, const float *background, const float *colors, const uint8_t *geom,
                          const GeomLayout &GL, const uint8_t *binning, const BinLayout &BL, uint8_t *image,
                          const ImgLayout &IL, float *out_color, float *out_invdepth, cudaStream_t stream);
 int launch_blend_backward(int W, int H, const float *background, const float *colors, const uint8_t *geom,

@@ -79,7 +79,7 @@ extern "C" int d3ga_raster_backward_noalloc(
 
     const GeomLayout GL = geom_layout(P);
     const BinLayout BL = bin_layout(capacity);
-    const ImgLayout IL = img_layout(W, H, capacity);
+    const ImgLayout IL = img_layout(P, W, H, capacity);
     const float *colors = colors_precomp ? colors_precomp : reinterpret_cast<const float *>((const uint8_t *)geom + GL.rgb);
     rc = launch_blend_backward(W, H, background, colors, (const uint8_t *)geom, GL, (const uint8_t *)binning, BL,
                                (const uint8_t *)image, IL, dL_dout_color, dL_dout_invdepth, acc, stream);

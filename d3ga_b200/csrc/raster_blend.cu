@@ -59,10 +59,6 @@ __device__ __forceinline__ void cp_async_16(void *smem_dst, const void *gmem_src
     asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(smem_dst)),
                  "l"(gmem_src) : "memory");
 }
-__device__ __forceinline__ void cp_async_4(void *smem_dst, const void *gmem_src) {
-    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((uint32_t)__cvta_generic_to_shared(smem_dst)),
-                 "l"(gmem_src) : "memory");
-}
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 
@@ -99,6 +95,15 @@ __device__ unsigned long long g_blend_stats[8];
 #define STAT_ADD(i, v) do { const unsigned long long _t = (unsigned long long)(v); if (_t) atomicAdd(&g_blend_stats[i], _t); } while (0)
 #else
 #define STAT_ADD(i, v) do { } while (0)
+#endif
+#ifdef D3GA_BLEND_TRACE
+// development trace of the forward: per (launch slot, warp) start ns, end ns, list entries walked, survivors blended
+__device__ unsigned long long g_fwd_trace[65536 * 8 * 4];
+__device__ __forceinline__ unsigned long long global_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
 #endif
 
 // Can the Gaussian reach a pixel centre of the warp's block with alpha >= 1/255?  alpha = o 2^q2(d) with
@@ -142,12 +147,14 @@ __device__ __noinline__ bool exact_cut(const float2 *__restrict__ xy, const floa
 }
 
 // The walk of a tile's list is a per-lane software pipeline in shared memory: lane l of a warp owns entry l of every
-// 32-entry chunk and keeps the copies of FWD_DEPTH chunks in flight (cp.async: 2 x 16 B of SplatRecord + 3 x 4 B of
+// 32-entry chunk and keeps the copies of FWD_DEPTH chunks in flight (cp.async: 2 x 16 B of SplatRecord + 16 B of packed
 // colour per entry, into a slot only this lane reads and refills -- no cross-lane hazard, no barrier).  Entry ids run two
 // more chunks ahead in registers.  The critical path of a step holds no global load: a heavy tile's warp used to wait
 // for its one-step-ahead register prefetch on every chunk (ncu: long-scoreboard the top stall of the forward, the
 // busiest SM active for the whole kernel, the average SM for half of it).
-constexpr int FWD_DEPTH = 4;
+#ifndef FWD_DEPTH
+#define FWD_DEPTH 3
+#endif
 struct FwdWarpSmem {
     float4 ring[RING][3];                 // staged survivors: [0] x, y, list position + 1 (bits), -   [1] conic, opacity
                                           //                   [2] r, g, b, 1/depth
@@ -158,7 +165,7 @@ template <bool INVDEPTH>
 __global__ void __launch_bounds__(FWD_WARPS * 32, FWD_MIN_CTAS) blend_forward_kernel(
     const RasterHeader *__restrict__ hdr, const uint2 *__restrict__ ranges, const uint32_t *__restrict__ vals0,
     const uint32_t *__restrict__ vals1, int W, int H, const SplatRecord *__restrict__ splat,
-    const float *__restrict__ colors, const float2 *__restrict__ xy, const float4 *__restrict__ conic_opacity,
+    const float4 *__restrict__ feat, const float2 *__restrict__ xy, const float4 *__restrict__ conic_opacity,
     const float *__restrict__ bg, float *__restrict__ final_T, uint32_t *__restrict__ n_contrib,
     float *__restrict__ out_color, float *__restrict__ out_invdepth, RasterHeader *__restrict__ hdr_rw, int grid_x,
     int num_tiles, const uint32_t *__restrict__ order_fwd, uint32_t *__restrict__ tile_nproc,
@@ -191,16 +198,16 @@ __global__ void __launch_bounds__(FWD_WARPS * 32, FWD_MIN_CTAS) blend_forward_ke
     uint32_t last = 0;
     uint32_t head = 0, tail = 0;
     bool all_done = __all_sync(0xffffffffu, done);
+#ifdef D3GA_BLEND_TRACE
+    const unsigned long long tr_t0 = global_ns();
+    uint32_t tr_chunks = 0;
+#endif
 
     // this lane's copies of one chunk entry: record + colour -> its private slot of stage `st`
     auto fetch = [&](uint32_t st, uint32_t id) {
         cp_async_16(&sm.stage[st][0][lane], &splat[id].g0);
         cp_async_16(&sm.stage[st][1][lane], &splat[id].g1);
-        const float *csrc = colors + 3 * (size_t)id;
-        float *cdst = reinterpret_cast<float *>(&sm.stage[st][2][lane]);
-        cp_async_4(cdst, csrc);
-        cp_async_4(cdst + 1, csrc + 1);
-        cp_async_4(cdst + 2, csrc + 2);
+        cp_async_16(&sm.stage[st][2][lane], feat + id);
     };
     // prologue: FWD_DEPTH chunks in flight (one commit group per chunk, empty ones included), ids of the next two
     uint32_t id_a = 0, id_b = 0;   // ids of this lane's entries in chunks c + FWD_DEPTH and c + FWD_DEPTH + 1
@@ -214,56 +221,87 @@ __global__ void __launch_bounds__(FWD_WARPS * 32, FWD_MIN_CTAS) blend_forward_ke
         if ((uint32_t)(FWD_DEPTH + 1) * 32u + lane < count) id_b = point_list[(uint32_t)(FWD_DEPTH + 1) * 32u + lane];
     }
 
-    // Blends the staged survivors, four ring entries at a time (head stays a multiple of four, so a group never wraps):
-    // their alphas are independent; the transmittance recurrence that follows is branch-free.
+    // Blends the staged survivors, four ring entries (a GROUP) at a time; head stays a multiple of four, so a group never
+    // wraps.  What bounds the kernel is the serial chain of the busiest warp of the densest tile (ncu: the busiest SM is
+    // active for the whole kernel, the average SM for half of it), so the loop is written for LATENCY:
+    //  - software pipeline: the alphas of group g + 1 (shared-memory loads, the quadratic form, ex2) are computed in the
+    //    same basic block as the recurrence of group g, so the in-order issue interleaves the two chains;
+    //  - the transmittance chain is four dependent multiplies p_k = p_{k-1} (1 - a_k); the stop T (1 - a) < 1e-4 is found
+    //    beside the chain from the four products (T only ever decreases) and applied as masks.  Same products, same
+    //    roundings, same decisions as the entry-by-entry form (and as upstream: subtract, then multiply).
+    float ga[4] = {0.f, 0.f, 0.f, 0.f};      // the pending group's alphas (0 = skipped entry) ...
+    uint32_t gpos[4] = {0u, 0u, 0u, 0u};     // ... and list positions + 1
+    uint32_t gavail = 0;                     // entries of the pending group (0: none pending)
+    float gnear = 1.f;
+    auto alphas_of = [&](uint32_t h, uint32_t avail, float (&a)[4], uint32_t (&posv)[4], float &nearest) {
+        const float4(*g)[3] = sm.ring + (h & (RING - 1));
+        nearest = 1.f;
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            const float4 e = g[u][0];
+            const float dx = e.x - pxf, dy = e.y - pyf;
+            const float4 co = g[u][1];   // pre-scaled: log2 domain
+            const float power = dx * (co.x * dx + co.y * dy) + co.z * dy * dy;
+            const float alpha = fminf(0.99f, co.w * fast_exp2(power));
+            const bool keep = (uint32_t)u < avail && !(power > 0.f) && alpha >= CUT;
+            a[u] = keep ? alpha : 0.f;
+            nearest = (uint32_t)u < avail ? fminf(nearest, fabsf(fmaf(alpha, 255.f, -1.f))) : nearest;
+            posv[u] = __float_as_uint(e.z);
+        }
+    };
+    // ~1e-6 of the pairs: the contributor set must not depend on this kernel's rounding
+    auto resolve_cuts = [&](uint32_t h, uint32_t avail, float (&a)[4], const uint32_t (&posv)[4]) {
+        const float4(*g)[3] = sm.ring + (h & (RING - 1));
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            const float4 e = g[u][0];
+            const float4 co = g[u][1];
+            const float dx = e.x - pxf, dy = e.y - pyf;
+            const float alpha = fminf(0.99f, co.w * fast_exp2(dx * (co.x * dx + co.y * dy) + co.z * dy * dy));
+            if ((uint32_t)u < avail && fabsf(fmaf(alpha, 255.f, -1.f)) < CUT_BAND) {
+                a[u] = exact_cut(xy, conic_opacity, point_list[posv[u] - 1u], pxf, pyf) ? alpha : 0.f;
+                STAT_ADD(3, 1);
+            }
+        }
+    };
     auto consume = [&](bool flush) {
-        while (tail - head >= 4u || (flush && tail != head)) {
-            const uint32_t avail = min(4u, tail - head);
-            const float4(*g)[3] = sm.ring + (head & (RING - 1));
-            float a[4];
-            uint32_t posv[4];
-            float nearest = 1.f;
+        auto ready = [&]() { return tail - head >= 4u || (flush && tail != head); };
+        if (!ready()) return;
+        gavail = min(4u, tail - head);
+        alphas_of(head, gavail, ga, gpos, gnear);
+        while (true) {
+            const uint32_t h = head;
+            if (gnear < CUT_BAND) resolve_cuts(h, gavail, ga, gpos);
+            head += gavail;
+            // ---- one basic block: alphas of the next group (if any) beside the recurrence of this one ----
+            const uint32_t navail = ready() ? min(4u, tail - head) : 0u;
+            float na[4] = {0.f, 0.f, 0.f, 0.f};
+            uint32_t npos[4] = {0u, 0u, 0u, 0u};
+            float nnear = 1.f;
+            if (navail) alphas_of(head, navail, na, npos, nnear);   // (warp-uniform; a third of the calls end here)
+            const float4(*g)[3] = sm.ring + (h & (RING - 1));
+            const float p0 = T;
+            const float p1 = p0 * (1.f - ga[0]), p2 = p1 * (1.f - ga[1]), p3 = p2 * (1.f - ga[2]), p4 = p3 * (1.f - ga[3]);
+            const bool s0 = done | (p1 < 0.0001f), s1 = s0 | (p2 < 0.0001f), s2 = s1 | (p3 < 0.0001f), s3 = s2 | (p4 < 0.0001f);
+            const float w0 = s0 ? 0.f : ga[0] * p0, w1 = s1 ? 0.f : ga[1] * p1, w2 = s2 ? 0.f : ga[2] * p2,
+                        w3 = s3 ? 0.f : ga[3] * p3;
+            T = s0 ? p0 : (s1 ? p1 : (s2 ? p2 : (s3 ? p3 : p4)));
+            done = s3;
+            const float4 f0 = g[0][2], f1 = g[1][2], f2 = g[2][2], f3 = g[3][2];
+            C0 += f0.x * w0 + f1.x * w1 + f2.x * w2 + f3.x * w3;
+            C1 += f0.y * w0 + f1.y * w1 + f2.y * w2 + f3.y * w3;
+            C2 += f0.z * w0 + f1.z * w1 + f2.z * w2 + f3.z * w3;
+            if (INVDEPTH) invd += f0.w * w0 + f1.w * w1 + f2.w * w2 + f3.w * w3;
+            last = w0 != 0.f ? gpos[0] : last;
+            last = w1 != 0.f ? gpos[1] : last;
+            last = w2 != 0.f ? gpos[2] : last;
+            last = w3 != 0.f ? gpos[3] : last;
+            if (__all_sync(0xffffffffu, done)) { all_done = true; return; }
+            if (navail == 0u) return;
 #pragma unroll
-            for (int u = 0; u < 4; u++) {
-                const float4 e = g[u][0];
-                const float dx = e.x - pxf, dy = e.y - pyf;
-                const float4 co = g[u][1];   // pre-scaled: log2 domain
-                const float power = dx * (co.x * dx + co.y * dy) + co.z * dy * dy;
-                const float alpha = fminf(0.99f, co.w * fast_exp2(power));
-                const bool keep = (uint32_t)u < avail && !(power > 0.f) && alpha >= CUT;
-                a[u] = keep ? alpha : 0.f;
-                nearest = fminf(nearest, fabsf(fmaf(alpha, 255.f, -1.f)));
-                posv[u] = __float_as_uint(e.z);
-            }
-            if (nearest < CUT_BAND) {   // ~1e-6 of the pairs: the contributor set must not depend on this kernel's rounding
-#pragma unroll
-                for (int u = 0; u < 4; u++) {
-                    const float4 e = g[u][0];
-                    const float4 co = g[u][1];
-                    const float dx = e.x - pxf, dy = e.y - pyf;
-                    const float alpha = fminf(0.99f, co.w * fast_exp2(dx * (co.x * dx + co.y * dy) + co.z * dy * dy));
-                    if ((uint32_t)u < avail && fabsf(fmaf(alpha, 255.f, -1.f)) < CUT_BAND) {
-                        a[u] = exact_cut(xy, conic_opacity, point_list[posv[u] - 1u], pxf, pyf) ? alpha : 0.f;
-                        STAT_ADD(3, 1);
-                    }
-                }
-            }
-            // Transmittance recurrence, branch-free.  `done` is sticky; T never drops below 1e-4 (it is only updated when
-            // the product stays above), so an entry with alpha = 0 cannot trip the stop, and after the stop every weight
-            // is zero.  T (1 - alpha) is rounded like upstream's (subtract, then multiply): the stop decision is theirs.
-#pragma unroll
-            for (int u = 0; u < 4; u++) {
-                const float4 f = g[u][2];
-                const float test_T = T * (1.f - a[u]);
-                done = done | (test_T < 0.0001f);
-                const float w = done ? 0.f : a[u] * T;
-                T = done ? T : test_T;
-                C0 += f.x * w; C1 += f.y * w; C2 += f.z * w;
-                if (INVDEPTH) invd += f.w * w;
-                last = w != 0.f ? posv[u] : last;
-            }
-            head += avail;
-            if (__all_sync(0xffffffffu, done)) { all_done = true; break; }
+            for (int u = 0; u < 4; u++) { ga[u] = na[u]; gpos[u] = npos[u]; }
+            gavail = navail;
+            gnear = nnear;
         }
     };
 
@@ -299,8 +337,17 @@ __global__ void __launch_bounds__(FWD_WARPS * 32, FWD_MIN_CTAS) blend_forward_ke
         if (ahead + 64u < count) id_b = point_list[ahead + 64u];
         __syncwarp();
         consume(false);
+#ifdef D3GA_BLEND_TRACE
+        tr_chunks++;
+#endif
     }
     if (!all_done) consume(true);
+#ifdef D3GA_BLEND_TRACE
+    if (lane == 0 && blockIdx.x < 65536) {
+        unsigned long long *o = g_fwd_trace + 4 * ((size_t)blockIdx.x * 8 + warp);
+        o[0] = tr_t0; o[1] = global_ns(); o[2] = ((unsigned long long)tile << 32) | tr_chunks; o[3] = ((unsigned long long)count << 32) | head;
+    }
+#endif
     cp_async_wait_all();   // nothing may still be landing in shared memory when the CTA retires
     if (inside) {
         const size_t pid = (size_t)py * W + px, plane = (size_t)H * W;
@@ -394,7 +441,7 @@ template <bool INVDEPTH>
 __global__ void __launch_bounds__(TILE_PIX, BWD_MIN_CTAS) blend_backward_kernel(
     const RasterHeader *__restrict__ hdr, const uint2 *__restrict__ ranges, const uint32_t *__restrict__ vals0,
     const uint32_t *__restrict__ vals1, int W, int H, const float *__restrict__ bg,
-    const SplatRecord *__restrict__ splat, const float *__restrict__ colors, const float2 *__restrict__ xy,
+    const SplatRecord *__restrict__ splat, const float4 *__restrict__ feat, const float2 *__restrict__ xy,
     const float4 *__restrict__ conic_opacity, const float *__restrict__ final_T, const uint32_t *__restrict__ n_contrib,
     const float *__restrict__ dL_dpix, const float *__restrict__ dL_dinvdepth_pix, float *__restrict__ grad_acc,
     int grid_x, const uint32_t *__restrict__ order_bwd, const uint32_t *__restrict__ ballots) {
@@ -526,11 +573,7 @@ __global__ void __launch_bounds__(TILE_PIX, BWD_MIN_CTAS) blend_backward_kernel(
             const uint32_t s = (tail + __popc(m & lanemask_lt())) & (RING - 1);
             cp_async_16(&sm.ring[s][0], &splat[id].g0);
             cp_async_16(&sm.ring[s][1], &splat[id].g1);
-            const float *csrc = colors + 3 * (size_t)id;
-            float *cdst = reinterpret_cast<float *>(&sm.ring[s][2]);
-            cp_async_4(cdst, csrc);
-            cp_async_4(cdst + 1, csrc + 1);
-            cp_async_4(cdst + 2, csrc + 2);
+            cp_async_16(&sm.ring[s][2], feat + id);
             sm.ring_m[s] = make_uint2(id, 32u * (uint32_t)fc + 31u - lane);
         }
         cp_async_commit();
@@ -546,8 +589,21 @@ __global__ void __launch_bounds__(TILE_PIX, BWD_MIN_CTAS) blend_backward_kernel(
     }
 }
 
+// This render's colours, [N,3] as the API hands them (or the SH colours of the preprocess), as one aligned float4 per
+// Gaussian: a list entry's colour is then ONE 16-byte asynchronous copy instead of three 4-byte ones.  28 B per Gaussian.
+__global__ void __launch_bounds__(256) pack_features_kernel(int P, const float *__restrict__ colors, float4 *__restrict__ feat) {
+    const int i = blockIdx.x * 256 + threadIdx.x;
+    if (i >= P) return;
+    feat[i] = make_float4(colors[3 * (size_t)i], colors[3 * (size_t)i + 1], colors[3 * (size_t)i + 2], 0.f);
+}
+
 }  // namespace
 
+#ifdef D3GA_BLEND_TRACE
+extern "C" int d3ga_debug_fwd_trace(unsigned long long *out, int ctas) {
+    return cudaMemcpyFromSymbol(out, g_fwd_trace, sizeof(unsigned long long) * 32 * (size_t)ctas) == cudaSuccess ? 0 : -2;
+}
+#endif
 #ifdef D3GA_BLEND_STATS
 extern "C" int d3ga_debug_blend_stats(unsigned long long *out, int reset) {
     if (cudaMemcpyFromSymbol(out, g_blend_stats, sizeof(g_blend_stats)) != cudaSuccess) return -2;
@@ -559,7 +615,7 @@ extern "C" int d3ga_debug_blend_stats(unsigned long long *out, int reset) {
 }
 #endif
 
-int launch_blend_forward(int W, int H, const float *background, const float *colors, const uint8_t *geom,
+int launch_blend_forward(int P, int W, int H, const float *background, const float *colors, const uint8_t *geom,
                          const GeomLayout &GL, const uint8_t *binning, const BinLayout &BL, uint8_t *image,
                          const ImgLayout &IL, float *out_color, float *out_invdepth, cudaStream_t stream) {
     const int gx = (W + TILE - 1) / TILE, gy = (H + TILE - 1) / TILE, num_tiles = gx * gy;
@@ -585,16 +641,28 @@ int launch_blend_forward(int W, int H, const float *background, const float *col
         return D3GA_OK;
     });
     if (arc) return arc;
+    // stage 1 packed the colours it was given into the geometry workspace; a render with OTHER colours on the same
+    // geometry (the silhouette pass of a training frame) packs its own into its image workspace
+    const float4 *feat = reinterpret_cast<const float4 *>(geom + GL.feat);
+    if (colors != recall_packed_colors(geom)) {
+        float4 *own = reinterpret_cast<float4 *>(image + IL.feat);
+        feat = own;
+        if (P > 0) {
+            ProfScope prof(K_PACK_FEAT, stream);
+            pack_features_kernel<<<(P + 255) / 256, 256, 0, stream>>>(P, colors, own);
+            D3GA_LAUNCH_CHECK();
+        }
+    }
     ProfScope prof(K_BLEND_FWD, stream);
     {
         D3GA_CUDA(cudaMemsetAsync(tile_nproc, 0, sizeof(uint32_t) * (size_t)num_tiles, stream));
         if (out_invdepth)
             blend_forward_kernel<true><<<num_tiles, FWD_WARPS * 32, smem, stream>>>(
-                hdr, ranges, v0, v1, W, H, splat, colors, xy, co, background, final_T, n_contrib, out_color, out_invdepth,
+                hdr, ranges, v0, v1, W, H, splat, feat, xy, co, background, final_T, n_contrib, out_color, out_invdepth,
                 hdr_rw, gx, num_tiles, order_fwd, tile_nproc, order_bwd, ballots);
         else
             blend_forward_kernel<false><<<num_tiles, FWD_WARPS * 32, smem, stream>>>(
-                hdr, ranges, v0, v1, W, H, splat, colors, xy, co, background, final_T, n_contrib, out_color, nullptr,
+                hdr, ranges, v0, v1, W, H, splat, feat, xy, co, background, final_T, n_contrib, out_color, nullptr,
                 hdr_rw, gx, num_tiles, order_fwd, tile_nproc, order_bwd, ballots);
     }
     D3GA_LAUNCH_CHECK();
@@ -614,6 +682,8 @@ int launch_blend_backward(int W, int H, const float *background, const float *co
     const float4 *co = reinterpret_cast<const float4 *>(geom + GL.conic_opacity);
     const SplatRecord *splat = reinterpret_cast<const SplatRecord *>(geom + GL.splat);
     const uint32_t *ballots = reinterpret_cast<const uint32_t *>(image + IL.ballots);
+    const float4 *feat = colors == recall_packed_colors(geom) ? reinterpret_cast<const float4 *>(geom + GL.feat)
+                                                              : reinterpret_cast<const float4 *>(image + IL.feat);
     const float *final_T = reinterpret_cast<const float *>(image + IL.final_T);
     const uint32_t *n_contrib = reinterpret_cast<const uint32_t *>(image + IL.n_contrib);
     const uint32_t *order_bwd = reinterpret_cast<const uint32_t *>(image + IL.order_bwd);
@@ -629,11 +699,11 @@ int launch_blend_backward(int W, int H, const float *background, const float *co
     {
         if (dL_dinvdepth_pix)
             blend_backward_kernel<true><<<num_tiles, TILE_PIX, smem, stream>>>(
-                hdr, ranges, v0, v1, W, H, background, splat, colors, xy, co, final_T, n_contrib, dL_dpix,
+                hdr, ranges, v0, v1, W, H, background, splat, feat, xy, co, final_T, n_contrib, dL_dpix,
                 dL_dinvdepth_pix, grad_acc, gx, order_bwd, ballots);
         else
             blend_backward_kernel<false><<<num_tiles, TILE_PIX, smem, stream>>>(
-                hdr, ranges, v0, v1, W, H, background, splat, colors, xy, co, final_T, n_contrib, dL_dpix, nullptr,
+                hdr, ranges, v0, v1, W, H, background, splat, feat, xy, co, final_T, n_contrib, dL_dpix, nullptr,
                 grad_acc, gx, order_bwd, ballots);
     }
     D3GA_LAUNCH_CHECK();

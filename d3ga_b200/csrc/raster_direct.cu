@@ -463,6 +463,7 @@ struct PlanRecord {
     int P, gx, gy;
     uint64_t capacity;
     DirectPlan plan;
+    const void *packed_colors;
 };
 constexpr int PLAN_RECORDS = 512;   // workspaces between their stage 1 and their last use of the plan
 std::mutex g_plan_mu;
@@ -579,16 +580,17 @@ int launch_copy_sorted_keys(const uint8_t *geom, const GeomLayout &GL, const uin
     return D3GA_OK;
 }
 
-void remember_direct_plan(const void *geom, int P, int gx, int gy, uint64_t capacity, const DirectPlan &pl) {
+void remember_direct_plan(const void *geom, int P, int gx, int gy, uint64_t capacity, const DirectPlan &pl,
+                          const void *packed_colors) {
     int dev = 0;
     (void)cudaGetDevice(&dev);
     std::lock_guard<std::mutex> lk(g_plan_mu);
     for (int i = 0; i < PLAN_RECORDS; i++)
         if (g_plans[i].geom == geom && g_plans[i].dev == dev) {
-            g_plans[i] = PlanRecord{dev, geom, P, gx, gy, capacity, pl};
+            g_plans[i] = PlanRecord{dev, geom, P, gx, gy, capacity, pl, packed_colors};
             return;
         }
-    g_plans[g_plan_next++ % PLAN_RECORDS] = PlanRecord{dev, geom, P, gx, gy, capacity, pl};
+    g_plans[g_plan_next++ % PLAN_RECORDS] = PlanRecord{dev, geom, P, gx, gy, capacity, pl, packed_colors};
 }
 bool recall_direct_plan(const void *geom, int P, int gx, int gy, uint64_t capacity, DirectPlan *pl) {
     int dev = 0;
@@ -603,6 +605,15 @@ bool recall_direct_plan(const void *geom, int P, int gx, int gy, uint64_t capaci
         }
     }
     return false;
+}
+
+const void *recall_packed_colors(const void *geom) {
+    int dev = 0;
+    (void)cudaGetDevice(&dev);
+    std::lock_guard<std::mutex> lk(g_plan_mu);
+    for (int i = 0; i < PLAN_RECORDS; i++)
+        if (g_plans[i].geom == geom && g_plans[i].dev == dev) return g_plans[i].packed_colors;
+    return nullptr;
 }
 
 void set_views_in_flight(int n) { g_views_in_flight.store(n < 1 ? 1 : (n > 64 ? 64 : n), std::memory_order_relaxed); }

@@ -73,6 +73,7 @@ struct GeoParams {
     int32_t *tile_diff;    // [(gy+1)][(gx+1)] +1/-1 at the rect corners (null: grid too large, counts come from the keys)
     uint4 *grec;           // direct tile scatter: [P] x0 | y0 << 16, width | height << 16, Gaussian id, depth bits (else null)
     SplatRecord *splat;    // [P] what the blend kernels gather per list entry (common.cuh)
+    float4 *feat;          // [P] the colours (given, or from SH) as (r, g, b, 0)
 };
 
 constexpr uint64_t FLAG_AGG = 1ull << 62, FLAG_INC = 2ull << 62, FLAG_MASK = 3ull << 62;
@@ -237,9 +238,13 @@ __device__ __forceinline__ void preprocess_one(const GeoParams &p, int idx, cons
                 const float len = sqrtf(d.x * d.x + d.y * d.y + d.z * d.z);
                 d.x /= len; d.y /= len; d.z /= len;
                 sh_to_rgb(p.sh_degree, p.shs + (size_t)idx * p.sh_coeffs * 3, d, rgb, cl);
+                p.feat[idx] = make_float4(rgb[0], rgb[1], rgb[2], 0.f);
             }
 #pragma unroll
             for (int c = 0; c < 3; c++) { p.rgb[3 * (size_t)idx + c] = rgb[c]; p.clamped[3 * (size_t)idx + c] = cl[c]; }
+        } else if (live) {
+            const float *cp = p.colors_precomp + 3 * (size_t)idx;
+            p.feat[idx] = make_float4(cp[0], cp[1], cp[2], 0.f);
         }
         p.depth[idx] = depth;
         p.xy[idx] = make_float2(pxi, pyi);
@@ -490,9 +495,10 @@ int launch_geometry(int P, int sh_degree, int sh_coeffs, const float *means3D, c
     p.P_pad = (uint32_t)GL.p_pad;
     p.tile_diff = nullptr;
     const DirectPlan direct = direct_plan(P, p.gx, p.gy, capacity);
-    remember_direct_plan(geom, P, p.gx, p.gy, capacity, direct);
+    remember_direct_plan(geom, P, p.gx, p.gy, capacity, direct, shs ? (const void *)(geom + GL.rgb) : (const void *)colors_precomp);
     p.grec = direct.ok ? reinterpret_cast<uint4 *>(geom + GL.grec) : nullptr;
     p.splat = reinterpret_cast<SplatRecord *>(geom + GL.splat);
+    p.feat = reinterpret_cast<float4 *>(geom + GL.feat);
     if (depth_first_mode(sort_mode()) && !direct.ok && tile_plan_from_grid(p.gx, p.gy)) {
         p.tile_diff = reinterpret_cast<int32_t *>(geom + GL.tile_diff);
         D3GA_CUDA(cudaMemsetAsync(p.tile_diff, 0, 4ull * (p.gx + 1) * (p.gy + 1), stream));

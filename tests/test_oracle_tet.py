@@ -68,3 +68,27 @@ def test_topology_matches_brute_force():
     for f, (a, b) in zip(faces, topo):
         owners = [i for i, tt in enumerate(tets) if set(f) <= set(tt)]
         assert owners == [x for x in (a, b) if x != -1]   # increasing tet id, -1 padded
+
+
+def test_tetra_matches_the_reference_constructor():
+    """Tetra.from_tensors against tests/golden/tetra_golden.npz: unique faces, the face -> (tet, tet | -1) map, the
+    surface split and gradient() as the reference's own Tetra.__init__ / build() produced them
+    (tetra_sampler/tetra.py:12-130, executed by tests/golden/make_tetra_golden.py) -- tets in arbitrary order with
+    arbitrary vertex order."""
+    import os
+
+    import torch
+
+    from d3ga_b200.tetra_sampler import Tetra
+
+    G = np.load(os.path.join(os.path.dirname(__file__), "golden", "tetra_golden.npz"))
+    for k in range(int(G["n_cases"])):
+        pts, tets = torch.from_numpy(G[f"{k}_points"]), torch.from_numpy(G[f"{k}_tetras"])
+        t = Tetra.from_tensors(pts, tets, device="cpu")
+        assert np.array_equal(t.tetra_faces.numpy(), G[f"{k}_tetra_faces"])
+        assert np.array_equal(t.triangle_to_tetra.numpy(), G[f"{k}_triangle_to_tetra"])
+        assert t.triangle_to_tetra.dtype == torch.int32
+        assert np.array_equal(t.surface_triangle.numpy(), G[f"{k}_surface_triangle"])
+        assert np.array_equal(t.surface_tetras.numpy(), G[f"{k}_surface_tetras"])
+        assert np.array_equal(t.gradient(pts[tets]).numpy(), G[f"{k}_gradient"])
+        assert [t.n(), t.n_points()] == list(G[f"{k}_n"])
