@@ -120,9 +120,9 @@ def cpu_view(scene, cam, weights):
     from oracle.raster_oracle import RasterOracle
 
     t = th.from_numpy
-    leaves = [t(a).clone().requires_grad_(True) for a in (scene.tetpoints, scene.barys, scene.scales, scene.rotation)]
+    leaves = [t(a).clone().requires_grad_(True) for a in (scene.tetpoints, scene.barys, np.log(scene.scales), scene.rotation)]
     means, cov6 = deform_oracle.deform_gaussians(leaves[0], t(scene.tets), t(scene.tetra_id), leaves[1],
-                                                 t(scene.canonical_gradient), leaves[2], leaves[3])
+                                                 t(scene.canonical_gradient), th.exp(leaves[2]), leaves[3])
     orc = RasterOracle(np.float32)
     st = orc.forward(means.detach().numpy(), scene.opacity, cam.viewmatrix, cam.projmatrix, cam.campos, scene.W,
                      scene.H, cam.tanfovx, cam.tanfovy, [1, 1, 1], colors_precomp=scene.colors,
@@ -206,7 +206,10 @@ def run_ours(args):
     bank = training.CameraBank(cams, dev)
     bg = torch.ones(3, device=dev)
     rng = np.random.default_rng(0)
-    weights_h = torch.from_numpy(rng.uniform(-1, 1, (3, scene.H, scene.W)).astype(np.float32)).pin_memory()
+    # the target / weight image of the loss lives on the host as uint8 (what a camera frame is: lib/batch.py:86-88 uploads
+    # uint8 and normalises on the GPU); the resident copy is the same image, normalised
+    weights_u8 = torch.from_numpy(rng.integers(0, 256, (3, scene.H, scene.W), dtype=np.uint8)).pin_memory()
+    weights_h = (weights_u8.float() * training.U8_SCALE + training.U8_OFFSET).pin_memory()
     weights = weights_h.to(dev)
     loss_h = torch.zeros((), dtype=torch.float32).pin_memory()
 
@@ -334,14 +337,15 @@ def run_ours(args):
     # e2e: the same steps through the public API with this step's inputs in pinned HOST memory
     e2e = None
     if not args.no_e2e:
-        feed = training.HostFeed(weights_h, dev, cam_host=bank.host, tetpoints_host=avatar.tetpoints_host,
+        feed = training.HostFeed(weights_u8, dev, cam_host=bank.host, tetpoints_host=avatar.tetpoints_host,
                                  slots=2 * max(1, args.lanes))
         region(1, 0, from_host=True, feed=feed, loss_host=loss_h)
         ms_e = region(args.steps, args.warmup, from_host=True, feed=feed, loss_host=loss_h)
-        h2d = 35 * 4 + avatar.tetpoints.numel() * 4 + weights.numel() * 4
+        h2d = 35 * 4 + avatar.tetpoints.numel() * 4 + weights_u8.numel()
         e2e = {"value": views_total / (ms_e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d * V,
                "d2h_bytes_per_step": 4,
-               "inputs_from_host": "per view: camera (35 floats), cage vertices tetpoints [V,3], target/weight image [3,H,W] "
+               "inputs_from_host": "per view: camera (35 floats), cage vertices tetpoints [V,3], target/weight image [3,H,W] as "
+                                   "uint8, normalised on the device like lib/batch.py:86-88 "
                                    "(all uploaded ahead of the view on a side stream); the step's loss is read back once per step; "
                                    "Gaussian parameters stay resident like nn.Parameters"}
 

@@ -10,7 +10,19 @@
 // and its autograd backward (index_put_ with accumulate into tetpoints).
 // One thread per Gaussian; nothing but inputs and outputs touches HBM (84 B read + 36 B written per Gaussian forward
 // against >= 0.6 kB of temporaries in the torch chain).  The cage (<= a few hundred kB) stays L2 resident.
+//
+// The same launches optionally take in what models/cage_net.py computes right before and beside that chain (the fused
+// entry points, d3ga_deform_forward_fused / _backward_fused):
+//   canon_barys = barys + delta_bary                  cage_net.py:213   (not renormalised)
+//   scales      = exp(scaling + delta_scale)          cage_net.py:214   (scaling_activation = exp, :78)
+//   rotation    = F.normalize(rotation + delta_rot)   cage_net.py:215   (the kernel normalises once: build_rotation's own
+//                                                                        normalisation makes F.normalize's a no-op except
+//                                                                        for the zero vector, NaN in both)
+//   fm_energy   = fem_energy(tetpoints)               cage_net.py:225, lib/cage.py:349-361 -- per-TET work, run by extra
+//                                                      CTAs appended to the grid (it gathers the same tetpoints[tets])
+// Base tensor and delta receive the same gradient, which the backward writes once.
 #include "common.cuh"
+#include "fem.cuh"
 
 namespace d3ga {
 
@@ -23,6 +35,39 @@ namespace {
 struct Tet4 {
     float v[4][3];
 };
+
+// What the fused entry points add to a launch; all null / zero for the plain ones.
+struct DeformExtra {
+    const float *delta_bary, *delta_scale, *delta_rot;   // [N,4], [N,3], [N,4] or null
+    int log_scales;                                      // scales are pre-activation: s = exp(scales (+ delta_scale))
+    const float *dn_inv;                                 // [T,3,3] inverse rest-pose edge matrices, or null (no energy)
+    float *energy;                                       // forward: [T] out
+    const float *dL_denergy;                             // backward: [T] or null
+    int gaussian_blocks;                                 // CTAs below this index work on Gaussians, the rest on tets
+};
+
+// barys, scales (activated) and the un-normalised quaternion of Gaussian n as the kernels use them
+__device__ __forceinline__ void load_gaussian(const DeformExtra &ex, const float *__restrict__ barys,
+                                              const float *__restrict__ scales, const float *__restrict__ rotation,
+                                              size_t n, float (&bw)[4], float (&s)[3], float4 &q) {
+    float4 b = *reinterpret_cast<const float4 *>(barys + 4 * n);
+    if (ex.delta_bary) {
+        const float4 d = *reinterpret_cast<const float4 *>(ex.delta_bary + 4 * n);
+        b.x += d.x; b.y += d.y; b.z += d.z; b.w += d.w;
+    }
+    bw[0] = b.x; bw[1] = b.y; bw[2] = b.z; bw[3] = b.w;
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+        float v = scales[3 * n + k];
+        if (ex.delta_scale) v += ex.delta_scale[3 * n + k];
+        s[k] = ex.log_scales ? expf(v) : v;
+    }
+    q = *reinterpret_cast<const float4 *>(rotation + 4 * n);
+    if (ex.delta_rot) {
+        const float4 d = *reinterpret_cast<const float4 *>(ex.delta_rot + 4 * n);
+        q.x += d.x; q.y += d.y; q.z += d.z; q.w += d.w;
+    }
+}
 
 __device__ __forceinline__ void load_tet(const float *__restrict__ tetpoints, const int64_t *__restrict__ tets,
                                          int64_t t, int64_t (&vid)[4], Tet4 &X) {
@@ -44,7 +89,12 @@ __global__ void __launch_bounds__(GEO_THREADS) deform_forward_kernel(
     int N, int T, const float *__restrict__ tetpoints, const int64_t *__restrict__ tets,
     const int64_t *__restrict__ tetra_id, const float *__restrict__ barys, const float *__restrict__ cgrad,
     const float *__restrict__ scales, const float *__restrict__ rotation, float *__restrict__ means3D,
-    float *__restrict__ cov3D) {
+    float *__restrict__ cov3D, const DeformExtra ex) {
+    if ((int)blockIdx.x >= ex.gaussian_blocks) {   // appended CTAs: the cage's neo-Hookean energy, one thread per tet
+        const int tt = ((int)blockIdx.x - ex.gaussian_blocks) * GEO_THREADS + (int)threadIdx.x;
+        if (tt < T) fem::fem_forward_tet(tt, tetpoints, tets, ex.dn_inv, ex.energy);
+        return;
+    }
     const int n = blockIdx.x * GEO_THREADS + threadIdx.x;
     if (n >= N) return;
     int64_t t = tetra_id[n];
@@ -52,8 +102,9 @@ __global__ void __launch_bounds__(GEO_THREADS) deform_forward_kernel(
     int64_t vid[4];
     Tet4 X;
     load_tet(tetpoints, tets, t, vid, X);
-    const float4 b = *reinterpret_cast<const float4 *>(barys + 4 * (size_t)n);
-    const float bw[4] = {b.x, b.y, b.z, b.w};
+    float bw[4], s[3];
+    float4 q;
+    load_gaussian(ex, barys, scales, rotation, (size_t)n, bw, s, q);
 #pragma unroll
     for (int c = 0; c < 3; c++)
         means3D[3 * (size_t)n + c] = X.v[0][c] * bw[0] + X.v[1][c] * bw[1] + X.v[2][c] * bw[2] + X.v[3][c] * bw[3];
@@ -69,11 +120,9 @@ __global__ void __launch_bounds__(GEO_THREADS) deform_forward_kernel(
     for (int i = 0; i < 3; i++)
 #pragma unroll
         for (int j = 0; j < 3; j++) J[i][j] = G[i][0] * Cg[0][j] + G[i][1] * Cg[1][j] + G[i][2] * Cg[2][j];
-    const float4 q = *reinterpret_cast<const float4 *>(rotation + 4 * (size_t)n);
     const float inv = 1.f / sqrtf(q.x * q.x + q.y * q.y + q.z * q.z + q.w * q.w);
     float Rm[3][3];
     rotation_from_unit_quat(q.x * inv, q.y * inv, q.z * inv, q.w * inv, Rm);
-    const float s[3] = {scales[3 * (size_t)n], scales[3 * (size_t)n + 1], scales[3 * (size_t)n + 2]};
     float B[3][3];   // B = J R diag(s); cov = B B^T
 #pragma unroll
     for (int i = 0; i < 3; i++)
@@ -119,7 +168,13 @@ __global__ void __launch_bounds__(GEO_THREADS, DEFORM_BWD_MIN_CTAS) deform_backw
     const int64_t *__restrict__ tetra_id, const float *__restrict__ barys, const float *__restrict__ cgrad,
     const float *__restrict__ scales, const float *__restrict__ rotation, const float *__restrict__ dL_dmeans,
     const float *__restrict__ dL_dcov, float *__restrict__ dL_dtetpoints, float *__restrict__ dL_dbarys,
-    float *__restrict__ dL_dscales, float *__restrict__ dL_drotation, const int32_t *__restrict__ order) {
+    float *__restrict__ dL_dscales, float *__restrict__ dL_drotation, const int32_t *__restrict__ order,
+    const DeformExtra ex) {
+    if ((int)blockIdx.x >= ex.gaussian_blocks) {   // appended CTAs: gradient of the cage energy into the cage vertices
+        const int tt = ((int)blockIdx.x - ex.gaussian_blocks) * GEO_THREADS + (int)threadIdx.x;
+        if (tt < T && dL_dtetpoints) fem::fem_backward_tet(tt, tetpoints, tets, ex.dn_inv, ex.dL_denergy, dL_dtetpoints);
+        return;
+    }
     const int i = blockIdx.x * GEO_THREADS + threadIdx.x;
     const bool live = i < N;
     // With `order` (a permutation that sorts tetra_id) neighbouring lanes share tets: their cage-vertex gradients are
@@ -136,8 +191,9 @@ __global__ void __launch_bounds__(GEO_THREADS, DEFORM_BWD_MIN_CTAS) deform_backw
         if (t < 0) t += T;
         Tet4 X;
         load_tet(tetpoints, tets, t, vid, X);
-        const float4 b = *reinterpret_cast<const float4 *>(barys + 4 * (size_t)n);
-        const float bw[4] = {b.x, b.y, b.z, b.w};
+        float bw[4], s[3];
+        float4 q;
+        load_gaussian(ex, barys, scales, rotation, (size_t)n, bw, s, q);
         const float dm[3] = {dL_dmeans[3 * (size_t)n], dL_dmeans[3 * (size_t)n + 1], dL_dmeans[3 * (size_t)n + 2]};
         float g6[6];
 #pragma unroll
@@ -155,12 +211,10 @@ __global__ void __launch_bounds__(GEO_THREADS, DEFORM_BWD_MIN_CTAS) deform_backw
         for (int r = 0; r < 3; r++)
 #pragma unroll
             for (int j = 0; j < 3; j++) J[r][j] = G[r][0] * Cg[0][j] + G[r][1] * Cg[1][j] + G[r][2] * Cg[2][j];
-        const float4 q = *reinterpret_cast<const float4 *>(rotation + 4 * (size_t)n);
         const float inv = 1.f / sqrtf(q.x * q.x + q.y * q.y + q.z * q.z + q.w * q.w);
         const float qr = q.x * inv, qx = q.y * inv, qy = q.z * inv, qz = q.w * inv;
         float Rm[3][3];
         rotation_from_unit_quat(qr, qx, qy, qz, Rm);
-        const float s[3] = {scales[3 * (size_t)n], scales[3 * (size_t)n + 1], scales[3 * (size_t)n + 2]};
         float JR[3][3], B[3][3];
 #pragma unroll
         for (int r = 0; r < 3; r++)
@@ -193,9 +247,9 @@ __global__ void __launch_bounds__(GEO_THREADS, DEFORM_BWD_MIN_CTAS) deform_backw
                 dJ[r][j] = dJR[r][0] * Rm[j][0] + dJR[r][1] * Rm[j][1] + dJR[r][2] * Rm[j][2];
                 A[r][j] = J[0][r] * dJR[0][j] + J[1][r] * dJR[1][j] + J[2][r] * dJR[2][j];
             }
-        if (dL_dscales) {
+        if (dL_dscales) {   // through exp when the scales came in pre-activation: d exp(x) = exp(x) dx
 #pragma unroll
-            for (int k = 0; k < 3; k++) dL_dscales[3 * (size_t)n + k] = ds[k];
+            for (int k = 0; k < 3; k++) dL_dscales[3 * (size_t)n + k] = ex.log_scales ? ds[k] * s[k] : ds[k];
         }
         if (dL_drotation) {
             const float r = qr, x = qx, y = qy, z = qz;
@@ -245,35 +299,62 @@ __global__ void __launch_bounds__(GEO_THREADS, DEFORM_BWD_MIN_CTAS) deform_backw
 
 using namespace d3ga;
 
+static int deform_forward_impl(int N, int V, int T, const float *tetpoints, const int64_t *tets, const int64_t *tetra_id,
+                               const float *barys, const float *canonical_gradient, const float *scales,
+                               const float *rotation, float *means3D, float *cov3D, DeformExtra ex, d3ga_stream_t stream) {
+    if (N < 0 || V <= 0 || T <= 0) return D3GA_EINVAL;
+    if (!tetpoints || !tets) return D3GA_EINVAL;
+    if (N > 0 && (!tetra_id || !barys || !canonical_gradient || !scales || !rotation || !means3D || !cov3D)) return D3GA_EINVAL;
+    if ((ex.dn_inv != nullptr) != (ex.energy != nullptr)) return D3GA_EINVAL;
+    ex.gaussian_blocks = (N + GEO_THREADS - 1) / GEO_THREADS;
+    const int blocks = ex.gaussian_blocks + (ex.dn_inv ? (T + GEO_THREADS - 1) / GEO_THREADS : 0);
+    if (blocks == 0) return D3GA_OK;
+    ProfScope prof(K_DEFORM_FWD, (cudaStream_t)stream);
+    deform_forward_kernel<<<blocks, GEO_THREADS, 0, (cudaStream_t)stream>>>(
+        N, T, tetpoints, tets, tetra_id, barys, canonical_gradient, scales, rotation, means3D, cov3D, ex);
+    D3GA_LAUNCH_CHECK();
+    return D3GA_OK;
+}
+
 extern "C" int d3ga_deform_forward(int N, int V, int T, const float *tetpoints, const int64_t *tets,
                                    const int64_t *tetra_id, const float *barys, const float *canonical_gradient,
                                    const float *scales, const float *rotation, float *means3D, float *cov3D,
                                    d3ga_stream_t stream) {
-    if (N < 0 || V <= 0 || T <= 0) return D3GA_EINVAL;
-    if (N == 0) return D3GA_OK;
-    if (!tetpoints || !tets || !tetra_id || !barys || !canonical_gradient || !scales || !rotation || !means3D || !cov3D)
-        return D3GA_EINVAL;
-    ProfScope prof(K_DEFORM_FWD, (cudaStream_t)stream);
-    deform_forward_kernel<<<(N + GEO_THREADS - 1) / GEO_THREADS, GEO_THREADS, 0, (cudaStream_t)stream>>>(
-        N, T, tetpoints, tets, tetra_id, barys, canonical_gradient, scales, rotation, means3D, cov3D);
-    D3GA_LAUNCH_CHECK();
-    return D3GA_OK;
+    if (N == 0) return (N < 0 || V <= 0 || T <= 0) ? D3GA_EINVAL : D3GA_OK;
+    return deform_forward_impl(N, V, T, tetpoints, tets, tetra_id, barys, canonical_gradient, scales, rotation, means3D,
+                               cov3D, DeformExtra{}, stream);
+}
+
+extern "C" int d3ga_deform_forward_fused(int N, int V, int T, const float *tetpoints, const int64_t *tets,
+                                         const int64_t *tetra_id, const float *barys, const float *delta_bary,
+                                         const float *canonical_gradient, const float *scales, const float *delta_scale,
+                                         int log_scales, const float *rotation, const float *delta_rot,
+                                         const float *dn_inv, float *energy, float *means3D, float *cov3D,
+                                         d3ga_stream_t stream) {
+    DeformExtra ex{};
+    ex.delta_bary = delta_bary; ex.delta_scale = delta_scale; ex.delta_rot = delta_rot; ex.log_scales = log_scales ? 1 : 0;
+    ex.dn_inv = dn_inv; ex.energy = energy;
+    return deform_forward_impl(N, V, T, tetpoints, tets, tetra_id, barys, canonical_gradient, scales, rotation, means3D,
+                               cov3D, ex, stream);
 }
 
 static int deform_backward_impl(int N, int V, int T, const float *tetpoints, const int64_t *tets,
                                 const int64_t *tetra_id, const float *barys, const float *canonical_gradient,
                                 const float *scales, const float *rotation, const float *dL_dmeans3D,
                                 const float *dL_dcov3D, float *dL_dtetpoints, float *dL_dbarys, float *dL_dscales,
-                                float *dL_drotation, const int32_t *order, d3ga_stream_t stream) {
+                                float *dL_drotation, const int32_t *order, DeformExtra ex, d3ga_stream_t stream) {
     if (N < 0 || V <= 0 || T <= 0) return D3GA_EINVAL;
-    if (N == 0) return D3GA_OK;
-    if (!tetpoints || !tets || !tetra_id || !barys || !canonical_gradient || !scales || !rotation || !dL_dmeans3D ||
-        !dL_dcov3D)
+    if (!tetpoints || !tets) return D3GA_EINVAL;
+    if (N > 0 && (!tetra_id || !barys || !canonical_gradient || !scales || !rotation || !dL_dmeans3D || !dL_dcov3D))
         return D3GA_EINVAL;
+    if (ex.dL_denergy && !ex.dn_inv) return D3GA_EINVAL;
+    ex.gaussian_blocks = (N + GEO_THREADS - 1) / GEO_THREADS;
+    const int blocks = ex.gaussian_blocks + (ex.dL_denergy ? (T + GEO_THREADS - 1) / GEO_THREADS : 0);
+    if (blocks == 0) return D3GA_OK;
     ProfScope prof(K_DEFORM_BWD, (cudaStream_t)stream);
-    deform_backward_kernel<<<(N + GEO_THREADS - 1) / GEO_THREADS, GEO_THREADS, 0, (cudaStream_t)stream>>>(
+    deform_backward_kernel<<<blocks, GEO_THREADS, 0, (cudaStream_t)stream>>>(
         N, T, tetpoints, tets, tetra_id, barys, canonical_gradient, scales, rotation, dL_dmeans3D, dL_dcov3D,
-        dL_dtetpoints, dL_dbarys, dL_dscales, dL_drotation, order);
+        dL_dtetpoints, dL_dbarys, dL_dscales, dL_drotation, order, ex);
     D3GA_LAUNCH_CHECK();
     return D3GA_OK;
 }
@@ -283,9 +364,10 @@ extern "C" int d3ga_deform_backward(int N, int V, int T, const float *tetpoints,
                                     const float *scales, const float *rotation, const float *dL_dmeans3D,
                                     const float *dL_dcov3D, float *dL_dtetpoints, float *dL_dbarys, float *dL_dscales,
                                     float *dL_drotation, d3ga_stream_t stream) {
+    if (N == 0) return (N < 0 || V <= 0 || T <= 0) ? D3GA_EINVAL : D3GA_OK;
     return deform_backward_impl(N, V, T, tetpoints, tets, tetra_id, barys, canonical_gradient, scales, rotation,
                                 dL_dmeans3D, dL_dcov3D, dL_dtetpoints, dL_dbarys, dL_dscales, dL_drotation, nullptr,
-                                stream);
+                                DeformExtra{}, stream);
 }
 
 extern "C" int d3ga_deform_backward_ordered(int N, int V, int T, const float *tetpoints, const int64_t *tets,
@@ -295,7 +377,24 @@ extern "C" int d3ga_deform_backward_ordered(int N, int V, int T, const float *te
                                             float *dL_dtetpoints, float *dL_dbarys, float *dL_dscales,
                                             float *dL_drotation, const int32_t *order, d3ga_stream_t stream) {
     if (!order) return D3GA_EINVAL;
+    if (N == 0) return (N < 0 || V <= 0 || T <= 0) ? D3GA_EINVAL : D3GA_OK;
     return deform_backward_impl(N, V, T, tetpoints, tets, tetra_id, barys, canonical_gradient, scales, rotation,
                                 dL_dmeans3D, dL_dcov3D, dL_dtetpoints, dL_dbarys, dL_dscales, dL_drotation, order,
+                                DeformExtra{}, stream);
+}
+
+extern "C" int d3ga_deform_backward_fused(int N, int V, int T, const float *tetpoints, const int64_t *tets,
+                                          const int64_t *tetra_id, const float *barys, const float *delta_bary,
+                                          const float *canonical_gradient, const float *scales, const float *delta_scale,
+                                          int log_scales, const float *rotation, const float *delta_rot,
+                                          const float *dn_inv, const float *dL_dmeans3D, const float *dL_dcov3D,
+                                          const float *dL_denergy, float *dL_dtetpoints, float *dL_dbarys,
+                                          float *dL_dscales, float *dL_drotation, const int32_t *order,
+                                          d3ga_stream_t stream) {
+    DeformExtra ex{};
+    ex.delta_bary = delta_bary; ex.delta_scale = delta_scale; ex.delta_rot = delta_rot; ex.log_scales = log_scales ? 1 : 0;
+    ex.dn_inv = dn_inv; ex.dL_denergy = dL_denergy;
+    return deform_backward_impl(N, V, T, tetpoints, tets, tetra_id, barys, canonical_gradient, scales, rotation,
+                                dL_dmeans3D, dL_dcov3D, dL_dtetpoints, dL_dbarys, dL_dscales, dL_drotation, order, ex,
                                 stream);
 }

@@ -159,59 +159,87 @@ def _tet_order(tetra_id):
 
 
 class _DeformGaussians(torch.autograd.Function):
+    """One launch each way for models/cage_net.py:213-230 (csrc/deform.cu).  Inputs 0-6 are the plain op's; 7-9 the
+    optional deltas, 10 the log-scales flag, 11 the optional inverse rest-pose edge matrices (then a third output, the
+    per-tet cage energy of lib/cage.py:349-361, comes out of the same launch)."""
+
     @staticmethod
-    def forward(ctx, tetpoints, tets, tetra_id, barys, canonical_gradient, scales, rotation):
+    def forward(ctx, tetpoints, tets, tetra_id, barys, canonical_gradient, scales, rotation, delta_bary, delta_scale,
+                delta_rot, log_scales, dn_inv):
         lib = _lib.load()
-        tetpoints = _check(tetpoints, "tetpoints", torch.float32)
+        f32 = torch.float32
+        tetpoints = _check(tetpoints, "tetpoints", f32)
         tets = _check(tets, "tets", torch.int64)
         tetra_id = _check(tetra_id, "tetra_id", torch.int64)
-        barys = _check(barys, "barys", torch.float32)
-        canonical_gradient = _check(canonical_gradient, "canonical_gradient", torch.float32)
-        scales = _check(scales, "scales", torch.float32)
-        rotation = _check(rotation, "rotation", torch.float32)
+        barys = _check(barys, "barys", f32)
+        canonical_gradient = _check(canonical_gradient, "canonical_gradient", f32)
+        scales = _check(scales, "scales", f32)
+        rotation = _check(rotation, "rotation", f32)
+        delta_bary = None if delta_bary is None else _check(delta_bary, "delta_bary", f32)
+        delta_scale = None if delta_scale is None else _check(delta_scale, "delta_scale", f32)
+        delta_rot = None if delta_rot is None else _check(delta_rot, "delta_rot", f32)
+        dn_inv = None if dn_inv is None else _check(dn_inv, "dn_inv", f32)
+        if delta_scale is not None and not log_scales:
+            raise RuntimeError("delta_scale is added before the exp (models/cage_net.py:214): pass log_scales=True")
         N, V, T, dev = int(tetra_id.shape[0]), int(tetpoints.shape[0]), int(tets.shape[0]), tetpoints.device
         with _lib.device_guard(dev):
-            means3D = torch.empty((N, 3), dtype=torch.float32, device=dev)
-            cov3D = torch.empty((N, 6), dtype=torch.float32, device=dev)
-            _lib.check(lib.d3ga_deform_forward(
-                N, V, T, tetpoints.data_ptr(), tets.data_ptr(), _lib.ptr(tetra_id), _lib.ptr(barys),
-                _lib.ptr(canonical_gradient), _lib.ptr(scales), _lib.ptr(rotation), _lib.ptr(means3D),
+            means3D = torch.empty((N, 3), dtype=f32, device=dev)
+            cov3D = torch.empty((N, 6), dtype=f32, device=dev)
+            energy = torch.empty((T,), dtype=f32, device=dev) if dn_inv is not None else None
+            _lib.check(lib.d3ga_deform_forward_fused(
+                N, V, T, tetpoints.data_ptr(), tets.data_ptr(), _lib.ptr(tetra_id), _lib.ptr(barys), _lib.ptr(delta_bary),
+                _lib.ptr(canonical_gradient), _lib.ptr(scales), _lib.ptr(delta_scale), int(bool(log_scales)),
+                _lib.ptr(rotation), _lib.ptr(delta_rot), _lib.ptr(dn_inv), _lib.ptr(energy), _lib.ptr(means3D),
                 _lib.ptr(cov3D), _lib.raw_stream(dev)), "deform_forward")
-        ctx.save_for_backward(tetpoints, tets, tetra_id, barys, canonical_gradient, scales, rotation)
+        ctx.save_for_backward(tetpoints, tets, tetra_id, barys, canonical_gradient, scales, rotation, delta_bary,
+                              delta_scale, delta_rot, dn_inv)
+        ctx.log_scales = bool(log_scales)
         ctx.set_materialize_grads(False)
-        return means3D, cov3D
+        if energy is None:
+            return means3D, cov3D
+        return means3D, cov3D, energy
 
     @staticmethod
-    def backward(ctx, g_means, g_cov):
+    def backward(ctx, g_means, g_cov, g_energy=None):
         lib = _lib.load()
-        tetpoints, tets, tetra_id, barys, canonical_gradient, scales, rotation = ctx.saved_tensors
+        (tetpoints, tets, tetra_id, barys, canonical_gradient, scales, rotation, delta_bary, delta_scale, delta_rot,
+         dn_inv) = ctx.saved_tensors
         N, V, T, dev = int(tetra_id.shape[0]), int(tetpoints.shape[0]), int(tets.shape[0]), tetpoints.device
         need = ctx.needs_input_grad
+        f32 = torch.float32
         with _lib.device_guard(dev):
-            g_means = torch.zeros((N, 3), dtype=torch.float32, device=dev) if g_means is None else g_means.contiguous()
-            g_cov = torch.zeros((N, 6), dtype=torch.float32, device=dev) if g_cov is None else g_cov.contiguous()
-            g_tet = torch.zeros((V, 3), dtype=torch.float32, device=dev) if need[0] else None
-            g_bary = torch.empty((N, 4), dtype=torch.float32, device=dev) if need[3] else None
-            g_scales = torch.empty((N, 3), dtype=torch.float32, device=dev) if need[5] else None
-            g_rot = torch.empty((N, 4), dtype=torch.float32, device=dev) if need[6] else None
-            if N > 0 and g_tet is not None and USE_TET_ORDER:
-                _lib.check(lib.d3ga_deform_backward_ordered(
-                    N, V, T, tetpoints.data_ptr(), tets.data_ptr(), _lib.ptr(tetra_id), _lib.ptr(barys),
-                    _lib.ptr(canonical_gradient), _lib.ptr(scales), _lib.ptr(rotation), _lib.ptr(g_means),
-                    _lib.ptr(g_cov), _lib.ptr(g_tet), _lib.ptr(g_bary), _lib.ptr(g_scales), _lib.ptr(g_rot),
-                    _tet_order(tetra_id).data_ptr(), _lib.raw_stream(dev)), "deform_backward_ordered")
-            else:
-                _lib.check(lib.d3ga_deform_backward(
-                    N, V, T, tetpoints.data_ptr(), tets.data_ptr(), _lib.ptr(tetra_id), _lib.ptr(barys),
-                    _lib.ptr(canonical_gradient), _lib.ptr(scales), _lib.ptr(rotation), _lib.ptr(g_means),
-                    _lib.ptr(g_cov), _lib.ptr(g_tet), _lib.ptr(g_bary), _lib.ptr(g_scales), _lib.ptr(g_rot),
-                    _lib.raw_stream(dev)), "deform_backward")
-        return g_tet, None, None, g_bary, None, g_scales, g_rot
+            g_means = torch.zeros((N, 3), dtype=f32, device=dev) if g_means is None else g_means.contiguous()
+            g_cov = torch.zeros((N, 6), dtype=f32, device=dev) if g_cov is None else g_cov.contiguous()
+            g_energy = None if (g_energy is None or dn_inv is None) else g_energy.contiguous()
+            g_tet = torch.zeros((V, 3), dtype=f32, device=dev) if need[0] else None
+            g_bary = torch.empty((N, 4), dtype=f32, device=dev) if (need[3] or need[7]) else None
+            g_scales = torch.empty((N, 3), dtype=f32, device=dev) if (need[5] or need[8]) else None
+            g_rot = torch.empty((N, 4), dtype=f32, device=dev) if (need[6] or need[9]) else None
+            order = _tet_order(tetra_id) if (N > 0 and g_tet is not None and USE_TET_ORDER) else None
+            _lib.check(lib.d3ga_deform_backward_fused(
+                N, V, T, tetpoints.data_ptr(), tets.data_ptr(), _lib.ptr(tetra_id), _lib.ptr(barys), _lib.ptr(delta_bary),
+                _lib.ptr(canonical_gradient), _lib.ptr(scales), _lib.ptr(delta_scale), int(ctx.log_scales),
+                _lib.ptr(rotation), _lib.ptr(delta_rot), _lib.ptr(dn_inv), _lib.ptr(g_means), _lib.ptr(g_cov),
+                _lib.ptr(g_energy) if g_tet is not None else None, _lib.ptr(g_tet), _lib.ptr(g_bary), _lib.ptr(g_scales),
+                _lib.ptr(g_rot), _lib.ptr(order), _lib.raw_stream(dev)), "deform_backward")
+        # a base tensor and its delta have the same gradient: one tensor serves both
+        return (g_tet, None, None, g_bary if need[3] else None, None, g_scales if need[5] else None,
+                g_rot if need[6] else None, g_bary if need[7] else None, g_scales if need[8] else None,
+                g_rot if need[9] else None, None, None)
 
 
-def deform_gaussians(tetpoints, tets, tetra_id, barys, canonical_gradient, scales, rotation):
-    """Fused cage -> Gaussian deformation (models/cage_net.py:218-230).  Returns (means3D, cov3D_precomp)."""
-    return _DeformGaussians.apply(tetpoints, tets, tetra_id, barys, canonical_gradient, scales, rotation)
+def deform_gaussians(tetpoints, tets, tetra_id, barys, canonical_gradient, scales, rotation, delta_bary=None,
+                     delta_scale=None, delta_rot=None, log_scales=False, dn_inv=None):
+    """Fused cage -> Gaussian deformation (models/cage_net.py:213-230).  Returns (means3D, cov3D_precomp).
+
+    With the seven positional arguments: lines 218-230 on activated inputs (scales post-exp, rotation any non-zero
+    quaternion).  The keyword arguments take lines 213-215 into the same kernel -- ``delta_bary``, ``delta_rot`` are added
+    to ``barys`` / ``rotation``; ``log_scales=True`` says ``scales`` is the pre-activation parameter (exp applied inside,
+    after adding ``delta_scale``) -- and ``dn_inv`` (inverse rest-pose edge matrices, lib/cage.py:312-313) makes the launch
+    also evaluate the cage's neo-Hookean energy of line 225: the return value is then (means3D, cov3D_precomp,
+    energy[T])."""
+    return _DeformGaussians.apply(tetpoints, tets, tetra_id, barys, canonical_gradient, scales, rotation, delta_bary,
+                                  delta_scale, delta_rot, log_scales, dn_inv)
 
 
 class _FemEnergy(torch.autograd.Function):

@@ -50,12 +50,18 @@ class Avatar:
         self.tets, self.tetra_id, self.cg = t(scene.tets), t(scene.tetra_id), t(scene.canonical_gradient)
         self.tetpoints = t(scene.tetpoints).requires_grad_(True)
         self.barys = t(scene.barys).requires_grad_(True)
-        self.scales = t(scene.scales).requires_grad_(True)
+        # the scale PARAMETER is pre-activation like the reference's (models/cage_net.py:66-70: log of a length; the exp of
+        # cage_net.py:214 runs inside the fused deformation launch)
+        self.scaling = t(np.log(scene.scales)).requires_grad_(True)
         self.rotation = t(scene.rotation).requires_grad_(True)
         self.opacity = t(scene.opacity).requires_grad_(True)
         self.colors = t(scene.colors).requires_grad_(True)
         self.silhouette = torch.ones_like(self.colors)   # models/cage_net.py:249 silhouette_rgb
-        self.params = [self.tetpoints, self.barys, self.scales, self.rotation, self.opacity, self.colors]
+        self.params = [self.tetpoints, self.barys, self.scaling, self.rotation, self.opacity, self.colors]
+        # inverse rest-pose edge matrices of the cage energy (lib/cage.py:312-313)
+        canon = t(scene.canon_points)
+        X = canon[self.tets]
+        self.dn_inv = torch.linalg.inv(torch.stack([X[:, 3] - X[:, 0], X[:, 2] - X[:, 0], X[:, 1] - X[:, 0]], dim=2)).contiguous()
         self.grads = ddist.FlatGrads(self.params)
         self._means2D = None
         self.tetpoints_host = torch.from_numpy(scene.tetpoints.copy())
@@ -68,16 +74,16 @@ class Avatar:
         import copy
         o = copy.copy(self)
         o.tetpoints = self.tetpoints.detach().clone().requires_grad_(True)
-        o.barys, o.scales, o.rotation, o.opacity, o.colors = (
-            p.detach().requires_grad_(True) for p in (self.barys, self.scales, self.rotation, self.opacity, self.colors))
-        o.params = [o.tetpoints, o.barys, o.scales, o.rotation, o.opacity, o.colors]
+        o.barys, o.scaling, o.rotation, o.opacity, o.colors = (
+            p.detach().requires_grad_(True) for p in (self.barys, self.scaling, self.rotation, self.opacity, self.colors))
+        o.params = [o.tetpoints, o.barys, o.scaling, o.rotation, o.opacity, o.colors]
         o.grads = ddist.FlatGrads(o.params)
         return o
 
     def render(self, rs):
-        """What GarmentNet.forward + render() do on the hot path (cage_net.py:218-230, renderer.py:122-141)."""
-        means3D, cov6 = deform_gaussians(self.tetpoints, self.tets, self.tetra_id, self.barys, self.cg, self.scales,
-                                         self.rotation)
+        """What GarmentNet.forward + render() do on the hot path (cage_net.py:213-230, renderer.py:122-141)."""
+        means3D, cov6 = deform_gaussians(self.tetpoints, self.tets, self.tetra_id, self.barys, self.cg, self.scaling,
+                                         self.rotation, log_scales=True)
         # renderer.py:122-126 allocates zeroed screen-space points per call only to receive a gradient nobody reads on
         # this path; a resident zero buffer serves the API without two extra kernels per view
         if self._means2D is None or self._means2D.shape != means3D.shape:
@@ -111,11 +117,29 @@ def view_step(avatar, rs, weights):
     return loss
 
 
+U8_SCALE, U8_OFFSET = 2.0 / 255.0, -1.0   # a uint8 target / weight image stands for u8 * U8_SCALE + U8_OFFSET
+_u8_offset: dict = {}
+
+
+def dequantise_into(dst, img):
+    """dst[3,H,W] f32 <- img: float32 is copied; uint8 is normalised on the device in one kernel, which is what the
+    reference does with the camera images it uploads (lib/batch.py:86-88: uint8 over PCIe, float on the GPU)."""
+    if img.dtype == torch.uint8:
+        off = _u8_offset.get(dst.device)
+        if off is None:
+            off = _u8_offset[dst.device] = torch.full((), U8_OFFSET, dtype=torch.float32, device=dst.device)
+        torch.add(off, img, alpha=U8_SCALE, out=dst)
+    elif img.data_ptr() != dst.data_ptr():
+        dst.copy_(img, non_blocking=True)
+    return dst
+
+
 class HostFeed:
-    """Per-view inputs that arrive from pinned host memory (the e2e arm of bench.py): the target / weight image, the
-    camera (35 floats) and the cage vertices are copied on a side stream ONE VIEW AHEAD into a double buffer, so the
-    uploads (12.6 MB at 1024^2) overlap the previous view's kernels and no host-to-device DMA sits on the compute stream
-    -- what a data loader with a prefetch queue does (train.py:426-434 uses pinned DataLoader memory)."""
+    """Per-view inputs that arrive from pinned host memory (the e2e arm of bench.py): the target / weight image (float32,
+    or uint8 like the reference's camera frames: a quarter of the bytes), the camera (35 floats) and the cage vertices
+    are copied on a side stream ONE VIEW AHEAD into a double buffer, so the uploads (3.1 MB as uint8 at 1024^2) overlap the
+    previous view's kernels and no host-to-device DMA sits on the compute stream -- what a data loader with a prefetch
+    queue does (train.py:426-434 uses pinned DataLoader memory)."""
 
     def __init__(self, weights_host, device, cam_host=None, tetpoints_host=None, slots=2):
         self.host = weights_host
@@ -163,6 +187,8 @@ def multi_view_step(avatar, bank, cam_ids, weights, bg, from_host=False, feed=No
     for n, i in enumerate(cam_ids):
         if from_host:
             weights = feed.acquire(slot)
+            if weights.dtype == torch.uint8:
+                weights = dequantise_into(torch.empty(weights.shape, dtype=torch.float32, device=weights.device), weights)
             with torch.no_grad():
                 if feed.tet_host is not None:
                     avatar.tetpoints.copy_(feed.tets[slot], non_blocking=True)
@@ -262,8 +288,8 @@ class GraphedViewStep:
         if self.graph is None:
             self.capture(cam_row)
         self.cam.copy_(cam_row, non_blocking=True)
-        if weights is not None and weights.data_ptr() != self.weights.data_ptr():
-            self.weights.copy_(weights, non_blocking=True)
+        if weights is not None:
+            dequantise_into(self.weights, weights)
         self.graph.replay()
         self.replays += 1
         _lib.note_graph_launches(self.launches_per_replay)
@@ -414,12 +440,13 @@ def multi_view_step_graphed(avatar, bank, cam_ids, gv, weights=None, from_host=F
         gv.capture(bank.dev[cam_ids[0]])     # the capacity hint now covers the largest view seen
 
 
-def frame_step(avatar, bank, cam_id, weights, bg):
-    """One D3GA training frame on the hot path (models/trainer.py:91-140): the deformation once, then TWO renders of the
-    same Gaussians -- RGB on a random background and the silhouette (constant colour, black background), each through
-    its own render() call with its own Camera object -- and one backward through both."""
-    means3D, cov6 = deform_gaussians(avatar.tetpoints, avatar.tets, avatar.tetra_id, avatar.barys, avatar.cg,
-                                     avatar.scales, avatar.rotation)
+def frame_step(avatar, bank, cam_id, weights, bg, fem_weight=1.0):
+    """One D3GA training frame on the hot path (models/trainer.py:91-140): the deformation block once -- with the cage's
+    neo-Hookean energy of cage_net.py:225 out of the same launch --, then TWO renders of the same Gaussians -- RGB on a
+    random background and the silhouette (constant colour, black background), each through its own render() call with its
+    own Camera object -- and one backward through both plus the energy term (train.py:186-244 adds it to the loss)."""
+    means3D, cov6, energy = deform_gaussians(avatar.tetpoints, avatar.tets, avatar.tetra_id, avatar.barys, avatar.cg,
+                                             avatar.scaling, avatar.rotation, log_scales=True, dn_inv=avatar.dn_inv)
     imgs = []
     for colors, background in ((avatar.colors, bg), (avatar.silhouette, torch.zeros_like(bg))):
         rs = bank.settings(cam_id, avatar.W, avatar.H, background)
@@ -428,6 +455,6 @@ def frame_step(avatar, bank, cam_id, weights, bg):
         imgs.append(GaussianRasterizer(raster_settings=rs)(
             means3D=means3D, means2D=means2D, shs=None, colors_precomp=colors, opacities=avatar.opacity, scales=None,
             rotations=None, cov3D_precomp=cov6)[0])
-    loss = (imgs[0] * weights).sum() + (imgs[1] * weights).sum()
+    loss = (imgs[0] * weights).sum() + (imgs[1] * weights).sum() + fem_weight * energy.mean()
     loss.backward()
     return loss

@@ -236,6 +236,33 @@ int d3ga_deform_backward_ordered(int N, int V, int T, const float *tetpoints, co
                                  const float *dL_dcov3D, float *dL_dtetpoints, float *dL_dbarys, float *dL_dscales,
                                  float *dL_drotation, const int32_t *order, d3ga_stream_t stream);
 
+/* The deformation block of models/cage_net.py:213-230 in ONE launch each way: the plain entry points above plus
+ *   canon_barys = barys + delta_bary                       (cage_net.py:213; delta_bary [N,4] or null)
+ *   scales      = exp(scaling + delta_scale)               (cage_net.py:214; log_scales != 0: `scales` and delta_scale
+ *                                                           [N,3] are pre-activation; delta_scale may be null)
+ *   rotation    = F.normalize(rotation + delta_rot)        (cage_net.py:215; delta_rot [N,4] or null; normalised once
+ *                                                           inside -- build_rotation normalises again in the reference,
+ *                                                           so the result is the same; the zero vector is NaN in both)
+ *   fm_energy   = fem_energy(tetpoints)  per tet           (cage_net.py:225, lib/cage.py:349-361; dn_inv [T,3,3] + energy
+ *                                                           [T] both given or both null) -- run by extra CTAs of the
+ *                                                           same launch, it gathers the same tetpoints[tets]
+ * Backward: a base tensor and its delta have the same gradient, written ONCE (dL_dbarys = dL/dbarys = dL/ddelta_bary,
+ * dL_dscales is the gradient of the PRE-activation scales when log_scales != 0, dL_drotation of the un-normalised sum);
+ * dL_denergy [T] or null adds the energy's gradient into dL_dtetpoints (which the caller zeroes, as above).
+ * `order` as in d3ga_deform_backward_ordered, or null. */
+int d3ga_deform_forward_fused(int N, int V, int T, const float *tetpoints, const int64_t *tets, const int64_t *tetra_id,
+                              const float *barys, const float *delta_bary, const float *canonical_gradient,
+                              const float *scales, const float *delta_scale, int log_scales, const float *rotation,
+                              const float *delta_rot, const float *dn_inv, float *energy, float *means3D,
+                              float *cov3D, d3ga_stream_t stream);
+int d3ga_deform_backward_fused(int N, int V, int T, const float *tetpoints, const int64_t *tets,
+                               const int64_t *tetra_id, const float *barys, const float *delta_bary,
+                               const float *canonical_gradient, const float *scales, const float *delta_scale,
+                               int log_scales, const float *rotation, const float *delta_rot, const float *dn_inv,
+                               const float *dL_dmeans3D, const float *dL_dcov3D, const float *dL_denergy,
+                               float *dL_dtetpoints, float *dL_dbarys, float *dL_dscales, float *dL_drotation,
+                               const int32_t *order, d3ga_stream_t stream);
+
 /* ---- cage FEM energy ------------------------------------------------------------
  * Replaces CageBase.fem_energy (lib/cage.py:349-361, called at models/cage_net.py:225) and its autograd backward:
  * per tet, F = G(tetpoints[tets]) @ dn_inv, energy = 0.5 (det F - 1)^2 + 0.5 (tr(F^T F) - 3).

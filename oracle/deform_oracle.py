@@ -73,6 +73,16 @@ def deform_gaussians(tetpoints, tets, tetra_id, canon_barys, canonical_gradient,
     return means3D, strip_symmetric(cov3D)                             # cage_net.py:223
 
 
+def deform_block(tetpoints, tets, tetra_id, barys, delta_bary, canonical_gradient, scaling, delta_scale, rotation,
+                 delta_rot):
+    """models/cage_net.py:213-215 in front of deform_gaussians: the canonical-field offsets and the activations
+    (scaling_activation = exp, rotation_activation = F.normalize, cage_net.py:79-81)."""
+    canon_barys = barys + delta_bary                                   # cage_net.py:213
+    scales = th.exp(scaling + delta_scale)                             # cage_net.py:214
+    rot = th.nn.functional.normalize(rotation + delta_rot)             # cage_net.py:215
+    return deform_gaussians(tetpoints, tets, tetra_id, canon_barys, canonical_gradient, scales, rot)
+
+
 def fem_energy(tetpoints, tets, Dn_inv):
     """lib/cage.py:349-361 -- stable neo-Hookean energy per tet (l = m = 0.5)."""
     Ds = tet_gradient(tetpoints[tets])

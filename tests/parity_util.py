@@ -63,9 +63,10 @@ def oracle_view(scene, cam, weights, bg=(1.0, 1.0, 1.0), raster_inputs=None):
     that noise from the comparison, and the deformation itself is compared separately to ~1e-6."""
     t = th.from_numpy
     leaves = {k: t(np.ascontiguousarray(getattr(scene, k))).clone().requires_grad_(True)
-              for k in ("tetpoints", "barys", "scales", "rotation")}
+              for k in ("tetpoints", "barys", "rotation")}
+    leaves["scaling"] = t(np.log(scene.scales)).clone().requires_grad_(True)      # pre-activation, like training.Avatar
     means, cov6 = deform_oracle.deform_gaussians(leaves["tetpoints"], t(scene.tets), t(scene.tetra_id), leaves["barys"],
-                                                 t(scene.canonical_gradient), leaves["scales"], leaves["rotation"])
+                                                 t(scene.canonical_gradient), th.exp(leaves["scaling"]), leaves["rotation"])
     m_in, c_in = (means.detach().numpy(), cov6.detach().numpy()) if raster_inputs is None else raster_inputs
     orc = RasterOracle(np.float32)
     st = orc.forward(np.ascontiguousarray(m_in), scene.opacity, cam.viewmatrix, cam.projmatrix, cam.campos, scene.W, scene.H,

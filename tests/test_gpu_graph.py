@@ -157,7 +157,7 @@ def test_pipelined_metric_step_matches_oracle(cuda_lib, oracle_libs):
     ids = [0, 20, 45, 70, 95, 110, 135, 159]           # 4 elevations x front / side / back
     with torch.no_grad():
         m_gpu, c_gpu = deform_gaussians(avatar.tetpoints, avatar.tets, avatar.tetra_id, avatar.barys, avatar.cg,
-                                        avatar.scales, avatar.rotation)
+                                        avatar.scaling, avatar.rotation, log_scales=True)
     m_gpu, c_gpu = m_gpu.cpu().numpy(), c_gpu.cpu().numpy()
     m_ref, c_ref = util.scene_geometry(scene)
     assert util.rel_l2(m_gpu, m_ref) < 2e-6 and util.rel_l2(c_gpu, c_ref) < 2e-6
@@ -173,7 +173,7 @@ def test_pipelined_metric_step_matches_oracle(cuda_lib, oracle_libs):
     pv = training.PipelinedViews(avatar, cams[0], bg, lanes=4)
     feed = training.HostFeed(wh, dev, cam_host=bank.host, tetpoints_host=avatar.tetpoints_host, slots=8)
     loss_h = torch.zeros((), dtype=torch.float32).pin_memory()
-    names = ("tetpoints", "barys", "scales", "rotation", "opacity", "colors")
+    names = ("tetpoints", "barys", "scaling", "rotation", "opacity", "colors")
     for from_host in (False, True):
         if from_host:
             training.multi_view_step_pipelined(avatar, bank, ids, pv, from_host=True, feed=feed, loss_host=loss_h)
@@ -207,5 +207,5 @@ def test_tet_sorted_storage_is_the_same_avatar(cuda_lib):
     tot2 = training.multi_view_step(av2, bank, ids, w, bg).clone()
     assert abs(float(tot2) - float(tot)) <= 2e-5 * abs(float(tot))
     assert rel(av2.tetpoints.grad, avatar.tetpoints.grad) < 1e-4
-    for name in ("barys", "scales", "rotation", "opacity", "colors"):
+    for name in ("barys", "scaling", "rotation", "opacity", "colors"):
         assert rel(getattr(av2, name).grad, getattr(avatar, name).grad[order]) < 1e-4, name

@@ -72,3 +72,23 @@ def test_fem_energy_zero_at_rest():
     Dn_inv = th.linalg.inv(do.tet_gradient(X[t(sc.tets)]))
     e = do.fem_energy(X, t(sc.tets), Dn_inv)
     assert float(e.abs().max()) < 1e-4
+
+
+def test_fused_block_oracle_matches_reference_golden():
+    """oracle.deform_block (cage_net.py:213-215 + :218-230) and oracle.fem_energy (lib/cage.py:348-361) against what the
+    reference's own source lines produced (tests/golden/make_deform_golden.py executes them as they stand)."""
+    import os
+
+    import numpy as np
+    import torch as th
+
+    from oracle import deform_oracle as do
+
+    G = np.load(os.path.join(os.path.dirname(__file__), "golden", "deform_golden.npz"))
+    t = lambda k: th.from_numpy(G[k])  # noqa: E731
+    m, c = do.deform_block(t("tetpoints"), t("tets"), t("tetra_id"), t("barys"), t("delta_bary"), t("canonical_gradient"),
+                           t("scaling"), t("delta_scale"), t("rotation"), t("delta_rot"))
+    assert np.allclose(m.numpy(), G["fused_means3D"], atol=1e-6)
+    assert np.abs(c.numpy() - G["fused_cov6"]).max() <= 1e-5 * np.abs(G["fused_cov6"]).max()
+    e = do.fem_energy(t("tetpoints"), t("tets"), t("Dn_inv"))
+    assert np.allclose(e.numpy(), G["fem_energy"], rtol=1e-5, atol=1e-6)
