@@ -169,17 +169,22 @@ def run_reference(args):
     line = {"metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": 1e3 * dt / max(1, args.steps), "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic", "impl": "reference",
-            "config": workload_config(scene, args, 1),
+            "config": workload_config(scene, args, 1, impl="reference"),
             "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
             "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line), flush=True)
 
 
-def workload_config(scene, args, views):
-    return {"workload": f"{scene.name}: {scene.N} Gaussians in {scene.tets.shape[0]} tets over {len(scene.meta['garments'])} "
+def workload_config(scene, args, views, impl="ours"):
+    base = {"workload": f"{scene.name}: {scene.N} Gaussians in {scene.tets.shape[0]} tets over {len(scene.meta['garments'])} "
                         f"cage(s), {scene.W}x{scene.H}, cov3D_precomp + colors_precomp path",
-            "views_per_rank_per_step": views, "cameras": args.cameras, "parallelism": f"camera-sharded dp{args.gpus}",
+            "views_per_rank_per_step": views, "cameras": args.cameras}
+    if impl == "reference":
+        base.update(parallelism="rank 0 only, all host threads (OpenMP rasterizer oracle + torch CPU deformation)",
+                    launch="CPU: one camera view (forward + backward) per step, no GPU work")
+        return base
+    return {**base, "parallelism": f"camera-sharded dp{args.gpus}",
             "launch": "eager" if args.no_graph else f"one CUDA-graph replay per view, {max(1, args.lanes)} view(s) in flight on separate streams",
             "l2": "working set (>= 150 MB of Gaussian state + binning buffers per view) exceeds the 126 MB L2; no flush",
             "binning": "direct tile scatter; inside the replayed graphs its rows are sized for the views in flight "
@@ -470,10 +475,17 @@ def run_ours(args):
 
 def main():
     args = parse()
+    # stdout carries ONE JSON line and nothing else: whatever a library prints to file descriptor 1 while the run lasts
+    # (NCCL's version banner does, on some boxes, whatever NCCL_DEBUG_FILE says) goes to stderr instead
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+    sys.stdout = os.fdopen(real_stdout, "w", buffering=1)
     if args.impl == "reference":
         run_reference(args)
     else:
         run_ours(args)
+    sys.stdout.flush()
 
 
 if __name__ == "__main__":

@@ -62,6 +62,45 @@ class FlatGrads:
             return dist.all_reduce(self.flat, op=dist.ReduceOp.SUM, async_op=async_op)
         return None
 
+    def sum_lanes_and_ranks(self, lane_flats, chunks: int = 4):
+        """self.flat = sum over `lane_flats` (the per-lane gradient buffers of training.PipelinedViews), then summed over
+        ranks -- the two steps pipelined chunk by chunk: while the collective of chunk k runs on a communication stream,
+        the lanes' chunk k + 1 is being added on the caller's stream, so of the 60 MB all-reduce that used to follow the
+        whole add only the last chunk's is exposed.  With one rank (or one chunk) it is the plain add.  The caller's
+        stream waits for the last collective before it returns control to later work (no host synchronisation).
+        The global clip_grad_norm_ of models/trainer.py:188 must still come after this."""
+        multi = dist.is_initialized() and dist.get_world_size() > 1
+        n = self.flat.numel()
+        k = max(1, int(chunks)) if (multi and n >= 1 << 16) else 1
+        edges = [((n * i // k) + 255) // 256 * 256 if 0 < i < k else (0 if i == 0 else n) for i in range(k + 1)]
+        cuda = self.flat.is_cuda
+        if cuda and multi and getattr(self, "_comm", None) is None:
+            self._comm = torch.cuda.Stream(device=self.flat.device)
+        works = []
+        for i in range(k):
+            a, b = edges[i], edges[i + 1]
+            if b <= a:
+                continue
+            dst = self.flat[a:b]
+            if len(lane_flats) == 1:
+                dst.copy_(lane_flats[0][a:b])
+            else:
+                torch.add(lane_flats[0][a:b], lane_flats[1][a:b], out=dst)
+                for f in lane_flats[2:]:
+                    dst.add_(f[a:b])
+            if not multi:
+                continue
+            if cuda:
+                ev = torch.cuda.Event()
+                ev.record()
+                with torch.cuda.stream(self._comm):
+                    self._comm.wait_event(ev)
+                    works.append(dist.all_reduce(dst, op=dist.ReduceOp.SUM, async_op=True))
+            else:
+                works.append(dist.all_reduce(dst, op=dist.ReduceOp.SUM, async_op=True))
+        for w in works:
+            w.wait()          # CUDA: makes the current stream wait for the collective; gloo: blocks
+
 
 def max_over_ranks(value: float, device) -> float:
     if dist.is_initialized() and dist.get_world_size() > 1:

@@ -358,13 +358,8 @@ class PipelinedViews:
         main = torch.cuda.current_stream()
         for st in self.streams:
             main.wait_stream(st)
-        flat = self.avatar.grads.flat
-        if len(self.shadows) == 1:
-            flat.copy_(self.shadows[0].grads.flat)
-        else:
-            torch.add(self.shadows[0].grads.flat, self.shadows[1].grads.flat, out=flat)
-            for sh in self.shadows[2:]:
-                flat.add_(sh.grads.flat)
+        # lanes' gradients -> the avatar's flat buffer -> sum over ranks, chunk by chunk (dist.FlatGrads)
+        self.avatar.grads.sum_lanes_and_ranks([sh.grads.flat for sh in self.shadows])
         total = self.gvs[0].total.clone()
         for g in self.gvs[1:]:
             total = total + g.total
@@ -399,8 +394,7 @@ def multi_view_step_pipelined(avatar, bank, cam_ids, pv, weights=None, from_host
                 gv.run(row, w)
                 if from_host:
                     feed.release(slot)
-        total, overflowed = pv.finish()
-        avatar.grads.all_reduce()
+        total, overflowed = pv.finish()      # includes the all-reduce over ranks
         if from_host:
             loss_host.copy_(total, non_blocking=True)
             torch.cuda.current_stream().synchronize()

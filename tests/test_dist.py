@@ -43,6 +43,20 @@ def _worker(rank, world, port, out):
         ((p * float(c + 1)).sum() + (q * float(c + 1)).sum()).backward()
     fg.all_reduce()
     ok = bool(torch.all(fg.flat == float(sum(range(1, 7)))))
+    # the chunked lane-sum + all-reduce (training.PipelinedViews.finish): the same bits as add-everything-then-one-call
+    g = torch.Generator().manual_seed(r)
+    big = torch.zeros(300_000, requires_grad=True)
+    fb = ddist.FlatGrads([big])
+    lanes = [torch.randn(300_000, generator=g) for _ in range(3)]
+    ref = lanes[0] + lanes[1]
+    ref += lanes[2]
+    torch.distributed.all_reduce(ref)
+    fb.sum_lanes_and_ranks(lanes, chunks=4)
+    ok = ok and bool(torch.equal(fb.flat, ref)) and big.grad.data_ptr() == fb.flat.data_ptr()
+    fb.sum_lanes_and_ranks(lanes[:1], chunks=3)
+    one = lanes[0].clone()
+    torch.distributed.all_reduce(one)
+    ok = ok and bool(torch.equal(fb.flat, one))
     mx = ddist.max_over_ranks(float(r), torch.device("cpu"))
     ddist.barrier()
     out.put((r, ok, mx, len(cams)))
