@@ -305,7 +305,8 @@ def run_ours(args):
         "deform_backward_kernel": 212 * N, "rect_grid_kernel": 12 * N, "tile_plan_kernel": 12 * Tl,
         # direct tile scatter (raster_direct.cu): gathers + records; ids written once, straight into their final slots
         # (the count rows and their prefix, 2-6 B x rows x tiles, are scratch traffic and not counted)
-        "direct_count_kernel": 36 * N, "direct_plan_kernel": 12 * Tl, "direct_scatter_kernel": 16 * N + 4 * D}
+        "direct_count_kernel": 36 * N, "direct_plan_kernel": 12 * Tl, "direct_scatter_kernel": 16 * N + 4 * D,
+        "pack_features_kernel": 28 * N}
     peak, peak_kind = measured_peak()
     kern = {}
     for name, (tms, cnt) in prof.items():
@@ -320,17 +321,27 @@ def run_ours(args):
         passes = 0
         view_bytes = 540 * N + (120 + 4) * D + 40 * P + 8 * Tl
     roof = None
-    traffic = None
-    try:   # DRAM bytes per launch of the dominant kernel from the committed `ncu --set full` capture (profiles/)
-        tj = json.load(open(os.path.join(ROOT, "profiles", "r1_traffic.json")))
+    traffic = traffic_src = issue = None
+    try:   # DRAM bytes per launch and the issue-slot figures of the dominant kernel come from the committed `ncu --set
+        #    full` capture (profiles/r2_traffic.json names the .csv it was read from and the commit that was profiled)
+        tj = json.load(open(os.path.join(ROOT, "profiles", "r2_traffic.json")))
         if args.workload == "metric" and dominant in tj["kernels"]:
-            traffic = tj["kernels"][dominant]["dram_bytes"]
+            rec = tj["kernels"][dominant]
+            traffic = rec["dram_bytes"]
+            traffic_src = {"file": "profiles/r2_traffic.json", "from": tj.get("source"), "commit": tj.get("commit")}
+            # the blend kernels are bound by issue slots, not by HBM: a second roofline says how full
+            # the schedulers and the busiest pipes were in that capture
+            issue = {"bound": "issue", "kernel": dominant, "achieved": rec.get("issue_active_pct"), "peak": 100.0,
+                     "unit": "% of issue slots (while an SM sub-partition holds warps)",
+                     "frac": rec.get("issue_active_pct", 0.0) / 100.0, "warp_instructions": rec.get("warp_instructions"),
+                     "pipes_pct": rec.get("pipes_pct"), "warps_active_pct": rec.get("warps_active_pct")}
     except Exception:
         traffic = None
     if dominant:
         ach = kern[dominant]["GBps"]
         roof = {"bound": "hbm", "kernel": dominant, "achieved": ach, "peak": peak, "unit": "GB/s",
-                "frac": ach / peak if ach else None, "traffic": traffic, "peak_kind": peak_kind,
+                "frac": ach / peak if ach else None, "traffic": traffic, "traffic_source": traffic_src,
+                "issue_roofline": issue, "peak_kind": peak_kind,
                 "algorithmic_bytes_per_launch": bytes_per_launch.get(dominant),
                 "avg_launch_ms": kern[dominant]["avg_ms"],
                 "whole_view": {"bytes": view_bytes, "GBps": view_bytes * (V * args.steps) / (ms * 1e-3) / 1e9,
@@ -376,7 +387,8 @@ def run_ours(args):
             torch.cuda.synchronize()
             pair["frames_per_s_shared_geometry" if share else "frames_per_s_independent_renders"] = nfr / (a.elapsed_time(b) * 1e-3)
         dgr.SHARE_GEOMETRY = True
-        pair["note"] = "1 frame = deformation + RGB render + silhouette render + backward of both (models/trainer.py:91-140)"
+        pair["note"] = ("1 frame = deformation block incl. the cage's FEM energy (one launch each way) + RGB render + silhouette "
+                        "render + backward of all three terms (models/trainer.py:91-140, models/cage_net.py:213-230)")
 
     # the cage-vertex skinning that produces tetpoints (Blueman.get), forward + backward to delta
     lbs = None

@@ -153,7 +153,7 @@ __device__ __noinline__ bool exact_cut(const float2 *__restrict__ xy, const floa
 // for its one-step-ahead register prefetch on every chunk (ncu: long-scoreboard the top stall of the forward, the
 // busiest SM active for the whole kernel, the average SM for half of it).
 #ifndef FWD_DEPTH
-#define FWD_DEPTH 3
+#define FWD_DEPTH 2   // 2 and 3 run the kernel equally fast; 2 leaves other views' kernels more shared memory (4: L1 starves)
 #endif
 struct FwdWarpSmem {
     float4 ring[RING][3];                 // staged survivors: [0] x, y, list position + 1 (bits), -   [1] conic, opacity
