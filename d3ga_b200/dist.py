@@ -71,6 +71,7 @@ class FlatGrads:
         The global clip_grad_norm_ of models/trainer.py:188 must still come after this."""
         multi = dist.is_initialized() and dist.get_world_size() > 1
         n = self.flat.numel()
+        chunks = int(os.environ.get("D3GA_REDUCE_CHUNKS", chunks))
         k = max(1, int(chunks)) if (multi and n >= 1 << 16) else 1
         edges = [((n * i // k) + 255) // 256 * 256 if 0 < i < k else (0 if i == 0 else n) for i in range(k + 1)]
         cuda = self.flat.is_cuda
