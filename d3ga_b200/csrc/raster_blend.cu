@@ -53,12 +53,27 @@ __device__ __forceinline__ float fast_exp2(float x) {
     asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
     return y;
 }
+__device__ __forceinline__ float fast_rcp(float x) {   // one MUFU (__fdividef(1, x) adds a denormal rescue: 6 instructions)
+    float y;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
 // Asynchronous global -> shared copies (LDGSTS): the data never passes through registers and the issuing lane does not
 // wait; cp_async_wait_all() + __syncwarp() make a warp's earlier copies visible to all its lanes.
 __device__ __forceinline__ void cp_async_16(void *smem_dst, const void *gmem_src) {
     asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(smem_dst)),
                  "l"(gmem_src) : "memory");
 }
+__device__ __forceinline__ void cp_async_16_l2(void *smem_dst, const void *gmem_src) {   // not allocated in L1
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(smem_dst)),
+                 "l"(gmem_src) : "memory");
+}
+// the backward's survivor copies bypass L1 (measured: 162.0 -> 159.6 us; its L1 hit rate was 25 % with ~30 KB of L1 left)
+#ifdef BWD_CP_L1
+#define bwd_cp_async_16 cp_async_16
+#else
+#define bwd_cp_async_16 cp_async_16_l2
+#endif
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 
@@ -119,12 +134,12 @@ __device__ __forceinline__ bool footprint_hit(const float4 g0, const float4 g1, 
     float qmax = -CUDART_INF_F;
     if (!in_x) {
         const float dx = xl > 0.f ? xl : xh;
-        const float dy = fminf(fmaxf(__fdividef(-0.5f * g1.y * dx, g1.z), yl), yh);
+        const float dy = fminf(fmaxf((-0.5f * g1.y * dx) * fast_rcp(g1.z), yl), yh);
         qmax = dx * (g1.x * dx + g1.y * dy) + g1.z * dy * dy;
     }
     if (!in_y) {
         const float dy = yl > 0.f ? yl : yh;
-        const float dx = fminf(fmaxf(__fdividef(-0.5f * g1.y * dy, g1.x), xl), xh);
+        const float dx = fminf(fmaxf((-0.5f * g1.y * dy) * fast_rcp(g1.x), xl), xh);
         qmax = fmaxf(qmax, dx * (g1.x * dx + g1.y * dy) + g1.z * dy * dy);
     }
     return g0.z < CUDART_INF_F && ((in_x && in_y) || !(qmax < g0.z));
@@ -209,16 +224,22 @@ __global__ void __launch_bounds__(FWD_WARPS * 32, FWD_MIN_CTAS) blend_forward_ke
         cp_async_16(&sm.stage[st][1][lane], &splat[id].g1);
         cp_async_16(&sm.stage[st][2][lane], feat + id);
     };
-    // prologue: FWD_DEPTH chunks in flight (one commit group per chunk, empty ones included), ids of the next two
-    uint32_t id_a = 0, id_b = 0;   // ids of this lane's entries in chunks c + FWD_DEPTH and c + FWD_DEPTH + 1
+    // prologue: FWD_DEPTH chunks in flight (one commit group per chunk, empty ones included).  idq[s] is the id of this
+    // lane's entry in the next chunk that will be fetched into stage s: it is loaded FWD_DEPTH steps before it is used,
+    // into a register that nothing touches in between (the chunk loop is unrolled over the stages, so the queue needs no
+    // moves -- a move of the newest id made every step wait for the load of the step before, at DRAM latency in the tail).
+    uint32_t idq[FWD_DEPTH];
+#pragma unroll
+    for (int j = 0; j < FWD_DEPTH; j++) idq[j] = 0;
     if (!all_done) {
 #pragma unroll
         for (uint32_t j = 0; j < (uint32_t)FWD_DEPTH; j++) {
             if (j * 32u + lane < count) fetch(j, point_list[j * 32u + lane]);
             cp_async_commit();
         }
-        if ((uint32_t)FWD_DEPTH * 32u + lane < count) id_a = point_list[(uint32_t)FWD_DEPTH * 32u + lane];
-        if ((uint32_t)(FWD_DEPTH + 1) * 32u + lane < count) id_b = point_list[(uint32_t)(FWD_DEPTH + 1) * 32u + lane];
+#pragma unroll
+        for (uint32_t j = 0; j < (uint32_t)FWD_DEPTH; j++)
+            if (((uint32_t)FWD_DEPTH + j) * 32u + lane < count) idq[j] = point_list[((uint32_t)FWD_DEPTH + j) * 32u + lane];
     }
 
     // Blends the staged survivors, four ring entries (a GROUP) at a time; head stays a multiple of four, so a group never
@@ -305,41 +326,47 @@ __global__ void __launch_bounds__(FWD_WARPS * 32, FWD_MIN_CTAS) blend_forward_ke
         }
     };
 
-    for (uint32_t c = 0; c < nchunks && !all_done; c++) {
-        // this lane's entry of chunk c has landed when at most FWD_DEPTH - 1 younger groups are still in flight
-        asm volatile("cp.async.wait_group %0;" ::"n"(FWD_DEPTH - 1) : "memory");
-        const uint32_t st = c % (uint32_t)FWD_DEPTH;
-        const uint32_t pos = c * 32u + lane;
-        float4 g0 = make_float4(0.f, 0.f, CUDART_INF_F, 0.f), g1 = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (pos < count) {
-            g0 = sm.stage[st][0][lane];
-            g1 = sm.stage[st][1][lane];
-        }
-        const bool hit = pos < count && footprint_hit(g0, g1, wb);
-        const uint32_t m = __ballot_sync(0xffffffffu, hit);
-        if (lane == 0) {
-            ballot_w[(size_t)c * 8] = m;     // replayed by the backward
-            STAT_ADD(0, 1); STAT_ADD(1, __popc(m));
-        }
-        if (hit) {
-            const float4 col = sm.stage[st][2][lane];
-            float4 *slot = sm.ring[(tail + __popc(m & lanemask_lt())) & (RING - 1)];
-            slot[0] = make_float4(g0.x, g0.y, __uint_as_float(pos + 1u), 0.f);
-            slot[1] = make_float4(g1.x, g1.y, g1.z, g0.w);
-            slot[2] = make_float4(col.x, col.y, col.z, g1.w);
-        }
-        tail += __popc(m);
-        // refill the slot with this lane's entry of chunk c + FWD_DEPTH; ids two further chunks ahead
-        const uint32_t ahead = pos + (uint32_t)FWD_DEPTH * 32u;
-        if (ahead < count) fetch(st, id_a);
-        cp_async_commit();
-        id_a = id_b;
-        if (ahead + 64u < count) id_b = point_list[ahead + 64u];
-        __syncwarp();
-        consume(false);
+    for (uint32_t c0 = 0; c0 < nchunks && !all_done; c0 += (uint32_t)FWD_DEPTH) {
+#pragma unroll
+        for (int st = 0; st < FWD_DEPTH; st++) {
+            const uint32_t c = c0 + (uint32_t)st;
+            if (c >= nchunks || all_done) break;
+            // this lane's entry of chunk c has landed when at most FWD_DEPTH - 1 younger groups are still in flight
+            asm volatile("cp.async.wait_group %0;" ::"n"(FWD_DEPTH - 1) : "memory");
+            const uint32_t pos = c * 32u + lane;
+            float4 g0 = make_float4(0.f, 0.f, CUDART_INF_F, 0.f), g1 = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (pos < count) {
+                g0 = sm.stage[st][0][lane];
+                g1 = sm.stage[st][1][lane];
+            }
+            const bool hit = pos < count && footprint_hit(g0, g1, wb);
+            const uint32_t m = __ballot_sync(0xffffffffu, hit);
+            if (lane == 0) {
+                ballot_w[(size_t)c * 8] = m;     // replayed by the backward
+                STAT_ADD(0, 1); STAT_ADD(1, __popc(m));
+            }
+            if (hit) {
+                const float4 col = sm.stage[st][2][lane];
+                float4 *slot = sm.ring[(tail + __popc(m & lanemask_lt())) & (RING - 1)];
+                slot[0] = make_float4(g0.x, g0.y, __uint_as_float(pos + 1u), 0.f);
+                slot[1] = make_float4(g1.x, g1.y, g1.z, g0.w);
+                slot[2] = make_float4(col.x, col.y, col.z, g1.w);
+            }
+            tail += __popc(m);
+            // refill the stage with this lane's entry of chunk c + FWD_DEPTH; its id for the chunk after that
+            const uint32_t ahead = pos + (uint32_t)FWD_DEPTH * 32u;
+            if (ahead < count) fetch((uint32_t)st, idq[st]);
+            cp_async_commit();
+            if (ahead + (uint32_t)FWD_DEPTH * 32u < count) idq[st] = point_list[ahead + (uint32_t)FWD_DEPTH * 32u];
+            // the list itself is streamed from HBM once per tile: pull its lines into L2 well ahead of the id loads
+            if (lane == 0 && pos + 32u * 24u < count)
+                asm volatile("prefetch.global.L2 [%0];" ::"l"(point_list + pos + 32u * 24u));
+            __syncwarp();
+            consume(false);
 #ifdef D3GA_BLEND_TRACE
-        tr_chunks++;
+            tr_chunks++;
 #endif
+        }
     }
     if (!all_done) consume(true);
 #ifdef D3GA_BLEND_TRACE
@@ -391,7 +418,7 @@ struct BwdWarpSmem {
     //   [2] r, g, b (from the colour tensor), unused
     float4 ring[RING][3];
     uint2 ring_m[RING];            // Gaussian id, forward list position
-    float4 meta[NB];               // x, y, Gaussian id (bits) of the parked Gaussians
+    uint32_t slot[NB];             // ring slot (centre, id) of the parked Gaussians
     float4 dpix[32];               // dL/dpixel (r, g, b, inverse depth) of the block's pixels
     float p[NB * NB_PITCH];
     float aT[NB * NB_PITCH];
@@ -404,23 +431,38 @@ __device__ __noinline__ void backward_turn_around(BwdWarpSmem &sm, int n, uint32
                                                   float *__restrict__ grad_acc) {
     const int g = (int)(lane & 15u), h = (int)(lane >> 4);
     float S0 = 0.f, Sx = 0.f, Sy = 0.f, Sxx = 0.f, Sxy = 0.f, Syy = 0.f, c0 = 0.f, c1 = 0.f, c2 = 0.f, c3 = 0.f;
-    const float4 m = sm.meta[g];
+    const uint32_t slot = sm.slot[g];
+    const float2 m = g < n ? *reinterpret_cast<const float2 *>(&sm.ring[slot][0]) : make_float2(0.f, 0.f);
+    const uint32_t gid = g < n ? sm.ring_m[slot].x : 0u;
     if (g < n) {
-        // pixel q = 16 h + l of the block sits at (x0 + l % 8, y0 + 2 h + l / 8);  d = centre - pixel
-        const float X0 = m.x - bx0, Y0 = m.y - (by0 + (float)(2 * h));
+        // pixel q = 16 h + l of the block sits at (x0 + l % 8, y0 + 2 h + l / 8).  The moments are first taken about the
+        // corner of the half-block with the INTEGER pixel offsets (lx, ly) as weights -- compile-time constants of the
+        // unrolled loop, ly in {0, 1}: ~3.7 instead of 10 instructions per pixel -- and then moved to the Gaussian's
+        // centre, d = (X0 - lx, Y0 - ly):  sum p dx = X0 M0 - Mx,  sum p dx^2 = X0^2 M0 - 2 X0 Mx + Mxx, ...
         const float *pp = sm.p + g * NB_PITCH + 16 * h, *pa = sm.aT + g * NB_PITCH + 16 * h;
         const float4 *pw = sm.dpix + 16 * h;
+        float M0 = 0.f, Mx = 0.f, My = 0.f, Mxx = 0.f, Mxy = 0.f;
 #pragma unroll
         for (int l = 0; l < 16; l++) {
             const float pv = pp[l], av = pa[l];
             const float4 w = pw[l];
-            const float dx = X0 - (float)(l & 7), dy = Y0 - (float)(l >> 3);
-            const float pdx = pv * dx, pdy = pv * dy;
-            S0 += pv; Sx += pdx; Sy += pdy;
-            Sxx += pdx * dx; Sxy += pdx * dy; Syy += pdy * dy;
+            const float lx = (float)(l & 7);
+            M0 += pv;
+            if ((l & 7) != 0) { Mx += pv * lx; Mxx += pv * (lx * lx); }
+            if ((l >> 3) != 0) {
+                My += pv;                                    // ly = 1 (and ly^2 = ly: Myy = My)
+                if ((l & 7) != 0) Mxy += pv * lx;
+            }
             c0 += av * w.x; c1 += av * w.y; c2 += av * w.z;
             if (INVDEPTH) c3 += av * w.w;
         }
+        const float X0 = m.x - bx0, Y0 = m.y - (by0 + (float)(2 * h));
+        S0 = M0;
+        Sx = X0 * M0 - Mx;
+        Sy = Y0 * M0 - My;
+        Sxx = X0 * Sx - (X0 * Mx - Mxx);                     // X0^2 M0 - 2 X0 Mx + Mxx
+        Sxy = Y0 * Sx - (X0 * My - Mxy);                     // X0 Y0 M0 - Y0 Mx - X0 My + Mxy
+        Syy = Y0 * Sy - (Y0 * My - My);                      // Y0^2 M0 - 2 Y0 My + Myy
     }
     S0 += __shfl_xor_sync(0xffffffffu, S0, 16); Sx += __shfl_xor_sync(0xffffffffu, Sx, 16);
     Sy += __shfl_xor_sync(0xffffffffu, Sy, 16); Sxx += __shfl_xor_sync(0xffffffffu, Sxx, 16);
@@ -429,7 +471,7 @@ __device__ __noinline__ void backward_turn_around(BwdWarpSmem &sm, int n, uint32
     c2 += __shfl_xor_sync(0xffffffffu, c2, 16);
     if (INVDEPTH) c3 += __shfl_xor_sync(0xffffffffu, c3, 16);
     if (h == 0 && g < n) {
-        float *row = grad_acc + (size_t)__float_as_uint(m.z) * GRAD_ACC_FLOATS;
+        float *row = grad_acc + (size_t)gid * GRAD_ACC_FLOATS;
         red_add_v4(row, Sx, Sy, Sxx, Sxy);
         red_add_v4(row + 4, Syy, S0, c0, c1);
         if (INVDEPTH) red_add_v2(row + 8, c2, c3);
@@ -501,40 +543,50 @@ __global__ void __launch_bounds__(TILE_PIX, BWD_MIN_CTAS) blend_backward_kernel(
             const uint32_t avail = min(4u, tail - head);
             const uint32_t base = head & (RING - 1);
             const float4(*g)[3] = sm.ring + base;
-            float G_[4], al[4], ex[4], ey[4];
-            uint32_t eid[4];
-            bool ok[4];
+            // al = the forward's alpha where this pixel took the Gaussian, else 0 (alpha >= 1/255 there, so "taken" is
+            // al != 0); Gk = G there, else 0.  A pair that is not taken then drops out of every sum below by itself:
+            // ra = 1 leaves T alone, alpha T = 0, G dL/dalpha = 0 -- one select in the recurrence instead of four.
+            float Gk[4], al[4];
             uint32_t near = 0;
 #pragma unroll
             for (int u = 0; u < 4; u++) {
                 const float4 e = g[u][0];     // x, y, -, opacity
                 const float4 co = g[u][1];    // pre-scaled conic (log2 domain): exactly the forward's alpha
-                const uint2 mq = sm.ring_m[base + u];
-                ex[u] = e.x; ey[u] = e.y; eid[u] = mq.x;
+                const uint32_t q = sm.ring_m[base + u].y;
                 const float dx = e.x - pxf, dy = e.y - pyf;
                 const float power = dx * (co.x * dx + co.y * dy) + co.z * dy * dy;
                 const float G = fast_exp2(power);
                 const float alpha = fminf(0.99f, e.w * G);
-                const bool mine = (uint32_t)u < avail && mq.y < last_contributor;
-                ok[u] = mine && !(power > 0.f) && alpha >= CUT;
+                const bool mine = (uint32_t)u < avail && q < last_contributor;
+                const bool ok = mine && !(power > 0.f) && alpha >= CUT;
                 near |= (mine && fabsf(fmaf(alpha, 255.f, -1.f)) < CUT_BAND) ? (1u << u) : 0u;
-                G_[u] = G; al[u] = alpha;
+                Gk[u] = ok ? G : 0.f;
+                al[u] = ok ? alpha : 0.f;
             }
             if (near) {   // the same decision as the forward's (see exact_cut)
 #pragma unroll
-                for (int u = 0; u < 4; u++)
-                    if ((near >> u) & 1u) ok[u] = exact_cut(xy, conic_opacity, eid[u], pxf, pyf);
+                for (int u = 0; u < 4; u++) {
+                    if (!((near >> u) & 1u)) continue;
+                    const float4 e = g[u][0];
+                    const float4 co = g[u][1];
+                    const float dx = e.x - pxf, dy = e.y - pyf;
+                    const float G = fast_exp2(dx * (co.x * dx + co.y * dy) + co.z * dy * dy);
+                    const bool ok = exact_cut(xy, conic_opacity, sm.ring_m[base + u].x, pxf, pyf);
+                    Gk[u] = ok ? G : 0.f;
+                    al[u] = ok ? fminf(0.99f, e.w * G) : 0.f;
+                }
             }
             head += avail;
             if (lane == 0) STAT_ADD(6, 1);
 #pragma unroll
             for (int u = 0; u < 4; u++) {
-                if (!__any_sync(0xffffffffu, ok[u])) continue;   // warp-uniform: no pixel of the block is touched
+                const bool taken = al[u] != 0.f;
+                if (!__any_sync(0xffffffffu, taken)) continue;     // warp-uniform: no pixel of the block is touched
                 const float4 f = g[u][2];
                 const float alpha = al[u];
-                const float ra = __fdividef(1.f, 1.f - alpha);
-                T = ok[u] ? T * ra : T;                            // transmittance in front of this Gaussian
-                const float aT = ok[u] ? alpha * T : 0.f;
+                const float ra = taken ? fast_rcp(1.f - alpha) : 1.f;   // 1 - alpha >= 0.01
+                T *= ra;                                           // transmittance in front of this Gaussian
+                const float aT = alpha * T;
                 float cg = f.x * g0 + f.y * g1 + f.z * g2;        // (colour . dL/dpixel)
                 if (INVDEPTH) cg += g[u][1].w * gi;
                 // dL/dalpha = (c - accum_rec) . g T - T_final/(1-alpha) (bg . g) with accum_rec T = behind / (1 - alpha),
@@ -542,9 +594,11 @@ __global__ void __launch_bounds__(TILE_PIX, BWD_MIN_CTAS) blend_backward_kernel(
                 // contracted with g before instead of after)
                 const float dL_dalpha = cg * T - (behind + bg_term) * ra;
                 behind += cg * aT;
-                sm.p[nb * NB_PITCH + (int)lane] = ok[u] ? G_[u] * dL_dalpha : 0.f;
+                sm.p[nb * NB_PITCH + (int)lane] = Gk[u] * dL_dalpha;
                 sm.aT[nb * NB_PITCH + (int)lane] = aT;
-                if (lane == 0) sm.meta[nb] = make_float4(ex[u], ey[u], __uint_as_float(eid[u]), 0.f);
+                // where the turn-around finds this Gaussian's centre and id: its ring slot (slots of the last 16 consumed
+                // entries cannot have been refilled: the ring never holds more than 35 staged ones)
+                if (lane == 0) sm.slot[nb] = base + (uint32_t)u;
                 nb++;
             }
             if (nb > NB - 4) {   // the next group may not fit: one call site per group, not one per entry
@@ -571,9 +625,9 @@ __global__ void __launch_bounds__(TILE_PIX, BWD_MIN_CTAS) blend_backward_kernel(
         const uint32_t m = __brev(mf);                       // bit l = lane l = forward position 32 fc + 31 - l
         if ((m >> lane) & 1u) {
             const uint32_t s = (tail + __popc(m & lanemask_lt())) & (RING - 1);
-            cp_async_16(&sm.ring[s][0], &splat[id].g0);
-            cp_async_16(&sm.ring[s][1], &splat[id].g1);
-            cp_async_16(&sm.ring[s][2], feat + id);
+            bwd_cp_async_16(&sm.ring[s][0], &splat[id].g0);
+            bwd_cp_async_16(&sm.ring[s][1], &splat[id].g1);
+            bwd_cp_async_16(&sm.ring[s][2], feat + id);
             sm.ring_m[s] = make_uint2(id, 32u * (uint32_t)fc + 31u - lane);
         }
         cp_async_commit();
