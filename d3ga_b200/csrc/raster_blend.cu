@@ -418,7 +418,7 @@ struct BwdWarpSmem {
     //   [2] r, g, b (from the colour tensor), unused
     float4 ring[RING][3];
     uint2 ring_m[RING];            // Gaussian id, forward list position
-    uint32_t slot[NB];             // ring slot (centre, id) of the parked Gaussians
+    float4 meta[NB];               // x, y, Gaussian id (bits) of the parked Gaussians
     float4 dpix[32];               // dL/dpixel (r, g, b, inverse depth) of the block's pixels
     float p[NB * NB_PITCH];
     float aT[NB * NB_PITCH];
@@ -431,9 +431,8 @@ __device__ __noinline__ void backward_turn_around(BwdWarpSmem &sm, int n, uint32
                                                   float *__restrict__ grad_acc) {
     const int g = (int)(lane & 15u), h = (int)(lane >> 4);
     float S0 = 0.f, Sx = 0.f, Sy = 0.f, Sxx = 0.f, Sxy = 0.f, Syy = 0.f, c0 = 0.f, c1 = 0.f, c2 = 0.f, c3 = 0.f;
-    const uint32_t slot = sm.slot[g];
-    const float2 m = g < n ? *reinterpret_cast<const float2 *>(&sm.ring[slot][0]) : make_float2(0.f, 0.f);
-    const uint32_t gid = g < n ? sm.ring_m[slot].x : 0u;
+    const float4 m = sm.meta[g];
+    const uint32_t gid = __float_as_uint(m.z);
     if (g < n) {
         // pixel q = 16 h + l of the block sits at (x0 + l % 8, y0 + 2 h + l / 8).  The moments are first taken about the
         // corner of the half-block with the INTEGER pixel offsets (lx, ly) as weights -- compile-time constants of the
@@ -596,9 +595,12 @@ __global__ void __launch_bounds__(TILE_PIX, BWD_MIN_CTAS) blend_backward_kernel(
                 behind += cg * aT;
                 sm.p[nb * NB_PITCH + (int)lane] = Gk[u] * dL_dalpha;
                 sm.aT[nb * NB_PITCH + (int)lane] = aT;
-                // where the turn-around finds this Gaussian's centre and id: its ring slot (slots of the last 16 consumed
-                // entries cannot have been refilled: the ring never holds more than 35 staged ones)
-                if (lane == 0) sm.slot[nb] = base + (uint32_t)u;
+                // centre and id for the turn-around, copied out of the ring slot (the slot may be refilled before the
+                // turn-around comes: parked entries are the TAKEN ones, any number of skipped ones can lie between them)
+                if (lane == 0) {
+                    const float4 e = g[u][0];
+                    sm.meta[nb] = make_float4(e.x, e.y, __uint_as_float(sm.ring_m[base + u].x), 0.f);
+                }
                 nb++;
             }
             if (nb > NB - 4) {   // the next group may not fit: one call site per group, not one per entry

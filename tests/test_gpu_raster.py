@@ -246,8 +246,14 @@ def test_full_size_properties(cuda_lib, oracle_libs, workload):
     g2 = gpu_util.backward(got, W, H, cam, 2 * w)
     assert util.rel_l2(g2["means3D"], 2 * g1["means3D"]) < 1e-5
     rg = orc.backward(ref, w)
-    for k in ("means3D", "cov3D", "opacity", "colors"):
-        assert util.rel_l2(g1[k], rg[k]) < GRAD_TOL, (k, util.rel_l2(g1[k], rg[k]))
+    errs = {k: util.rel_l2(g1[k], rg[k]) for k in ("means3D", "cov3D", "opacity", "colors")}
+    report_parity(dict(test="full_size_gradients", workload=workload, **errs))
+    for k, e in errs.items():
+        assert e < GRAD_TOL, (k, e)
+        # Regression guard, far inside the bar: fed the oracle's own inputs the kernels agree with it to ~1e-6 (the lists
+        # are bit-identical, so nothing discontinuous separates the two).  A bookkeeping bug in the backward's staging once
+        # showed as 3e-3 on one camera of the pipelined test while this comparison still passed the 1e-3 bar.
+        assert e < 5e-5, (k, e)
 
 
 def test_mark_visible(cuda_lib, oracle_libs):
