@@ -355,6 +355,31 @@ __global__ void __launch_bounds__(256) direct_plan_kernel(RasterHeader *hdr, con
         for (int u = 0; u < 8; u++) { const int i = i0 + u * 256 + tid; if (i < num_tiles) s_cnt[i] = v[u]; }
     }
     __syncthreads();
+    // Two CTAs, side by side: CTA 0 scans the totals (what the next kernels wait for), CTA 1 orders the tiles for the
+    // forward blend (needed much later).  One after the other in a single CTA they were 20 us of serial latency.
+    if (blockIdx.x == 1) {
+        // Launch order of the forward blend: longest WALK first.  A tile's list is walked until its last pixel saturates:
+        // inside the body that happens after ~1.5 k entries however long the list is, while a tile on the silhouette (a
+        // neighbour with a much shorter list: some of its pixels never saturate) is walked to the end.  Ordering by list
+        // length alone started those tiles ~640 slots late and their 8 serial warps ended the kernel alone (a per-warp
+        // %globaltimer trace: 126 us of chain starting at t = 40 us); the estimate below starts them first.
+        const uint32_t *c = s_cnt;
+        const int gx = grid_x, gy = num_tiles / grid_x;
+        auto walk = [c, gx, gy](int t) {
+            const uint32_t n = c[t];
+            constexpr uint32_t SAT = 1536u;
+            if (n <= SAT) return n;
+            const int x = t % gx, y = t / gx;
+            uint32_t mn = n;
+            if (x > 0) mn = min(mn, c[t - 1]);
+            if (x + 1 < gx) mn = min(mn, c[t + 1]);
+            if (y > 0) mn = min(mn, c[t - gx]);
+            if (y + 1 < gy) mn = min(mn, c[t + gx]);
+            return 4u * mn < n ? n : SAT + (n - SAT) / 8u;
+        };
+        order_tiles_descending(num_tiles, walk, order_fwd, s_bins);
+        return;
+    }
     const int per = (num_tiles + 255) / 256, t0 = min(num_tiles, tid * per), t1 = min(num_tiles, t0 + per);
     uint32_t local = 0;
     for (int t = t0; t < t1; t++) local += s_cnt[t];
@@ -382,27 +407,6 @@ __global__ void __launch_bounds__(256) direct_plan_kernel(RasterHeader *hdr, con
         hdr->num_passes = (uint32_t)num_passes;
     }
     if (tid < SORT_MAX_PASSES) { hdr->pass_skip[tid] = 1u; hdr->pass_src[tid] = 0u; }   // no radix pass runs
-    __syncthreads();
-    // Launch order of the forward blend: longest WALK first.  A tile's list is walked until its last pixel saturates:
-    // inside the body that happens after ~1.5 k entries however long the list is, while a tile on the silhouette (a
-    // neighbour with a much shorter list: some of its pixels never saturate) is walked to the end.  Ordering by list
-    // length alone started those tiles ~640 slots late and their 8 serial warps ended the kernel alone (a per-warp
-    // %globaltimer trace: 126 us of chain starting at t = 40 us); the estimate below starts them first.
-    const uint32_t *c = s_cnt;
-    const int gx = grid_x, gy = num_tiles / grid_x;
-    auto walk = [c, gx, gy](int t) {
-        const uint32_t n = c[t];
-        constexpr uint32_t SAT = 1536u;
-        if (n <= SAT) return n;
-        const int x = t % gx, y = t / gx;
-        uint32_t mn = n;
-        if (x > 0) mn = min(mn, c[t - 1]);
-        if (x + 1 < gx) mn = min(mn, c[t + 1]);
-        if (y > 0) mn = min(mn, c[t - gx]);
-        if (y + 1 < gy) mn = min(mn, c[t + gx]);
-        return 4u * mn < n ? n : SAT + (n - SAT) / 8u;
-    };
-    order_tiles_descending(num_tiles, walk, order_fwd, s_bins);
 }
 
 // Segment offsets += start[tile] (they become absolute slots); before[row][tile] = exclusive prefix of M over the rows of
@@ -673,7 +677,7 @@ int launch_direct_scatter(int P, int gx, int gy, uint8_t *geom, const GeomLayout
     D3GA_LAUNCH_CHECK();
     {
         ProfScope prof(K_DIRECT_PLAN, stream);
-        direct_plan_kernel<<<1, 256, 4 * (size_t)num_tiles, stream>>>(
+        direct_plan_kernel<<<2, 256, 4 * (size_t)num_tiles, stream>>>(
             p.hdr, reinterpret_cast<const uint32_t *>(tot), reinterpret_cast<uint32_t *>(start), num_tiles,
             reinterpret_cast<uint2 *>(image + IL.ranges), reinterpret_cast<uint32_t *>(image + IL.order_fwd), sort_bits,
             (sort_bits + 7) / 8, gx);

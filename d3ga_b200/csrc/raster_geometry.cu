@@ -119,6 +119,14 @@ __device__ __forceinline__ void preprocess_one(const GeoParams &p, int idx, cons
         float depth = 0.f, pxi = 0.f, pyi = 0.f;
         float4 co = make_float4(0.f, 0.f, 0.f, 0.f);
         const float mx = p.means3D[3 * idx], my = p.means3D[3 * idx + 1], mz = p.means3D[3 * idx + 2];
+        // opacity and colour are only needed by Gaussians that survive the culls, but loading them there put a second
+        // DRAM round trip behind the first (ncu: 8.4 long-scoreboard stalls per issue); they are read up front
+        const float opacity_in = p.opacities[idx];
+        float col_in[3] = {0.f, 0.f, 0.f};
+        if (!p.shs) {
+            const float *cp = p.colors_precomp + 3 * (size_t)idx;
+            col_in[0] = cp[0]; col_in[1] = cp[1]; col_in[2] = cp[2];
+        }
         float c6[6];
         if (p.cov3D_precomp) {
             const float2 *src = reinterpret_cast<const float2 *>(p.cov3D_precomp + 6 * (size_t)idx);
@@ -208,7 +216,7 @@ __device__ __forceinline__ void preprocess_one(const GeoParams &p, int idx, cons
                     depth = zv;
                     dbits = __float_as_uint(zv);
                     co = make_float4(MUL(cyy, det_inv), MUL(-cxy, det_inv), MUL(cxx, det_inv),
-                                     MUL(p.opacities[idx], hscale));
+                                     MUL(opacity_in, hscale));
                 }
             }
         }
@@ -243,8 +251,7 @@ __device__ __forceinline__ void preprocess_one(const GeoParams &p, int idx, cons
 #pragma unroll
             for (int c = 0; c < 3; c++) { p.rgb[3 * (size_t)idx + c] = rgb[c]; p.clamped[3 * (size_t)idx + c] = cl[c]; }
         } else if (live) {
-            const float *cp = p.colors_precomp + 3 * (size_t)idx;
-            p.feat[idx] = make_float4(cp[0], cp[1], cp[2], 0.f);
+            p.feat[idx] = make_float4(col_in[0], col_in[1], col_in[2], 0.f);
         }
         p.depth[idx] = depth;
         p.xy[idx] = make_float2(pxi, pyi);

@@ -300,11 +300,20 @@ __global__ void __launch_bounds__(HIST_THREADS) depth_histogram_kernel(RasterHea
     if (tid == 0) s_culled = 0;
     __syncthreads();
     uint32_t culled = 0;
-    for (uint32_t i = blockIdx.x * HIST_THREADS + tid; i < n; i += gridDim.x * HIST_THREADS) {
-        const uint32_t k = __ldcs(keys + i);
-        culled += k == 0xffffffffu;
+    // eight loads in flight per thread: with one, every trip of the loop waited a DRAM round trip (ncu: 30 long-scoreboard
+    // stalls per issue, 15.6 us for 4 MB)
+    const uint32_t stride = gridDim.x * HIST_THREADS;
+    for (uint32_t i0 = blockIdx.x * HIST_THREADS + tid; i0 < n; i0 += 8 * stride) {
+        uint32_t k[8];
 #pragma unroll
-        for (int p = 0; p < 4; p++) atomicAdd(&s_hist[p][(k >> (8 * p)) & 255u], 1u);
+        for (int u = 0; u < 8; u++) k[u] = i0 + u * stride < n ? __ldcs(keys + i0 + u * stride) : 0u;
+#pragma unroll
+        for (int u = 0; u < 8; u++) {
+            if (i0 + u * stride >= n) continue;
+            culled += k[u] == 0xffffffffu;
+#pragma unroll
+            for (int p = 0; p < 4; p++) atomicAdd(&s_hist[p][(k[u] >> (8 * p)) & 255u], 1u);
+        }
     }
     culled = __reduce_add_sync(0xffffffffu, culled);
     if ((tid & 31) == 0 && culled) atomicAdd(&s_culled, culled);
