@@ -85,7 +85,7 @@ def load() -> C.CDLL:
     lib.d3ga_deform_backward.argtypes = [i32, i32, i32, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp]
     lib.d3ga_deform_backward_ordered.argtypes = [i32, i32, i32] + [vp] * 15
     lib.d3ga_deform_forward_fused.argtypes = [i32, i32, i32] + [vp] * 8 + [i32] + [vp] * 7
-    lib.d3ga_deform_backward_fused.argtypes = [i32, i32, i32] + [vp] * 8 + [i32] + [vp] * 12
+    lib.d3ga_deform_backward_fused.argtypes = [i32, i32, i32] + [vp] * 8 + [i32] + [vp] * 11 + [i32, i32, vp]
     lib.d3ga_fem_energy_forward.argtypes = [i32, i32, vp, vp, vp, vp, vp]
     lib.d3ga_fem_energy_backward.argtypes = [i32, i32, vp, vp, vp, vp, vp, vp]
     lib.d3ga_ssim_l1_forward.argtypes = [i32, i32, i32, vp, vp, vp, vp, vp, vp, vp]

@@ -44,11 +44,53 @@ struct DeformExtra {
     float *energy;                                       // forward: [T] out
     const float *dL_denergy;                             // backward: [T] or null
     int gaussian_blocks;                                 // CTAs below this index work on Gaussians, the rest on tets
+    int grad_pitch;                                      // floats per row of dL_dtetpoints: 3, or 4 (padded: vector REDs)
+    int tet_sorted;                                      // rows are already in tet order: warp-summed like `order`
 };
 
-// barys, scales (activated) and the un-normalised quaternion of Gaussian n as the kernels use them
+// The warp's 32 consecutive rows of K floats lie contiguous in memory: they are read as K coalesced requests of four
+// sectors each and every lane takes its row out of shared memory (stride K).  A scalar load of ONE column of a [N,K]
+// array touches up to 9 K sectors per request; ncu showed the forward's LSU queue full (lg_throttle 15 stalls per
+// issue, 27 M sector accesses for 120 MB).  All 32 lanes call (rows past the end read as 0 / are not stored).
+constexpr int STAGE_FLOATS = 32 * 9;
+// Two phases, so that a kernel can issue the global loads of ALL its streams before it waits for the first one.
+template <int K>
+__device__ __forceinline__ void warp_rows_fetch(const float *__restrict__ base, size_t row0, size_t rows, uint32_t lane,
+                                                float (&raw)[K]) {
+    const size_t first = row0 * K, limit = rows * K;
+#pragma unroll
+    for (int j = 0; j < K; j++) {
+        const size_t i = first + (size_t)(j * 32) + lane;
+        raw[j] = i < limit ? __ldg(base + i) : 0.f;
+    }
+}
+template <int K>
+__device__ __forceinline__ void warp_rows_take(float *s_w, uint32_t lane, const float (&raw)[K], float (&out)[K]) {
+#pragma unroll
+    for (int j = 0; j < K; j++) s_w[j * 32 + (int)lane] = raw[j];
+    __syncwarp();
+#pragma unroll
+    for (int j = 0; j < K; j++) out[j] = s_w[(int)lane * K + j];
+    __syncwarp();
+}
+template <int K>
+__device__ __forceinline__ void warp_rows_store(float *__restrict__ base, size_t row0, size_t rows, float *s_w,
+                                                uint32_t lane, const float (&in)[K]) {
+    const size_t first = row0 * K, limit = rows * K;
+#pragma unroll
+    for (int j = 0; j < K; j++) s_w[(int)lane * K + j] = in[j];
+    __syncwarp();
+#pragma unroll
+    for (int j = 0; j < K; j++) {
+        const size_t i = first + (size_t)(j * 32) + lane;
+        if (i < limit) base[i] = s_w[j * 32 + (int)lane];
+    }
+    __syncwarp();
+}
+// barys, scales (activated) and the un-normalised quaternion of Gaussian n as the kernels use them; `sraw` = the scale
+// row as it lies in memory (Delta already added), read by the caller
 __device__ __forceinline__ void load_gaussian(const DeformExtra &ex, const float *__restrict__ barys,
-                                              const float *__restrict__ scales, const float *__restrict__ rotation,
+                                              const float (&sraw)[3], const float *__restrict__ rotation,
                                               size_t n, float (&bw)[4], float (&s)[3], float4 &q) {
     float4 b = *reinterpret_cast<const float4 *>(barys + 4 * n);
     if (ex.delta_bary) {
@@ -57,11 +99,7 @@ __device__ __forceinline__ void load_gaussian(const DeformExtra &ex, const float
     }
     bw[0] = b.x; bw[1] = b.y; bw[2] = b.z; bw[3] = b.w;
 #pragma unroll
-    for (int k = 0; k < 3; k++) {
-        float v = scales[3 * n + k];
-        if (ex.delta_scale) v += ex.delta_scale[3 * n + k];
-        s[k] = ex.log_scales ? expf(v) : v;
-    }
+    for (int k = 0; k < 3; k++) s[k] = ex.log_scales ? expf(sraw[k]) : sraw[k];
     q = *reinterpret_cast<const float4 *>(rotation + 4 * n);
     if (ex.delta_rot) {
         const float4 d = *reinterpret_cast<const float4 *>(ex.delta_rot + 4 * n);
@@ -71,12 +109,13 @@ __device__ __forceinline__ void load_gaussian(const DeformExtra &ex, const float
 
 __device__ __forceinline__ void load_tet(const float *__restrict__ tetpoints, const int64_t *__restrict__ tets,
                                          int64_t t, int64_t (&vid)[4], Tet4 &X) {
+    const longlong2 *row = reinterpret_cast<const longlong2 *>(tets + 4 * t);   // one 32-byte row: two 16-byte loads
+    const longlong2 a = __ldg(row), b = __ldg(row + 1);
+    vid[0] = a.x; vid[1] = a.y; vid[2] = b.x; vid[3] = b.y;
 #pragma unroll
-    for (int k = 0; k < 4; k++) {
-        vid[k] = tets[4 * t + k];
+    for (int k = 0; k < 4; k++)
 #pragma unroll
         for (int c = 0; c < 3; c++) X.v[k][c] = __ldg(tetpoints + 3 * vid[k] + c);
-    }
 }
 
 __device__ __forceinline__ void rotation_from_unit_quat(float r, float x, float y, float z, float (&Rm)[3][3]) {
@@ -95,19 +134,35 @@ __global__ void __launch_bounds__(GEO_THREADS) deform_forward_kernel(
         if (tt < T) fem::fem_forward_tet(tt, tetpoints, tets, ex.dn_inv, ex.energy);
         return;
     }
-    const int n = blockIdx.x * GEO_THREADS + threadIdx.x;
-    if (n >= N) return;
-    int64_t t = tetra_id[n];
+    __shared__ float s_stage[GEO_THREADS / 32][STAGE_FLOATS];
+    const uint32_t lane = threadIdx.x & 31;
+    float *s_w = s_stage[threadIdx.x >> 5];
+    const size_t row0 = (size_t)blockIdx.x * GEO_THREADS + (threadIdx.x & ~31u);   // the warp's first Gaussian
+    const bool live = row0 + lane < (size_t)N;
+    const int n = live ? (int)(row0 + lane) : N - 1;          // dead lanes of the last warp shadow the last Gaussian
+    // the [N,K] streams, coalesced through shared memory
+    float cg9[9], sraw[3];
+    int64_t t = __ldg(tetra_id + n);                         // head of the only dependent chain: id -> tet -> vertices
+    {
+        float r9[9], r3[3], rd[3] = {0.f, 0.f, 0.f};
+        warp_rows_fetch<9>(cgrad, row0, (size_t)N, lane, r9);
+        warp_rows_fetch<3>(scales, row0, (size_t)N, lane, r3);
+        if (ex.delta_scale) warp_rows_fetch<3>(ex.delta_scale, row0, (size_t)N, lane, rd);   // same offsets: added raw
+        r3[0] += rd[0]; r3[1] += rd[1]; r3[2] += rd[2];
+        warp_rows_take<9>(s_w, lane, r9, cg9);
+        warp_rows_take<3>(s_w, lane, r3, sraw);
+    }
     if (t < 0) t += T;   // torch indexing wraps a -1 from compute_bary to the last tet
+    float bw[4], s[3];
+    float4 q;
+    load_gaussian(ex, barys, sraw, rotation, (size_t)n, bw, s, q);
     int64_t vid[4];
     Tet4 X;
     load_tet(tetpoints, tets, t, vid, X);
-    float bw[4], s[3];
-    float4 q;
-    load_gaussian(ex, barys, scales, rotation, (size_t)n, bw, s, q);
+    float mean[3];
 #pragma unroll
-    for (int c = 0; c < 3; c++)
-        means3D[3 * (size_t)n + c] = X.v[0][c] * bw[0] + X.v[1][c] * bw[1] + X.v[2][c] * bw[2] + X.v[3][c] * bw[3];
+    for (int c = 0; c < 3; c++) mean[c] = X.v[0][c] * bw[0] + X.v[1][c] * bw[1] + X.v[2][c] * bw[2] + X.v[3][c] * bw[3];
+    warp_rows_store<3>(means3D, row0, (size_t)N, s_w, lane, mean);
     // G: edges (v3-v0, v2-v0, v1-v0) as columns
     float G[3][3], Cg[3][3], J[3][3];
 #pragma unroll
@@ -115,7 +170,7 @@ __global__ void __launch_bounds__(GEO_THREADS) deform_forward_kernel(
         G[i][0] = X.v[3][i] - X.v[0][i]; G[i][1] = X.v[2][i] - X.v[0][i]; G[i][2] = X.v[1][i] - X.v[0][i];
     }
 #pragma unroll
-    for (int k = 0; k < 9; k++) Cg[k / 3][k % 3] = cgrad[9 * (size_t)n + k];
+    for (int k = 0; k < 9; k++) Cg[k / 3][k % 3] = cg9[k];
 #pragma unroll
     for (int i = 0; i < 3; i++)
 #pragma unroll
@@ -128,18 +183,19 @@ __global__ void __launch_bounds__(GEO_THREADS) deform_forward_kernel(
     for (int i = 0; i < 3; i++)
 #pragma unroll
         for (int k = 0; k < 3; k++) B[i][k] = (J[i][0] * Rm[0][k] + J[i][1] * Rm[1][k] + J[i][2] * Rm[2][k]) * s[k];
+    float c6[6];
     int o = 0;
 #pragma unroll
     for (int i = 0; i < 3; i++)
 #pragma unroll
-        for (int j = i; j < 3; j++)
-            cov3D[6 * (size_t)n + o++] = B[i][0] * B[j][0] + B[i][1] * B[j][1] + B[i][2] * B[j][2];
+        for (int j = i; j < 3; j++) c6[o++] = B[i][0] * B[j][0] + B[i][1] * B[j][1] + B[i][2] * B[j][2];
+    warp_rows_store<6>(cov3D, row0, (size_t)N, s_w, lane, c6);
 }
 
 // Warp-level segmented sum over runs of equal tet id (lanes are tet-sorted), then one set of 12 atomics per run.
 // Every lane of the warp calls it from the same place (full-mask shuffles); lanes without a contribution pass zeros.
 __device__ __forceinline__ void segmented_vertex_scatter(int64_t t, const int64_t (&vid)[4], float (&v)[12],
-                                                         float *__restrict__ dL_dtetpoints) {
+                                                         float *__restrict__ dL_dtetpoints, int pitch) {
     const uint32_t lane = threadIdx.x & 31;
     const int64_t tprev = __shfl_up_sync(0xffffffffu, t, 1);
     const bool head = lane == 0 || t != tprev;
@@ -155,11 +211,18 @@ __device__ __forceinline__ void segmented_vertex_scatter(int64_t t, const int64_
         }
     }
     if (head) {
+        if (pitch == 4) {   // padded rows: one 16-byte vector reduction per vertex
 #pragma unroll
-        for (int k = 0; k < 4; k++)
+            for (int k = 0; k < 4; k++)
+                if (v[3 * k] != 0.f || v[3 * k + 1] != 0.f || v[3 * k + 2] != 0.f)
+                    red_add_v4(dL_dtetpoints + 4 * vid[k], v[3 * k], v[3 * k + 1], v[3 * k + 2], 0.f);
+        } else {
 #pragma unroll
-            for (int c = 0; c < 3; c++)
-                if (v[3 * k + c] != 0.f) atomicAdd(dL_dtetpoints + 3 * vid[k] + c, v[3 * k + c]);
+            for (int k = 0; k < 4; k++)
+#pragma unroll
+                for (int c = 0; c < 3; c++)
+                    if (v[3 * k + c] != 0.f) atomicAdd(dL_dtetpoints + 3 * vid[k] + c, v[3 * k + c]);
+        }
     }
 }
 
@@ -172,7 +235,7 @@ __global__ void __launch_bounds__(GEO_THREADS, DEFORM_BWD_MIN_CTAS) deform_backw
     const DeformExtra ex) {
     if ((int)blockIdx.x >= ex.gaussian_blocks) {   // appended CTAs: gradient of the cage energy into the cage vertices
         const int tt = ((int)blockIdx.x - ex.gaussian_blocks) * GEO_THREADS + (int)threadIdx.x;
-        if (tt < T && dL_dtetpoints) fem::fem_backward_tet(tt, tetpoints, tets, ex.dn_inv, ex.dL_denergy, dL_dtetpoints);
+        if (tt < T && dL_dtetpoints) fem::fem_backward_tet(tt, tetpoints, tets, ex.dn_inv, ex.dL_denergy, dL_dtetpoints, ex.grad_pitch);
         return;
     }
     const int i = blockIdx.x * GEO_THREADS + threadIdx.x;
@@ -186,18 +249,47 @@ __global__ void __launch_bounds__(GEO_THREADS, DEFORM_BWD_MIN_CTAS) deform_backw
 #pragma unroll
     for (int k = 0; k < 12; k++) dvf[k] = 0.f;
 
+    // The [N,K] streams.  In natural order the warp's rows are contiguous and go through shared memory as coalesced
+    // requests (every lane takes part); with `order` the rows are gathered, one lane one row.
+    __shared__ float s_stage[GEO_THREADS / 32][STAGE_FLOATS];
+    const uint32_t lane = threadIdx.x & 31;
+    float *s_w = s_stage[threadIdx.x >> 5];
+    const size_t row0 = (size_t)blockIdx.x * GEO_THREADS + (threadIdx.x & ~31u);
+    float cg9[9], sraw[3], dm[3], g6[6], ds_out[3] = {0.f, 0.f, 0.f};
+    if (!order) {
+        float r9[9], r6[6], rm[3], r3[3], rd[3] = {0.f, 0.f, 0.f};
+        warp_rows_fetch<9>(cgrad, row0, (size_t)N, lane, r9);
+        warp_rows_fetch<6>(dL_dcov, row0, (size_t)N, lane, r6);
+        warp_rows_fetch<3>(dL_dmeans, row0, (size_t)N, lane, rm);
+        warp_rows_fetch<3>(scales, row0, (size_t)N, lane, r3);
+        if (ex.delta_scale) warp_rows_fetch<3>(ex.delta_scale, row0, (size_t)N, lane, rd);
+        if (live) t = __ldg(tetra_id + n);
+        r3[0] += rd[0]; r3[1] += rd[1]; r3[2] += rd[2];
+        warp_rows_take<9>(s_w, lane, r9, cg9);
+        warp_rows_take<6>(s_w, lane, r6, g6);
+        warp_rows_take<3>(s_w, lane, rm, dm);
+        warp_rows_take<3>(s_w, lane, r3, sraw);
+    } else if (live) {
+        t = __ldg(tetra_id + n);
+#pragma unroll
+        for (int k = 0; k < 9; k++) cg9[k] = cgrad[9 * (size_t)n + k];
+#pragma unroll
+        for (int k = 0; k < 6; k++) g6[k] = dL_dcov[6 * (size_t)n + k];
+#pragma unroll
+        for (int k = 0; k < 3; k++) {
+            dm[k] = dL_dmeans[3 * (size_t)n + k];
+            sraw[k] = scales[3 * (size_t)n + k];
+            if (ex.delta_scale) sraw[k] += ex.delta_scale[3 * (size_t)n + k];
+        }
+    }
+
     if (live) {
-        t = tetra_id[n];
         if (t < 0) t += T;
         Tet4 X;
         load_tet(tetpoints, tets, t, vid, X);
         float bw[4], s[3];
         float4 q;
-        load_gaussian(ex, barys, scales, rotation, (size_t)n, bw, s, q);
-        const float dm[3] = {dL_dmeans[3 * (size_t)n], dL_dmeans[3 * (size_t)n + 1], dL_dmeans[3 * (size_t)n + 2]};
-        float g6[6];
-#pragma unroll
-        for (int k = 0; k < 6; k++) g6[k] = dL_dcov[6 * (size_t)n + k];
+        load_gaussian(ex, barys, sraw, rotation, (size_t)n, bw, s, q);
 
         // recompute the forward
         float G[3][3], Cg[3][3], J[3][3];
@@ -206,7 +298,7 @@ __global__ void __launch_bounds__(GEO_THREADS, DEFORM_BWD_MIN_CTAS) deform_backw
             G[r][0] = X.v[3][r] - X.v[0][r]; G[r][1] = X.v[2][r] - X.v[0][r]; G[r][2] = X.v[1][r] - X.v[0][r];
         }
 #pragma unroll
-        for (int k = 0; k < 9; k++) Cg[k / 3][k % 3] = cgrad[9 * (size_t)n + k];
+        for (int k = 0; k < 9; k++) Cg[k / 3][k % 3] = cg9[k];
 #pragma unroll
         for (int r = 0; r < 3; r++)
 #pragma unroll
@@ -247,9 +339,12 @@ __global__ void __launch_bounds__(GEO_THREADS, DEFORM_BWD_MIN_CTAS) deform_backw
                 dJ[r][j] = dJR[r][0] * Rm[j][0] + dJR[r][1] * Rm[j][1] + dJR[r][2] * Rm[j][2];
                 A[r][j] = J[0][r] * dJR[0][j] + J[1][r] * dJR[1][j] + J[2][r] * dJR[2][j];
             }
-        if (dL_dscales) {   // through exp when the scales came in pre-activation: d exp(x) = exp(x) dx
+        // through exp when the scales came in pre-activation: d exp(x) = exp(x) dx
 #pragma unroll
-            for (int k = 0; k < 3; k++) dL_dscales[3 * (size_t)n + k] = ex.log_scales ? ds[k] * s[k] : ds[k];
+        for (int k = 0; k < 3; k++) ds_out[k] = ex.log_scales ? ds[k] * s[k] : ds[k];
+        if (dL_dscales && order) {
+#pragma unroll
+            for (int k = 0; k < 3; k++) dL_dscales[3 * (size_t)n + k] = ds_out[k];
         }
         if (dL_drotation) {
             const float r = qr, x = qx, y = qy, z = qz;
@@ -283,14 +378,21 @@ __global__ void __launch_bounds__(GEO_THREADS, DEFORM_BWD_MIN_CTAS) deform_backw
             }
         }
     }
+    if (dL_dscales && !order) warp_rows_store<3>(dL_dscales, row0, (size_t)N, s_w, lane, ds_out);
     if (!dL_dtetpoints) return;
-    if (order) {
-        segmented_vertex_scatter(t, vid, dvf, dL_dtetpoints);   // every lane, one call site
+    if (order || ex.tet_sorted) {
+        segmented_vertex_scatter(t, vid, dvf, dL_dtetpoints, ex.grad_pitch);   // every lane, one call site
     } else if (live) {
+        if (ex.grad_pitch == 4) {
+            // padded rows: a vertex's three components go out as ONE 16-byte vector reduction (4 per Gaussian, not 12)
 #pragma unroll
-        for (int k = 0; k < 4; k++)
+            for (int k = 0; k < 4; k++) red_add_v4(dL_dtetpoints + 4 * vid[k], dvf[3 * k], dvf[3 * k + 1], dvf[3 * k + 2], 0.f);
+        } else {
 #pragma unroll
-            for (int c = 0; c < 3; c++) atomicAdd(dL_dtetpoints + 3 * vid[k] + c, dvf[3 * k + c]);
+            for (int k = 0; k < 4; k++)
+#pragma unroll
+                for (int c = 0; c < 3; c++) atomicAdd(dL_dtetpoints + 3 * vid[k] + c, dvf[3 * k + c]);
+        }
     }
 }
 
@@ -348,6 +450,7 @@ static int deform_backward_impl(int N, int V, int T, const float *tetpoints, con
     if (N > 0 && (!tetra_id || !barys || !canonical_gradient || !scales || !rotation || !dL_dmeans3D || !dL_dcov3D))
         return D3GA_EINVAL;
     if (ex.dL_denergy && !ex.dn_inv) return D3GA_EINVAL;
+    if (ex.grad_pitch != 4) ex.grad_pitch = 3;
     ex.gaussian_blocks = (N + GEO_THREADS - 1) / GEO_THREADS;
     const int blocks = ex.gaussian_blocks + (ex.dL_denergy ? (T + GEO_THREADS - 1) / GEO_THREADS : 0);
     if (blocks == 0) return D3GA_OK;
@@ -390,8 +493,12 @@ extern "C" int d3ga_deform_backward_fused(int N, int V, int T, const float *tetp
                                           const float *dn_inv, const float *dL_dmeans3D, const float *dL_dcov3D,
                                           const float *dL_denergy, float *dL_dtetpoints, float *dL_dbarys,
                                           float *dL_dscales, float *dL_drotation, const int32_t *order,
-                                          d3ga_stream_t stream) {
+                                          int rows_tet_sorted, int dL_dtetpoints_pitch, d3ga_stream_t stream) {
+    if (dL_dtetpoints_pitch != 3 && dL_dtetpoints_pitch != 4) return D3GA_EINVAL;
+    if (order && rows_tet_sorted) return D3GA_EINVAL;
     DeformExtra ex{};
+    ex.grad_pitch = dL_dtetpoints_pitch;
+    ex.tet_sorted = rows_tet_sorted ? 1 : 0;
     ex.delta_bary = delta_bary; ex.delta_scale = delta_scale; ex.delta_rot = delta_rot; ex.log_scales = log_scales ? 1 : 0;
     ex.dn_inv = dn_inv; ex.dL_denergy = dL_denergy;
     return deform_backward_impl(N, V, T, tetpoints, tets, tetra_id, barys, canonical_gradient, scales, rotation,

@@ -50,7 +50,7 @@ __device__ __forceinline__ void fem_forward_tet(int t, const float *__restrict__
 
 __device__ __forceinline__ void fem_backward_tet(int t, const float *__restrict__ tetpoints, const int64_t *__restrict__ tets,
                                                  const float *__restrict__ dn_inv, const float *__restrict__ dL_denergy,
-                                                 float *__restrict__ dL_dtetpoints) {
+                                                 float *__restrict__ dL_dtetpoints, int pitch = 3) {
     const float g = dL_denergy[t];
     if (g == 0.f) return;
     int64_t vid[4];
@@ -73,10 +73,10 @@ __device__ __forceinline__ void fem_backward_tet(int t, const float *__restrict_
         const float d0 = dF[r][0] * Dn[0][0] + dF[r][1] * Dn[0][1] + dF[r][2] * Dn[0][2];
         const float d1 = dF[r][0] * Dn[1][0] + dF[r][1] * Dn[1][1] + dF[r][2] * Dn[1][2];
         const float d2 = dF[r][0] * Dn[2][0] + dF[r][1] * Dn[2][1] + dF[r][2] * Dn[2][2];
-        atomicAdd(dL_dtetpoints + 3 * vid[3] + r, d0);
-        atomicAdd(dL_dtetpoints + 3 * vid[2] + r, d1);
-        atomicAdd(dL_dtetpoints + 3 * vid[1] + r, d2);
-        atomicAdd(dL_dtetpoints + 3 * vid[0] + r, -(d0 + d1 + d2));
+        atomicAdd(dL_dtetpoints + pitch * vid[3] + r, d0);
+        atomicAdd(dL_dtetpoints + pitch * vid[2] + r, d1);
+        atomicAdd(dL_dtetpoints + pitch * vid[1] + r, d2);
+        atomicAdd(dL_dtetpoints + pitch * vid[0] + r, -(d0 + d1 + d2));
     }
 }
 

@@ -23,7 +23,16 @@ import torch
 from d3ga_b200 import _lib
 
 
-USE_TET_ORDER = os.environ.get("D3GA_DEFORM_ORDERED", "1") != "0"
+# how the deformation backward sums the cage-vertex gradients: "ordered" = a tet's contributions summed inside the warp
+# before the atomics -- Gaussians walked in natural order when tetra_id is already sorted along the rows (coalesced
+# reads), else through the sort permutation; "padded" = natural order, one 16-byte vector reduction per (Gaussian,
+# vertex) into a padded [V,4] accumulator; "plain" = natural order, 12 scalar atomics per Gaussian.  DEFORM_PITCH4:
+# "ordered" also accumulates into the padded buffer (4 vector reductions per tet instead of 12 scalar atomics).
+# "auto" (measured at 1 M Gaussians / 100 k tets on B200, tools/deform_sweep.sh): rows in tet order -> "ordered" with the
+# padded buffer (61 us; 67 without the padding, 87 "padded", 226 "plain"); rows in any other order -> "padded" (83 us;
+# 107-120 "ordered" through the permutation, whose row reads are gathers; 169 "plain").
+DEFORM_BACKWARD = os.environ.get("D3GA_DEFORM_BACKWARD", "auto")
+DEFORM_PITCH4 = os.environ.get("D3GA_DEFORM_PITCH4", "0") == "1"
 
 
 def _check(t, name, dtype):
@@ -148,12 +157,17 @@ _order_cache: dict = {}
 
 
 def _tet_order(tetra_id):
+    """The int32 permutation that sorts tetra_id, or True when the rows already lie in tet order (no permutation needed:
+    the kernel reads them in natural order and still sums a tet's neighbours in the warp)."""
     key = (tetra_id.data_ptr(), tetra_id._version, int(tetra_id.shape[0]), tetra_id.device)
     order = _order_cache.get(key)
     if order is None:
         if len(_order_cache) > 16:
             _order_cache.clear()
-        order = torch.argsort(tetra_id, stable=True).to(torch.int32).contiguous()
+        if bool((tetra_id[1:] >= tetra_id[:-1]).all()):       # one read-back per constant buffer, before any capture
+            order = True
+        else:
+            order = torch.argsort(tetra_id, stable=True).to(torch.int32).contiguous()
         _order_cache[key] = order
     return order
 
@@ -211,17 +225,24 @@ class _DeformGaussians(torch.autograd.Function):
             g_means = torch.zeros((N, 3), dtype=f32, device=dev) if g_means is None else g_means.contiguous()
             g_cov = torch.zeros((N, 6), dtype=f32, device=dev) if g_cov is None else g_cov.contiguous()
             g_energy = None if (g_energy is None or dn_inv is None) else g_energy.contiguous()
-            g_tet = torch.zeros((V, 3), dtype=f32, device=dev) if need[0] else None
+            mode, pitch4 = DEFORM_BACKWARD, DEFORM_PITCH4
+            if mode == "auto":
+                mode, pitch4 = ("ordered", True) if (N > 0 and need[0] and _tet_order(tetra_id) is True) else ("padded", False)
+            pitch = 4 if (mode == "padded" or (mode == "ordered" and pitch4)) else 3
+            g_tet = torch.zeros((V, pitch), dtype=f32, device=dev) if need[0] else None
             g_bary = torch.empty((N, 4), dtype=f32, device=dev) if (need[3] or need[7]) else None
             g_scales = torch.empty((N, 3), dtype=f32, device=dev) if (need[5] or need[8]) else None
             g_rot = torch.empty((N, 4), dtype=f32, device=dev) if (need[6] or need[9]) else None
-            order = _tet_order(tetra_id) if (N > 0 and g_tet is not None and USE_TET_ORDER) else None
+            order = _tet_order(tetra_id) if (N > 0 and g_tet is not None and mode == "ordered") else None
+            rows_sorted, order = (1, None) if order is True else (0, order)
             _lib.check(lib.d3ga_deform_backward_fused(
                 N, V, T, tetpoints.data_ptr(), tets.data_ptr(), _lib.ptr(tetra_id), _lib.ptr(barys), _lib.ptr(delta_bary),
                 _lib.ptr(canonical_gradient), _lib.ptr(scales), _lib.ptr(delta_scale), int(ctx.log_scales),
                 _lib.ptr(rotation), _lib.ptr(delta_rot), _lib.ptr(dn_inv), _lib.ptr(g_means), _lib.ptr(g_cov),
                 _lib.ptr(g_energy) if g_tet is not None else None, _lib.ptr(g_tet), _lib.ptr(g_bary), _lib.ptr(g_scales),
-                _lib.ptr(g_rot), _lib.ptr(order), _lib.raw_stream(dev)), "deform_backward")
+                _lib.ptr(g_rot), _lib.ptr(order), rows_sorted, pitch, _lib.raw_stream(dev)), "deform_backward")
+            if g_tet is not None and pitch == 4:
+                g_tet = g_tet[:, :3]
         # a base tensor and its delta have the same gradient: one tensor serves both
         return (g_tet, None, None, g_bary if need[3] else None, None, g_scales if need[5] else None,
                 g_rot if need[6] else None, g_bary if need[7] else None, g_scales if need[8] else None,

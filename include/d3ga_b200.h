@@ -249,7 +249,12 @@ int d3ga_deform_backward_ordered(int N, int V, int T, const float *tetpoints, co
  * Backward: a base tensor and its delta have the same gradient, written ONCE (dL_dbarys = dL/dbarys = dL/ddelta_bary,
  * dL_dscales is the gradient of the PRE-activation scales when log_scales != 0, dL_drotation of the un-normalised sum);
  * dL_denergy [T] or null adds the energy's gradient into dL_dtetpoints (which the caller zeroes, as above).
- * `order` as in d3ga_deform_backward_ordered, or null. */
+ * `order` as in d3ga_deform_backward_ordered, or null.  rows_tet_sorted != 0 (with order == null) tells the kernel that
+ * tetra_id is non-decreasing along the rows as they lie in memory: the Gaussians are then read in natural order --
+ * coalesced -- and a tet's cage-vertex gradients are still summed inside the warp before the atomics.  It is a hint:
+ * results are right for any tetra_id, only the number of atomics depends on it.  dL_dtetpoints_pitch = floats per row of
+ * dL_dtetpoints: 3 (the tensor's own layout) or 4 (a padded [V,4] buffer, 16-byte aligned: a vertex's three components
+ * then go out as one vector reduction instead of three scalar atomics; the fourth float stays 0). */
 int d3ga_deform_forward_fused(int N, int V, int T, const float *tetpoints, const int64_t *tets, const int64_t *tetra_id,
                               const float *barys, const float *delta_bary, const float *canonical_gradient,
                               const float *scales, const float *delta_scale, int log_scales, const float *rotation,
@@ -261,7 +266,8 @@ int d3ga_deform_backward_fused(int N, int V, int T, const float *tetpoints, cons
                                int log_scales, const float *rotation, const float *delta_rot, const float *dn_inv,
                                const float *dL_dmeans3D, const float *dL_dcov3D, const float *dL_denergy,
                                float *dL_dtetpoints, float *dL_dbarys, float *dL_dscales, float *dL_drotation,
-                               const int32_t *order, d3ga_stream_t stream);
+                               const int32_t *order, int rows_tet_sorted, int dL_dtetpoints_pitch,
+                               d3ga_stream_t stream);
 
 /* ---- cage FEM energy ------------------------------------------------------------
  * Replaces CageBase.fem_energy (lib/cage.py:349-361, called at models/cage_net.py:225) and its autograd backward:

@@ -74,6 +74,43 @@ def test_fused_block_forward_backward_vs_oracle(cuda_lib, workload):
     assert torch.equal(gpu["barys"].grad, gpu["delta_bary"].grad) and torch.equal(gpu["scaling"].grad, gpu["delta_scale"].grad)
 
 
+@pytest.mark.parametrize("layout", ["as_built", "tet_sorted"])
+@pytest.mark.parametrize("mode,pitch4", [("auto", False), ("ordered", False), ("ordered", True), ("padded", False),
+                                         ("plain", False)])
+def test_backward_accumulation_modes_agree_with_oracle(cuda_lib, monkeypatch, layout, mode, pitch4):
+    """Every way the backward sums the cage-vertex gradients (warp-summed through the sort permutation, warp-summed in
+    natural order on tet-sorted rows, padded vector reductions, plain atomics), on rows in both layouts and with a
+    Gaussian count that is not a multiple of the warp (the row streams go through shared memory 32 rows at a time)."""
+    import d3ga_b200.tetra_sampler as ts
+    monkeypatch.setattr(ts, "DEFORM_BACKWARD", mode)
+    monkeypatch.setattr(ts, "DEFORM_PITCH4", pitch4)
+    sc = synth.make_workload("c2")
+    if layout == "tet_sorted":
+        sc = synth.sort_scene_by_tet(sc)
+    N = sc.N - 13
+    assert N % 32 != 0
+    rng = np.random.default_rng(5)
+    base = dict(tetpoints=sc.tetpoints, barys=sc.barys[:N], scaling=np.log(sc.scales[:N]), rotation=sc.rotation[:N])
+    cpu = {k: t(np.ascontiguousarray(v, dtype=np.float32)).clone().requires_grad_(True) for k, v in base.items()}
+    gpu = {k: v.detach().cuda().requires_grad_(True) for k, v in cpu.items()}
+    tets, tid, cg = t(sc.tets), t(np.ascontiguousarray(sc.tetra_id[:N])), t(np.ascontiguousarray(sc.canonical_gradient[:N]))
+    assert bool((tid[1:] >= tid[:-1]).all()) == (layout == "tet_sorted")
+    zeros4, zeros3 = torch.zeros(N, 4), torch.zeros(N, 3)
+    m_ref, c_ref = do.deform_block(cpu["tetpoints"], tets, tid, cpu["barys"], zeros4, cg, cpu["scaling"], zeros3,
+                                   cpu["rotation"], zeros4)
+    m, c = deform_gaussians(gpu["tetpoints"], tets.cuda(), tid.cuda(), gpu["barys"], cg.cuda(), gpu["scaling"],
+                            gpu["rotation"], log_scales=True)
+    assert np.allclose(m.detach().cpu().numpy(), m_ref.detach().numpy(), atol=2e-6)
+    assert util.rel_l2(c.detach().cpu().numpy(), c_ref.detach().numpy()) < 1e-5
+    wm = t(rng.normal(size=m_ref.shape).astype(np.float32))
+    wc = t((rng.normal(size=c_ref.shape) * 1e3).astype(np.float32))
+    ((m_ref * wm).sum() + (c_ref * wc).sum()).backward()
+    ((m * wm.cuda()).sum() + (c * wc.cuda()).sum()).backward()
+    for k in base:
+        assert gpu[k].grad.shape == cpu[k].grad.shape
+        assert util.rel_l2(gpu[k].grad.cpu().numpy(), cpu[k].grad.numpy()) < 1e-3, k
+
+
 def test_zero_quaternion_is_nan_like_the_reference(cuda_lib):
     """A zero quaternion: F.normalize (eps 1e-12, cage_net.py:215) leaves it zero, build_rotation then divides 0 by its
     zero norm (utils/general_utils.py:59-61) -> NaN covariance in the reference.  The kernel does the same (and only
