@@ -48,45 +48,6 @@ struct DeformExtra {
     int tet_sorted;                                      // rows are already in tet order: warp-summed like `order`
 };
 
-// The warp's 32 consecutive rows of K floats lie contiguous in memory: they are read as K coalesced requests of four
-// sectors each and every lane takes its row out of shared memory (stride K).  A scalar load of ONE column of a [N,K]
-// array touches up to 9 K sectors per request; ncu showed the forward's LSU queue full (lg_throttle 15 stalls per
-// issue, 27 M sector accesses for 120 MB).  All 32 lanes call (rows past the end read as 0 / are not stored).
-constexpr int STAGE_FLOATS = 32 * 9;
-// Two phases, so that a kernel can issue the global loads of ALL its streams before it waits for the first one.
-template <int K>
-__device__ __forceinline__ void warp_rows_fetch(const float *__restrict__ base, size_t row0, size_t rows, uint32_t lane,
-                                                float (&raw)[K]) {
-    const size_t first = row0 * K, limit = rows * K;
-#pragma unroll
-    for (int j = 0; j < K; j++) {
-        const size_t i = first + (size_t)(j * 32) + lane;
-        raw[j] = i < limit ? __ldg(base + i) : 0.f;
-    }
-}
-template <int K>
-__device__ __forceinline__ void warp_rows_take(float *s_w, uint32_t lane, const float (&raw)[K], float (&out)[K]) {
-#pragma unroll
-    for (int j = 0; j < K; j++) s_w[j * 32 + (int)lane] = raw[j];
-    __syncwarp();
-#pragma unroll
-    for (int j = 0; j < K; j++) out[j] = s_w[(int)lane * K + j];
-    __syncwarp();
-}
-template <int K>
-__device__ __forceinline__ void warp_rows_store(float *__restrict__ base, size_t row0, size_t rows, float *s_w,
-                                                uint32_t lane, const float (&in)[K]) {
-    const size_t first = row0 * K, limit = rows * K;
-#pragma unroll
-    for (int j = 0; j < K; j++) s_w[(int)lane * K + j] = in[j];
-    __syncwarp();
-#pragma unroll
-    for (int j = 0; j < K; j++) {
-        const size_t i = first + (size_t)(j * 32) + lane;
-        if (i < limit) base[i] = s_w[j * 32 + (int)lane];
-    }
-    __syncwarp();
-}
 // barys, scales (activated) and the un-normalised quaternion of Gaussian n as the kernels use them; `sraw` = the scale
 // row as it lies in memory (Delta already added), read by the caller
 __device__ __forceinline__ void load_gaussian(const DeformExtra &ex, const float *__restrict__ barys,

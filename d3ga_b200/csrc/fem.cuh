@@ -68,15 +68,25 @@ __device__ __forceinline__ void fem_backward_tet(int t, const float *__restrict_
 #pragma unroll
         for (int c = 0; c < 3; c++) dF[r][c] = g * ((J - 1.f) * C[r][c] + F[r][c]);
     // F = Ds Dn : dDs = dF Dn^T ; columns of Ds are (v3-v0, v2-v0, v1-v0)
+    float dv[4][3];
 #pragma unroll
     for (int r = 0; r < 3; r++) {
         const float d0 = dF[r][0] * Dn[0][0] + dF[r][1] * Dn[0][1] + dF[r][2] * Dn[0][2];
         const float d1 = dF[r][0] * Dn[1][0] + dF[r][1] * Dn[1][1] + dF[r][2] * Dn[1][2];
         const float d2 = dF[r][0] * Dn[2][0] + dF[r][1] * Dn[2][1] + dF[r][2] * Dn[2][2];
-        atomicAdd(dL_dtetpoints + pitch * vid[3] + r, d0);
-        atomicAdd(dL_dtetpoints + pitch * vid[2] + r, d1);
-        atomicAdd(dL_dtetpoints + pitch * vid[1] + r, d2);
-        atomicAdd(dL_dtetpoints + pitch * vid[0] + r, -(d0 + d1 + d2));
+        dv[3][r] = d0; dv[2][r] = d1; dv[1][r] = d2; dv[0][r] = -(d0 + d1 + d2);
+    }
+    if (pitch == 4) {   // padded accumulator: a vertex's three components as one 16-byte vector reduction
+#pragma unroll
+        for (int k = 0; k < 4; k++) red_add_v4(dL_dtetpoints + 4 * vid[k], dv[k][0], dv[k][1], dv[k][2], 0.f);
+    } else {
+#pragma unroll
+        for (int r = 0; r < 3; r++) {
+            atomicAdd(dL_dtetpoints + 3 * vid[3] + r, dv[3][r]);
+            atomicAdd(dL_dtetpoints + 3 * vid[2] + r, dv[2][r]);
+            atomicAdd(dL_dtetpoints + 3 * vid[1] + r, dv[1][r]);
+            atomicAdd(dL_dtetpoints + 3 * vid[0] + r, dv[0][r]);
+        }
     }
 }
 

@@ -143,7 +143,10 @@ __global__ void __launch_bounds__(COUNT_WARPS * 32) direct_count_kernel(const Di
 //     below the owner) -- owners that share a tile are ordered by queue position = by depth, whatever order the walks reach
 //     the tile in -- and the value and the (tile | depth) key go straight into their final slots; (C) the highest owner of
 //     mask[t] advances pos[t] by popc(mask[t]) and clears the mask.
-constexpr int SC_WARPS = 4, BLK_SHIFT = 2, BLK_ROWS = 1 << BLK_SHIFT;
+#ifndef DIRECT_BLK_SHIFT
+#define DIRECT_BLK_SHIFT 0
+#endif
+constexpr int SC_WARPS = 4, BLK_SHIFT = DIRECT_BLK_SHIFT, BLK_ROWS = 1 << BLK_SHIFT;
 constexpr int QUEUE = 64, STRIP_CAP = 32 * BLK_ROWS, STRIP_ROUNDS = STRIP_CAP / 32;
 
 struct ScatterWarp {
@@ -209,10 +212,25 @@ __device__ DIRECT_INLINE void scatter_batch(const DirectParams &p, ScatterWarp &
     __syncwarp();
 }
 
+#ifdef D3GA_SCATTER_TRACE
+// development trace: per (row, warp) start ns, set-up done ns, end ns, SM id | batches << 32
+__device__ unsigned long long g_sc_trace[8192 * SC_WARPS * 4];
+__device__ __forceinline__ unsigned long long sc_global_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+#endif
+
 __global__ void __launch_bounds__(SC_WARPS * 32) direct_scatter_kernel(const DirectParams p, int gy, int band_rows) {
     extern __shared__ __align__(16) uint8_t smem[];
     __shared__ ScatterWarp s_warp[SC_WARPS];
     const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, row = blockIdx.x;
+#ifdef D3GA_SCATTER_TRACE
+    const unsigned long long tr_t0 = sc_global_ns();
+    unsigned long long tr_t1 = 0;
+    uint32_t tr_batches = 0;
+#endif
     if (p.hdr->overflow) return;
     // this CTA's band of tile rows [yb0, yb1) (the whole image when it fits the shared memory budget); tiles, tile rows
     // and blocks below are relative to the band
@@ -233,6 +251,9 @@ __global__ void __launch_bounds__(SC_WARPS * 32) direct_scatter_kernel(const Dir
         }
     }
     __syncthreads();
+#ifdef D3GA_SCATTER_TRACE
+    tr_t1 = sc_global_ns();
+#endif
     if (warp << BLK_SHIFT >= yb1 - yb0) return;   // fewer blocks of tile rows than warps
     ScatterWarp &sw = s_warp[warp];
     const uint32_t slot0 = row * p.chunk, nb = p.chunk / 32, below = (1u << lane) - 1u;
@@ -296,8 +317,29 @@ __global__ void __launch_bounds__(SC_WARPS * 32) direct_scatter_kernel(const Dir
         scatter_batch(p, sw, pm, qh, n, lane);
         qh += n;
         qn -= n;
+#ifdef D3GA_SCATTER_TRACE
+        tr_batches++;
+#endif
     }
+#ifdef D3GA_SCATTER_TRACE
+    if (lane == 0 && row < 8192 && blockIdx.y == 0) {
+        uint32_t smid;
+        asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+        unsigned long long *o = g_sc_trace + 4 * ((size_t)row * SC_WARPS + warp);
+        o[0] = tr_t0; o[1] = tr_t1; o[2] = sc_global_ns(); o[3] = ((unsigned long long)tr_batches << 32) | smid;
+    }
+#endif
 }
+
+#ifdef D3GA_SCATTER_TRACE
+}  // namespace
+}  // namespace d3ga
+extern "C" int d3ga_debug_scatter_trace(unsigned long long *out, int rows) {
+    return cudaMemcpyFromSymbol(out, d3ga::g_sc_trace, sizeof(unsigned long long) * 4 * d3ga::SC_WARPS * (size_t)rows) == cudaSuccess ? 0 : -2;
+}
+namespace d3ga {
+namespace {
+#endif
 
 // Column sums of M over segments of rows (two tiles per thread: M's 16-bit counts are read as pairs); the last CTA of a
 // column block then scans its columns over the segments (exclusive, in place) and writes the per-tile totals.
