@@ -298,7 +298,7 @@ def run_ours(args):
     N, P, Tl = scene.N, scene.W * scene.H, ((scene.W + 15) // 16) * ((scene.H + 15) // 16)
     bytes_per_launch = {
         "deform_forward_kernel": 120 * N, "geometry_kernel": 84 * N + 12 * D, "sort_histogram_kernel": 8 * D,
-        "preprocess_kernel": 96 * N, "emit_sorted_kernel": 20 * N + 12 * D, "depth_histogram_kernel": 4 * N,
+        "preprocess_kernel": 96 * N, "emit_sorted_kernel": 20 * N + 12 * D, "depth_plan_kernel": 0,
         "depth_sort_pass_kernel": 16 * N,
         "sort_pass_kernel": 24 * D, "tile_ranges_kernel": 8 * D + 8 * Tl, "blend_forward_kernel": 40 * D + 20 * P,
         "blend_backward_kernel": 80 * D + 20 * P, "preprocess_backward_kernel": 104 * N,

@@ -28,7 +28,7 @@ static std::vector<ProfRec> g_prof_recs;
 static const char *const g_kernel_names[K_COUNT] = {
     "geometry_kernel", "sort_histogram_kernel", "sort_pass_kernel", "tile_ranges_kernel", "blend_forward_kernel",
     "blend_backward_kernel", "preprocess_backward_kernel", "deform_forward_kernel", "deform_backward_kernel",
-    "compute_bary_kernel", "preprocess_kernel", "emit_sorted_kernel", "depth_histogram_kernel",
+    "compute_bary_kernel", "preprocess_kernel", "emit_sorted_kernel", "depth_plan_kernel",
     "depth_sort_pass_kernel", "fem_energy_forward_kernel", "fem_energy_backward_kernel",
     "ssim_forward_kernel", "ssim_backward_kernel", "lbs_skeleton_kernel", "lbs_skin_forward_kernel",
     "lbs_skin_backward_kernel", "lbs_unskin_kernel", "lbs_skin_dense_forward_kernel", "lbs_skin_dense_backward_kernel",

@@ -33,30 +33,6 @@ __device__ __forceinline__ uint32_t st_value(uint32_t s) { return (s & ST_INC) ?
 constexpr int HIST_THREADS = 256;
 constexpr int HIST_ITEMS = 8;
 
-// exclusive scan of one value per thread over the FIRST 256 threads of a CTA (every thread of the CTA must call it:
-// it contains barriers); s_tmp needs 8 words
-__device__ __forceinline__ uint32_t block_excl_scan_256(uint32_t v, uint32_t *s_tmp, uint32_t *total) {
-    const uint32_t lane = lane_id(), warp = threadIdx.x >> 5;
-    uint32_t incl = v;
-#pragma unroll
-    for (int d = 1; d < 32; d <<= 1) {
-        uint32_t n = __shfl_up_sync(0xffffffffu, incl, d);
-        if (lane >= (uint32_t)d) incl += n;
-    }
-    __syncthreads();   // s_tmp may still be in use by a previous call
-    if (lane == 31 && warp < 8) s_tmp[warp] = incl;
-    __syncthreads();
-    uint32_t off = 0, tot = 0;
-#pragma unroll
-    for (int w = 0; w < 8; w++) {
-        uint32_t x = s_tmp[w];
-        if (w < (int)warp) off += x;
-        tot += x;
-    }
-    if (total) *total = tot;
-    return off + incl - v;
-}
-
 __global__ void __launch_bounds__(HIST_THREADS) sort_histogram_kernel(RasterHeader *hdr, const uint64_t *keys,
                                                                       uint32_t *ghist, uint32_t *bins, int sort_bits,
                                                                       int num_passes, int first_pass) {
@@ -142,6 +118,9 @@ __global__ void __launch_bounds__(HIST_THREADS) sort_histogram_kernel(RasterHead
     }
 }
 
+#ifndef LOOKBACK_WIDTH
+#define LOOKBACK_WIDTH 8   // predecessors read per round trip of the look-back
+#endif
 constexpr int SORT_WARPS = SORT_THREADS / 32;
 template <typename KeyT>
 constexpr int sort_smem_bytes() {
@@ -242,13 +221,13 @@ __global__ void __launch_bounds__(SORT_THREADS) sort_pass_kernel(RasterHeader *h
             int p = (int)tile - 1;
             bool resolved = false;
             while (!resolved) {
-                uint32_t sv[8];
+                uint32_t sv[LOOKBACK_WIDTH];
 #pragma unroll
-                for (int u = 0; u < 8; u++)
+                for (int u = 0; u < LOOKBACK_WIDTH; u++)
                     sv[u] = p - u >= 0 ? ld_volatile_u32(state + d - (size_t)256 * (tile - (uint32_t)(p - u))) : ST_INC;
                 int used = 0;
 #pragma unroll
-                for (int u = 0; u < 8; u++) {
+                for (int u = 0; u < LOOKBACK_WIDTH; u++) {
                     if (resolved || used != u) continue;       // stop at the first inclusive word or unready word
                     if (!st_ready(sv[u])) continue;             // not published yet: retry from here
                     excl += st_value(sv[u]);
@@ -285,66 +264,6 @@ __global__ void __launch_bounds__(SORT_THREADS) sort_pass_kernel(RasterHeader *h
         kout[dst] = k;
         vout[dst] = s_vals[i];
     }
-}
-
-// Digit counts of the Gaussians' 32-bit depth keys (depth-first binning) and the plan of that sort.  Culled Gaussians
-// carry the key 0xffffffff: they are counted (they move in every executed pass) but do not stop a pass from being
-// skipped -- a pass in which every VISIBLE key has the same digit is the identity for the visible keys.
-__global__ void __launch_bounds__(HIST_THREADS) depth_histogram_kernel(RasterHeader *hdr, const uint32_t *keys,
-                                                                       uint32_t n, uint32_t *ghist, uint32_t *bins) {
-    __shared__ uint32_t s_hist[4][256];
-    __shared__ uint32_t s_tmp[8];
-    __shared__ uint32_t s_culled, s_flag;
-    const int tid = threadIdx.x;
-    for (int p = 0; p < 4; p++) s_hist[p][tid] = 0;
-    if (tid == 0) s_culled = 0;
-    __syncthreads();
-    uint32_t culled = 0;
-    // eight loads in flight per thread: with one, every trip of the loop waited a DRAM round trip (ncu: 30 long-scoreboard
-    // stalls per issue, 15.6 us for 4 MB)
-    const uint32_t stride = gridDim.x * HIST_THREADS;
-    for (uint32_t i0 = blockIdx.x * HIST_THREADS + tid; i0 < n; i0 += 8 * stride) {
-        uint32_t k[8];
-#pragma unroll
-        for (int u = 0; u < 8; u++) k[u] = i0 + u * stride < n ? __ldcs(keys + i0 + u * stride) : 0u;
-#pragma unroll
-        for (int u = 0; u < 8; u++) {
-            if (i0 + u * stride >= n) continue;
-            culled += k[u] == 0xffffffffu;
-#pragma unroll
-            for (int p = 0; p < 4; p++) atomicAdd(&s_hist[p][(k[u] >> (8 * p)) & 255u], 1u);
-        }
-    }
-    culled = __reduce_add_sync(0xffffffffu, culled);
-    if ((tid & 31) == 0 && culled) atomicAdd(&s_culled, culled);
-    __syncthreads();
-    for (int p = 0; p < 4; p++) {
-        const uint32_t c = s_hist[p][tid];
-        if (c) atomicAdd(&ghist[p * 256 + tid], c);
-    }
-    if (tid == 0 && s_culled) atomicAdd(&hdr->dep_culled, s_culled);
-    __threadfence();
-    __syncthreads();
-    if (tid == 0) s_flag = atomicAdd(&hdr->dep_hist_done, 1u) == gridDim.x - 1;
-    __syncthreads();
-    if (!s_flag) return;
-    __threadfence();
-    const uint32_t n_culled = *((volatile uint32_t *)&hdr->dep_culled);
-    const uint32_t n_visible = n - n_culled;
-    uint32_t src = 0;
-    for (int p = 0; p < 4; p++) {
-        const uint32_t c = __ldcg(ghist + p * 256 + tid);
-        const uint32_t cv = c - (tid == 255 ? n_culled : 0u);
-        const int all_in_one = __syncthreads_or(n_visible == 0 || cv == n_visible);
-        const uint32_t ex = block_excl_scan_256(c, s_tmp, nullptr);
-        bins[p * 256 + tid] = ex;
-        if (tid == 0) {
-            hdr->dep_skip[p] = all_in_one ? 1u : 0u;
-            hdr->dep_src[p] = src;
-        }
-        if (!all_in_one) src ^= 1u;
-    }
-    if (tid == 0) hdr->dep_final_sel = src;
 }
 
 // Depth-first binning: ranges, tile-digit histograms, pass plan and the forward's tile order from the rects' 2-D difference
@@ -554,7 +473,6 @@ int launch_depth_sort(int P, uint8_t *geom, const GeomLayout &GL, cudaStream_t s
     RasterHeader *hdr = reinterpret_cast<RasterHeader *>(geom + GL.header);
     uint32_t *dkeys = reinterpret_cast<uint32_t *>(geom + GL.dkeys);
     uint32_t *dvals = reinterpret_cast<uint32_t *>(geom + GL.dvals);
-    uint32_t *ghist = reinterpret_cast<uint32_t *>(geom + GL.dep_hist);
     uint32_t *bins = reinterpret_cast<uint32_t *>(geom + GL.dep_bins);
     uint32_t *state = reinterpret_cast<uint32_t *>(geom + GL.dep_state);
     const uint32_t tiles = (uint32_t)((P + SORT_TILE - 1) / SORT_TILE);
@@ -562,19 +480,8 @@ int launch_depth_sort(int P, uint8_t *geom, const GeomLayout &GL, cudaStream_t s
         const int arc = set_sort_attrs();
         if (arc) return arc;
     }
-    D3GA_CUDA(cudaMemsetAsync(ghist, 0, 4 * 256 * 4, stream));
+    // (digit counts, bin offsets and the pass plan were left by preprocess_kernel)
     D3GA_CUDA(cudaMemsetAsync(state, 0, 4ull * 256 * 4 * (tiles + 1), stream));
-    int grid = (P + HIST_THREADS * 4 - 1) / (HIST_THREADS * 4);
-#ifndef DEPTH_HIST_PER_SM
-#define DEPTH_HIST_PER_SM 2   // measured at 1 M keys: 1 -> 16.7, 2 -> 14.6, 4 -> 15.3, 8 -> 18.5 us
-#endif
-    if (grid > 148 * DEPTH_HIST_PER_SM) grid = 148 * DEPTH_HIST_PER_SM;
-    if (grid < 1) grid = 1;
-    {
-        ProfScope prof(K_DEPTH_HIST, stream);
-        depth_histogram_kernel<<<grid, HIST_THREADS, 0, stream>>>(hdr, dkeys, (uint32_t)P, ghist, bins);
-    }
-    D3GA_LAUNCH_CHECK();
     for (int p = 0; p < 4; p++) {
         {
             ProfScope prof(K_DEPTH_PASS, stream);
