@@ -114,6 +114,8 @@ __device__ unsigned long long g_blend_stats[8];
 #ifdef D3GA_BLEND_TRACE
 // development trace of the forward: per (launch slot, warp) start ns, end ns, list entries walked, survivors blended
 __device__ unsigned long long g_fwd_trace[65536 * 8 * 4];
+// same for the backward: start ns, end ns, tile << 32 | list entries walked, survivors
+__device__ unsigned long long g_bwd_trace[65536 * 8 * 4];
 __device__ __forceinline__ unsigned long long global_ns() {
     unsigned long long t;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
@@ -491,6 +493,10 @@ __global__ void __launch_bounds__(TILE_PIX, BWD_MIN_CTAS) blend_backward_kernel(
     const uint32_t lane = tid & 31, warp = tid >> 5;
     BwdWarpSmem &sm = reinterpret_cast<BwdWarpSmem *>(s_raw)[warp];
 
+#ifdef D3GA_BLEND_TRACE
+    const unsigned long long tr_t0 = global_ns();
+    uint32_t tr_surv = 0;
+#endif
     const uint32_t tile = order_bwd[blockIdx.x];   // deepest contributor first
     const WarpBlock wb = warp_block(tid, (int)(tile % (uint32_t)grid_x), (int)(tile / (uint32_t)grid_x));
     const int px = wb.px, py = wb.py;
@@ -634,6 +640,9 @@ __global__ void __launch_bounds__(TILE_PIX, BWD_MIN_CTAS) blend_backward_kernel(
         }
         cp_async_commit();
         tail += __popc(m);
+#ifdef D3GA_BLEND_TRACE
+        tr_surv += __popc(m);
+#endif
         if (lane == 0) { STAT_ADD(4, 1); STAT_ADD(5, __popc(m)); }
     }
     cp_async_wait_all();
@@ -643,6 +652,12 @@ __global__ void __launch_bounds__(TILE_PIX, BWD_MIN_CTAS) blend_backward_kernel(
         __syncwarp();
         backward_turn_around<INVDEPTH>(sm, nb, lane, wb.x0, wb.y0, grad_acc);
     }
+#ifdef D3GA_BLEND_TRACE
+    if (lane == 0 && blockIdx.x < 65536) {
+        unsigned long long *o = g_bwd_trace + 4 * ((size_t)blockIdx.x * 8 + warp);
+        o[0] = tr_t0; o[1] = global_ns(); o[2] = ((unsigned long long)tile << 32) | n_proc; o[3] = tr_surv;
+    }
+#endif
 }
 
 // This render's colours, [N,3] as the API hands them (or the SH colours of the preprocess), as one aligned float4 per
@@ -656,6 +671,9 @@ __global__ void __launch_bounds__(256) pack_features_kernel(int P, const float *
 }  // namespace
 
 #ifdef D3GA_BLEND_TRACE
+extern "C" int d3ga_debug_bwd_trace(unsigned long long *out, int ctas) {
+    return cudaMemcpyFromSymbol(out, g_bwd_trace, sizeof(unsigned long long) * 32 * (size_t)ctas) == cudaSuccess ? 0 : -2;
+}
 extern "C" int d3ga_debug_fwd_trace(unsigned long long *out, int ctas) {
     return cudaMemcpyFromSymbol(out, g_fwd_trace, sizeof(unsigned long long) * 32 * (size_t)ctas) == cudaSuccess ? 0 : -2;
 }

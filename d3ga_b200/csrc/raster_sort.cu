@@ -129,6 +129,19 @@ constexpr int sort_smem_bytes() {
 
 // PLAN 0: the (tile|depth) duplicate list, count and plan from the header (num_rendered, pass_*).
 // PLAN 1: the 32-bit depth keys of the Gaussians (depth-first binning), count = n_fixed, plan in dep_*.
+#ifdef D3GA_SORT_TRACE
+// development trace of the depth-sort passes: per (pass, tile) ns at start / keys loaded / ranked / look-back done / end
+__device__ unsigned long long g_sort_trace[4 * 512 * 8];
+__device__ __forceinline__ unsigned long long sort_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+#define SORT_TRACE_MARK(i) if (PLAN == 1 && threadIdx.x == 0 && tr_tile < 512) g_sort_trace[((size_t)pass * 512 + tr_tile) * 8 + (i)] = sort_ns();
+#else
+#define SORT_TRACE_MARK(i)
+#endif
+
 template <typename KeyT, int PLAN>
 __global__ void __launch_bounds__(SORT_THREADS) sort_pass_kernel(RasterHeader *hdr, KeyT *keys0, KeyT *keys1,
                                                                  uint32_t *vals0, uint32_t *vals1,
@@ -143,6 +156,10 @@ __global__ void __launch_bounds__(SORT_THREADS) sort_pass_kernel(RasterHeader *h
     uint32_t *s_gbase = s_start + 256;              // [256] global slot of s_start[d] minus s_start[d]
     uint32_t *s_misc = s_gbase + 256;               // [0..7] scan scratch, [8] tile id
 
+#ifdef D3GA_SORT_TRACE
+    uint32_t tr_tile = blockIdx.x;
+    SORT_TRACE_MARK(0)
+#endif
     if (PLAN == 0 ? (hdr->overflow || hdr->pass_skip[pass]) : hdr->dep_skip[pass]) return;
     const uint32_t D = PLAN == 0 ? hdr->num_rendered : n_fixed;
     uint32_t *ticket = PLAN == 0 ? &hdr->pass_ticket[pass] : &hdr->dep_ticket[pass];
@@ -154,6 +171,10 @@ __global__ void __launch_bounds__(SORT_THREADS) sort_pass_kernel(RasterHeader *h
     const uint32_t tile = s_misc[8];
     const uint64_t tile_base = (uint64_t)tile * SORT_TILE;
     if (tile_base >= D) return;
+#ifdef D3GA_SORT_TRACE
+    tr_tile = tile;
+    SORT_TRACE_MARK(1)
+#endif
     const uint32_t n_valid = (uint32_t)min((uint64_t)SORT_TILE, (uint64_t)D - tile_base);
     const KeyT *kin = src ? keys1 : keys0;
     const uint32_t *vin = src ? vals1 : vals0;
@@ -177,6 +198,7 @@ __global__ void __launch_bounds__(SORT_THREADS) sort_pass_kernel(RasterHeader *h
         val[r] = ok ? __ldcs(vin + tile_base + local) : 0u;
     }
     __syncwarp();
+    SORT_TRACE_MARK(2)
     uint32_t rank[SORT_ITEMS];   // holds the peer mask between the two phases
     // phase 1: digit groups per round (independent across rounds: the match latencies overlap)
 #pragma unroll
@@ -198,6 +220,7 @@ __global__ void __launch_bounds__(SORT_THREADS) sort_pass_kernel(RasterHeader *h
         rank[r] = pre + __popc(peers & lanemask_lt());
     }
     __syncthreads();
+    SORT_TRACE_MARK(3)
 
     // thread d (< 256): exclusive prefix of digit d over the warps, tile total, look-back for the global offset
     const uint32_t d = tid;
@@ -239,6 +262,7 @@ __global__ void __launch_bounds__(SORT_THREADS) sort_pass_kernel(RasterHeader *h
             st_volatile_u32(state + d, ST_INC | (excl + count));
         }
     }
+    SORT_TRACE_MARK(4)
     const uint32_t start = block_excl_scan_256(total, s_misc, nullptr);
     if (tid < 256) {
         s_start[d] = start;
@@ -256,6 +280,7 @@ __global__ void __launch_bounds__(SORT_THREADS) sort_pass_kernel(RasterHeader *h
         s_vals[pos] = val[r];
     }
     __syncthreads();
+    SORT_TRACE_MARK(5)
     // runs of equal digits go to consecutive global slots
     for (uint32_t i = tid; i < n_valid; i += SORT_THREADS) {
         const KeyT k = s_keys[i];
@@ -264,6 +289,7 @@ __global__ void __launch_bounds__(SORT_THREADS) sort_pass_kernel(RasterHeader *h
         kout[dst] = k;
         vout[dst] = s_vals[i];
     }
+    SORT_TRACE_MARK(6)
 }
 
 // Depth-first binning: ranges, tile-digit histograms, pass plan and the forward's tile order from the rects' 2-D difference
@@ -494,3 +520,9 @@ int launch_depth_sort(int P, uint8_t *geom, const GeomLayout &GL, cudaStream_t s
 }
 
 }  // namespace d3ga
+
+#ifdef D3GA_SORT_TRACE
+extern "C" int d3ga_debug_sort_trace(unsigned long long *out) {
+    return cudaMemcpyFromSymbol(out, d3ga::g_sort_trace, sizeof(unsigned long long) * 4 * 512 * 8) == cudaSuccess ? 0 : -2;
+}
+#endif

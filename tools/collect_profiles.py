@@ -8,7 +8,8 @@ import sys
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 os.chdir(ROOT)
-for rep, out in (("gpurun_out/r2_blend.ncu-rep", "profiles/r2_ncu_full_blend.csv"), ("gpurun_out/r2_small.ncu-rep", "profiles/r2_ncu_full_small.csv")):
+for rep, out in (("gpurun_out/r2_blend.ncu-rep", "profiles/r2_ncu_full_blend.csv"), ("gpurun_out/r2_small.ncu-rep", "profiles/r2_ncu_full_small.csv"),
+                 ("gpurun_out/r2_deform.ncu-rep", "profiles/r2_ncu_full_deform.csv")):
     with open(out, "w") as f:
         subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], stdout=f, stderr=subprocess.DEVNULL, check=True)
 for a, b in (("r2_bench_metric.json", "r2_bench_metric.json"), ("r2_bench_reference.json", "r2_bench_metric_reference_arm.json"),

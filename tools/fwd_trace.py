@@ -25,7 +25,7 @@ buf = np.zeros((n, 8, 4), np.uint64)
 lib = _lib.load()
 assert lib.d3ga_debug_fwd_trace(buf.ctypes.data_as(C.c_void_p), n) == 0
 t0 = buf[..., 0].astype(np.int64); t1 = buf[..., 1].astype(np.int64)
-live = t1 > 0
+live = (t1 > 0) & (t0 > t0.max() - 2_000_000)   # the last launch only
 start = t0[live].min()
 dur = (t1 - t0) / 1e3
 end = (t1 - start) / 1e3

@@ -14,4 +14,6 @@ timeout 900 ncu --set full --import-source on --clock-control none -k regex:"ble
     python tools/one_view.py metric 3 20 > gpurun_out/r2_ncu_blend.log 2>&1
 timeout 900 ncu --set full --clock-control none -k regex:"preprocess|depth_|direct_|sort_pass" --launch-skip 24 -c 12 -o gpurun_out/r2_small \
     python tools/one_view.py metric 3 20 > gpurun_out/r2_ncu_small.log 2>&1
+timeout 600 ncu --set full --import-source on --clock-control none -k regex:"deform_" --launch-skip 4 -c 2 -o gpurun_out/r2_deform \
+    python tools/deform_probe.py metric sorted full > gpurun_out/r2_ncu_deform.log 2>&1
 ls -la gpurun_out/ | tail -20
