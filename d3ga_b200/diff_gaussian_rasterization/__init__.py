@@ -343,7 +343,9 @@ def rasterize_forward(means3D, sh, colors_precomp, opacities, scales, rotations,
 
 
 def rasterize_backward(st, grad_color, grad_invdepth, means3D, sh, colors_precomp, opacities, scales, rotations,
-                       cov3Ds_precomp, radii, rs):
+                       cov3Ds_precomp, radii, rs, want_means2D=True):
+    """`want_means2D=False` skips the screen-space gradient (12 B per Gaussian nobody reads when means2D does not require
+    grad; the reference's own call site retains it: renderer.py:122-126)."""
     lib = _lib.load()
     dev = means3D.device
     P, W, H = st.P, st.W, st.H
@@ -354,7 +356,7 @@ def rasterize_backward(st, grad_color, grad_invdepth, means3D, sh, colors_precom
         grad_invdepth = _f32c(grad_invdepth, "grad_invdepth")
         scratch = torch.empty(int(lib.d3ga_raster_backward_scratch_bytes(P)), dtype=torch.uint8, device=dev)
         g_means3D = torch.empty((P, 3), dtype=torch.float32, device=dev)
-        g_means2D = torch.empty((P, 3), dtype=torch.float32, device=dev)
+        g_means2D = torch.empty((P, 3), dtype=torch.float32, device=dev) if want_means2D else None
         g_opacity = torch.empty((P, 1), dtype=torch.float32, device=dev)
         g_colors = torch.empty((P, 3), dtype=torch.float32, device=dev) if colors_precomp is not None else None
         g_sh = torch.empty((P, M, 3), dtype=torch.float32, device=dev) if sh is not None else None
@@ -368,7 +370,7 @@ def rasterize_backward(st, grad_color, grad_invdepth, means3D, sh, colors_precom
             _f32c(rs.projmatrix, "projmatrix").data_ptr(), _f32c(rs.campos, "campos").data_ptr(), float(rs.tanfovx),
             float(rs.tanfovy), int(bool(rs.antialiasing)), _lib.ptr(radii), st.geom.data_ptr(), st.binning.data_ptr(),
             st.capacity, st.image.data_ptr(), grad_color.data_ptr(), _lib.ptr(grad_invdepth), scratch.data_ptr(),
-            g_means2D.data_ptr(), g_opacity.data_ptr(), _lib.ptr(g_colors), g_means3D.data_ptr(), _lib.ptr(g_cov),
+            _lib.ptr(g_means2D), g_opacity.data_ptr(), _lib.ptr(g_colors), g_means3D.data_ptr(), _lib.ptr(g_cov),
             _lib.ptr(g_sh), _lib.ptr(g_scales), _lib.ptr(g_rot), stream), "raster_backward")
     return g_means3D, g_means2D, g_sh, g_colors, g_opacity, g_scales, g_rot, g_cov
 
@@ -400,7 +402,7 @@ class _RasterizeGaussians(torch.autograd.Function):
         if grad_color is None:
             grad_color = torch.zeros((3, st.H, st.W), dtype=torch.float32, device=means3D.device)
         g = rasterize_backward(st, grad_color, grad_invdepth, means3D, sh, colors_precomp, opacities, scales,
-                               rotations, cov3Ds_precomp, radii, rs)
+                               rotations, cov3Ds_precomp, radii, rs, want_means2D=ctx.needs_input_grad[1])
         g_means3D, g_means2D, g_sh, g_colors, g_opacity, g_scales, g_rot, g_cov = g
         if opacities is not None and g_opacity.shape != opacities.shape:
             g_opacity = g_opacity.reshape(opacities.shape)

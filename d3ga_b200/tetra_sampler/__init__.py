@@ -162,6 +162,8 @@ def _tet_order(tetra_id):
     key = (tetra_id.data_ptr(), tetra_id._version, int(tetra_id.shape[0]), tetra_id.device)
     order = _order_cache.get(key)
     if order is None:
+        if tetra_id.is_cuda and torch.cuda.is_current_stream_capturing():
+            return None                                        # a read-back cannot sit in a capture: the caller falls back
         if len(_order_cache) > 16:
             _order_cache.clear()
         if bool((tetra_id[1:] >= tetra_id[:-1]).all()):       # one read-back per constant buffer, before any capture
@@ -228,6 +230,8 @@ class _DeformGaussians(torch.autograd.Function):
             mode, pitch4 = DEFORM_BACKWARD, DEFORM_PITCH4
             if mode == "auto":
                 mode, pitch4 = ("ordered", True) if (N > 0 and need[0] and _tet_order(tetra_id) is True) else ("padded", False)
+            elif mode == "ordered" and N > 0 and need[0] and _tet_order(tetra_id) is None:
+                mode = "padded"    # first sight of this tetra_id inside a graph capture: no read-back, no permutation
             pitch = 4 if (mode == "padded" or (mode == "ordered" and pitch4)) else 3
             g_tet = torch.zeros((V, pitch), dtype=f32, device=dev) if need[0] else None
             g_bary = torch.empty((N, 4), dtype=f32, device=dev) if (need[3] or need[7]) else None

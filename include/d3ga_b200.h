@@ -138,7 +138,7 @@ int d3ga_raster_forward_blend(int P, int W, int H, const float *background, cons
 
 /* Backward = blend backward (R7) + preprocess backward (R8).
  * Inputs are the forward's inputs and workspaces plus dL_dout_color [3,H,W] (and optionally dL_dout_invdepth
- * [H,W]).  Outputs (written, not accumulated): dL_dmeans3D [P,3], dL_dmeans2D [P,3], dL_dopacity [P],
+ * [H,W]).  Outputs (written, not accumulated): dL_dmeans3D [P,3], dL_dmeans2D [P,3] (may be null: not wanted), dL_dopacity [P],
  * dL_dcolors [P,3] (when colors_precomp was given) or dL_dsh [P,sh_coeffs,3], dL_dcov3D [P,6] (when
  * cov3D_precomp was given) or dL_dscales [P,3] + dL_drotations [P,4].
  * grad_scratch: d3ga_raster_backward_scratch_bytes(P) bytes, contents undefined on entry. */
