@@ -380,8 +380,10 @@ __device__ PREPROCESS_ENTRY_ATTR uint32_t preprocess_block_entry(const GeoParams
                                                                   const float *s_proj, const float *s_cam) {
     uint32_t count, rect, width, dbits;
     preprocess_one(p, idx, s_view, s_proj, s_cam, count, rect, width, dbits);
-    p.rect_pack[idx] = make_uint2(rect, width);
+    // the rect goes where the binning path that follows reads it: the direct tile scatter's 16-byte record, or the
+    // (rect, width) pair of the depth-first emission and its rect grid
     if (p.grec) p.grec[idx] = make_uint4(rect, count ? (width | ((count / width) << 16)) : 0u, (uint32_t)idx, dbits);
+    else p.rect_pack[idx] = make_uint2(rect, width);
     const uint32_t key = count ? dbits : 0xffffffffu;   // (a live Gaussian's depth is > 0.2: never all ones)
     p.dkeys[idx] = key;
     p.dvals[idx] = (uint32_t)idx;
