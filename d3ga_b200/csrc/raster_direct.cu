@@ -146,7 +146,10 @@ __global__ void __launch_bounds__(COUNT_WARPS * 32) direct_count_kernel(const Di
 #ifndef DIRECT_BLK_SHIFT
 #define DIRECT_BLK_SHIFT 0
 #endif
-constexpr int SC_WARPS = 4, BLK_SHIFT = DIRECT_BLK_SHIFT, BLK_ROWS = 1 << BLK_SHIFT;
+#ifndef DIRECT_SC_WARPS
+#define DIRECT_SC_WARPS 4
+#endif
+constexpr int SC_WARPS = DIRECT_SC_WARPS, BLK_SHIFT = DIRECT_BLK_SHIFT, BLK_ROWS = 1 << BLK_SHIFT;
 constexpr int QUEUE = 64, STRIP_CAP = 32 * BLK_ROWS, STRIP_ROUNDS = STRIP_CAP / 32;
 
 struct ScatterWarp {
