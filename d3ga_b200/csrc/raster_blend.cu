@@ -75,6 +75,33 @@ __device__ __forceinline__ void cp_async_16_l2(void *smem_dst, const void *gmem_
 #define bwd_cp_async_16 cp_async_16_l2
 #endif
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+#ifdef FWD_BULK_STAGE
+// The measured bulk-copy variant of the forward's staging (-DFWD_BULK_STAGE): the copies go
+// through the bulk asynchronous copy unit (cp.async.bulk, the 1-D form of TMA) and complete on an mbarrier per stage
+// instead of through LDGSTS and commit groups.  Local memory only: source and destination are this GPU's.
+__device__ __forceinline__ void bulk_copy(void *smem_dst, const void *gmem_src, uint32_t bytes, unsigned long long *bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     (uint32_t)__cvta_generic_to_shared(smem_dst)),
+                 "l"(gmem_src), "r"(bytes), "r"((uint32_t)__cvta_generic_to_shared(bar))
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_init(unsigned long long *bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"((uint32_t)__cvta_generic_to_shared(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long *bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"((uint32_t)__cvta_generic_to_shared(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long *bar, uint32_t parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_LOOP:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@!p bra WAIT_LOOP;\n"
+        "}\n" ::"r"((uint32_t)__cvta_generic_to_shared(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+#endif
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 
 // Each warp owns an 8x4 pixel block of the 16x16 tile (compact blocks cull better than 16x2 strips).
@@ -175,7 +202,13 @@ __device__ __noinline__ bool exact_cut(const float2 *__restrict__ xy, const floa
 struct FwdWarpSmem {
     float4 ring[RING][3];                 // staged survivors: [0] x, y, list position + 1 (bits), -   [1] conic, opacity
                                           //                   [2] r, g, b, 1/depth
+#ifndef FWD_BULK_STAGE
     float4 stage[FWD_DEPTH][3][32];       // chunks in flight: [chunk][g0 | g1 | colour][lane]
+#else
+    SplatRecord rec[FWD_DEPTH][32];       // chunks in flight: a lane's record contiguous (one 32-byte bulk copy)
+    float4 col[FWD_DEPTH][32];
+    unsigned long long bar[FWD_DEPTH];    // one mbarrier per stage: completes when the chunk's bytes have landed
+#endif
 };
 
 template <bool INVDEPTH>
@@ -221,11 +254,36 @@ __global__ void __launch_bounds__(FWD_WARPS * 32, FWD_MIN_CTAS) blend_forward_ke
 #endif
 
     // this lane's copies of one chunk entry: record + colour -> its private slot of stage `st`
+#ifndef FWD_BULK_STAGE
     auto fetch = [&](uint32_t st, uint32_t id) {
         cp_async_16(&sm.stage[st][0][lane], &splat[id].g0);
         cp_async_16(&sm.stage[st][1][lane], &splat[id].g1);
         cp_async_16(&sm.stage[st][2][lane], feat + id);
     };
+#else
+    uint32_t bulk_parity = 0, bulk_pending = 0;   // per stage: the phase to wait for next / a chunk is in flight
+    if (lane == 0) {
+#pragma unroll
+        for (int j = 0; j < FWD_DEPTH; j++) mbar_init(&sm.bar[j], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    fence_proxy_async();
+    __syncwarp();
+    // chunk `chunk` into stage st: lane 0 arms the barrier with the chunk's bytes, every lane with an entry issues its two
+    // bulk copies (the phase cannot complete before lane 0's arrive, whatever order the copies land in)
+    auto fetch_chunk = [&](uint32_t st, uint32_t chunk, uint32_t id) {
+        const uint32_t first = chunk * 32u;
+        if (first >= count) return;
+        const uint32_t nvalid = min(32u, count - first);
+        fence_proxy_async();                       // the stage was last read through the generic proxy
+        if (lane == 0) mbar_expect_tx(&sm.bar[st], 48u * nvalid);
+        if (lane < nvalid) {
+            bulk_copy(&sm.rec[st][lane], splat + id, 32u, &sm.bar[st]);
+            bulk_copy(&sm.col[st][lane], feat + id, 16u, &sm.bar[st]);
+        }
+        bulk_pending |= 1u << st;
+    };
+#endif
     // prologue: FWD_DEPTH chunks in flight (one commit group per chunk, empty ones included).  idq[s] is the id of this
     // lane's entry in the next chunk that will be fetched into stage s: it is loaded FWD_DEPTH steps before it is used,
     // into a register that nothing touches in between (the chunk loop is unrolled over the stages, so the queue needs no
@@ -236,8 +294,12 @@ __global__ void __launch_bounds__(FWD_WARPS * 32, FWD_MIN_CTAS) blend_forward_ke
     if (!all_done) {
 #pragma unroll
         for (uint32_t j = 0; j < (uint32_t)FWD_DEPTH; j++) {
+#ifndef FWD_BULK_STAGE
             if (j * 32u + lane < count) fetch(j, point_list[j * 32u + lane]);
             cp_async_commit();
+#else
+            fetch_chunk(j, j, j * 32u + lane < count ? point_list[j * 32u + lane] : 0u);
+#endif
         }
 #pragma unroll
         for (uint32_t j = 0; j < (uint32_t)FWD_DEPTH; j++)
@@ -334,12 +396,23 @@ __global__ void __launch_bounds__(FWD_WARPS * 32, FWD_MIN_CTAS) blend_forward_ke
             const uint32_t c = c0 + (uint32_t)st;
             if (c >= nchunks || all_done) break;
             // this lane's entry of chunk c has landed when at most FWD_DEPTH - 1 younger groups are still in flight
+#ifndef FWD_BULK_STAGE
             asm volatile("cp.async.wait_group %0;" ::"n"(FWD_DEPTH - 1) : "memory");
+#else
+            mbar_wait(&sm.bar[st], (bulk_parity >> st) & 1u);
+            bulk_parity ^= 1u << st;
+            bulk_pending &= ~(1u << st);
+#endif
             const uint32_t pos = c * 32u + lane;
             float4 g0 = make_float4(0.f, 0.f, CUDART_INF_F, 0.f), g1 = make_float4(0.f, 0.f, 0.f, 0.f);
             if (pos < count) {
+#ifndef FWD_BULK_STAGE
                 g0 = sm.stage[st][0][lane];
                 g1 = sm.stage[st][1][lane];
+#else
+                g0 = sm.rec[st][lane].g0;
+                g1 = sm.rec[st][lane].g1;
+#endif
             }
             const bool hit = pos < count && footprint_hit(g0, g1, wb);
             const uint32_t m = __ballot_sync(0xffffffffu, hit);
@@ -348,7 +421,11 @@ __global__ void __launch_bounds__(FWD_WARPS * 32, FWD_MIN_CTAS) blend_forward_ke
                 STAT_ADD(0, 1); STAT_ADD(1, __popc(m));
             }
             if (hit) {
+#ifndef FWD_BULK_STAGE
                 const float4 col = sm.stage[st][2][lane];
+#else
+                const float4 col = sm.col[st][lane];
+#endif
                 float4 *slot = sm.ring[(tail + __popc(m & lanemask_lt())) & (RING - 1)];
                 slot[0] = make_float4(g0.x, g0.y, __uint_as_float(pos + 1u), 0.f);
                 slot[1] = make_float4(g1.x, g1.y, g1.z, g0.w);
@@ -357,8 +434,13 @@ __global__ void __launch_bounds__(FWD_WARPS * 32, FWD_MIN_CTAS) blend_forward_ke
             tail += __popc(m);
             // refill the stage with this lane's entry of chunk c + FWD_DEPTH; its id for the chunk after that
             const uint32_t ahead = pos + (uint32_t)FWD_DEPTH * 32u;
+#ifndef FWD_BULK_STAGE
             if (ahead < count) fetch((uint32_t)st, idq[st]);
             cp_async_commit();
+#else
+            __syncwarp();                          // every lane has taken its entry out of the stage
+            fetch_chunk((uint32_t)st, c + (uint32_t)FWD_DEPTH, idq[st]);
+#endif
             if (ahead + (uint32_t)FWD_DEPTH * 32u < count) idq[st] = point_list[ahead + (uint32_t)FWD_DEPTH * 32u];
             // the list itself is streamed from HBM once per tile: pull its lines into L2 well ahead of the id loads
             if (lane == 0 && pos + 32u * 24u < count)
@@ -378,6 +460,11 @@ __global__ void __launch_bounds__(FWD_WARPS * 32, FWD_MIN_CTAS) blend_forward_ke
     }
 #endif
     cp_async_wait_all();   // nothing may still be landing in shared memory when the CTA retires
+#ifdef FWD_BULK_STAGE
+#pragma unroll
+    for (int j = 0; j < FWD_DEPTH; j++)
+        if ((bulk_pending >> j) & 1u) mbar_wait(&sm.bar[j], (bulk_parity >> j) & 1u);
+#endif
     if (inside) {
         const size_t pid = (size_t)py * W + px, plane = (size_t)H * W;
         final_T[pid] = T;

@@ -371,38 +371,16 @@ __global__ void __launch_bounds__(GEO_THREADS) geometry_kernel(const GeoParams p
                   s_gidx, s_warp, &s_base);
 }
 
-// One Gaussian of the persistent preprocess loop; returns its depth-sort key.  Out of line on purpose: inlined into the
-// loop, the compiler keeps every pointer of GeoParams in registers across the iterations (63 registers instead of 46).
-#ifndef PREPROCESS_ENTRY_ATTR
-#define PREPROCESS_ENTRY_ATTR __forceinline__
-#endif
-__device__ PREPROCESS_ENTRY_ATTR uint32_t preprocess_block_entry(const GeoParams &p, int idx, const float *s_view,
-                                                                  const float *s_proj, const float *s_cam) {
-    uint32_t count, rect, width, dbits;
-    preprocess_one(p, idx, s_view, s_proj, s_cam, count, rect, width, dbits);
-    // the rect goes where the binning path that follows reads it: the direct tile scatter's 16-byte record, or the
-    // (rect, width) pair of the depth-first emission and its rect grid
-    if (p.grec) p.grec[idx] = make_uint4(rect, count ? (width | ((count / width) << 16)) : 0u, (uint32_t)idx, dbits);
-    else p.rect_pack[idx] = make_uint2(rect, width);
-    const uint32_t key = count ? dbits : 0xffffffffu;   // (a live Gaussian's depth is > 0.2: never all ones)
-    p.dkeys[idx] = key;
-    p.dvals[idx] = (uint32_t)idx;
-    return key;
-}
-
-#ifndef PREPROCESS_PERSISTENT
-#define PREPROCESS_PERSISTENT 0
-#endif
-#ifndef PREPROCESS_CTAS_PER_SM
-#define PREPROCESS_CTAS_PER_SM 5
-#endif
 // Depth-first binning, step 1: R1 only.  Also writes the 32-bit sort key of every Gaussian (its depth bits; culled
-// Gaussians get 0xffffffff) and its rect, so that the emission can run later in depth order -- and counts the four digits
-// of those keys while it holds them: the CTAs are persistent (a few per SM, each walking blocks of 256 Gaussians), keep
-// the counts in shared memory, add their non-zero bins to the global counts once, and the last CTA to finish turns the
-// counts into the plan of the depth sort (common.cuh: depth_sort_plan).  This used to be a kernel of its own that read the
-// 4 N bytes of keys back (14 us at 1 M Gaussians, all of it launch and DRAM latency).
-__global__ void __launch_bounds__(GEO_THREADS, PREPROCESS_CTAS_PER_SM) preprocess_kernel(const GeoParams p) {
+// Gaussians get 0xffffffff) and its rect, so that the emission / scatter can run later in depth order -- and counts the
+// four digits of the key while it holds it: per CTA in shared memory, the non-zero bins then added to one of
+// DEP_HIST_COPIES global tables.  This used to be a kernel of its own that read the 4 N bytes of keys back (14 us at 1 M
+// Gaussians, all of it launch and DRAM latency).  Measured on the way (1 M Gaussians): one global table 58 us (the top
+// digits' two or three hot words serialise 3907 CTAs in the L2), 8+ tables 36 us; a last-CTA ticket for the plan needs a
+// fence per CTA, which holds the CTA until its ~116 B of stores per Gaussian are acknowledged (52-60 us) -- hence no fence
+// and the plan in depth_plan_kernel, behind the kernel boundary; persistent CTAs that flush once each: 40-42 us (63
+// registers in the loop: four CTAs per SM instead of five).
+__global__ void __launch_bounds__(GEO_THREADS, 5) preprocess_kernel(const GeoParams p) {
     __shared__ float s_view[16], s_proj[16], s_cam[3];
     __shared__ uint32_t s_hist[4][256];
     __shared__ uint32_t s_culled;
@@ -413,23 +391,21 @@ __global__ void __launch_bounds__(GEO_THREADS, PREPROCESS_CTAS_PER_SM) preproces
     for (int d = 0; d < 4; d++) s_hist[d][tid] = 0;
     if (tid == 0) s_culled = 0;
     __syncthreads();
+    const int idx = (int)(blockIdx.x * GEO_THREADS + tid);
     uint32_t culled = 0;
-#if PREPROCESS_PERSISTENT
-    for (uint32_t blk = blockIdx.x; blk < p.num_ctas; blk += gridDim.x) {
-        const int idx = (int)(blk * GEO_THREADS + tid);
-        if (idx >= p.P) break;
-#else
-    {
-        const int idx = (int)(blockIdx.x * GEO_THREADS + tid);
-        if (idx < p.P) {
-#endif
-        const uint32_t key = preprocess_block_entry(p, idx, s_view, s_proj, s_cam);
-        culled += key == 0xffffffffu ? 1u : 0u;
+    if (idx < p.P) {
+        uint32_t count, rect, width, dbits;
+        preprocess_one(p, idx, s_view, s_proj, s_cam, count, rect, width, dbits);
+        // the rect goes where the binning path that follows reads it: the direct tile scatter's 16-byte record, or the
+        // (rect, width) pair of the depth-first emission and its rect grid
+        if (p.grec) p.grec[idx] = make_uint4(rect, count ? (width | ((count / width) << 16)) : 0u, (uint32_t)idx, dbits);
+        else p.rect_pack[idx] = make_uint2(rect, width);
+        const uint32_t key = count ? dbits : 0xffffffffu;   // (a live Gaussian's depth is > 0.2: never all ones)
+        p.dkeys[idx] = key;
+        p.dvals[idx] = (uint32_t)idx;
+        culled = count ? 0u : 1u;
 #pragma unroll
         for (int d = 0; d < 4; d++) atomicAdd(&s_hist[d][(key >> (8 * d)) & 255u], 1u);
-#if !PREPROCESS_PERSISTENT
-        }
-#endif
     }
     culled = __reduce_add_sync(0xffffffffu, culled);
     if ((tid & 31) == 0 && culled) atomicAdd(&s_culled, culled);
@@ -440,8 +416,6 @@ __global__ void __launch_bounds__(GEO_THREADS, PREPROCESS_CTAS_PER_SM) preproces
         if (c) atomicAdd(&p.dep_ghist[(blockIdx.x % DEP_HIST_COPIES) * 1024 + d * 256 + tid], c);
     }
     if (tid == 0 && s_culled) atomicAdd(&p.hdr->dep_culled, s_culled);
-    // (no fence, no last-CTA ticket: a fence here would hold every CTA until its ~116 B of stores per Gaussian have been
-    // acknowledged -- measured 34 -> 52 us; the plan is made by depth_plan_kernel, behind the kernel boundary)
 }
 
 // One CTA: the digit counts of the depth keys -> the plan of the depth sort (common.cuh: depth_sort_plan).
@@ -583,12 +557,7 @@ int launch_geometry(int P, int sh_degree, int sh_coeffs, const float *means3D, c
         p.dep_ghist = reinterpret_cast<uint32_t *>(geom + GL.dep_hist);
         p.dep_bins = reinterpret_cast<uint32_t *>(geom + GL.dep_bins);
         D3GA_CUDA(cudaMemsetAsync(p.dep_ghist, 0, 4 * 256 * 4 * DEP_HIST_COPIES, stream));
-        // persistent CTAs: as many as are resident at once (46 registers: five per SM), so that each adds its digit counts
-        // to the global ones once
-        uint32_t grid = p.num_ctas;
-#if PREPROCESS_PERSISTENT
-        if (grid > (uint32_t)device_sm_count() * PREPROCESS_CTAS_PER_SM) grid = (uint32_t)device_sm_count() * PREPROCESS_CTAS_PER_SM;
-#endif
+        const uint32_t grid = p.num_ctas;
         ProfScope prof(K_PREPROCESS, stream);
         preprocess_kernel<<<grid, GEO_THREADS, 0, stream>>>(p);
     }
