@@ -371,24 +371,28 @@ def run_ours(args):
     if rank == 0 and world == 1 and not args.no_e2e:
         from d3ga_b200 import diff_gaussian_rasterization as dgr
         pair = {}
-        for share in (True, False):
+        for name, share, fused in (("frames_per_s_fused_pair", True, True), ("frames_per_s_shared_geometry", True, False),
+                                   ("frames_per_s_independent_renders", False, False)):
             dgr.SHARE_GEOMETRY = share
             dgr._geom_cache.clear()
             for i in range(3):
                 avatar.grads.zero_()
-                training.frame_step(avatar, bank, mine[i % len(mine)], weights, bg)
+                training.frame_step(avatar, bank, mine[i % len(mine)], weights, bg, fused_pair=fused)
             torch.cuda.synchronize()
             a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             nfr = 2 * V
             a.record()
             for i in range(nfr):
-                training.frame_step(avatar, bank, mine[(3 + i) % len(mine)], weights, bg)
+                training.frame_step(avatar, bank, mine[(3 + i) % len(mine)], weights, bg, fused_pair=fused)
             b.record()
             torch.cuda.synchronize()
-            pair["frames_per_s_shared_geometry" if share else "frames_per_s_independent_renders"] = nfr / (a.elapsed_time(b) * 1e-3)
+            pair[name] = nfr / (a.elapsed_time(b) * 1e-3)
         dgr.SHARE_GEOMETRY = True
         pair["note"] = ("1 frame = deformation block incl. the cage's FEM energy (one launch each way) + RGB render + silhouette "
-                        "render + backward of all three terms (models/trainer.py:91-140, models/cage_net.py:213-230)")
+                        "render + backward of all three terms (models/trainer.py:91-140, models/cage_net.py:213-230), eager "
+                        "launches; fused_pair = both images from one GaussianRasterizer.forward_pair call (one binning, one "
+                        "blend forward, one blend backward), shared_geometry = the reference's two render() calls with the "
+                        "second one re-using the first one's binning")
 
     # the cage-vertex skinning that produces tetpoints (Blueman.get), forward + backward to delta
     lbs = None

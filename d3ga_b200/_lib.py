@@ -18,6 +18,7 @@ EXPORTS = [
     "d3ga_raster_workspace_bytes", "d3ga_raster_forward_geometry", "d3ga_raster_forward_render",
     "d3ga_raster_forward_blend", "d3ga_raster_binning_path", "d3ga_set_views_in_flight", "d3ga_mark_visible", "d3ga_raster_sorted_keys",
     "d3ga_raster_backward_scratch_bytes", "d3ga_raster_backward", "d3ga_raster_backward_noalloc", "d3ga_raster_layout",
+    "d3ga_raster_forward_render_pair", "d3ga_raster_backward_pair",
     "d3ga_deform_forward", "d3ga_deform_backward", "d3ga_deform_backward_ordered", "d3ga_deform_forward_fused",
     "d3ga_deform_backward_fused", "d3ga_compute_bary",
     "d3ga_fem_energy_forward", "d3ga_fem_energy_backward", "d3ga_ssim_l1_forward", "d3ga_ssim_l1_backward",
@@ -76,6 +77,10 @@ def load() -> C.CDLL:
     lib.d3ga_raster_backward.argtypes = (
         [i32, i32, i32, i32, i32, vp, vp, vp, vp, vp, f32, vp, vp, vp, vp, vp, vp, f32, f32, i32, vp, vp, vp, u64, vp,
          vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp]
+    )
+    lib.d3ga_raster_forward_render_pair.argtypes = [i32, i32, i32, vp, vp, vp, vp, vp, vp, u64, vp, vp, vp, vp]
+    lib.d3ga_raster_backward_pair.argtypes = (
+        [i32] * 5 + [vp] * 6 + [f32] + [vp] * 6 + [f32, f32, i32] + [vp] * 3 + [u64] + [vp] * 13
     )
     lib.d3ga_raster_backward_noalloc.argtypes = (
         [i32, i32, i32, i32, i32, vp, vp, vp, vp, vp, f32, vp, vp, vp, vp, vp, vp, f32, f32, i32, vp, vp, vp, u64, vp,

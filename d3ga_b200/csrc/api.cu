@@ -213,8 +213,9 @@ int d3ga_raster_forward_geometry(int P, int sh_degree, int sh_coeffs, const floa
     return D3GA_OK;
 }
 
-int d3ga_raster_forward_render(int P, int W, int H, const float *background, const float *colors_precomp, void *geom,
+static int forward_render_impl(int P, int W, int H, const float *background, const float *colors_precomp, void *geom,
                                void *binning, uint64_t capacity, void *image, float *out_color, float *out_invdepth,
+                               const float *background_b, const float *colors_b, float *out_color_b,
                                d3ga_stream_t stream_) {
     cudaStream_t stream = (cudaStream_t)stream_;
     if (P < 0 || W <= 0 || H <= 0 || !geom || !binning || !image || !background || !out_color) return D3GA_EINVAL;
@@ -229,7 +230,23 @@ int d3ga_raster_forward_render(int P, int W, int H, const float *background, con
     if (rc) return rc;
     const float *colors = colors_precomp ? colors_precomp : reinterpret_cast<const float *>((uint8_t *)geom + GL.rgb);
     return launch_blend_forward(P, W, H, background, colors, (const uint8_t *)geom, GL, (const uint8_t *)binning, BL,
-                                (uint8_t *)image, IL, out_color, out_invdepth, stream);
+                                (uint8_t *)image, IL, out_color, out_invdepth, stream, background_b, colors_b, out_color_b);
+}
+
+int d3ga_raster_forward_render(int P, int W, int H, const float *background, const float *colors_precomp, void *geom,
+                               void *binning, uint64_t capacity, void *image, float *out_color, float *out_invdepth,
+                               d3ga_stream_t stream) {
+    return forward_render_impl(P, W, H, background, colors_precomp, geom, binning, capacity, image, out_color,
+                               out_invdepth, nullptr, nullptr, nullptr, stream);
+}
+
+int d3ga_raster_forward_render_pair(int P, int W, int H, const float *background, const float *colors_precomp,
+                                    const float *background_b, const float *colors_b, void *geom, void *binning,
+                                    uint64_t capacity, void *image, float *out_color, float *out_color_b,
+                                    d3ga_stream_t stream) {
+    if (!background_b || !colors_b || !out_color_b) return D3GA_EINVAL;
+    return forward_render_impl(P, W, H, background, colors_precomp, geom, binning, capacity, image, out_color, nullptr,
+                               background_b, colors_b, out_color_b, stream);
 }
 
 int d3ga_raster_forward_blend(int P, int W, int H, const float *background, const float *colors_precomp, void *geom,
@@ -257,7 +274,7 @@ int d3ga_raster_forward_blend(int P, int W, int H, const float *background, cons
 
 uint64_t d3ga_raster_backward_scratch_bytes(int P) { return align256((uint64_t)(P > 0 ? P : 1) * GRAD_ACC_FLOATS * 4); }
 
-int d3ga_raster_backward(int P, int sh_degree, int sh_coeffs, int W, int H, const float *background,
+static int backward_impl(int P, int sh_degree, int sh_coeffs, int W, int H, const float *background,
                          const float *means3D, const float *colors_precomp, const float *opacities,
                          const float *scales, float scale_modifier, const float *rotations,
                          const float *cov3D_precomp, const float *shs, const float *viewmatrix,
@@ -266,7 +283,7 @@ int d3ga_raster_backward(int P, int sh_degree, int sh_coeffs, int W, int H, cons
                          const void *image, const float *dL_dout_color, const float *dL_dout_invdepth,
                          void *grad_scratch, float *dL_dmeans2D, float *dL_dopacity, float *dL_dcolors,
                          float *dL_dmeans3D, float *dL_dcov3D, float *dL_dsh, float *dL_dscales, float *dL_drotations,
-                         d3ga_stream_t stream_) {
+                         const float *background_b, const float *dL_dout_color_b, d3ga_stream_t stream_) {
     cudaStream_t stream = (cudaStream_t)stream_;
     if (P < 0 || W <= 0 || H <= 0 || !geom || !binning || !image || !background || !dL_dout_color || !grad_scratch ||
         !viewmatrix || !projmatrix || !campos)
@@ -285,13 +302,49 @@ int d3ga_raster_backward(int P, int sh_degree, int sh_coeffs, int W, int H, cons
     D3GA_CUDA(cudaMemsetAsync(acc, 0, (size_t)P * GRAD_ACC_FLOATS * 4, stream));
     const float *colors = colors_precomp ? colors_precomp : reinterpret_cast<const float *>((const uint8_t *)geom + GL.rgb);
     int rc = launch_blend_backward(W, H, background, colors, (const uint8_t *)geom, GL, (const uint8_t *)binning, BL,
-                                   (const uint8_t *)image, IL, dL_dout_color, dL_dout_invdepth, acc, stream);
+                                   (const uint8_t *)image, IL, dL_dout_color, dL_dout_invdepth, acc, stream, background_b,
+                                   dL_dout_color_b);
     if (rc) return rc;
     return launch_preprocess_backward(P, sh_degree, sh_coeffs, W, H, means3D, opacities, scales, scale_modifier,
                                       rotations, cov3D_precomp, shs, viewmatrix, projmatrix, campos, tanfovx, tanfovy,
                                       antialiasing, radii, (const uint8_t *)geom, GL, acc, dL_dout_invdepth != nullptr,
                                       dL_dmeans2D, dL_dopacity, dL_dcolors, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales,
                                       dL_drotations, stream);
+}
+
+int d3ga_raster_backward(int P, int sh_degree, int sh_coeffs, int W, int H, const float *background,
+                         const float *means3D, const float *colors_precomp, const float *opacities,
+                         const float *scales, float scale_modifier, const float *rotations,
+                         const float *cov3D_precomp, const float *shs, const float *viewmatrix,
+                         const float *projmatrix, const float *campos, float tanfovx, float tanfovy, int antialiasing,
+                         const int32_t *radii, const void *geom, const void *binning, uint64_t capacity,
+                         const void *image, const float *dL_dout_color, const float *dL_dout_invdepth,
+                         void *grad_scratch, float *dL_dmeans2D, float *dL_dopacity, float *dL_dcolors,
+                         float *dL_dmeans3D, float *dL_dcov3D, float *dL_dsh, float *dL_dscales, float *dL_drotations,
+                         d3ga_stream_t stream) {
+    return backward_impl(P, sh_degree, sh_coeffs, W, H, background, means3D, colors_precomp, opacities, scales,
+                         scale_modifier, rotations, cov3D_precomp, shs, viewmatrix, projmatrix, campos, tanfovx, tanfovy,
+                         antialiasing, radii, geom, binning, capacity, image, dL_dout_color, dL_dout_invdepth, grad_scratch,
+                         dL_dmeans2D, dL_dopacity, dL_dcolors, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations,
+                         nullptr, nullptr, stream);
+}
+
+int d3ga_raster_backward_pair(int P, int sh_degree, int sh_coeffs, int W, int H, const float *background,
+                              const float *background_b, const float *means3D, const float *colors_precomp,
+                              const float *opacities, const float *scales, float scale_modifier, const float *rotations,
+                              const float *cov3D_precomp, const float *shs, const float *viewmatrix,
+                              const float *projmatrix, const float *campos, float tanfovx, float tanfovy,
+                              int antialiasing, const int32_t *radii, const void *geom, const void *binning,
+                              uint64_t capacity, const void *image, const float *dL_dout_color,
+                              const float *dL_dout_color_b, void *grad_scratch, float *dL_dmeans2D, float *dL_dopacity,
+                              float *dL_dcolors, float *dL_dmeans3D, float *dL_dcov3D, float *dL_dsh, float *dL_dscales,
+                              float *dL_drotations, d3ga_stream_t stream) {
+    if (!background_b || !dL_dout_color_b) return D3GA_EINVAL;
+    return backward_impl(P, sh_degree, sh_coeffs, W, H, background, means3D, colors_precomp, opacities, scales,
+                         scale_modifier, rotations, cov3D_precomp, shs, viewmatrix, projmatrix, campos, tanfovx, tanfovy,
+                         antialiasing, radii, geom, binning, capacity, image, dL_dout_color, nullptr, grad_scratch,
+                         dL_dmeans2D, dL_dopacity, dL_dcolors, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations,
+                         background_b, dL_dout_color_b, stream);
 }
 
 }  // extern "C"

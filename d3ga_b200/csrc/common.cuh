@@ -71,7 +71,7 @@ struct BinLayout {
     uint64_t tile_state_bytes;
 };
 struct ImgLayout {
-    uint64_t ranges, final_T, n_contrib, order_fwd, order_bwd, tile_nproc, ballots, feat, total;
+    uint64_t ranges, final_T, n_contrib, order_fwd, order_bwd, tile_nproc, ballots, feat, feat_b, total;
 };
 // The blend kernels' per-Gaussian gather: ONE 32-byte sector, two 16-byte loads (before: xy 8 B + conic/opacity 16 B +
 // depth 4 B from three arrays).  The conic is pre-scaled to the log2 domain (log2 G = A dx^2 + B dx dy + C dy^2) and the
@@ -147,6 +147,8 @@ inline ImgLayout img_layout(int P, int W, int H, uint64_t capacity) {
     // packed into the geometry workspace: the second render of a training frame shares that workspace but blends
     // other colours (the blend launchers pick by the colour pointer: recall_packed_colors)
     L.feat = o;       o = align256(o + 16ull * (uint64_t)(P < 1 ? 1 : P));
+    // the second image's colours of a PAIR render (d3ga_raster_forward_render_pair), packed the same way
+    L.feat_b = o;     o = align256(o + 16ull * (uint64_t)(P < 1 ? 1 : P));
     L.total = o;
     return L;
 }
@@ -246,11 +248,13 @@ int launch_direct_scatter(int P, int gx, int gy, uint8_t *geom, const GeomLayout
                           cudaStream_t stream);
 int launch_blend_forward(int P, int W, int H, const float *background, const float *colors, const uint8_t *geom,
                          const GeomLayout &GL, const uint8_t *binning, const BinLayout &BL, uint8_t *image,
-                         const ImgLayout &IL, float *out_color, float *out_invdepth, cudaStream_t stream);
+                         const ImgLayout &IL, float *out_color, float *out_invdepth, cudaStream_t stream,
+                         const float *background_b = nullptr, const float *colors_b = nullptr,
+                         float *out_color_b = nullptr);   // the three together: a PAIR render (no inverse depth)
 int launch_blend_backward(int W, int H, const float *background, const float *colors, const uint8_t *geom,
                           const GeomLayout &GL, const uint8_t *binning, const BinLayout &BL, const uint8_t *image,
                           const ImgLayout &IL, const float *dL_dpix, const float *dL_dinvdepth_pix, float *grad_acc,
-                          cudaStream_t stream);
+                          cudaStream_t stream, const float *background_b = nullptr, const float *dL_dpix_b = nullptr);
 int launch_preprocess_backward(int P, int sh_degree, int sh_coeffs, int W, int H, const float *means3D,
                                const float *opacities, const float *scales, float scale_modifier,
                                const float *rotations, const float *cov3D_precomp, const float *shs,

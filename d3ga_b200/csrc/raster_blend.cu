@@ -199,11 +199,13 @@ __device__ __noinline__ bool exact_cut(const float2 *__restrict__ xy, const floa
 #ifndef FWD_DEPTH
 #define FWD_DEPTH 2   // 2 and 3 run the kernel equally fast; 2 leaves other views' kernels more shared memory (4: L1 starves)
 #endif
-struct FwdWarpSmem {
-    float4 ring[RING][3];                 // staged survivors: [0] x, y, list position + 1 (bits), -   [1] conic, opacity
-                                          //                   [2] r, g, b, 1/depth
+// NF = float4s per entry: 3, or 4 for a PAIR render (two images of the same Gaussians in one walk: the second colour)
+template <int NF>
+struct FwdWarpSmemT {
+    float4 ring[RING][NF];                // staged survivors: [0] x, y, list position + 1 (bits), -   [1] conic, opacity
+                                          //                   [2] r, g, b, 1/depth   ([3] second colour)
 #ifndef FWD_BULK_STAGE
-    float4 stage[FWD_DEPTH][3][32];       // chunks in flight: [chunk][g0 | g1 | colour][lane]
+    float4 stage[FWD_DEPTH][NF][32];      // chunks in flight: [chunk][g0 | g1 | colour (| second colour)][lane]
 #else
     SplatRecord rec[FWD_DEPTH][32];       // chunks in flight: a lane's record contiguous (one 32-byte bulk copy)
     float4 col[FWD_DEPTH][32];
@@ -211,7 +213,10 @@ struct FwdWarpSmem {
 #endif
 };
 
-template <bool INVDEPTH>
+// PAIR: a second image of the SAME Gaussians with other colours and another background (the silhouette pass of a D3GA
+// training frame, models/trainer.py:102-110) is blended in the same walk: same alphas, same transmittance, same
+// contributor set -- one more 16-byte colour per survivor and three more accumulators per pixel.
+template <bool INVDEPTH, bool PAIR>
 __global__ void __launch_bounds__(FWD_WARPS * 32, FWD_MIN_CTAS) blend_forward_kernel(
     const RasterHeader *__restrict__ hdr, const uint2 *__restrict__ ranges, const uint32_t *__restrict__ vals0,
     const uint32_t *__restrict__ vals1, int W, int H, const SplatRecord *__restrict__ splat,
@@ -219,7 +224,10 @@ __global__ void __launch_bounds__(FWD_WARPS * 32, FWD_MIN_CTAS) blend_forward_ke
     const float *__restrict__ bg, float *__restrict__ final_T, uint32_t *__restrict__ n_contrib,
     float *__restrict__ out_color, float *__restrict__ out_invdepth, RasterHeader *__restrict__ hdr_rw, int grid_x,
     int num_tiles, const uint32_t *__restrict__ order_fwd, uint32_t *__restrict__ tile_nproc,
-    uint32_t *__restrict__ order_bwd, uint32_t *__restrict__ ballots) {
+    uint32_t *__restrict__ order_bwd, uint32_t *__restrict__ ballots, const float4 *__restrict__ feat_b,
+    const float *__restrict__ bg_b, float *__restrict__ out_color_b) {
+    constexpr int NF = PAIR ? 4 : 3;
+    using FwdWarpSmem = FwdWarpSmemT<NF>;
     extern __shared__ __align__(16) unsigned char s_raw[];
     __shared__ uint32_t s_bins[257];
     __shared__ uint32_t s_last;
@@ -229,7 +237,7 @@ __global__ void __launch_bounds__(FWD_WARPS * 32, FWD_MIN_CTAS) blend_forward_ke
 
     // The blend loop below is branch-free: entries of a partly filled last group are multiplied by a weight of zero
     // rather than skipped, so a ring slot that was never written must not hold a NaN or Inf bit pattern.
-    for (int i = (int)lane; i < RING * 3; i += 32) (&sm.ring[0][0])[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int i = (int)lane; i < RING * NF; i += 32) (&sm.ring[0][0])[i] = make_float4(0.f, 0.f, 0.f, 0.f);
     __syncwarp();
     const uint32_t tile = order_fwd[blockIdx.x];   // longest Gaussian list first
     const WarpBlock wb = warp_block((int)warp, (int)lane, (int)(tile % (uint32_t)grid_x), (int)(tile / (uint32_t)grid_x));
@@ -245,6 +253,7 @@ __global__ void __launch_bounds__(FWD_WARPS * 32, FWD_MIN_CTAS) blend_forward_ke
 
     bool done = !inside;
     float T = 1.f, C0 = 0.f, C1 = 0.f, C2 = 0.f, invd = 0.f;
+    float D0 = 0.f, D1 = 0.f, D2 = 0.f;     // PAIR: the second image
     uint32_t last = 0;
     uint32_t head = 0, tail = 0;
     bool all_done = __all_sync(0xffffffffu, done);
@@ -259,8 +268,10 @@ __global__ void __launch_bounds__(FWD_WARPS * 32, FWD_MIN_CTAS) blend_forward_ke
         cp_async_16(&sm.stage[st][0][lane], &splat[id].g0);
         cp_async_16(&sm.stage[st][1][lane], &splat[id].g1);
         cp_async_16(&sm.stage[st][2][lane], feat + id);
+        if (PAIR) cp_async_16(&sm.stage[st][NF - 1][lane], feat_b + id);
     };
 #else
+    static_assert(!PAIR, "the bulk-copy staging variant has no pair render");
     uint32_t bulk_parity = 0, bulk_pending = 0;   // per stage: the phase to wait for next / a chunk is in flight
     if (lane == 0) {
 #pragma unroll
@@ -319,7 +330,7 @@ __global__ void __launch_bounds__(FWD_WARPS * 32, FWD_MIN_CTAS) blend_forward_ke
     uint32_t gavail = 0;                     // entries of the pending group (0: none pending)
     float gnear = 1.f;
     auto alphas_of = [&](uint32_t h, uint32_t avail, float (&a)[4], uint32_t (&posv)[4], float &nearest) {
-        const float4(*g)[3] = sm.ring + (h & (RING - 1));
+        const float4(*g)[NF] = sm.ring + (h & (RING - 1));
         nearest = 1.f;
 #pragma unroll
         for (int u = 0; u < 4; u++) {
@@ -336,7 +347,7 @@ __global__ void __launch_bounds__(FWD_WARPS * 32, FWD_MIN_CTAS) blend_forward_ke
     };
     // ~1e-6 of the pairs: the contributor set must not depend on this kernel's rounding
     auto resolve_cuts = [&](uint32_t h, uint32_t avail, float (&a)[4], const uint32_t (&posv)[4]) {
-        const float4(*g)[3] = sm.ring + (h & (RING - 1));
+        const float4(*g)[NF] = sm.ring + (h & (RING - 1));
 #pragma unroll
         for (int u = 0; u < 4; u++) {
             const float4 e = g[u][0];
@@ -364,7 +375,7 @@ __global__ void __launch_bounds__(FWD_WARPS * 32, FWD_MIN_CTAS) blend_forward_ke
             uint32_t npos[4] = {0u, 0u, 0u, 0u};
             float nnear = 1.f;
             if (navail) alphas_of(head, navail, na, npos, nnear);   // (warp-uniform; a third of the calls end here)
-            const float4(*g)[3] = sm.ring + (h & (RING - 1));
+            const float4(*g)[NF] = sm.ring + (h & (RING - 1));
             const float p0 = T;
             const float p1 = p0 * (1.f - ga[0]), p2 = p1 * (1.f - ga[1]), p3 = p2 * (1.f - ga[2]), p4 = p3 * (1.f - ga[3]);
             const bool s0 = done | (p1 < 0.0001f), s1 = s0 | (p2 < 0.0001f), s2 = s1 | (p3 < 0.0001f), s3 = s2 | (p4 < 0.0001f);
@@ -377,6 +388,12 @@ __global__ void __launch_bounds__(FWD_WARPS * 32, FWD_MIN_CTAS) blend_forward_ke
             C1 += f0.y * w0 + f1.y * w1 + f2.y * w2 + f3.y * w3;
             C2 += f0.z * w0 + f1.z * w1 + f2.z * w2 + f3.z * w3;
             if (INVDEPTH) invd += f0.w * w0 + f1.w * w1 + f2.w * w2 + f3.w * w3;
+            if (PAIR) {
+                const float4 e0 = g[0][NF - 1], e1 = g[1][NF - 1], e2 = g[2][NF - 1], e3 = g[3][NF - 1];
+                D0 += e0.x * w0 + e1.x * w1 + e2.x * w2 + e3.x * w3;
+                D1 += e0.y * w0 + e1.y * w1 + e2.y * w2 + e3.y * w3;
+                D2 += e0.z * w0 + e1.z * w1 + e2.z * w2 + e3.z * w3;
+            }
             last = w0 != 0.f ? gpos[0] : last;
             last = w1 != 0.f ? gpos[1] : last;
             last = w2 != 0.f ? gpos[2] : last;
@@ -430,6 +447,9 @@ __global__ void __launch_bounds__(FWD_WARPS * 32, FWD_MIN_CTAS) blend_forward_ke
                 slot[0] = make_float4(g0.x, g0.y, __uint_as_float(pos + 1u), 0.f);
                 slot[1] = make_float4(g1.x, g1.y, g1.z, g0.w);
                 slot[2] = make_float4(col.x, col.y, col.z, g1.w);
+#ifndef FWD_BULK_STAGE
+                if (PAIR) slot[NF - 1] = sm.stage[st][NF - 1][lane];
+#endif
             }
             tail += __popc(m);
             // refill the stage with this lane's entry of chunk c + FWD_DEPTH; its id for the chunk after that
@@ -473,6 +493,11 @@ __global__ void __launch_bounds__(FWD_WARPS * 32, FWD_MIN_CTAS) blend_forward_ke
         out_color[plane + pid] = C1 + T * bg[1];
         out_color[2 * plane + pid] = C2 + T * bg[2];
         if (INVDEPTH) out_invdepth[pid] = invd;
+        if (PAIR) {
+            out_color_b[pid] = D0 + T * bg_b[0];
+            out_color_b[plane + pid] = D1 + T * bg_b[1];
+            out_color_b[2 * plane + pid] = D2 + T * bg_b[2];
+        }
     }
     // deepest contributor of the tile = how far the backward has to go; the last CTA orders the backward's tiles
     const uint32_t wmax = __reduce_max_sync(0xffffffffu, inside ? last : 0u);
@@ -501,11 +526,12 @@ __global__ void __launch_bounds__(FWD_WARPS * 32, FWD_MIN_CTAS) blend_forward_ke
 // Gaussians) that the kernel used before.
 constexpr int NB = 16;             // Gaussians per turn-around
 constexpr int NB_PITCH = 33;       // floats per Gaussian row: lanes of both halves hit 32 different banks
-struct BwdWarpSmem {
+template <int NF>
+struct BwdWarpSmemT {
     // per staged survivor 48 contiguous bytes, all landing by cp.async:
     //   [0] SplatRecord.g0 as it lies in global memory: x, y, (lim2), opacity   [1] SplatRecord.g1: pre-scaled conic, 1/depth
-    //   [2] r, g, b (from the colour tensor), unused
-    float4 ring[RING][3];
+    //   [2] r, g, b (from the colour tensor), unused   ([3] PAIR render: the second image's colour)
+    float4 ring[RING][NF];
     uint2 ring_m[RING];            // Gaussian id, forward list position
     float4 meta[NB];               // x, y, Gaussian id (bits) of the parked Gaussians
     float4 dpix[32];               // dL/dpixel (r, g, b, inverse depth) of the block's pixels
@@ -515,7 +541,7 @@ struct BwdWarpSmem {
 
 // (Out of line: inlined at every place a group can fill the park, the kernel was ~95 KB of code and a tenth of its
 // issue slots were lost waiting for instructions.)
-template <bool INVDEPTH>
+template <bool INVDEPTH, typename BwdWarpSmem>
 __device__ __noinline__ void backward_turn_around(BwdWarpSmem &sm, int n, uint32_t lane, float bx0, float by0,
                                                   float *__restrict__ grad_acc) {
     const int g = (int)(lane & 15u), h = (int)(lane >> 4);
@@ -567,14 +593,20 @@ __device__ __noinline__ void backward_turn_around(BwdWarpSmem &sm, int n, uint32
     }
 }
 
-template <bool INVDEPTH>
+// PAIR: the backward of a pair render (see blend_forward_kernel): the second image's dL/dpixel joins the first's in
+// dL/dalpha -- (c . g) becomes (c . g) + (c_b . g_b), the background term likewise -- so geometry and opacity receive the
+// gradient of both images from ONE walk; the second image's colours (constants in D3GA: cage_net.py:243) get no gradient.
+template <bool INVDEPTH, bool PAIR>
 __global__ void __launch_bounds__(TILE_PIX, BWD_MIN_CTAS) blend_backward_kernel(
     const RasterHeader *__restrict__ hdr, const uint2 *__restrict__ ranges, const uint32_t *__restrict__ vals0,
     const uint32_t *__restrict__ vals1, int W, int H, const float *__restrict__ bg,
     const SplatRecord *__restrict__ splat, const float4 *__restrict__ feat, const float2 *__restrict__ xy,
     const float4 *__restrict__ conic_opacity, const float *__restrict__ final_T, const uint32_t *__restrict__ n_contrib,
     const float *__restrict__ dL_dpix, const float *__restrict__ dL_dinvdepth_pix, float *__restrict__ grad_acc,
-    int grid_x, const uint32_t *__restrict__ order_bwd, const uint32_t *__restrict__ ballots) {
+    int grid_x, const uint32_t *__restrict__ order_bwd, const uint32_t *__restrict__ ballots,
+    const float4 *__restrict__ feat_b, const float *__restrict__ bg_b, const float *__restrict__ dL_dpix_b) {
+    constexpr int NF = PAIR ? 4 : 3;
+    using BwdWarpSmem = BwdWarpSmemT<NF>;
     extern __shared__ __align__(16) unsigned char s_raw[];
     const int tid = threadIdx.x;
     const uint32_t lane = tid & 31, warp = tid >> 5;
@@ -610,7 +642,10 @@ __global__ void __launch_bounds__(TILE_PIX, BWD_MIN_CTAS) blend_backward_kernel(
         if (INVDEPTH) gi = dL_dinvdepth_pix[pid];
     }
     sm.dpix[lane] = make_float4(g0, g1, g2, gi);
-    const float bg_term = T_final * (bg[0] * g0 + bg[1] * g1 + bg[2] * g2);
+    float h0 = 0.f, h1 = 0.f, h2 = 0.f;     // PAIR: dL/dpixel of the second image
+    if (PAIR && inside) { h0 = dL_dpix_b[pid]; h1 = dL_dpix_b[plane + pid]; h2 = dL_dpix_b[2 * plane + pid]; }
+    float bg_term = T_final * (bg[0] * g0 + bg[1] * g1 + bg[2] * g2);
+    if (PAIR) bg_term += T_final * (bg_b[0] * h0 + bg_b[1] * h1 + bg_b[2] * h2);
 
     // The forward's chunks, last one first; lane l of a step looks at forward position q = 32 fc + 31 - l, so that the
     // compaction (lower lanes first) keeps the back-to-front order.  The forward's ballot of (chunk, warp) says which of
@@ -634,7 +669,7 @@ __global__ void __launch_bounds__(TILE_PIX, BWD_MIN_CTAS) blend_backward_kernel(
         while (tail - head >= 4u || (flush && tail != head)) {
             const uint32_t avail = min(4u, tail - head);
             const uint32_t base = head & (RING - 1);
-            const float4(*g)[3] = sm.ring + base;
+            const float4(*g)[NF] = sm.ring + base;
             // al = the forward's alpha where this pixel took the Gaussian, else 0 (alpha >= 1/255 there, so "taken" is
             // al != 0); Gk = G there, else 0.  A pair that is not taken then drops out of every sum below by itself:
             // ra = 1 leaves T alone, alpha T = 0, G dL/dalpha = 0 -- one select in the recurrence instead of four.
@@ -681,6 +716,7 @@ __global__ void __launch_bounds__(TILE_PIX, BWD_MIN_CTAS) blend_backward_kernel(
                 const float aT = alpha * T;
                 float cg = f.x * g0 + f.y * g1 + f.z * g2;        // (colour . dL/dpixel)
                 if (INVDEPTH) cg += g[u][1].w * gi;
+                if (PAIR) { const float4 fb = g[u][NF - 1]; cg += fb.x * h0 + fb.y * h1 + fb.z * h2; }
                 // dL/dalpha = (c - accum_rec) . g T - T_final/(1-alpha) (bg . g) with accum_rec T = behind / (1 - alpha),
                 // behind = sum over the contributors behind this one of (c . g) alpha T  (the upstream recurrence,
                 // contracted with g before instead of after)
@@ -723,6 +759,7 @@ __global__ void __launch_bounds__(TILE_PIX, BWD_MIN_CTAS) blend_backward_kernel(
             bwd_cp_async_16(&sm.ring[s][0], &splat[id].g0);
             bwd_cp_async_16(&sm.ring[s][1], &splat[id].g1);
             bwd_cp_async_16(&sm.ring[s][2], feat + id);
+            if (PAIR) bwd_cp_async_16(&sm.ring[s][NF - 1], feat_b + id);
             sm.ring_m[s] = make_uint2(id, 32u * (uint32_t)fc + 31u - lane);
         }
         cp_async_commit();
@@ -778,7 +815,13 @@ extern "C" int d3ga_debug_blend_stats(unsigned long long *out, int reset) {
 
 int launch_blend_forward(int P, int W, int H, const float *background, const float *colors, const uint8_t *geom,
                          const GeomLayout &GL, const uint8_t *binning, const BinLayout &BL, uint8_t *image,
-                         const ImgLayout &IL, float *out_color, float *out_invdepth, cudaStream_t stream) {
+                         const ImgLayout &IL, float *out_color, float *out_invdepth, cudaStream_t stream,
+                         const float *background_b, const float *colors_b, float *out_color_b) {
+    const bool pair = background_b || colors_b || out_color_b;
+    if (pair && (!background_b || !colors_b || !out_color_b || out_invdepth)) return D3GA_EINVAL;
+#ifdef FWD_BULK_STAGE
+    if (pair) return D3GA_EINVAL;
+#endif
     const int gx = (W + TILE - 1) / TILE, gy = (H + TILE - 1) / TILE, num_tiles = gx * gy;
     const RasterHeader *hdr = reinterpret_cast<const RasterHeader *>(geom + GL.header);
     RasterHeader *hdr_rw = const_cast<RasterHeader *>(hdr);
@@ -794,11 +837,16 @@ int launch_blend_forward(int P, int W, int H, const float *background, const flo
     const uint32_t *order_fwd = reinterpret_cast<const uint32_t *>(image + IL.order_fwd);
     uint32_t *order_bwd = reinterpret_cast<uint32_t *>(image + IL.order_bwd);
     uint32_t *tile_nproc = reinterpret_cast<uint32_t *>(image + IL.tile_nproc);
-    const size_t smem = sizeof(FwdWarpSmem) * FWD_WARPS;
+    const size_t smem = (pair ? sizeof(FwdWarpSmemT<4>) : sizeof(FwdWarpSmemT<3>)) * FWD_WARPS;
     static std::atomic<uint64_t> attr_devices{0};
     const int arc = once_per_device(attr_devices, [&]() -> int {
-        D3GA_CUDA(cudaFuncSetAttribute(blend_forward_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        D3GA_CUDA(cudaFuncSetAttribute(blend_forward_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        const int s3 = (int)(sizeof(FwdWarpSmemT<3>) * FWD_WARPS);
+        D3GA_CUDA(cudaFuncSetAttribute(blend_forward_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, s3));
+        D3GA_CUDA(cudaFuncSetAttribute(blend_forward_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, s3));
+#ifndef FWD_BULK_STAGE
+        D3GA_CUDA(cudaFuncSetAttribute(blend_forward_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (int)(sizeof(FwdWarpSmemT<4>) * FWD_WARPS)));
+#endif
         return D3GA_OK;
     });
     if (arc) return arc;
@@ -814,17 +862,29 @@ int launch_blend_forward(int P, int W, int H, const float *background, const flo
             D3GA_LAUNCH_CHECK();
         }
     }
+    float4 *feat_b = reinterpret_cast<float4 *>(image + IL.feat_b);
+    if (pair && P > 0) {
+        ProfScope prof(K_PACK_FEAT, stream);
+        pack_features_kernel<<<(P + 255) / 256, 256, 0, stream>>>(P, colors_b, feat_b);
+        D3GA_LAUNCH_CHECK();
+    }
     ProfScope prof(K_BLEND_FWD, stream);
     {
         D3GA_CUDA(cudaMemsetAsync(tile_nproc, 0, sizeof(uint32_t) * (size_t)num_tiles, stream));
         if (out_invdepth)
-            blend_forward_kernel<true><<<num_tiles, FWD_WARPS * 32, smem, stream>>>(
+            blend_forward_kernel<true, false><<<num_tiles, FWD_WARPS * 32, smem, stream>>>(
                 hdr, ranges, v0, v1, W, H, splat, feat, xy, co, background, final_T, n_contrib, out_color, out_invdepth,
-                hdr_rw, gx, num_tiles, order_fwd, tile_nproc, order_bwd, ballots);
-        else
-            blend_forward_kernel<false><<<num_tiles, FWD_WARPS * 32, smem, stream>>>(
+                hdr_rw, gx, num_tiles, order_fwd, tile_nproc, order_bwd, ballots, nullptr, nullptr, nullptr);
+#ifndef FWD_BULK_STAGE
+        else if (pair)
+            blend_forward_kernel<false, true><<<num_tiles, FWD_WARPS * 32, smem, stream>>>(
                 hdr, ranges, v0, v1, W, H, splat, feat, xy, co, background, final_T, n_contrib, out_color, nullptr,
-                hdr_rw, gx, num_tiles, order_fwd, tile_nproc, order_bwd, ballots);
+                hdr_rw, gx, num_tiles, order_fwd, tile_nproc, order_bwd, ballots, feat_b, background_b, out_color_b);
+#endif
+        else
+            blend_forward_kernel<false, false><<<num_tiles, FWD_WARPS * 32, smem, stream>>>(
+                hdr, ranges, v0, v1, W, H, splat, feat, xy, co, background, final_T, n_contrib, out_color, nullptr,
+                hdr_rw, gx, num_tiles, order_fwd, tile_nproc, order_bwd, ballots, nullptr, nullptr, nullptr);
     }
     D3GA_LAUNCH_CHECK();
     return D3GA_OK;
@@ -833,7 +893,9 @@ int launch_blend_forward(int P, int W, int H, const float *background, const flo
 int launch_blend_backward(int W, int H, const float *background, const float *colors, const uint8_t *geom,
                           const GeomLayout &GL, const uint8_t *binning, const BinLayout &BL, const uint8_t *image,
                           const ImgLayout &IL, const float *dL_dpix, const float *dL_dinvdepth_pix, float *grad_acc,
-                          cudaStream_t stream) {
+                          cudaStream_t stream, const float *background_b, const float *dL_dpix_b) {
+    const bool pair = background_b || dL_dpix_b;
+    if (pair && (!background_b || !dL_dpix_b || dL_dinvdepth_pix)) return D3GA_EINVAL;
     const int gx = (W + TILE - 1) / TILE, gy = (H + TILE - 1) / TILE, num_tiles = gx * gy;
     const RasterHeader *hdr = reinterpret_cast<const RasterHeader *>(geom + GL.header);
     const uint2 *ranges = reinterpret_cast<const uint2 *>(image + IL.ranges);
@@ -848,24 +910,32 @@ int launch_blend_backward(int W, int H, const float *background, const float *co
     const float *final_T = reinterpret_cast<const float *>(image + IL.final_T);
     const uint32_t *n_contrib = reinterpret_cast<const uint32_t *>(image + IL.n_contrib);
     const uint32_t *order_bwd = reinterpret_cast<const uint32_t *>(image + IL.order_bwd);
-    const size_t smem = sizeof(BwdWarpSmem) * (TILE_PIX / 32);
+    const size_t smem = (pair ? sizeof(BwdWarpSmemT<4>) : sizeof(BwdWarpSmemT<3>)) * (TILE_PIX / 32);
     static std::atomic<uint64_t> attr_devices{0};
     const int arc = once_per_device(attr_devices, [&]() -> int {
-        D3GA_CUDA(cudaFuncSetAttribute(blend_backward_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        D3GA_CUDA(cudaFuncSetAttribute(blend_backward_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        const int s3 = (int)(sizeof(BwdWarpSmemT<3>) * (TILE_PIX / 32));
+        D3GA_CUDA(cudaFuncSetAttribute(blend_backward_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, s3));
+        D3GA_CUDA(cudaFuncSetAttribute(blend_backward_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, s3));
+        D3GA_CUDA(cudaFuncSetAttribute(blend_backward_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (int)(sizeof(BwdWarpSmemT<4>) * (TILE_PIX / 32))));
         return D3GA_OK;
     });
     if (arc) return arc;
     ProfScope prof(K_BLEND_BWD, stream);
     {
+        const float4 *feat_b = reinterpret_cast<const float4 *>(image + IL.feat_b);   // packed by the pair forward
         if (dL_dinvdepth_pix)
-            blend_backward_kernel<true><<<num_tiles, TILE_PIX, smem, stream>>>(
+            blend_backward_kernel<true, false><<<num_tiles, TILE_PIX, smem, stream>>>(
                 hdr, ranges, v0, v1, W, H, background, splat, feat, xy, co, final_T, n_contrib, dL_dpix,
-                dL_dinvdepth_pix, grad_acc, gx, order_bwd, ballots);
-        else
-            blend_backward_kernel<false><<<num_tiles, TILE_PIX, smem, stream>>>(
+                dL_dinvdepth_pix, grad_acc, gx, order_bwd, ballots, nullptr, nullptr, nullptr);
+        else if (pair)
+            blend_backward_kernel<false, true><<<num_tiles, TILE_PIX, smem, stream>>>(
                 hdr, ranges, v0, v1, W, H, background, splat, feat, xy, co, final_T, n_contrib, dL_dpix, nullptr,
-                grad_acc, gx, order_bwd, ballots);
+                grad_acc, gx, order_bwd, ballots, feat_b, background_b, dL_dpix_b);
+        else
+            blend_backward_kernel<false, false><<<num_tiles, TILE_PIX, smem, stream>>>(
+                hdr, ranges, v0, v1, W, H, background, splat, feat, xy, co, final_T, n_contrib, dL_dpix, nullptr,
+                grad_acc, gx, order_bwd, ballots, nullptr, nullptr, nullptr);
     }
     D3GA_LAUNCH_CHECK();
     return D3GA_OK;

@@ -259,14 +259,19 @@ def _shared_forward(lib, dev, P, W, H, rs, colors_precomp, want_invdepth, gkey, 
 
 
 def rasterize_forward(means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp, rs,
-                      want_invdepth=True):
+                      want_invdepth=True, pair=None):
+    """`pair` = (colors_b [P,3], bg_b [3]): a second image of the same Gaussians is blended in the same walk
+    (d3ga_raster_forward_render_pair) and returned as a fifth value; no inverse depth then."""
     lib = _lib.load()
     dev = means3D.device
     P = int(means3D.shape[0])
     W, H = int(rs.image_width), int(rs.image_height)
     M = 0 if sh is None else int(sh.shape[1])
     gkey = cam = None
-    if SHARE_GEOMETRY and P > 0 and sh is None:
+    if pair is not None:
+        want_invdepth = False
+        colors_b, bg_b = _f32c(pair[0], "colors_b"), _f32c(pair[1], "bg_b")
+    if SHARE_GEOMETRY and P > 0 and sh is None and pair is None:
         gkey = (P, W, H, float(rs.tanfovx), float(rs.tanfovy), float(rs.scale_modifier), bool(rs.antialiasing))
         geo_now = (means3D, opacities, scales, rotations, cov3Ds_precomp)
         ent = _geom_cache.get(dev)
@@ -285,6 +290,7 @@ def rasterize_forward(means3D, sh, colors_precomp, opacities, scales, rotations,
         stream = _lib.raw_stream(dev)
         color = torch.empty((3, H, W), dtype=torch.float32, device=dev)
         invdepth = torch.empty((1, H, W), dtype=torch.float32, device=dev) if want_invdepth else None
+        color_b = torch.empty((3, H, W), dtype=torch.float32, device=dev) if pair is not None else None
         radii = torch.empty((P,), dtype=torch.int32, device=dev)
         st = RasterState()
         st.P, st.W, st.H = P, W, H
@@ -308,9 +314,15 @@ def rasterize_forward(means3D, sh, colors_precomp, opacities, scales, rotations,
                 "raster_forward_geometry")
             if not defer:
                 ev.record()
-            _lib.check(lib.d3ga_raster_forward_render(
-                P, W, H, bg.data_ptr(), _lib.ptr(colors_precomp), st.geom.data_ptr(), st.binning.data_ptr(), cap,
-                st.image.data_ptr(), color.data_ptr(), _lib.ptr(invdepth), stream), "raster_forward_render")
+            if pair is None:
+                _lib.check(lib.d3ga_raster_forward_render(
+                    P, W, H, bg.data_ptr(), _lib.ptr(colors_precomp), st.geom.data_ptr(), st.binning.data_ptr(), cap,
+                    st.image.data_ptr(), color.data_ptr(), _lib.ptr(invdepth), stream), "raster_forward_render")
+            else:
+                _lib.check(lib.d3ga_raster_forward_render_pair(
+                    P, W, H, bg.data_ptr(), _lib.ptr(colors_precomp), bg_b.data_ptr(), colors_b.data_ptr(),
+                    st.geom.data_ptr(), st.binning.data_ptr(), cap, st.image.data_ptr(), color.data_ptr(),
+                    color_b.data_ptr(), stream), "raster_forward_render_pair")
             if defer:
                 # (num_rendered, overflow) are the first two words of the geometry workspace's header
                 stats = _deferred_stats_tensor(dev)
@@ -339,13 +351,16 @@ def rasterize_forward(means3D, sh, colors_precomp, opacities, scales, rotations,
         _geom_cache[dev] = {"key": gkey, "cam": cam, "state": st, "radii": radii,
                             "tensors": tuple(None if t is None else (t.detach(), t._version) for t in geo_now)}
         share_stats["misses"] += 1
+    if pair is not None:
+        return color, radii, invdepth, st, color_b
     return color, radii, invdepth, st
 
 
 def rasterize_backward(st, grad_color, grad_invdepth, means3D, sh, colors_precomp, opacities, scales, rotations,
-                       cov3Ds_precomp, radii, rs, want_means2D=True):
+                       cov3Ds_precomp, radii, rs, want_means2D=True, pair=None):
     """`want_means2D=False` skips the screen-space gradient (12 B per Gaussian nobody reads when means2D does not require
-    grad; the reference's own call site retains it: renderer.py:122-126)."""
+    grad; the reference's own call site retains it: renderer.py:122-126).  `pair` = (bg_b, grad_color_b): the backward of
+    a pair render (d3ga_raster_backward_pair)."""
     lib = _lib.load()
     dev = means3D.device
     P, W, H = st.P, st.W, st.H
@@ -363,15 +378,22 @@ def rasterize_backward(st, grad_color, grad_invdepth, means3D, sh, colors_precom
         g_cov = torch.empty((P, 6), dtype=torch.float32, device=dev) if cov3Ds_precomp is not None else None
         g_scales = torch.empty((P, 3), dtype=torch.float32, device=dev) if scales is not None else None
         g_rot = torch.empty((P, 4), dtype=torch.float32, device=dev) if rotations is not None else None
-        _lib.check(lib.d3ga_raster_backward(
-            P, int(rs.sh_degree), M, W, H, _f32c(rs.bg, "bg").data_ptr(), _lib.ptr(means3D), _lib.ptr(colors_precomp),
-            _lib.ptr(opacities), _lib.ptr(scales), float(rs.scale_modifier), _lib.ptr(rotations),
-            _lib.ptr(cov3Ds_precomp), _lib.ptr(sh), _f32c(rs.viewmatrix, "viewmatrix").data_ptr(),
-            _f32c(rs.projmatrix, "projmatrix").data_ptr(), _f32c(rs.campos, "campos").data_ptr(), float(rs.tanfovx),
-            float(rs.tanfovy), int(bool(rs.antialiasing)), _lib.ptr(radii), st.geom.data_ptr(), st.binning.data_ptr(),
-            st.capacity, st.image.data_ptr(), grad_color.data_ptr(), _lib.ptr(grad_invdepth), scratch.data_ptr(),
-            _lib.ptr(g_means2D), g_opacity.data_ptr(), _lib.ptr(g_colors), g_means3D.data_ptr(), _lib.ptr(g_cov),
-            _lib.ptr(g_sh), _lib.ptr(g_scales), _lib.ptr(g_rot), stream), "raster_backward")
+        common = (_lib.ptr(means3D), _lib.ptr(colors_precomp),
+                  _lib.ptr(opacities), _lib.ptr(scales), float(rs.scale_modifier), _lib.ptr(rotations),
+                  _lib.ptr(cov3Ds_precomp), _lib.ptr(sh), _f32c(rs.viewmatrix, "viewmatrix").data_ptr(),
+                  _f32c(rs.projmatrix, "projmatrix").data_ptr(), _f32c(rs.campos, "campos").data_ptr(), float(rs.tanfovx),
+                  float(rs.tanfovy), int(bool(rs.antialiasing)), _lib.ptr(radii), st.geom.data_ptr(), st.binning.data_ptr(),
+                  st.capacity, st.image.data_ptr(), grad_color.data_ptr())
+        outs = (scratch.data_ptr(), _lib.ptr(g_means2D), g_opacity.data_ptr(), _lib.ptr(g_colors), g_means3D.data_ptr(),
+                _lib.ptr(g_cov), _lib.ptr(g_sh), _lib.ptr(g_scales), _lib.ptr(g_rot), stream)
+        if pair is None:
+            _lib.check(lib.d3ga_raster_backward(P, int(rs.sh_degree), M, W, H, _f32c(rs.bg, "bg").data_ptr(), *common,
+                                                _lib.ptr(grad_invdepth), *outs), "raster_backward")
+        else:
+            bg_b, grad_b = _f32c(pair[0], "bg_b"), _f32c(pair[1], "grad_color_b")
+            _lib.check(lib.d3ga_raster_backward_pair(P, int(rs.sh_degree), M, W, H, _f32c(rs.bg, "bg").data_ptr(),
+                                                     bg_b.data_ptr(), *common, grad_b.data_ptr(), *outs),
+                       "raster_backward_pair")
     return g_means3D, g_means2D, g_sh, g_colors, g_opacity, g_scales, g_rot, g_cov
 
 
@@ -409,6 +431,52 @@ class _RasterizeGaussians(torch.autograd.Function):
         return g_means3D, g_means2D, g_sh, g_colors, g_opacity, g_scales, g_rot, g_cov, None
 
 
+class _RasterizePair(torch.autograd.Function):
+    """Two images of the same Gaussians from the same camera in one pass over the tile lists: what
+    the two render() calls of models/trainer.py:102-110 produce -- (colors_precomp, raster_settings.bg) and (colors_b,
+    bg_b) -- with ONE binning, ONE blend forward and ONE blend backward.  colors_b and bg_b get no gradient (D3GA's
+    silhouette colours are constants: models/cage_net.py:243)."""
+
+    @staticmethod
+    def forward(ctx, means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp, colors_b, bg_b,
+                raster_settings):
+        if colors_b.requires_grad or bg_b.requires_grad:
+            raise RuntimeError("the second image's colours and background get no gradient from a pair render: "
+                               "detach them, or render twice")
+        means3D = _f32c(means3D, "means3D")
+        sh = _f32c(sh, "shs")
+        colors_precomp = _f32c(colors_precomp, "colors_precomp")
+        opacities = _f32c(opacities, "opacities")
+        scales = _f32c(scales, "scales")
+        rotations = _f32c(rotations, "rotations")
+        cov3Ds_precomp = _f32c(cov3Ds_precomp, "cov3D_precomp")
+        colors_b, bg_b = _f32c(colors_b, "colors_b"), _f32c(bg_b, "bg_b")
+        if colors_b.shape != (means3D.shape[0], 3) or bg_b.numel() != 3:
+            raise RuntimeError("colors_b must be [P,3] and bg_b [3]")
+        color, radii, _, st, color_b = rasterize_forward(means3D, sh, colors_precomp, opacities, scales, rotations,
+                                                         cov3Ds_precomp, raster_settings, pair=(colors_b, bg_b))
+        ctx.raster_settings = raster_settings
+        ctx.state = st
+        ctx.save_for_backward(means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp, radii, bg_b)
+        ctx.mark_non_differentiable(radii)
+        ctx.set_materialize_grads(False)
+        return color, color_b, radii
+
+    @staticmethod
+    def backward(ctx, grad_color, grad_color_b, _grad_radii):
+        means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp, radii, bg_b = ctx.saved_tensors
+        st, rs = ctx.state, ctx.raster_settings
+        zeros = lambda: torch.zeros((3, st.H, st.W), dtype=torch.float32, device=means3D.device)  # noqa: E731
+        grad_color = zeros() if grad_color is None else grad_color
+        grad_color_b = zeros() if grad_color_b is None else grad_color_b
+        g = rasterize_backward(st, grad_color, None, means3D, sh, colors_precomp, opacities, scales, rotations,
+                               cov3Ds_precomp, radii, rs, want_means2D=ctx.needs_input_grad[1], pair=(bg_b, grad_color_b))
+        g_means3D, g_means2D, g_sh, g_colors, g_opacity, g_scales, g_rot, g_cov = g
+        if opacities is not None and g_opacity.shape != opacities.shape:
+            g_opacity = g_opacity.reshape(opacities.shape)
+        return g_means3D, g_means2D, g_sh, g_colors, g_opacity, g_scales, g_rot, g_cov, None, None, None
+
+
 def rasterize_gaussians(means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
                         raster_settings):
     return _RasterizeGaussians.apply(means3D, means2D, sh, colors_precomp, opacities, scales, rotations,
@@ -433,6 +501,20 @@ class GaussianRasterizer(nn.Module):
                                                      _lib.ptr(present), torch.cuda.current_stream().cuda_stream),
                        "mark_visible")
         return present
+
+    def forward_pair(self, means3D, means2D, opacities, colors_b, bg_b, shs=None, colors_precomp=None, scales=None,
+                     rotations=None, cov3D_precomp=None):
+        """(image, image_b, radii): `forward(...)`'s image plus a second image of the same Gaussians with colours
+        `colors_b` [P,3] over background `bg_b` [3], from one pass (see _RasterizePair).  An addition to the reference's
+        API: its two render() calls per training frame (models/trainer.py:102-110) become one."""
+        if (shs is None) == (colors_precomp is None):
+            raise Exception("Please provide excatly one of either SHs or precomputed colors!")
+        if ((scales is None or rotations is None) and cov3D_precomp is None) or (
+            (scales is not None or rotations is not None) and cov3D_precomp is not None
+        ):
+            raise Exception("Please provide exactly one of either scale/rotation pair or precomputed 3D covariance!")
+        return _RasterizePair.apply(means3D, means2D, shs, colors_precomp, opacities, scales, rotations, cov3D_precomp,
+                                    colors_b, bg_b, self.raster_settings)
 
     def forward(self, means3D, means2D, opacities, shs=None, colors_precomp=None, scales=None, rotations=None,
                 cov3D_precomp=None):

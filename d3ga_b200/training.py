@@ -424,13 +424,23 @@ def multi_view_step_graphed(avatar, bank, cam_ids, gv, weights=None, from_host=F
         gv.capture(bank.dev[cam_ids[0]])     # the capacity hint now covers the largest view seen
 
 
-def frame_step(avatar, bank, cam_id, weights, bg, fem_weight=1.0):
+def frame_step(avatar, bank, cam_id, weights, bg, fem_weight=1.0, fused_pair=False):
     """One D3GA training frame on the hot path (models/trainer.py:91-140): the deformation block once -- with the cage's
     neo-Hookean energy of cage_net.py:225 out of the same launch --, then TWO renders of the same Gaussians -- RGB on a
     random background and the silhouette (constant colour, black background), each through its own render() call with its
-    own Camera object -- and one backward through both plus the energy term (train.py:186-244 adds it to the loss)."""
+    own Camera object -- and one backward through both plus the energy term (train.py:186-244 adds it to the loss).
+    `fused_pair`: the two renders as ONE GaussianRasterizer.forward_pair call (one binning, one blend each way)."""
     means3D, cov6, energy = deform_gaussians(avatar.tetpoints, avatar.tets, avatar.tetra_id, avatar.barys, avatar.cg,
                                              avatar.scaling, avatar.rotation, log_scales=True, dn_inv=avatar.dn_inv)
+    if fused_pair:
+        rs = bank.settings(cam_id, avatar.W, avatar.H, bg)
+        means2D = torch.zeros_like(means3D, requires_grad=True) + 0
+        img, sil, _ = GaussianRasterizer(raster_settings=rs).forward_pair(
+            means3D=means3D, means2D=means2D, opacities=avatar.opacity, colors_b=avatar.silhouette,
+            bg_b=torch.zeros_like(bg), colors_precomp=avatar.colors, cov3D_precomp=cov6)
+        loss = (img * weights).sum() + (sil * weights).sum() + fem_weight * energy.mean()
+        loss.backward()
+        return loss
     imgs = []
     for colors, background in ((avatar.colors, bg), (avatar.silhouette, torch.zeros_like(bg))):
         rs = bank.settings(cam_id, avatar.W, avatar.H, background)

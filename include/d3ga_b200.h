@@ -125,6 +125,19 @@ int d3ga_raster_forward_render(int P, int W, int H, const float *background, con
                                void *geom, void *binning, uint64_t capacity, void *image,
                                float *out_color, float *out_invdepth, d3ga_stream_t stream);
 
+/* Stage 2 for a PAIR of images of the same Gaussians from the same camera (the RGB and the
+ * silhouette render of a D3GA training frame, models/trainer.py:102-110) in ONE walk of the tile lists: out_color is what
+ * d3ga_raster_forward_render(background, colors_precomp) gives and out_color_b what a second render with
+ * (background_b, colors_b [P,3]) on the same geometry would give -- same alphas, same transmittance, same contributor
+ * set, so the two images are bit-identical to the two separate renders'.  No inverse depth in this form.
+ * d3ga_raster_backward_pair is its backward: dL_dout_color and dL_dout_color_b [3,H,W] both flow into dL_dmeans3D,
+ * dL_dmeans2D, dL_dopacity, dL_dcov3D / dL_dscales + dL_drotations; dL_dcolors (or dL_dsh) is the FIRST image's colour
+ * gradient; colors_b receives none (in D3GA it is a constant, models/cage_net.py:243). */
+int d3ga_raster_forward_render_pair(int P, int W, int H, const float *background, const float *colors_precomp,
+                                    const float *background_b, const float *colors_b, void *geom, void *binning,
+                                    uint64_t capacity, void *image, float *out_color, float *out_color_b,
+                                    d3ga_stream_t stream);
+
 /* Alpha blending (R6) alone, on the geometry and binning state an earlier d3ga_raster_forward_geometry +
  * d3ga_raster_forward_render pair left in `geom` / `binning` -- for a second render of the SAME Gaussians from the SAME
  * camera with other colours / background.  D3GA does exactly that every training frame: the RGB and the silhouette
@@ -155,6 +168,17 @@ int d3ga_raster_backward(int P, int sh_degree, int sh_coeffs, int W, int H, cons
                          float *dL_dmeans2D, float *dL_dopacity, float *dL_dcolors, float *dL_dmeans3D,
                          float *dL_dcov3D, float *dL_dsh, float *dL_dscales, float *dL_drotations,
                          d3ga_stream_t stream);
+
+int d3ga_raster_backward_pair(int P, int sh_degree, int sh_coeffs, int W, int H, const float *background,
+                              const float *background_b, const float *means3D, const float *colors_precomp,
+                              const float *opacities, const float *scales, float scale_modifier, const float *rotations,
+                              const float *cov3D_precomp, const float *shs, const float *viewmatrix,
+                              const float *projmatrix, const float *campos, float tanfovx, float tanfovy,
+                              int antialiasing, const int32_t *radii, const void *geom, const void *binning,
+                              uint64_t capacity, const void *image, const float *dL_dout_color,
+                              const float *dL_dout_color_b, void *grad_scratch, float *dL_dmeans2D, float *dL_dopacity,
+                              float *dL_dcolors, float *dL_dmeans3D, float *dL_dcov3D, float *dL_dsh, float *dL_dscales,
+                              float *dL_drotations, d3ga_stream_t stream);
 
 /* The same backward for hosts that cannot allocate device memory (no counterpart in the reference, whose Python
  * glue always has torch's allocator): a C/C++ playback or fitting loop without a caching allocator, where

@@ -579,3 +579,88 @@ def test_shared_geometry_second_render(cuda_lib, oracle_libs):
     assert dgr.share_stats["hits"] == h1
     _, r3 = util.oracle_forward(g2, cam2, W, H, [0, 0, 0])
     assert_image_close(img3.detach().cpu().numpy(), r3["color"])
+
+
+@pytest.mark.parametrize("case,layout", [("tiny_avatar", "cov"), ("tiny_avatar", "scale_rot"), ("c1", "cov")])
+def test_pair_render_is_the_two_renders_in_one_pass(cuda_lib, oracle_libs, case, layout):
+    """SURVEY.md 8(f) rank 1, the fused form: GaussianRasterizer.forward_pair gives the RGB image and the silhouette image of
+    models/trainer.py:102-110 from ONE binning, ONE blend forward and ONE blend backward.  Both images must be bit-identical
+    to two separate renders (same alphas, same transmittance, same contributor set), the geometry / opacity gradients must be
+    the SUM of the two renders' (checked against the oracle's two independent views), the first image's colours get their
+    own gradient and the second image's colours none."""
+    from d3ga_b200 import diff_gaussian_rasterization as dgr
+    from d3ga_b200.diff_gaussian_rasterization import GaussianRasterizationSettings, GaussianRasterizer
+
+    if case == "c1":
+        sc = synth.make_workload("c1")
+        means_np, cov_np = util.scene_geometry(sc)
+        g = dict(means=means_np, cov6=cov_np, opacity=sc.opacity, colors=sc.colors)
+        cam, W, H = synth.make_camera(sc.W, sc.H, 20, 10), sc.W, sc.H
+    else:
+        g, cam, W, H = CASES["tiny_avatar"]
+    if layout == "scale_rot" and "scales" not in g:
+        pytest.skip("case has no scale / rotation form")
+    d = gpu_util.dev
+    rng = np.random.default_rng(12)
+    P = g["means"].shape[0]
+    # piecewise-constant second colours, like the per-garment mask colours of models/cage_net.py:243
+    sil_np = np.where((np.arange(P) % 3 == 0)[:, None], [1.0, 0.0, 0.5], [0.2, 1.0, 0.0]).astype(np.float32)
+    bg_a, bg_b = [0.3, 0.6, 0.9], [0.0, 0.1, 0.0]
+
+    def settings(bg):
+        return GaussianRasterizationSettings(
+            image_height=H, image_width=W, tanfovx=cam.tanfovx, tanfovy=cam.tanfovy, bg=d(np.asarray(bg, np.float32)),
+            scale_modifier=1.0, viewmatrix=d(cam.viewmatrix), projmatrix=d(cam.projmatrix), sh_degree=0,
+            campos=d(cam.campos), prefiltered=False, debug=False, antialiasing=False)
+
+    def leaves():
+        out = dict(means=d(g["means"]).requires_grad_(True), op=d(g["opacity"]).requires_grad_(True),
+                   rgb=d(g["colors"]).requires_grad_(True))
+        if layout == "cov":
+            out["cov"] = d(g["cov6"]).requires_grad_(True)
+            out["geo"] = dict(cov3D_precomp=out["cov"])
+        else:
+            out["sc"], out["rot"] = d(g["scales"]).requires_grad_(True), d(g["rot"]).requires_grad_(True)
+            out["geo"] = dict(scales=out["sc"], rotations=out["rot"])
+        return out
+
+    w1, w2 = (d(rng.uniform(-1, 1, (3, H, W)).astype(np.float32)) for _ in range(2))
+    sil = d(sil_np)
+    # two separate renders
+    a = leaves()
+    dgr._geom_cache.clear()
+    i1 = GaussianRasterizer(settings(bg_a))(means3D=a["means"], means2D=torch.zeros_like(a["means"]), opacities=a["op"],
+                                            colors_precomp=a["rgb"], **a["geo"])[0]
+    i2 = GaussianRasterizer(settings(bg_b))(means3D=a["means"], means2D=torch.zeros_like(a["means"]), opacities=a["op"],
+                                            colors_precomp=sil, **a["geo"])[0]
+    ((i1 * w1).sum() + (i2 * w2).sum()).backward()
+    # one pair render
+    b = leaves()
+    j1, j2, radii = GaussianRasterizer(settings(bg_a)).forward_pair(
+        means3D=b["means"], means2D=torch.zeros_like(b["means"]), opacities=b["op"], colors_b=sil,
+        bg_b=d(np.asarray(bg_b, np.float32)), colors_precomp=b["rgb"], **b["geo"])
+    ((j1 * w1).sum() + (j2 * w2).sum()).backward()
+    assert torch.equal(j1, i1) and torch.equal(j2, i2)
+    for k in a:
+        if k == "geo":
+            continue
+        ga_, gb_ = a[k].grad, b[k].grad
+        assert gb_ is not None and float((ga_ - gb_).norm() / ga_.norm()) < 2e-5, k     # float atomics reorder
+    # and against the oracle's two independent views
+    if layout == "cov":
+        g2 = dict(g, colors=sil_np)
+        o1, r1 = util.oracle_forward(g, cam, W, H, bg_a)
+        o2, r2 = util.oracle_forward(g2, cam, W, H, bg_b)
+        assert_image_close(j1.detach().cpu().numpy(), r1["color"])
+        assert_image_close(j2.detach().cpu().numpy(), r2["color"])
+        ga, gb = o1.backward(r1, w1.cpu().numpy()), o2.backward(r2, w2.cpu().numpy())
+        assert util.rel_l2(b["means"].grad.cpu().numpy(), ga["means3D"] + gb["means3D"]) < GRAD_TOL
+        assert util.rel_l2(b["cov"].grad.cpu().numpy(), ga["cov3D"] + gb["cov3D"]) < GRAD_TOL
+        assert util.rel_l2(b["op"].grad.cpu().numpy().ravel(), ga["opacity"] + gb["opacity"]) < GRAD_TOL
+        assert util.rel_l2(b["rgb"].grad.cpu().numpy(), ga["colors"]) < GRAD_TOL
+    # the second image's colours cannot ask for a gradient
+    with pytest.raises(RuntimeError):
+        GaussianRasterizer(settings(bg_a)).forward_pair(
+            means3D=b["means"], means2D=torch.zeros_like(b["means"]), opacities=b["op"],
+            colors_b=sil.clone().requires_grad_(True), bg_b=d(np.asarray(bg_b, np.float32)), colors_precomp=b["rgb"],
+            **b["geo"])
