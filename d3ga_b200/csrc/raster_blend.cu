@@ -216,8 +216,11 @@ struct FwdWarpSmemT {
 // PAIR: a second image of the SAME Gaussians with other colours and another background (the silhouette pass of a D3GA
 // training frame, models/trainer.py:102-110) is blended in the same walk: same alphas, same transmittance, same
 // contributor set -- one more 16-byte colour per survivor and three more accumulators per pixel.
+#ifndef FWD_PAIR_MIN_CTAS
+#define FWD_PAIR_MIN_CTAS 2   // 99 registers, no spills: 180 us at 1 M / 1024^2; 3 CTAs (80 registers, 52 B of spills, 192 KB of shared memory): 292 us
+#endif
 template <bool INVDEPTH, bool PAIR>
-__global__ void __launch_bounds__(FWD_WARPS * 32, FWD_MIN_CTAS) blend_forward_kernel(
+__global__ void __launch_bounds__(FWD_WARPS * 32, PAIR ? FWD_PAIR_MIN_CTAS : FWD_MIN_CTAS) blend_forward_kernel(
     const RasterHeader *__restrict__ hdr, const uint2 *__restrict__ ranges, const uint32_t *__restrict__ vals0,
     const uint32_t *__restrict__ vals1, int W, int H, const SplatRecord *__restrict__ splat,
     const float4 *__restrict__ feat, const float2 *__restrict__ xy, const float4 *__restrict__ conic_opacity,
