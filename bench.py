@@ -388,11 +388,30 @@ def run_ours(args):
             torch.cuda.synchronize()
             pair[name] = nfr / (a.elapsed_time(b) * 1e-3)
         dgr.SHARE_GEOMETRY = True
+        # the fused frame captured into CUDA graphs and replayed with several frames in flight, like the headline's views
+        if pv is not None:
+            try:
+                pvf = training.PipelinedViews(avatar, cams[0], bg, lanes=args.lanes, step=training.frame_pair_step)
+                stepf = lambda ids: training.multi_view_step_pipelined(avatar, bank, ids, pvf, weights=weights)  # noqa: E731
+                for s_ in range(3):
+                    stepf(cam_ids(s_))
+                torch.cuda.synchronize()
+                a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                a.record()
+                for s_ in range(args.steps):
+                    stepf(cam_ids(args.warmup + s_))
+                b.record()
+                torch.cuda.synchronize()
+                pair["frames_per_s_fused_pair_graph_replay"] = V * args.steps / (a.elapsed_time(b) * 1e-3)
+                del pvf
+            except Exception as e:   # noqa: BLE001
+                pair["frames_per_s_fused_pair_graph_replay"] = f"{type(e).__name__}: {e}"
         pair["note"] = ("1 frame = deformation block incl. the cage's FEM energy (one launch each way) + RGB render + silhouette "
                         "render + backward of all three terms (models/trainer.py:91-140, models/cage_net.py:213-230), eager "
                         "launches; fused_pair = both images from one GaussianRasterizer.forward_pair call (one binning, one "
                         "blend forward, one blend backward), shared_geometry = the reference's two render() calls with the "
-                        "second one re-using the first one's binning")
+                        "second one re-using the first one's binning; fused_pair_graph_replay = the fused frame as one CUDA-graph replay "
+                        "per frame with the headline's number of frames in flight")
 
     # the cage-vertex skinning that produces tetpoints (Blueman.get), forward + backward to delta
     lbs = None

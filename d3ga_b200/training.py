@@ -107,6 +107,24 @@ def view_step(avatar, rs, weights):
     return loss
 
 
+def frame_pair_step(avatar, rs, weights, fem_weight=1.0):
+    """One D3GA training FRAME with the settings `rs` (models/trainer.py:91-140): the deformation block with the cage's
+    energy out of the same launch, the RGB render over rs.bg and the silhouette render over black as ONE
+    GaussianRasterizer.forward_pair call, and one backward through both images and the energy term.  Same signature as
+    view_step, so GraphedViewStep / PipelinedViews can capture and replay it (step=frame_pair_step)."""
+    means3D, cov6, energy = deform_gaussians(avatar.tetpoints, avatar.tets, avatar.tetra_id, avatar.barys, avatar.cg,
+                                             avatar.scaling, avatar.rotation, log_scales=True, dn_inv=avatar.dn_inv)
+    if avatar._means2D is None or avatar._means2D.shape != means3D.shape:
+        avatar._means2D = torch.zeros_like(means3D)
+    img, sil, _ = GaussianRasterizer(raster_settings=rs).forward_pair(
+        means3D=means3D, means2D=avatar._means2D, opacities=avatar.opacity, colors_b=avatar.silhouette,
+        bg_b=torch.zeros_like(rs.bg), colors_precomp=avatar.colors, cov3D_precomp=cov6)
+    loss = (torch.dot(img.detach().reshape(-1), weights.reshape(-1)) + torch.dot(sil.detach().reshape(-1), weights.reshape(-1))
+            + fem_weight * energy.detach().mean())
+    torch.autograd.backward([img, sil, energy], [weights, weights, torch.full_like(energy, fem_weight / energy.numel())])
+    return loss
+
+
 U8_SCALE, U8_OFFSET = 2.0 / 255.0, -1.0   # a uint8 target / weight image stands for u8 * U8_SCALE + U8_OFFSET
 _u8_offset: dict = {}
 
@@ -215,11 +233,12 @@ class GraphedViewStep:
     overflow) into a device counter and `finish()` reads it back: if a view overflowed, the hint has been raised, the
     graph must be captured again (`capture()`) and the step redone -- `multi_view_step(..., graphed=...)` does that."""
 
-    def __init__(self, avatar, cam, bg, weights=None, views_in_flight=1):
+    def __init__(self, avatar, cam, bg, weights=None, views_in_flight=1, step=None):
         from d3ga_b200 import diff_gaussian_rasterization as dgr
         self.dgr = dgr
         self.avatar = avatar
         self.views_in_flight = int(views_in_flight)   # how many such graphs the caller replays concurrently
+        self.step = view_step if step is None else step   # what one replay does: (avatar, settings, weights) -> loss
         dev = avatar.device
         self.cam = torch.zeros(35, dtype=torch.float32, device=dev)
         self.weights = torch.empty((3, avatar.H, avatar.W), dtype=torch.float32, device=dev) if weights is None else weights
@@ -249,7 +268,7 @@ class GraphedViewStep:
             side.wait_stream(torch.cuda.current_stream())
             with torch.cuda.stream(side):
                 for _ in range(2):
-                    view_step(self.avatar, self.rs, self.weights)
+                    self.step(self.avatar, self.rs, self.weights)
             torch.cuda.current_stream().wait_stream(side)
             self.avatar.grads.flat.copy_(keep)
             self.dgr._capacity_hint[hkey] = max(hint, self.dgr._capacity_hint.get(hkey, 0))
@@ -265,7 +284,7 @@ class GraphedViewStep:
         lib.d3ga_set_views_in_flight(self.views_in_flight)
         try:
             with self.dgr.deferred_overflow_check(), torch.cuda.graph(self.graph, stream=self.capture_stream):
-                loss = view_step(self.avatar, self.rs, self.weights)
+                loss = self.step(self.avatar, self.rs, self.weights)
                 self.total += loss.detach()
         finally:
             lib.d3ga_set_views_in_flight(1)
@@ -312,11 +331,11 @@ class PipelinedViews:
         free, _ = torch.cuda.mem_get_info(avatar.device)
         return int(max(1, min(wanted, fraction * free // per_lane)))
 
-    def __init__(self, avatar, cam, bg, lanes=2):
+    def __init__(self, avatar, cam, bg, lanes=2, step=None):
         self.avatar = avatar
         self.shadows = [avatar.shadow() for _ in range(lanes)]
         self.streams = [torch.cuda.Stream(device=avatar.device) for _ in range(lanes)]
-        self.gvs = [GraphedViewStep(sh, cam, bg, views_in_flight=lanes) for sh in self.shadows]
+        self.gvs = [GraphedViewStep(sh, cam, bg, views_in_flight=lanes, step=step) for sh in self.shadows]
 
     @property
     def captures(self):

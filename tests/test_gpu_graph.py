@@ -209,3 +209,27 @@ def test_tet_sorted_storage_is_the_same_avatar(cuda_lib):
     assert rel(av2.tetpoints.grad, avatar.tetpoints.grad) < 1e-4
     for name in ("barys", "scaling", "rotation", "opacity", "colors"):
         assert rel(getattr(av2, name).grad, getattr(avatar, name).grad[order]) < 1e-4, name
+
+
+def test_graphed_frame_pair_matches_eager(cuda_lib):
+    """training.frame_pair_step (deformation with the cage energy + the fused RGB / silhouette render + backward) captured
+    into graphs and replayed with two frames in flight gives the eager frame loop's loss and gradients."""
+    dev, scene, cams, avatar, bank, bg, wh = setup()
+    w = wh.to(dev)
+    ids = [0, 3, 5, 6]
+    avatar.grads.zero_()
+    tot_e = None
+    for i in ids:
+        rs = bank.settings(i, avatar.W, avatar.H, bg)
+        loss = training.frame_pair_step(avatar, rs, w)
+        tot_e = loss.detach().clone() if tot_e is None else tot_e + loss.detach()
+    g_e = avatar.grads.flat.clone()
+    # the eager two-call frame of the reference's trainer gives the same gradients
+    avatar.grads.zero_()
+    for i in ids:
+        training.frame_step(avatar, bank, i, w, bg)
+    assert rel(avatar.grads.flat, g_e) < 1e-5
+    pv = training.PipelinedViews(avatar, cams[0], bg, lanes=2, step=training.frame_pair_step)
+    tot_p = training.multi_view_step_pipelined(avatar, bank, ids, pv, weights=w)
+    assert abs(float(tot_p) - float(tot_e)) <= 1e-5 * abs(float(tot_e))
+    assert rel(avatar.grads.flat, g_e) < 1e-5
