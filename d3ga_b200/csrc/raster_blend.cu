@@ -243,10 +243,27 @@ __global__ void __launch_bounds__(FWD_WARPS * 32, PAIR ? FWD_PAIR_MIN_CTAS : FWD
     for (int i = (int)lane; i < RING * NF; i += 32) (&sm.ring[0][0])[i] = make_float4(0.f, 0.f, 0.f, 0.f);
     __syncwarp();
     const uint32_t tile = order_fwd[blockIdx.x];   // longest Gaussian list first
-    const WarpBlock wb = warp_block((int)warp, (int)lane, (int)(tile % (uint32_t)grid_x), (int)(tile / (uint32_t)grid_x));
+    WarpBlock wb = warp_block((int)warp, (int)lane, (int)(tile % (uint32_t)grid_x), (int)(tile / (uint32_t)grid_x));
     const int px = wb.px, py = wb.py;
     const bool inside = px < W && py < H;
     const float pxf = (float)px, pyf = (float)py;
+    const float blk_x0 = wb.x0, blk_y0 = wb.y0;
+    // The footprint test runs against the bounding box of the block's pixels that are STILL BEING BLENDED, not against
+    // the whole 8x4 block: on a silhouette tile the pixels inside the body saturate early and the rest of the (long) list
+    // only matters to the few pixels outside it, so most of what follows no longer survives -- in this kernel and, through
+    // the ballots, in the backward.  An entry culled this way contributes nothing: a finished pixel takes no entry, an
+    // active pixel lies inside the box the (conservative) test was made against.  active_box() is called when the set of
+    // active pixels has changed (bit l of the mask = lane l = pixel (l % 8, l / 8) of the block).
+    uint32_t act_mask = 0xffffffffu;
+    auto active_box = [&](uint32_t m) {
+        act_mask = m;
+        if (m == 0u) return;
+        const uint32_t cols = (m | (m >> 8) | (m >> 16) | (m >> 24)) & 0xffu;        // columns with an active pixel
+        const int xlo = __ffs((int)cols) - 1, xhi = 31 - __clz((int)cols);
+        const int ylo = (__ffs((int)m) - 1) >> 3, yhi = (31 - __clz((int)m)) >> 3;
+        wb.x0 = blk_x0 + (float)xlo; wb.x1 = blk_x0 + (float)xhi;
+        wb.y0 = blk_y0 + (float)ylo; wb.y1 = blk_y0 + (float)yhi;
+    };
     uint2 range = make_uint2(0, 0);
     if (!hdr->overflow) range = ranges[tile];
     const uint32_t *point_list = (hdr->final_sel ? vals1 : vals0) + range.x;
@@ -259,7 +276,8 @@ __global__ void __launch_bounds__(FWD_WARPS * 32, PAIR ? FWD_PAIR_MIN_CTAS : FWD
     float D0 = 0.f, D1 = 0.f, D2 = 0.f;     // PAIR: the second image
     uint32_t last = 0;
     uint32_t head = 0, tail = 0;
-    bool all_done = __all_sync(0xffffffffu, done);
+    active_box(__ballot_sync(0xffffffffu, !done));
+    bool all_done = act_mask == 0u;
 #ifdef D3GA_BLEND_TRACE
     const unsigned long long tr_t0 = global_ns();
     uint32_t tr_chunks = 0;
@@ -401,7 +419,11 @@ __global__ void __launch_bounds__(FWD_WARPS * 32, PAIR ? FWD_PAIR_MIN_CTAS : FWD
             last = w1 != 0.f ? gpos[1] : last;
             last = w2 != 0.f ? gpos[2] : last;
             last = w3 != 0.f ? gpos[3] : last;
-            if (__all_sync(0xffffffffu, done)) { all_done = true; return; }
+            {
+                const uint32_t still = __ballot_sync(0xffffffffu, !done);
+                if (still == 0u) { all_done = true; return; }
+                if (still != act_mask) active_box(still);
+            }
             if (navail == 0u) return;
 #pragma unroll
             for (int u = 0; u < 4; u++) { ga[u] = na[u]; gpos[u] = npos[u]; }
