@@ -767,11 +767,16 @@ __global__ void __launch_bounds__(TILE_PIX, BWD_MIN_CTAS) blend_backward_kernel(
     };
 
     for (int fc = top; fc >= 0; fc--) {
-        // the survivors staged by the previous steps (their records have had a whole step to land)
-        cp_async_wait_all();
-        __syncwarp();
-        consume(false);
         const uint32_t mf = m_next, id = id_next;
+        // a chunk none of whose entries reached this warp's pixels, with less than a group waiting: nothing to blend and
+        // nothing to stage -- only the look-ahead moves on (deep in a silhouette tile's list most chunks are like that)
+        const bool idle = mf == 0u && tail - head < 4u;
+        if (!idle) {
+            // the survivors staged by the previous steps (their records have had a whole step to land)
+            cp_async_wait_all();
+            __syncwarp();
+            consume(false);
+        }
         m_next = m_next2;
         id_next = id_next2;
         if (fc > 1) {
@@ -787,7 +792,7 @@ __global__ void __launch_bounds__(TILE_PIX, BWD_MIN_CTAS) blend_backward_kernel(
             if (PAIR) bwd_cp_async_16(&sm.ring[s][NF - 1], feat_b + id);
             sm.ring_m[s] = make_uint2(id, 32u * (uint32_t)fc + 31u - lane);
         }
-        cp_async_commit();
+        if (mf != 0u) cp_async_commit();
         tail += __popc(m);
 #ifdef D3GA_BLEND_TRACE
         tr_surv += __popc(m);
