@@ -20,7 +20,8 @@ EXPORTS = [
     "d3ga_raster_backward_scratch_bytes", "d3ga_raster_backward", "d3ga_raster_backward_noalloc", "d3ga_raster_layout",
     "d3ga_raster_forward_render_pair", "d3ga_raster_backward_pair",
     "d3ga_deform_forward", "d3ga_deform_backward", "d3ga_deform_backward_ordered", "d3ga_deform_forward_fused",
-    "d3ga_deform_backward_fused", "d3ga_compute_bary",
+    "d3ga_deform_backward_fused", "d3ga_deform_backward_fused_sparse", "d3ga_deform_backward_scratch_bytes",
+    "d3ga_compute_bary",
     "d3ga_fem_energy_forward", "d3ga_fem_energy_backward", "d3ga_ssim_l1_forward", "d3ga_ssim_l1_backward",
     "d3ga_lbs_skeleton_forward", "d3ga_lbs_states_to_matrix", "d3ga_lbs_skin_forward", "d3ga_lbs_skin_backward", "d3ga_lbs_unskin_forward",
     "d3ga_lbs_skin_dense_forward", "d3ga_lbs_skin_dense_backward",
@@ -91,6 +92,9 @@ def load() -> C.CDLL:
     lib.d3ga_deform_backward_ordered.argtypes = [i32, i32, i32] + [vp] * 15
     lib.d3ga_deform_forward_fused.argtypes = [i32, i32, i32] + [vp] * 8 + [i32] + [vp] * 7
     lib.d3ga_deform_backward_fused.argtypes = [i32, i32, i32] + [vp] * 8 + [i32] + [vp] * 11 + [i32, i32, vp]
+    lib.d3ga_deform_backward_fused_sparse.argtypes = [i32, i32, i32] + [vp] * 8 + [i32] + [vp] * 10 + [i32, i32, vp, vp]
+    lib.d3ga_deform_backward_scratch_bytes.argtypes = [i32]
+    lib.d3ga_deform_backward_scratch_bytes.restype = u64
     lib.d3ga_fem_energy_forward.argtypes = [i32, i32, vp, vp, vp, vp, vp]
     lib.d3ga_fem_energy_backward.argtypes = [i32, i32, vp, vp, vp, vp, vp, vp]
     lib.d3ga_ssim_l1_forward.argtypes = [i32, i32, i32, vp, vp, vp, vp, vp, vp, vp]

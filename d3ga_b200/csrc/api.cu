@@ -33,7 +33,7 @@ static const char *const g_kernel_names[K_COUNT] = {
     "ssim_forward_kernel", "ssim_backward_kernel", "lbs_skeleton_kernel", "lbs_skin_forward_kernel",
     "lbs_skin_backward_kernel", "lbs_unskin_kernel", "lbs_skin_dense_forward_kernel", "lbs_skin_dense_backward_kernel",
     "rect_grid_kernel", "tile_plan_kernel", "direct_count_kernel", "direct_segsum_kernel", "direct_plan_kernel",
-    "direct_base_kernel", "direct_scatter_kernel", "pack_features_kernel"};
+    "direct_base_kernel", "direct_scatter_kernel", "pack_features_kernel", "deform_select_kernel"};
 
 bool profiling_enabled() { return g_prof_on.load(std::memory_order_relaxed) != 0; }
 

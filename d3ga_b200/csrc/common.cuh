@@ -164,7 +164,7 @@ enum KernelId {
     K_GEOMETRY = 0, K_SORT_HIST, K_SORT_PASS, K_RANGES, K_BLEND_FWD, K_BLEND_BWD, K_PRE_BWD, K_DEFORM_FWD, K_DEFORM_BWD,
     K_BARY, K_PREPROCESS, K_EMIT, K_DEPTH_HIST, K_DEPTH_PASS, K_FEM_FWD, K_FEM_BWD, K_SSIM_FWD, K_SSIM_BWD,
     K_LBS_SKELETON, K_LBS_SKIN_FWD, K_LBS_SKIN_BWD, K_LBS_UNSKIN, K_LBS_DENSE_FWD, K_LBS_DENSE_BWD, K_RECT_GRID, K_TILE_PLAN,
-    K_DIRECT_COUNT, K_DIRECT_SEGSUM, K_DIRECT_PLAN, K_DIRECT_BASE, K_DIRECT_SCATTER, K_PACK_FEAT, K_COUNT
+    K_DIRECT_COUNT, K_DIRECT_SEGSUM, K_DIRECT_PLAN, K_DIRECT_BASE, K_DIRECT_SCATTER, K_PACK_FEAT, K_DEFORM_SELECT, K_COUNT
 };
 // Optional per-kernel CUDA-event timing (d3ga_profile_* in the C-ABI; bench.py's roofline figures come from it).
 // A no-op unless profiling is enabled.

@@ -36,8 +36,6 @@ __global__ void __launch_bounds__(GEO_THREADS) preprocess_backward_kernel(const 
     __syncthreads();
     const int i = blockIdx.x * GEO_THREADS + tid;
     if (i >= p.P) return;
-    const bool live = p.radii[i] > 0;
-
     float acc[GRAD_ACC_FLOATS];
     {
         const float4 *row = reinterpret_cast<const float4 *>(p.grad_acc + (size_t)i * GRAD_ACC_FLOATS);
@@ -46,7 +44,15 @@ __global__ void __launch_bounds__(GEO_THREADS) preprocess_backward_kernel(const 
         acc[4] = b.x; acc[5] = b.y; acc[6] = b.z; acc[7] = b.w;
         acc[8] = c.x; acc[9] = c.y; acc[10] = c.z; acc[11] = c.w;
     }
-    {
+    // A Gaussian the blend backward never added to -- culled, or behind the surface that saturated the pixels: 86-93 % of
+    // a 1 M-Gaussian avatar per camera -- has an all-zero accumulator and all-zero gradients: nothing else of it is read
+    // (52 of its 104 B), nothing is computed, its zeros are written.
+    bool live = false;
+#pragma unroll
+    for (int k = 0; k < GRAD_ACC_FLOATS; k++) live |= acc[k] != 0.f;
+    live = live && p.radii[i] > 0;
+    float mx = 0.f, my = 0.f, mz = 0.f, c6[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    if (live) {
         // the blend backward accumulates raw moments of p = G dL/dalpha about the 2-D centre:
         // (sum p dx, sum p dy, sum p dx^2, sum p dx dy, sum p dy^2, sum p); with dL/dG = opacity dL/dalpha they give
         // the six derivatives upstream accumulates per pixel
@@ -57,13 +63,12 @@ __global__ void __launch_bounds__(GEO_THREADS) preprocess_backward_kernel(const 
         acc[2] *= -0.5f * co.w;
         acc[3] *= -0.5f * co.w;
         acc[4] *= -0.5f * co.w;
+        mx = p.means3D[3 * (size_t)i]; my = p.means3D[3 * (size_t)i + 1]; mz = p.means3D[3 * (size_t)i + 2];
+#pragma unroll
+        for (int k = 0; k < 6; k++) c6[k] = p.cov3D[6 * (size_t)i + k];
     }
     float dmean[3] = {0.f, 0.f, 0.f}, dc[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
     float dop = live ? acc[5] : 0.f;
-    const float mx = p.means3D[3 * (size_t)i], my = p.means3D[3 * (size_t)i + 1], mz = p.means3D[3 * (size_t)i + 2];
-    float c6[6];
-#pragma unroll
-    for (int k = 0; k < 6; k++) c6[k] = p.cov3D[6 * (size_t)i + k];
 
     if (live) {
         // ---- conic -> cov2D -> cov3D and view-space mean ------------------------------------------------------------

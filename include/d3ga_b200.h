@@ -293,6 +293,21 @@ int d3ga_deform_backward_fused(int N, int V, int T, const float *tetpoints, cons
                                const int32_t *order, int rows_tet_sorted, int dL_dtetpoints_pitch,
                                d3ga_stream_t stream);
 
+/* The same backward for the gradients a RENDERED view hands back: most Gaussians were never blended (everything behind
+ * the surface that saturated the pixels) and arrive with dL_dmeans3D = dL_dcov3D = 0 exactly -- 86-93 % of a 1 M-Gaussian
+ * avatar per camera.  A first kernel streams the incoming gradients, writes those Gaussians' zero gradients itself and
+ * lists the others; the backward proper then runs over the list alone.  Results are identical to
+ * d3ga_deform_backward_fused (order = null); `scratch` = d3ga_deform_backward_scratch_bytes(N) bytes of device memory,
+ * contents undefined on entry.  (With gradients that are dense -- every Gaussian non-zero -- it is the slower form.) */
+uint64_t d3ga_deform_backward_scratch_bytes(int N);
+int d3ga_deform_backward_fused_sparse(int N, int V, int T, const float *tetpoints, const int64_t *tets,
+                                      const int64_t *tetra_id, const float *barys, const float *delta_bary,
+                                      const float *canonical_gradient, const float *scales, const float *delta_scale,
+                                      int log_scales, const float *rotation, const float *delta_rot, const float *dn_inv,
+                                      const float *dL_dmeans3D, const float *dL_dcov3D, const float *dL_denergy,
+                                      float *dL_dtetpoints, float *dL_dbarys, float *dL_dscales, float *dL_drotation,
+                                      int rows_tet_sorted, int dL_dtetpoints_pitch, void *scratch, d3ga_stream_t stream);
+
 /* ---- cage FEM energy ------------------------------------------------------------
  * Replaces CageBase.fem_energy (lib/cage.py:349-361, called at models/cage_net.py:225) and its autograd backward:
  * per tet, F = G(tetpoints[tets]) @ dn_inv, energy = 0.5 (det F - 1)^2 + 0.5 (tr(F^T F) - 3).

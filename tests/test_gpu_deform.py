@@ -74,10 +74,11 @@ def test_fused_block_forward_backward_vs_oracle(cuda_lib, workload):
     assert torch.equal(gpu["barys"].grad, gpu["delta_bary"].grad) and torch.equal(gpu["scaling"].grad, gpu["delta_scale"].grad)
 
 
+@pytest.mark.parametrize("sparse", [False, True])
 @pytest.mark.parametrize("layout", ["as_built", "tet_sorted"])
 @pytest.mark.parametrize("mode,pitch4", [("auto", False), ("ordered", False), ("ordered", True), ("padded", False),
                                          ("plain", False)])
-def test_backward_accumulation_modes_agree_with_oracle(cuda_lib, monkeypatch, layout, mode, pitch4):
+def test_backward_accumulation_modes_agree_with_oracle(cuda_lib, monkeypatch, layout, mode, pitch4, sparse):
     """Every way the backward sums the cage-vertex gradients (warp-summed through the sort permutation, warp-summed in
     natural order on tet-sorted rows, padded vector reductions, plain atomics), on rows in both layouts and with a
     Gaussian count that is not a multiple of the warp (the row streams go through shared memory 32 rows at a time)."""
@@ -104,8 +105,19 @@ def test_backward_accumulation_modes_agree_with_oracle(cuda_lib, monkeypatch, la
     assert util.rel_l2(c.detach().cpu().numpy(), c_ref.detach().numpy()) < 1e-5
     wm = t(rng.normal(size=m_ref.shape).astype(np.float32))
     wc = t((rng.normal(size=c_ref.shape) * 1e3).astype(np.float32))
+    if sparse:
+        # what a rendered view hands back: most Gaussians were never blended and get an exactly-zero incoming gradient
+        # (the kernel writes their zeros and compacts the rest over the CTA); some CTAs stay dense, one is all zero
+        keep = torch.from_numpy(rng.random(N) < 0.12)
+        keep[1024:1536] = True
+        keep[2048:2304] = False
+        wm[~keep] = 0
+        wc[~keep] = 0
     ((m_ref * wm).sum() + (c_ref * wc).sum()).backward()
     ((m * wm.cuda()).sum() + (c * wc.cuda()).sum()).backward()
+    if sparse:
+        for k in ("barys", "scaling", "rotation"):
+            assert not gpu[k].grad[~keep.cuda()].any(), k
     for k in base:
         assert gpu[k].grad.shape == cpu[k].grad.shape
         assert util.rel_l2(gpu[k].grad.cpu().numpy(), cpu[k].grad.numpy()) < 1e-3, k

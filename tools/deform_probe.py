@@ -1,5 +1,5 @@
 """Development: the deformation launch pair at a workload's size (what ncu is pointed at).
-    python tools/deform_probe.py metric [sorted] [full]      full = with the three deltas and the cage energy, like bench.py"""
+    python tools/deform_probe.py metric [sorted] [full] [sparse]      full = with the three deltas and the cage energy, like bench.py"""
 import os
 import sys
 
@@ -18,6 +18,10 @@ t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).cuda()  # noqa: E731
 tp, ba, scl, rot = (t(a).requires_grad_(True) for a in (sc.tetpoints, sc.barys, np.log(sc.scales), sc.rotation))
 tets, tid, cg = t(sc.tets), t(sc.tetra_id), t(sc.canonical_gradient)
 gm, gc = torch.randn(sc.N, 3, device="cuda"), torch.randn(sc.N, 6, device="cuda")
+if "sparse" in sys.argv[2:]:      # like a rendered view: ~90 % of the Gaussians get an exactly-zero incoming gradient
+    dead = torch.rand(sc.N, device="cuda") < 0.9
+    gm[dead] = 0
+    gc[dead] = 0
 full = "full" in sys.argv[2:]
 if full:
     from oracle import deform_oracle as do
