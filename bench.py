@@ -302,7 +302,12 @@ def run_ours(args):
         "depth_sort_pass_kernel": 16 * N,
         "sort_pass_kernel": 24 * D, "tile_ranges_kernel": 8 * D + 8 * Tl, "blend_forward_kernel": 40 * D + 20 * P,
         "blend_backward_kernel": 80 * D + 20 * P, "preprocess_backward_kernel": 104 * N,
-        "deform_backward_kernel": 212 * N, "rect_grid_kernel": 12 * N, "tile_plan_kernel": 12 * Tl,
+        # the deformation backward is two launches since the sparse form: the selection streams the incoming gradients and
+        # writes the zero rows (36 + 44 B per Gaussian), the backward proper runs over the Gaussians that have a gradient;
+        # together they do the 212 B per Gaussian of algorithmic work of the dense definition
+        "deform_select_kernel": 80 * N,
+        "deform_backward_kernel": (132 if prof.get("deform_select_kernel", (0, 0))[1] else 212) * N,
+        "rect_grid_kernel": 12 * N, "tile_plan_kernel": 12 * Tl,
         # direct tile scatter (raster_direct.cu): gathers + records; ids written once, straight into their final slots
         # (the count rows and their prefix, 2-6 B x rows x tiles, are scratch traffic and not counted)
         "direct_count_kernel": 36 * N, "direct_plan_kernel": 12 * Tl, "direct_scatter_kernel": 16 * N + 4 * D,
